@@ -1,0 +1,203 @@
+// common.cuh -- shared definitions of the B200-native FLIP substep library (libflipb200.so).
+// Product code: never includes or links anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+#include "flipb200.h"
+
+// ---------------------------------------------------------------------------------------------
+// Grid layout in HBM.  All node arrays share one geometry: x fastest with a padded row pitch
+// `px` (multiple of 32 elements => every row of an 8-byte array starts 256-byte aligned, rows of
+// the 1-byte flag array 32-byte aligned), then y, then z:  idx = (k*ny + j)*px + i.
+// z is the slowest index so that z-slabs and ghost planes are contiguous (multi-GPU split).
+// ---------------------------------------------------------------------------------------------
+struct Grid {
+  int nx, ny, nz;   // nodes per axis
+  int px;           // row pitch in elements
+  int ox, oy, oz;   // index of reference coordinate 0
+  int wall;         // solid shell thickness
+  int plane;        // px*ny
+  int total;        // px*ny*nz  (< 2^31, checked at create)
+};
+
+__host__ __device__ __forceinline__ int gidx(const Grid& g, int i, int j, int k) {
+  return (k * g.ny + j) * g.px + i;
+}
+__host__ __device__ __forceinline__ bool in_box(const Grid& g, int i, int j, int k) {
+  return i >= 0 && j >= 0 && k >= 0 && i < g.nx && j < g.ny && k < g.nz;
+}
+// isWithinBounds(c, 58) of fluid.cc:38-45 in index space: inside the solid shell
+__host__ __device__ __forceinline__ bool inside_shell(const Grid& g, int i, int j, int k) {
+  return i >= g.wall && j >= g.wall && k >= g.wall && i <= g.nx - 1 - g.wall &&
+         j <= g.ny - 1 - g.wall && k <= g.nz - 1 - g.wall;
+}
+
+// flag byte per node
+enum : uint8_t {
+  FB_SXM = 1, FB_SXP = 2, FB_SYM = 4, FB_SYP = 8, FB_SZM = 16, FB_SZP = 32,  // neighbour is solid
+  FB_FLUID = 64,   // fluid cell == row of the pressure system (fluid.cc:1423-1428)
+  FB_SOLID = 128   // cell itself is solid (fluid.cc:46-57)
+};
+#define FB_SMASK 63
+
+// A sub-box of the grid that kernels sweep (bounding box of the fluid cells +-1, x-aligned)
+struct Box { int x0, y0, z0, x1, y1, z1; };   // half-open
+
+// Scalars that live in device memory (one struct per ctx) -- reductions, PCG control, dt.
+struct DevScalars {
+  double pAp[4], rz[4], rr[4];       // PCG dot products, ring indexed by iteration & 3
+  double bnorm2;                     // |b|^2 of the current right-hand side
+  double err_num, err_den;           // |b-b2|^2, |b|^2 of the relaxation test (fluid.cc:1483)
+  double threshold;                  // tol^2 * |b|^2 (Eigen ConjugateGradient.h:53)
+  double rr_final;                   // |r|^2 at exit
+  unsigned long long max_speed_bits; // max |v_p| as ordered bits (fluid.cc:976-991)
+  double dt_out;                     // FLIPadvect's dt (fluid.cc:992-999)
+  int n_fluid;
+  int bbox[6];                       // min x,y,z / max x,y,z of fluid cells
+  int pcg_done, pcg_iters, pcg_status;
+  int n_invalid;                     // particles whose support lies outside the box
+  int pad;
+};
+
+struct Particles {
+  double* a[6];      // px,py,pz,vx,vy,vz  (current, cell-sorted after sort)
+  double* b[6];      // alternate buffers (sort destination)
+  uint32_t* key;     // cell key of each particle (base cell of its 2x2x2 support)
+  uint32_t* rank;    // arrival rank inside the cell
+  int64_t n, cap;
+};
+
+struct flipb200_ctx {
+  flipb200_params P;
+  Grid g;
+  int device;
+  int num_sms;
+  cudaStream_t stream;
+  // node arrays
+  uint8_t* solid;          // input solid mask incl. shell (1 byte)
+  uint8_t* flags;          // FB_* (static solid part + per-step fluid bit)
+  uint8_t* flags_static;   // solid part only
+  double *u[3];            // vels; during P2G: momentum accumulators
+  double *ub[3];           // velBeforeUpdate; after the relaxation loop: cell-centred FLIP delta
+  double *wacc;            // weight accumulator (fp64), rounded once to fp32 into wf
+  float  *wf;              // weights == containerGrid
+  float  *bf[2];           // diver (= b) ping-pong: [cur] is b of this pass, [cur^1] receives b2
+  int     bcur;
+  double *x, *r, *pd, *Ap; // PCG vectors (x = pressure on the grid)
+  // cell-sort arrays
+  int32_t* cell_count;     // total+2 entries (last bucket: invalid particles)
+  int32_t* cell_start;
+  int32_t* scan_tmp;
+  Particles pt;
+  bool sorted;             // particle arrays are in cell order and cell_start is valid
+  DevScalars* ds;          // device
+  DevScalars* hs;          // pinned host mirror
+  Box box;                 // sweep box of this step
+  int n_fluid;
+  int stage;               // bookkeeping for stage-level calls
+  cudaEvent_t ev[8];
+  int64_t launches;
+  char errmsg[256];
+};
+
+#define CK(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e__ = (call);                                                             \
+    if (e__ != cudaSuccess) {                                                             \
+      snprintf(c->errmsg, sizeof(c->errmsg), "%s:%d %s", __FILE__, __LINE__,              \
+               cudaGetErrorString(e__));                                                  \
+      fprintf(stderr, "flipb200: CUDA error %s\n", c->errmsg);                            \
+      return FLIPB200_ERR_CUDA;                                                           \
+    }                                                                                     \
+  } while (0)
+
+#define CK_LAUNCH() CK(cudaGetLastError())
+
+// ---------------------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------------------
+// spline() of fluid.cc:22-37.  Value-identical to the reference away from |x| -> 1; within 1e-4
+// of the support edge the polynomial is pure cancellation noise (~1e-16) whose SIGN decides
+// `w > 0`, so there the reference's exact operation sequence is reproduced (no FMA, true division).
+__device__ __forceinline__ double spline_ref(double x) {
+  x = fabs(x);
+  if (x < 0.5) return 1.5 * (4.0 * x * x * x - 4.0 * x * x + 2.0 / 3.0);
+  if (x < 1.0) {
+    if (x > 1.0 - 1e-4) {
+      double x3 = __dmul_rn(__dmul_rn(x, x), x);
+      double t1 = __ddiv_rn(__dmul_rn(-8.0, x3), 6.0);
+      double t2 = __dmul_rn(__dmul_rn(4.0, x), x);
+      double t3 = __dmul_rn(4.0, x);
+      double s = __dadd_rn(__dsub_rn(__dadd_rn(t1, t2), t3), 4.0 / 3.0);
+      return __dmul_rn(1.5, s);
+    }
+    return 1.5 * ((-4.0 / 3.0) * (x * x * x) + 4.0 * x * x - 4.0 * x + 4.0 / 3.0);
+  }
+  return 0.0;
+}
+
+// Base cell (lower corner of the 2x2x2 non-zero support) of a coordinate along one axis.
+// The reference visits round(p)-1..round(p)+1 (fluid.cc:267-276); spline(|d| >= 1) == 0 leaves
+// round(p) and the neighbour on the side of the fractional part.  Returns index-space base.
+__device__ __forceinline__ int base_cell(double p, int o) {
+  double f = round(p);            // C99 half-away-from-zero, in reference coordinates
+  int fi = (int)f + o;
+  return (p - f) < 0.0 ? fi - 1 : fi;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block-wide sum of up to NV doubles per thread; result valid in thread 0.  blockDim <= 1024.
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* >= 32*NV */) {
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  const int nthreads = blockDim.x * blockDim.y * blockDim.z;
+  const int lane = tid & 31, wid = tid >> 5, nw = (nthreads + 31) >> 5;
+#pragma unroll
+  for (int q = 0; q < NV; ++q) v[q] = warp_sum(v[q]);
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int q = 0; q < NV; ++q) smem[q * 32 + wid] = v[q];
+  }
+  __syncthreads();
+  if (wid == 0) {
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+      double t = lane < nw ? smem[q * 32 + lane] : 0.0;
+      v[q] = warp_sum(t);
+    }
+  }
+}
+
+// internal API between translation units
+int fb_sort_particles(flipb200_ctx* c);
+int fb_p2g(flipb200_ctx* c);
+int fb_classify(flipb200_ctx* c);
+int fb_rhs_div(flipb200_ctx* c, double dt, int mode);
+int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters, double* rel);
+int fb_vel_update(flipb200_ctx* c, double dt_sub);
+int fb_cell_delta(flipb200_ctx* c);
+int fb_g2p_advect(flipb200_ctx* c);
+int fb_fetch_scalars(flipb200_ctx* c);
+int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units);
+int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
+int fb_reserve_particles(flipb200_ctx* c, int64_t n);
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }

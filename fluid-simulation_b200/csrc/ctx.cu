@@ -1,0 +1,275 @@
+// ctx.cu -- context lifetime, particle/grid transfer, error strings (C ABI of include/flipb200.h).
+#include "common.cuh"
+#include <string.h>
+#include <stdlib.h>
+#include <vector>
+
+extern "C" {
+
+void flipb200_default_params(flipb200_params* p) {
+  memset(p, 0, sizeof(*p));
+  p->nx = p->ny = p->nz = 121;   // fluid.cc:1159
+  p->ox = p->oy = p->oz = 60;
+  p->wall = 2;                   // fluid.cc:1264
+  p->relax_div = 10;             // fluid.cc:1475
+  p->dx = 1.0; p->rho = 1.0;     // fluid.cc:1358,1471
+  p->gx = 0.0; p->gy = -10.0; p->gz = 0.0;   // fluid.cc:1357
+  p->dt_max = 0.1;               // fluid.cc:1490
+  p->relax_tol = 0.1;            // fluid.cc:1484
+  p->restitution = 0.0;          // fluid.cc:974
+  p->flip_ratio = 1.0;           // fluid.cc:981
+  p->pcg_tol = 2.220446049250313e-16;   // NumTraits<double>::epsilon(), IterativeSolverBase.h:363
+  p->pcg_max_iter = -1;
+  p->max_passes = 200;
+  p->precond = 0;
+  p->device = -1;
+  p->max_particles = 0;
+}
+
+const char* flipb200_strerror(int s) {
+  switch (s) {
+    case FLIPB200_OK: return "ok";
+    case FLIPB200_ERR_ARG: return "bad argument";
+    case FLIPB200_ERR_CUDA: return "CUDA error (no device, out of memory or launch failure)";
+    case FLIPB200_ERR_BREAKDOWN: return "PCG breakdown (p.Ap <= 0 or non-finite)";
+    case FLIPB200_ERR_NOCONV: return "PCG reached the iteration limit";
+    case FLIPB200_ERR_STATE: return "stage called out of order";
+    case FLIPB200_ERR_COMM: return "multi-GPU communication error";
+    default: return "unknown status";
+  }
+}
+
+int flipb200_version(void) { return FLIPB200_VERSION; }
+
+}  // extern "C"
+
+// static solid-neighbour mask (the solid grid never changes after scene setup, fluid.cc:1256-1331)
+__global__ void k_static_flags(Grid g, const uint8_t* __restrict__ solid, uint8_t* __restrict__ fl) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  int k = blockIdx.z;
+  if (i >= g.px || j >= g.ny) return;
+  int q = gidx(g, i, j, k);
+  if (i >= g.nx) { fl[q] = FB_SOLID | FB_SMASK; return; }   // pitch padding: inert
+  auto sol = [&](int a, int b, int cc) -> bool {
+    return in_box(g, a, b, cc) && solid[gidx(g, a, b, cc)] != 0;   // out of box: VDB background => not solid
+  };
+  uint8_t f = 0;
+  if (sol(i, j, k)) f |= FB_SOLID;
+  if (sol(i - 1, j, k)) f |= FB_SXM;
+  if (sol(i + 1, j, k)) f |= FB_SXP;
+  if (sol(i, j - 1, k)) f |= FB_SYM;
+  if (sol(i, j + 1, k)) f |= FB_SYP;
+  if (sol(i, j, k - 1)) f |= FB_SZM;
+  if (sol(i, j, k + 1)) f |= FB_SZP;
+  fl[q] = f;
+}
+
+template <typename T>
+static int alloc_n(flipb200_ctx* c, T** p, size_t n) {
+  CK(cudaMalloc((void**)p, n * sizeof(T)));
+  CK(cudaMemsetAsync(*p, 0, n * sizeof(T), c->stream));
+  return 0;
+}
+
+int fb_reserve_particles(flipb200_ctx* c, int64_t n) {
+  Particles& pt = c->pt;
+  if (n <= pt.cap) return 0;
+  // grow: keep contents of the current buffers
+  int64_t ncap = n + n / 16 + 1024;
+  ncap = (ncap + 63) & ~(int64_t)63;
+  double* na[6]; double* nb[6];
+  for (int q = 0; q < 6; ++q) {
+    CK(cudaMalloc((void**)&na[q], ncap * sizeof(double)));
+    CK(cudaMalloc((void**)&nb[q], ncap * sizeof(double)));
+    if (pt.n > 0) CK(cudaMemcpyAsync(na[q], pt.a[q], pt.n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  }
+  uint32_t *nk, *nr;
+  CK(cudaMalloc((void**)&nk, ncap * sizeof(uint32_t)));
+  CK(cudaMalloc((void**)&nr, ncap * sizeof(uint32_t)));
+  CK(cudaStreamSynchronize(c->stream));
+  for (int q = 0; q < 6; ++q) { cudaFree(pt.a[q]); cudaFree(pt.b[q]); pt.a[q] = na[q]; pt.b[q] = nb[q]; }
+  cudaFree(pt.key); cudaFree(pt.rank);
+  pt.key = nk; pt.rank = nr; pt.cap = ncap;
+  return 0;
+}
+
+extern "C" {
+
+int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb200_ctx** out) {
+  if (!p || !out) return FLIPB200_ERR_ARG;
+  *out = nullptr;
+  if (p->nx < 2 * p->wall + 2 || p->ny < 2 * p->wall + 2 || p->nz < 2 * p->wall + 2) return FLIPB200_ERR_ARG;
+  if (p->wall < 1 || p->relax_div < 1 || !(p->dx > 0) || !(p->rho > 0)) return FLIPB200_ERR_ARG;
+  if (p->flip_ratio != 1.0) return FLIPB200_ERR_ARG;   // reference runs pure FLIP (fluid.cc:981)
+  flipb200_ctx* c = (flipb200_ctx*)calloc(1, sizeof(flipb200_ctx));
+  if (!c) return FLIPB200_ERR_ARG;
+  c->P = *p;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    fprintf(stderr, "flipb200: no CUDA device -- this library has no CPU fallback\n");
+    free(c);
+    return FLIPB200_ERR_CUDA;
+  }
+  int dev = p->device;
+  if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) { free(c); return FLIPB200_ERR_CUDA; } }
+  c->device = dev;
+  CK(cudaSetDevice(dev));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, dev));
+  c->num_sms = prop.multiProcessorCount;
+  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (int e = 0; e < 8; ++e) CK(cudaEventCreate(&c->ev[e]));
+
+  Grid& g = c->g;
+  g.nx = p->nx; g.ny = p->ny; g.nz = p->nz;
+  g.px = (p->nx + 31) & ~31;
+  g.ox = p->ox; g.oy = p->oy; g.oz = p->oz;
+  g.wall = p->wall;
+  int64_t plane = (int64_t)g.px * g.ny, total = plane * g.nz;
+  if (total >= (int64_t)2147483647 - 4) { flipb200_destroy(c); return FLIPB200_ERR_ARG; }
+  g.plane = (int)plane; g.total = (int)total;
+  const size_t T = (size_t)total;
+
+  if (alloc_n(c, &c->solid, T) || alloc_n(c, &c->flags, T) || alloc_n(c, &c->flags_static, T)) goto fail;
+  for (int a = 0; a < 3; ++a)
+    if (alloc_n(c, &c->u[a], T) || alloc_n(c, &c->ub[a], T)) goto fail;
+  if (alloc_n(c, &c->wacc, T) || alloc_n(c, &c->wf, T) || alloc_n(c, &c->bf[0], T) || alloc_n(c, &c->bf[1], T)) goto fail;
+  if (alloc_n(c, &c->x, T) || alloc_n(c, &c->r, T) || alloc_n(c, &c->pd, T) || alloc_n(c, &c->Ap, T)) goto fail;
+  if (alloc_n(c, &c->cell_count, T + 2) || alloc_n(c, &c->cell_start, T + 2) || alloc_n(c, &c->scan_tmp, T / 2048 + 64)) goto fail;
+  if (alloc_n(c, &c->ds, 1)) goto fail;
+  if (cudaHostAlloc((void**)&c->hs, sizeof(DevScalars), cudaHostAllocDefault) != cudaSuccess) goto fail;
+  memset(c->hs, 0, sizeof(DevScalars));
+
+  {
+    // solid mask with the shell forced solid (fluid.cc:1264-1266), laid out with the row pitch
+    std::vector<uint8_t> h(T, 0);
+    for (int k = 0; k < g.nz; ++k)
+      for (int j = 0; j < g.ny; ++j)
+        for (int i = 0; i < g.nx; ++i) {
+          bool s = !inside_shell(g, i, j, k);
+          if (!s && solid_host) s = solid_host[((size_t)k * g.ny + j) * g.nx + i] != 0;
+          h[gidx(g, i, j, k)] = s ? 1 : 0;
+        }
+    if (cudaMemcpyAsync(c->solid, h.data(), T, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) goto fail;
+    dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.nz);
+    k_static_flags<<<grd, blk, 0, c->stream>>>(g, c->solid, c->flags_static);
+    if (cudaMemcpyAsync(c->flags, c->flags_static, T, cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) goto fail;
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) goto fail;
+  }
+  c->box = Box{0, 0, 0, g.nx, g.ny, g.nz};
+  if (p->max_particles > 0 && fb_reserve_particles(c, p->max_particles)) goto fail;
+  *out = c;
+  return FLIPB200_OK;
+fail:
+  fprintf(stderr, "flipb200_create failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+  flipb200_destroy(c);
+  return FLIPB200_ERR_CUDA;
+}
+
+void flipb200_destroy(flipb200_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static);
+  for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }
+  cudaFree(c->wacc); cudaFree(c->wf); cudaFree(c->bf[0]); cudaFree(c->bf[1]);
+  cudaFree(c->x); cudaFree(c->r); cudaFree(c->pd); cudaFree(c->Ap);
+  cudaFree(c->cell_count); cudaFree(c->cell_start); cudaFree(c->scan_tmp);
+  for (int q = 0; q < 6; ++q) { cudaFree(c->pt.a[q]); cudaFree(c->pt.b[q]); }
+  cudaFree(c->pt.key); cudaFree(c->pt.rank);
+  cudaFree(c->ds);
+  if (c->hs) cudaFreeHost(c->hs);
+  for (int e = 0; e < 8; ++e) if (c->ev[e]) cudaEventDestroy(c->ev[e]);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  free(c);
+}
+
+int flipb200_set_particles(flipb200_ctx* c, const double* px, const double* py, const double* pz,
+                           const double* vx, const double* vy, const double* vz, int64_t n) {
+  if (!c || n < 0 || (n > 0 && (!px || !py || !pz || !vx || !vy || !vz))) return FLIPB200_ERR_ARG;
+  if (n >= (int64_t)2147483647) return FLIPB200_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  c->pt.n = 0;
+  if (fb_reserve_particles(c, n)) return FLIPB200_ERR_CUDA;
+  const double* src[6] = {px, py, pz, vx, vy, vz};
+  for (int q = 0; q < 6; ++q)
+    if (n) CK(cudaMemcpyAsync(c->pt.a[q], src[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  c->pt.n = n;
+  c->sorted = false;
+  return FLIPB200_OK;
+}
+
+int flipb200_get_particles(flipb200_ctx* c, double* px, double* py, double* pz, double* vx, double* vy,
+                           double* vz, int64_t cap, int64_t* n) {
+  if (!c) return FLIPB200_ERR_ARG;
+  if (n) *n = c->pt.n;
+  if (cap < c->pt.n) return FLIPB200_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  double* dst[6] = {px, py, pz, vx, vy, vz};
+  for (int q = 0; q < 6; ++q)
+    if (dst[q] && c->pt.n) CK(cudaMemcpyAsync(dst[q], c->pt.a[q], c->pt.n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return FLIPB200_OK;
+}
+
+int flipb200_num_particles(flipb200_ctx* c, int64_t* n) {
+  if (!c || !n) return FLIPB200_ERR_ARG;
+  *n = c->pt.n;
+  return FLIPB200_OK;
+}
+
+static int grid_ptr(flipb200_ctx* c, int which, void** p, size_t* esz) {
+  switch (which) {
+    case FLIPB200_GRID_U: case FLIPB200_GRID_V: case FLIPB200_GRID_W: *p = c->u[which]; *esz = 8; return 0;
+    case FLIPB200_GRID_UB: case FLIPB200_GRID_VB: case FLIPB200_GRID_WB: *p = c->ub[which - 3]; *esz = 8; return 0;
+    case FLIPB200_GRID_P: *p = c->x; *esz = 8; return 0;
+    case FLIPB200_GRID_WEIGHT: *p = c->wf; *esz = 4; return 0;
+    case FLIPB200_GRID_B: *p = c->bf[c->bcur]; *esz = 4; return 0;
+    case FLIPB200_GRID_FLAGS: *p = c->flags; *esz = 1; return 0;
+    default: return -1;
+  }
+}
+
+int flipb200_get_grid(flipb200_ctx* c, int which, void* host_out, size_t bytes) {
+  if (!c || !host_out) return FLIPB200_ERR_ARG;
+  void* d; size_t esz;
+  if (grid_ptr(c, which, &d, &esz)) return FLIPB200_ERR_ARG;
+  const Grid& g = c->g;
+  if (bytes != (size_t)g.nx * g.ny * g.nz * esz) return FLIPB200_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemcpy2DAsync(host_out, g.nx * esz, d, g.px * esz, g.nx * esz, (size_t)g.ny * g.nz,
+                       cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return FLIPB200_OK;
+}
+
+int flipb200_set_grid(flipb200_ctx* c, int which, const void* host_in, size_t bytes) {
+  if (!c || !host_in) return FLIPB200_ERR_ARG;
+  void* d; size_t esz;
+  if (grid_ptr(c, which, &d, &esz)) return FLIPB200_ERR_ARG;
+  const Grid& g = c->g;
+  if (bytes != (size_t)g.nx * g.ny * g.nz * esz) return FLIPB200_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemcpy2DAsync(d, g.px * esz, host_in, g.nx * esz, g.nx * esz, (size_t)g.ny * g.nz,
+                       cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return FLIPB200_OK;
+}
+
+int flipb200_host_alloc(void** ptr, size_t bytes) {
+  if (!ptr) return FLIPB200_ERR_ARG;
+  return cudaHostAlloc(ptr, bytes, cudaHostAllocDefault) == cudaSuccess ? FLIPB200_OK : FLIPB200_ERR_CUDA;
+}
+int flipb200_host_free(void* ptr) {
+  return cudaFreeHost(ptr) == cudaSuccess ? FLIPB200_OK : FLIPB200_ERR_CUDA;
+}
+
+}  // extern "C"
+
+int fb_fetch_scalars(flipb200_ctx* c) {
+  CK(cudaMemcpyAsync(c->hs, c->ds, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}

@@ -1,0 +1,291 @@
+// grid.cu -- grid side of the FLIP substep: normalise + classify, rhs/divergence (+ relaxation
+// error), pressure-gradient/gravity velocity update, cell-centred FLIP delta.
+//   reference: P2Gtransfer normalise fluid.cc:1131-1146; main :1388-1455; setRHS :414-479;
+//              setDiver :566-610; setOnlyB :543-564; velUpdate :612-703; getVelocity :59-70
+#include "common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// normalise + classify + velBeforeUpdate copy, whole grid, one pass:
+//   wf = float(w)                    weights / containerGrid are FloatGrids (fluid.cc:809,1157)
+//   if (wf > 0) u /= wf              fluid.cc:1138-1141
+//   ub = u                           velBeforeUpdate = vels->deepCopy(), fluid.cc:1455
+//   fluid = !solid && wf > 0         fluid.cc:1423-1428 (inside-shell is implied: the shell is solid)
+// The second splat PointList::interpolate (fluid.cc:843-882) accumulates the same cw into
+// containerGrid as p2gCatmullRom does into weights, so container := weights (no second pass).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
+           double* __restrict__ u0, double* __restrict__ u1, double* __restrict__ u2,
+           double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
+           double* __restrict__ xpress,
+           const uint8_t* __restrict__ fs, uint8_t* __restrict__ fl, DevScalars* __restrict__ ds) {
+  __shared__ int sred[7][8];
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  int k = blockIdx.z;
+  int cnt = 0, mnx = 1 << 30, mny = 1 << 30, mnz = 1 << 30, mxx = -1, mxy = -1, mxz = -1;
+  if (i < g.nx && j < g.ny) {
+    int q = gidx(g, i, j, k);
+    float w = (float)wacc[q];
+    wf[q] = w;
+    double a = u0[q], b = u1[q], cc = u2[q];
+    if (w > 0.0f) {
+      double wd = (double)w;
+      a = a / wd; b = b / wd; cc = cc / wd;
+      u0[q] = a; u1[q] = b; u2[q] = cc;
+    }
+    b0[q] = a; b1[q] = b; b2[q] = cc;
+    xpress[q] = 0.0;
+    uint8_t f = fs[q];
+    // a fluid cell whose six neighbours are all solid has Adiag == 0 and no row in the
+    // reference's matrix (fluid.cc:498); it is left out of the system here as well.
+    bool fluid = !(f & FB_SOLID) && w > 0.0f && (f & FB_SMASK) != FB_SMASK;
+    if (fluid) {
+      f |= FB_FLUID; cnt = 1;
+      mnx = mxx = i; mny = mxy = j; mnz = mxz = k;
+    }
+    fl[q] = f;
+  }
+  // block reduction (count, bbox) -> one atomic set per block
+  int tid = threadIdx.x + blockDim.x * threadIdx.y, lane = tid & 31, wid = tid >> 5;
+  cnt = warp_sum_i(cnt);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+    mnz = min(mnz, __shfl_xor_sync(0xffffffffu, mnz, o)); mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+    mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o)); mxz = max(mxz, __shfl_xor_sync(0xffffffffu, mxz, o));
+  }
+  if (lane == 0) {
+    sred[0][wid] = cnt; sred[1][wid] = mnx; sred[2][wid] = mny; sred[3][wid] = mnz;
+    sred[4][wid] = mxx; sred[5][wid] = mxy; sred[6][wid] = mxz;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int nw = (blockDim.x * blockDim.y + 31) >> 5;
+    for (int w = 1; w < nw; ++w) {
+      cnt += sred[0][w];
+      mnx = min(mnx, sred[1][w]); mny = min(mny, sred[2][w]); mnz = min(mnz, sred[3][w]);
+      mxx = max(mxx, sred[4][w]); mxy = max(mxy, sred[5][w]); mxz = max(mxz, sred[6][w]);
+    }
+    if (cnt) {
+      atomicAdd(&ds->n_fluid, cnt);
+      atomicMin(&ds->bbox[0], mnx); atomicMin(&ds->bbox[1], mny); atomicMin(&ds->bbox[2], mnz);
+      atomicMax(&ds->bbox[3], mxx); atomicMax(&ds->bbox[4], mxy); atomicMax(&ds->bbox[5], mxz);
+    }
+  }
+}
+
+__global__ void k_reset_classify(DevScalars* ds) {
+  ds->n_fluid = 0;
+  ds->bbox[0] = ds->bbox[1] = ds->bbox[2] = 1 << 30;
+  ds->bbox[3] = ds->bbox[4] = ds->bbox[5] = -1;
+}
+
+int fb_classify(flipb200_ctx* c) {
+  const Grid& g = c->g;
+  k_reset_classify<<<1, 1, 0, c->stream>>>(c->ds);
+  dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.nz);
+  k_classify<<<grd, blk, 0, c->stream>>>(g, c->wacc, c->wf, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1],
+                                         c->ub[2], c->x, c->flags_static, c->flags, c->ds);
+  CK_LAUNCH(); c->launches += 2;
+  int rc = fb_fetch_scalars(c);
+  if (rc) return rc;
+  c->n_fluid = c->hs->n_fluid;
+  Box b;
+  if (c->n_fluid == 0) {
+    b = Box{0, 0, 0, 0, 0, 0};
+  } else {
+    const int* bb = c->hs->bbox;
+    b.x0 = max(0, bb[0] - 2) & ~31;            // rows stay sector/line aligned
+    b.y0 = max(0, bb[1] - 2); b.z0 = max(0, bb[2] - 2);
+    b.x1 = min(g.nx, bb[3] + 3); b.y1 = min(g.ny, bb[4] + 3); b.z1 = min(g.nz, bb[5] + 3);
+  }
+  c->box = b;
+  c->bcur = 0;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// rhs + divergence in one sweep (setRHS fluid.cc:414-479, setDiver :566-610).  Arithmetic and
+// fp32 stores follow the reference statement by statement (explicit _rn intrinsics: no FMA).
+//   MODE 0: bout = b;           ds->bnorm2  = |b|^2
+//   MODE 1: bout = b2 (new);    ds->err_num = |bold - b2|^2, ds->err_den = |bold|^2 (fluid.cc:1483)
+//           and ds->bnorm2 = |b2|^2 (b2 is the next pass's b: same velocities, same dt)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float rhs_div_cell(const Grid& g, int q, uint8_t f, const double* __restrict__ u0,
+                                              const double* __restrict__ u1, const double* __restrict__ u2,
+                                              double scale, double dx, double gx, double gy, double gz) {
+  double vx = u0[q], vy = u1[q], vz = u2[q];
+  double vix = u0[q + 1], vjy = u1[q + g.px], vkz = u2[q + g.plane];   // fluid cells are inside the shell
+  float R = 0.0f;
+  if (f & FB_SXM) R = __double2float_rn(__dsub_rn((double)R, __dmul_rn(scale, __dadd_rn(vx, gx))));    // :449
+  if (f & FB_SXP) R = __double2float_rn(__dadd_rn((double)R, __dmul_rn(scale, __dadd_rn(vix, gx))));   // :453
+  if (f & FB_SYM) R = __double2float_rn(__dsub_rn((double)R, __dmul_rn(scale, __dadd_rn(vy, gy))));    // :458
+  if (f & FB_SYP) R = __double2float_rn(__dadd_rn((double)R, __dmul_rn(scale, __dadd_rn(vjy, gy))));   // :462
+  if (f & FB_SZM) R = __double2float_rn(__dsub_rn((double)R, __dmul_rn(scale, __dadd_rn(vz, gz))));    // :467
+  if (f & FB_SZP) R = __double2float_rn(__dadd_rn((double)R, __dmul_rn(scale, __dadd_rn(vkz, gz))));   // :471
+  double du = 0.0, dv = 0.0, dw = 0.0;
+  if (!(f & FB_SXP)) du = __ddiv_rn(__dsub_rn(vix, vx), dx);   // :592-595
+  if (!(f & FB_SYP)) dv = __ddiv_rn(__dsub_rn(vjy, vy), dx);
+  if (!(f & FB_SZP)) dw = __ddiv_rn(__dsub_rn(vkz, vz), dx);
+  return __double2float_rn(__dsub_rn(__dsub_rn(__dsub_rn((double)R, du), dv), dw));   // :605
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+k_rhs_div(Grid g, Box box, int tiles_x, int tiles_y, int nitems, const uint8_t* __restrict__ fl,
+          const double* __restrict__ u0, const double* __restrict__ u1, const double* __restrict__ u2,
+          const float* __restrict__ bold, float* __restrict__ bout, double scale, double dx, double gx, double gy,
+          double gz, DevScalars* __restrict__ ds) {
+  __shared__ double sm[3 * 32];
+  double acc[3] = {0.0, 0.0, 0.0};
+  for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+    int tz = item / (tiles_x * tiles_y), rem = item - tz * tiles_x * tiles_y;
+    int ty = rem / tiles_x, tx = rem - ty * tiles_x;
+    int i = box.x0 + tx * 32 + threadIdx.x, j = box.y0 + ty * 8 + threadIdx.y, k = box.z0 + tz;
+    if (i < box.x1 && j < box.y1) {
+      int q = gidx(g, i, j, k);
+      uint8_t f = fl[q];
+      float D = 0.0f;
+      if (f & FB_FLUID) D = rhs_div_cell(g, q, f, u0, u1, u2, scale, dx, gx, gy, gz);
+      if (MODE == 1) {
+        double bo = (double)bold[q];
+        double d = bo - (double)D;
+        acc[1] += d * d; acc[2] += bo * bo;
+      }
+      acc[0] += (double)D * (double)D;
+      bout[q] = D;
+    }
+  }
+  block_sum<3>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    atomicAdd(&ds->bnorm2, acc[0]);
+    if (MODE == 1) { atomicAdd(&ds->err_num, acc[1]); atomicAdd(&ds->err_den, acc[2]); }
+  }
+}
+
+__global__ void k_reset_norms(DevScalars* ds) { ds->bnorm2 = 0.0; ds->err_num = 0.0; ds->err_den = 0.0; }
+
+// mode 0: b of the first pass into bf[bcur].  mode 1: b2 into bf[bcur^1] + error sums; then flip.
+int fb_rhs_div(flipb200_ctx* c, double dt, int mode) {
+  const Grid& g = c->g;
+  const Box& b = c->box;
+  k_reset_norms<<<1, 1, 0, c->stream>>>(c->ds);
+  c->launches++;
+  if (b.x1 > b.x0 && b.y1 > b.y0 && b.z1 > b.z0) {
+    int tiles_x = cdiv(b.x1 - b.x0, 32), tiles_y = cdiv(b.y1 - b.y0, 8);
+    int nitems = tiles_x * tiles_y * (b.z1 - b.z0);
+    int grid = min(nitems, c->num_sms * 8);
+    dim3 blk(32, 8, 1);
+    const double scale = 1.0 / c->P.dx;                                  // fluid.cc:416
+    const double gx = c->P.gx * dt, gy = c->P.gy * dt, gz = c->P.gz * dt;   // :420 (full dt)
+    if (mode == 0)
+      k_rhs_div<0><<<grid, blk, 0, c->stream>>>(g, b, tiles_x, tiles_y, nitems, c->flags, c->u[0], c->u[1], c->u[2],
+                                                nullptr, c->bf[c->bcur], scale, c->P.dx, gx, gy, gz, c->ds);
+    else
+      k_rhs_div<1><<<grid, blk, 0, c->stream>>>(g, b, tiles_x, tiles_y, nitems, c->flags, c->u[0], c->u[1], c->u[2],
+                                                c->bf[c->bcur], c->bf[c->bcur ^ 1], scale, c->P.dx, gx, gy, gz, c->ds);
+    CK_LAUNCH(); c->launches++;
+  }
+  if (mode == 1) c->bcur ^= 1;
+  return fb_fetch_scalars(c);
+}
+
+// ---------------------------------------------------------------------------------------------
+// velUpdate (fluid.cc:612-703) as a per-face gather.  The reference scatters, in scan order:
+//   loop 1, fluid cell c:  u[c] = u[c] - s*p_c + g'   (all 3 comps);  u_a[c+e_a] += s*p_c
+//   loop 2, solid cell c:  u[c] = 0;  u_a[c+e_a] = 0
+// so component a at node c receives, in this order, (+ s*p_m) from m = c-e_a if m is fluid, then
+// (- s*p_c + g'_a) if c is fluid, and is zeroed if c or m is solid.  Same order, no FMA.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_vel_update(Grid g, Box box, int tiles_x, int tiles_y, int nitems, const uint8_t* __restrict__ fl,
+             const double* __restrict__ p, double* __restrict__ u0, double* __restrict__ u1,
+             double* __restrict__ u2, double scale, double gx, double gy, double gz) {
+  for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+    int tz = item / (tiles_x * tiles_y), rem = item - tz * tiles_x * tiles_y;
+    int ty = rem / tiles_x, tx = rem - ty * tiles_x;
+    int i = box.x0 + tx * 32 + threadIdx.x, j = box.y0 + ty * 8 + threadIdx.y, k = box.z0 + tz;
+    if (i >= box.x1 || j >= box.y1) continue;
+    int q = gidx(g, i, j, k);
+    uint8_t f = fl[q];
+    if (f & FB_SOLID) { u0[q] = 0.0; u1[q] = 0.0; u2[q] = 0.0; continue; }   // :680-683
+    // non-solid nodes are inside the shell, so q-1, q-px, q-plane are in the box
+    double sp = 0.0;
+    if (f & FB_FLUID) sp = __dmul_rn(scale, p[q]);                            // scale * pre, :637-641
+    {
+      double v = u0[q];
+      if (f & FB_SXM) v = 0.0;                                               // :684-688 seen from c+e_x
+      else {
+        if (fl[q - 1] & FB_FLUID) v = __dadd_rn(v, __dmul_rn(scale, p[q - 1]));     // :646
+        if (f & FB_FLUID) v = __dadd_rn(__dsub_rn(v, sp), gx);                      // :639
+      }
+      u0[q] = v;
+    }
+    {
+      double v = u1[q];
+      if (f & FB_SYM) v = 0.0;
+      else {
+        if (fl[q - g.px] & FB_FLUID) v = __dadd_rn(v, __dmul_rn(scale, p[q - g.px]));   // :653
+        if (f & FB_FLUID) v = __dadd_rn(__dsub_rn(v, sp), gy);                          // :640
+      }
+      u1[q] = v;
+    }
+    {
+      double v = u2[q];
+      if (f & FB_SZM) v = 0.0;
+      else {
+        if (fl[q - g.plane] & FB_FLUID) v = __dadd_rn(v, __dmul_rn(scale, p[q - g.plane]));   // :660
+        if (f & FB_FLUID) v = __dadd_rn(__dsub_rn(v, sp), gz);                                // :641
+      }
+      u2[q] = v;
+    }
+  }
+}
+
+int fb_vel_update(flipb200_ctx* c, double dt_sub) {
+  const Grid& g = c->g;
+  const Box& b = c->box;
+  if (!(b.x1 > b.x0 && b.y1 > b.y0 && b.z1 > b.z0)) return 0;
+  int tiles_x = cdiv(b.x1 - b.x0, 32), tiles_y = cdiv(b.y1 - b.y0, 8);
+  int nitems = tiles_x * tiles_y * (b.z1 - b.z0);
+  int grid = min(nitems, c->num_sms * 8);
+  const double scale = dt_sub / (c->P.rho * c->P.dx);                     // fluid.cc:614
+  k_vel_update<<<grid, dim3(32, 8, 1), 0, c->stream>>>(g, b, tiles_x, tiles_y, nitems, c->flags, c->x, c->u[0],
+                                                       c->u[1], c->u[2], scale, c->P.gx * dt_sub, c->P.gy * dt_sub,
+                                                       c->P.gz * dt_sub);   // g = gravity*dt, :638
+  CK_LAUNCH(); c->launches++;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// cell-centred FLIP delta for every node inside the shell (CatmullRomFLIP fluid.cc:237-240,252):
+//   dc_a[c] = (u_a[c] + u_a[c+e_a])/2 - (ub_a[c] + ub_a[c+e_a])/2
+// written into the (now idle) PCG vectors r, pd, Ap; zero outside the shell.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u1, const double* __restrict__ u2,
+             const double* __restrict__ b0, const double* __restrict__ b1, const double* __restrict__ b2,
+             double* __restrict__ d0, double* __restrict__ d1, double* __restrict__ d2) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  int k = blockIdx.z;
+  if (i >= g.px || j >= g.ny) return;
+  int q = gidx(g, i, j, k);
+  double a = 0.0, b = 0.0, cc = 0.0;
+  if (inside_shell(g, i, j, k)) {
+    a = (u0[q] + u0[q + 1]) / 2.0 - (b0[q] + b0[q + 1]) / 2.0;
+    b = (u1[q] + u1[q + g.px]) / 2.0 - (b1[q] + b1[q + g.px]) / 2.0;
+    cc = (u2[q] + u2[q + g.plane]) / 2.0 - (b2[q] + b2[q + g.plane]) / 2.0;
+  }
+  d0[q] = a; d1[q] = b; d2[q] = cc;
+}
+
+int fb_cell_delta(flipb200_ctx* c) {
+  const Grid& g = c->g;
+  dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.nz);
+  k_cell_delta<<<grd, blk, 0, c->stream>>>(g, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->r, c->pd,
+                                           c->Ap);
+  CK_LAUNCH(); c->launches++;
+  return 0;
+}

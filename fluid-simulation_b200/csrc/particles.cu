@@ -1,0 +1,400 @@
+// particles.cu -- particle side of the FLIP substep: cell sort, P2G splat, G2P FLIP update,
+// advection with solid collision, device seeding.
+//   reference: PointList::P2Gtransfer fluid.cc:1106-1148, p2gCatmullRom :265-299,
+//              PointList::interpolate :843-882, PointList::FLIPadvect :972-1038, CatmullRomFLIP :210-263
+#include "common.cuh"
+#include <stdlib.h>
+
+// ---------------------------------------------------------------------------------------------
+// cell sort: key = linear index of the base cell of the particle's 2x2x2 support; particles
+// whose support leaves the box (they touch no writable node because the shell is solid) go to
+// the trailing bucket `total`.  Counting sort: histogram (atomic, returns the in-cell rank),
+// exclusive scan, scatter.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t particle_key(const Grid& g, double x, double y, double z) {
+  // guard against NaN / huge coordinates before the int conversion
+  if (!(fabs(x) < 1.0e9) || !(fabs(y) < 1.0e9) || !(fabs(z) < 1.0e9)) return (uint32_t)g.total;
+  int bi = base_cell(x, g.ox), bj = base_cell(y, g.oy), bk = base_cell(z, g.oz);
+  if (bi < 0 || bj < 0 || bk < 0 || bi > g.nx - 2 || bj > g.ny - 2 || bk > g.nz - 2) return (uint32_t)g.total;
+  return (uint32_t)gidx(g, bi, bj, bk);
+}
+
+__global__ void k_key_count(Grid g, int64_t n, const double* __restrict__ px, const double* __restrict__ py,
+                            const double* __restrict__ pz, uint32_t* __restrict__ key,
+                            uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t kx = particle_key(g, px[i], py[i], pz[i]);
+  key[i] = kx;
+  rank[i] = (uint32_t)atomicAdd(&count[kx], 1);
+}
+
+// exclusive scan of int32[n]: 2048 items per block (1024 threads x 2)
+#define SCAN_ITEMS 2048
+__global__ void k_scan_block(const int32_t* __restrict__ in, int32_t* __restrict__ out,
+                             int32_t* __restrict__ block_sum, int n) {
+  __shared__ int32_t wsum[32];
+  int base = blockIdx.x * SCAN_ITEMS;
+  int t = threadIdx.x;
+  int i0 = base + 2 * t, i1 = i0 + 1;
+  int a = i0 < n ? in[i0] : 0, b = i1 < n ? in[i1] : 0;
+  int s = a + b;
+  int lane = t & 31, w = t >> 5;
+  int v = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += y; }
+  if (lane == 31) wsum[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    int x = wsum[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    wsum[lane] = x;
+  }
+  __syncthreads();
+  int excl = v - s + (w > 0 ? wsum[w - 1] : 0);
+  if (i0 < n) out[i0] = excl;
+  if (i1 < n) out[i1] = excl + a;
+  if (t == 1023) block_sum[blockIdx.x] = wsum[31];
+}
+__global__ void k_scan_sums(int32_t* __restrict__ sums, int nb) {
+  // single block: sequential over chunks of 1024
+  __shared__ int32_t wsum[32];
+  __shared__ int32_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  for (int base = 0; base < nb; base += 1024) {
+    int i = base + t;
+    int s = i < nb ? sums[i] : 0;
+    int v = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += y; }
+    if (lane == 31) wsum[w] = v;
+    __syncthreads();
+    if (w == 0) {
+      int x = wsum[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+      wsum[lane] = x;
+    }
+    __syncthreads();
+    int excl = v - s + (w > 0 ? wsum[w - 1] : 0) + carry;
+    if (i < nb) sums[i] = excl;
+    __syncthreads();
+    if (t == 1023) carry = excl + s;
+    __syncthreads();
+  }
+}
+__global__ void k_scan_add(int32_t* __restrict__ out, const int32_t* __restrict__ sums, int n) {
+  int i = blockIdx.x * SCAN_ITEMS + threadIdx.x;
+  int add = sums[blockIdx.x];
+  if (i < n) out[i] += add;
+  if (i + 1024 < n) out[i + 1024] += add;
+}
+
+__global__ void k_reorder(int64_t n, const uint32_t* __restrict__ key, const uint32_t* __restrict__ rank,
+                          const int32_t* __restrict__ start,
+                          const double* __restrict__ a0, const double* __restrict__ a1, const double* __restrict__ a2,
+                          const double* __restrict__ a3, const double* __restrict__ a4, const double* __restrict__ a5,
+                          double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
+                          double* __restrict__ b3, double* __restrict__ b4, double* __restrict__ b5) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int64_t d = (int64_t)start[key[i]] + rank[i];
+  b0[d] = a0[i]; b1[d] = a1[i]; b2[d] = a2[i];
+  b3[d] = a3[i]; b4[d] = a4[i]; b5[d] = a5[i];
+}
+
+int fb_sort_particles(flipb200_ctx* c) {
+  const Grid& g = c->g;
+  Particles& pt = c->pt;
+  const int nb = g.total + 1;                 // buckets incl. the trailing "outside" bucket
+  CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(nb + 1) * sizeof(int32_t), c->stream));
+  if (pt.n > 0) {
+    int blocks = (int)((pt.n + 255) / 256);
+    k_key_count<<<blocks, 256, 0, c->stream>>>(g, pt.n, pt.a[0], pt.a[1], pt.a[2], pt.key, pt.rank, c->cell_count);
+    CK_LAUNCH(); c->launches++;
+  }
+  // scan nb+1 entries so that cell_start[nb] == n
+  int ns = nb + 1;
+  int sb = cdiv(ns, SCAN_ITEMS);
+  k_scan_block<<<sb, 1024, 0, c->stream>>>(c->cell_count, c->cell_start, c->scan_tmp, ns);
+  k_scan_sums<<<1, 1024, 0, c->stream>>>(c->scan_tmp, sb);
+  k_scan_add<<<sb, 1024, 0, c->stream>>>(c->cell_start, c->scan_tmp, ns);
+  CK_LAUNCH(); c->launches += 3;
+  if (pt.n > 0) {
+    int blocks = (int)((pt.n + 255) / 256);
+    k_reorder<<<blocks, 256, 0, c->stream>>>(pt.n, pt.key, pt.rank, c->cell_start, pt.a[0], pt.a[1], pt.a[2],
+                                             pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2], pt.b[3],
+                                             pt.b[4], pt.b[5]);
+    CK_LAUNCH(); c->launches++;
+    for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
+  }
+  c->sorted = true;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// P2G.  One thread per base cell: every particle of the cell touches the same 2x2x2 nodes, so
+// the 8 x (w, w*vx, w*vy, w*vz) partial sums stay in registers and are flushed once per cell with
+// native fp64 RED atomics (REDG.E.ADD.F64) -- 32 atomics per cell instead of 32 per particle.
+// Node predicate of the reference (fluid.cc:288): !solid && inside the shell; the shell is always
+// solid here, so the flag byte alone decides.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+k_p2g_cell(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
+           const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+           const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+           double* __restrict__ wacc, double* __restrict__ ux, double* __restrict__ uy, double* __restrict__ uz) {
+  int i = box.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int j = box.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int k = box.z0 + blockIdx.z;
+  if (i >= box.x1 || j >= box.y1 || i > g.nx - 2 || j > g.ny - 2 || k > g.nz - 2) return;
+  int q = gidx(g, i, j, k);
+  int s = start[q], e = start[q + 1];
+  if (s == e) return;
+  double aw[8], ax[8], ay[8], az[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { aw[m] = 0; ax[m] = 0; ay[m] = 0; az[m] = 0; }
+  const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+  for (int n = s; n < e; ++n) {
+    double x = px[n], y = py[n], z = pz[n];
+    double a = vx[n], b = vy[n], cc = vz[n];
+    double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+    double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+    double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);   // (sx*sy)*sz, fluid.cc:291
+      aw[m] += cw; ax[m] += cw * a; ay[m] += cw * b; az[m] += cw * cc;
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+    if (fl[qq] & FB_SOLID) continue;            // fluid.cc:288
+    atomicAdd(&wacc[qq], aw[m]);
+    atomicAdd(&ux[qq], ax[m]);
+    atomicAdd(&uy[qq], ay[m]);
+    atomicAdd(&uz[qq], az[m]);
+  }
+}
+
+// Reference-shaped variant: one thread per particle, 32 atomics each.  Kept as the cross-check of
+// the cell kernel (FLIPB200_P2G=particle) and as the path for unsorted input.
+__global__ void k_p2g_particle(Grid g, int64_t n, const uint8_t* __restrict__ fl,
+                               const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+                               const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+                               double* __restrict__ wacc, double* __restrict__ ux, double* __restrict__ uy, double* __restrict__ uz) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  double x = px[t], y = py[t], z = pz[t];
+  uint32_t key = particle_key(g, x, y, z);
+  if (key == (uint32_t)g.total) return;
+  int q = (int)key;
+  int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
+  double a = vx[t], b = vy[t], cc = vz[t];
+  const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+  double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+  double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+  double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+    if (fl[qq] & FB_SOLID) continue;
+    double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+    atomicAdd(&wacc[qq], cw);
+    atomicAdd(&ux[qq], cw * a);
+    atomicAdd(&uy[qq], cw * b);
+    atomicAdd(&uz[qq], cw * cc);
+  }
+}
+
+// bounding box (in base cells) of the particles, from the sorted cell histogram is expensive;
+// P2G sweeps every base cell of the box instead -- a cell with no particles costs two int loads.
+int fb_p2g(flipb200_ctx* c) {
+  const Grid& g = c->g;
+  const size_t T = (size_t)g.total;
+  // vels.fill(0) (fluid.cc:1378), weights.fill(0) (:1108)
+  CK(cudaMemsetAsync(c->wacc, 0, T * sizeof(double), c->stream));
+  for (int a = 0; a < 3; ++a) CK(cudaMemsetAsync(c->u[a], 0, T * sizeof(double), c->stream));
+  Particles& pt = c->pt;
+  if (pt.n == 0) return 0;
+  const char* mode = getenv("FLIPB200_P2G");
+  if (mode && mode[0] == 'p') {
+    int blocks = (int)((pt.n + 127) / 128);
+    k_p2g_particle<<<blocks, 128, 0, c->stream>>>(g, pt.n, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                                  pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    CK_LAUNCH(); c->launches++;
+    return 0;
+  }
+  if (!c->sorted) { int rc = fb_sort_particles(c); if (rc) return rc; }
+  Box b{0, 0, 0, g.nx - 1, g.ny - 1, g.nz - 1};
+  dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
+  k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                         pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+  CK_LAUNCH(); c->launches++;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// G2P (FLIP) + advection.  `dc` holds the cell-centred FLIP delta
+//   dc_a[c] = getVelocity(c, vels)_a - getVelocity(c, velBeforeUpdate)_a      (fluid.cc:59-70,239-240,252)
+// precomputed once per step for every node inside the shell (zero elsewhere, fluid.cc:237).
+// Phase 1 (fluid.cc:978-991): v_p += sum(cw*dc)/sum(cw), maxSpeed.  Phase 2 (:1000-1036) needs the
+// global max => second kernel.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_g2p(Grid g, int64_t n, const uint8_t* __restrict__ fl,
+      const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+      double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
+      const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
+      DevScalars* __restrict__ ds) {
+  __shared__ double red[32];
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double speed = 0.0;
+  if (t < n) {
+    double x = px[t], y = py[t], z = pz[t];
+    double a = vx[t], b = vy[t], cc = vz[t];
+    uint32_t key = particle_key(g, x, y, z);
+    if (key != (uint32_t)g.total) {
+      int q = (int)key;
+      int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
+      const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+      double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+      double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+      double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+      double wsum = 0, dx = 0, dy = 0, dz = 0;
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
+        if (!inside_shell(g, ii, jj, kk)) continue;          // fluid.cc:237 (no solid test)
+        int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+        double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+        wsum += cw;
+        dx += dcx[qq] * cw; dy += dcy[qq] * cw; dz += dcz[qq] * cw;
+      }
+      if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; }   // fluid.cc:258-262, 981
+      vx[t] = a; vy[t] = b; vz[t] = cc;
+    }
+    speed = sqrt(a * a + b * b + cc * cc);                  // Vec3::length, fluid.cc:982
+  }
+  speed = warp_max(speed);
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = speed;
+  __syncthreads();
+  if (w == 0) {
+    double s = lane < (blockDim.x >> 5) ? red[lane] : 0.0;
+    s = warp_max(s);
+    if (lane == 0 && s > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(s));
+  }
+}
+
+__device__ __forceinline__ bool solid_at(const Grid& g, const uint8_t* __restrict__ fl, int i, int j, int k) {
+  return in_box(g, i, j, k) && (fl[gidx(g, i, j, k)] & FB_SOLID);
+}
+
+__global__ void __launch_bounds__(256)
+k_advect(Grid g, int64_t n, const uint8_t* __restrict__ fl, double dt_max, double dxc, double e,
+         double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+         double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
+         DevScalars* __restrict__ ds) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double maxSpeed = __longlong_as_double((long long)ds->max_speed_bits);
+  double timestep = dt_max;                                   // fluid.cc:992-999
+  if (maxSpeed != 0.0) timestep = dt_max < dxc / maxSpeed ? dt_max : dxc / maxSpeed;
+  if (t == 0) ds->dt_out = timestep;
+  if (t >= n) return;
+  double x = px[t], y = py[t], z = pz[t];
+  double a = vx[t], b = vy[t], cc = vz[t];
+  // position += timestep * velocity without FMA contraction (fluid.cc:1003)
+  double nxp = __dadd_rn(x, __dmul_rn(timestep, a));
+  double nyp = __dadd_rn(y, __dmul_rn(timestep, b));
+  double nzp = __dadd_rn(z, __dmul_rn(timestep, cc));
+  bool bad = !(fabs(nxp) < 1.0e9) || !(fabs(nyp) < 1.0e9) || !(fabs(nzp) < 1.0e9);
+  int rx = bad ? 0 : (int)round(nxp), ry = bad ? 0 : (int)round(nyp), rz = bad ? 0 : (int)round(nzp);
+  if (!bad && solid_at(g, fl, rx + g.ox, ry + g.oy, rz + g.oz)) {   // fluid.cc:1011
+    double sx = __dmul_rn(a, timestep), sy = __dmul_rn(b, timestep), sz = __dmul_rn(cc, timestep);
+    // openvdb::Coord(double,double,double) truncates toward zero (openvdb/math/Coord.h:61)
+    int tx = (int)x, ty = (int)y, tz = (int)z;
+    bool changed = false;
+    if (solid_at(g, fl, (int)round(__dadd_rn(x, sx)) + g.ox, ty + g.oy, tz + g.oz)) { a *= -1.0 * e; changed = true; }   // :1017-1020
+    if (solid_at(g, fl, tx + g.ox, (int)round(__dadd_rn(y, sy)) + g.oy, tz + g.oz)) { b *= -1.0 * e; changed = true; }   // :1021-1024
+    if (solid_at(g, fl, tx + g.ox, ty + g.oy, (int)round(__dadd_rn(z, sz)) + g.oz)) { cc *= -1.0 * e; changed = true; }  // :1025-1028
+    px[t] = __dadd_rn(x, __dmul_rn(a, timestep));             // fluid.cc:1029
+    py[t] = __dadd_rn(y, __dmul_rn(b, timestep));
+    pz[t] = __dadd_rn(z, __dmul_rn(cc, timestep));
+    if (changed) { vx[t] = a; vy[t] = b; vz[t] = cc; }
+  } else {
+    px[t] = nxp; py[t] = nyp; pz[t] = nzp;                    // fluid.cc:1033
+  }
+}
+
+__global__ void k_reset_max(DevScalars* ds) { ds->max_speed_bits = 0ull; }
+
+int fb_g2p_advect(flipb200_ctx* c) {
+  const Grid& g = c->g;
+  Particles& pt = c->pt;
+  k_reset_max<<<1, 1, 0, c->stream>>>(c->ds);
+  c->launches++;
+  int blocks = (int)((pt.n + 255) / 256);
+  if (blocks == 0) blocks = 1;
+  k_g2p<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                       c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+  CK_LAUNCH(); c->launches++;
+  k_advect<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
+                                          pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds);
+  CK_LAUNCH(); c->launches++;
+  c->sorted = false;   // positions moved: cell order is stale
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// device seeding: 8 particles per voxel, one per 2x2x2 sub-cell, jittered with a counter hash
+// (role of UniformPointScatter at fluid.cc:1348-1350; stratified like SURVEY 8d config 2/3)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__device__ __forceinline__ double u01(uint64_t h) {   // (0,1) open
+  return ((double)(h >> 11) + 0.5) * (1.0 / 9007199254740992.0);
+}
+__global__ void k_seed_box(Grid g, int lx, int ly, int lz, int dxn, int dyn, int dzn, uint64_t seed, int64_t base,
+                           double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+                           double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t nvox = (int64_t)dxn * dyn * dzn;
+  if (t >= nvox * 8) return;
+  int64_t v = t >> 3; int sub = (int)(t & 7);
+  int i = (int)(v % dxn), j = (int)((v / dxn) % dyn), k = (int)(v / ((int64_t)dxn * dyn));
+  uint64_t h = splitmix64(seed ^ (uint64_t)t * 0xD1B54A32D192ED03ull);
+  double jx = u01(h); h = splitmix64(h); double jy = u01(h); h = splitmix64(h); double jz = u01(h);
+  int64_t o = base + t;
+  px[o] = (double)(lx + i - g.ox) - 0.5 + ((sub & 1) + jx) * 0.5;
+  py[o] = (double)(ly + j - g.oy) - 0.5 + (((sub >> 1) & 1) + jy) * 0.5;
+  pz[o] = (double)(lz + k - g.oz) - 0.5 + (((sub >> 2) & 1) + jz) * 0.5;
+  vx[o] = 0.0; vy[o] = 0.0; vz[o] = 0.0;
+}
+
+int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed) {
+  const Grid& g = c->g;
+  int dxn = hi[0] - lo[0] + 1, dyn = hi[1] - lo[1] + 1, dzn = hi[2] - lo[2] + 1;
+  if (dxn <= 0 || dyn <= 0 || dzn <= 0) return FLIPB200_ERR_ARG;
+  int64_t add = (int64_t)dxn * dyn * dzn * 8;
+  int64_t base = c->pt.n;
+  if (base + add >= (int64_t)2147483647) return FLIPB200_ERR_ARG;
+  int rc = fb_reserve_particles(c, base + add);
+  if (rc) return rc;
+  int64_t blocks = (add + 255) / 256;
+  k_seed_box<<<(unsigned)blocks, 256, 0, c->stream>>>(g, lo[0], lo[1], lo[2], dxn, dyn, dzn, seed, base, c->pt.a[0],
+                                                      c->pt.a[1], c->pt.a[2], c->pt.a[3], c->pt.a[4], c->pt.a[5]);
+  CK_LAUNCH(); c->launches++;
+  CK(cudaStreamSynchronize(c->stream));
+  c->pt.n = base + add;
+  c->sorted = false;
+  return 0;
+}

@@ -1,0 +1,139 @@
+/*
+ * flipb200.h -- C ABI of the B200-native FLIP substep (drop-in for the step body of the
+ * reference's fluid.cc).  Plain C types only: no exceptions, STL or torch types cross this
+ * boundary.  Every entry point cites the reference interface it replaces (file:line relative to
+ * the reference repository).  The reference has no FFI today; the seam is the call sequence of
+ * its step loop, fluid.cc:1378-1490 (see INTEGRATION.md for the binding a maintainer would add).
+ *
+ * Conventions
+ *  - all calls return FLIPB200_OK (0) or a negative status; flipb200_strerror() names it.
+ *  - caller owns host buffers, the library owns device buffers.
+ *  - host grid arrays are dense, idx = (k*ny + j)*nx + i (x fastest), i = x + ox, where
+ *    (x,y,z) is the reference's integer coordinate (fluid.cc uses [-60,60]^3, ox = 60).
+ *  - particle positions/velocities are SoA doubles in REFERENCE coordinates.
+ *  - one ctx is not thread-safe; independent ctxs are.  Calls are synchronous for the caller.
+ *  - there is NO CPU fallback: without a CUDA device every compute call fails with
+ *    FLIPB200_ERR_CUDA.
+ */
+#ifndef FLIPB200_H
+#define FLIPB200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLIPB200_VERSION 100
+
+enum {
+  FLIPB200_OK = 0,
+  FLIPB200_ERR_ARG = -1,        /* bad argument                                   */
+  FLIPB200_ERR_CUDA = -2,       /* CUDA runtime error (no device, OOM, launch)    */
+  FLIPB200_ERR_BREAKDOWN = -3,  /* PCG breakdown: p.Ap <= 0 or non-finite scalar  */
+  FLIPB200_ERR_NOCONV = -4,     /* PCG hit max iterations (solution still stored) */
+  FLIPB200_ERR_STATE = -5,      /* stage called out of order                      */
+  FLIPB200_ERR_COMM = -6        /* NCCL / multi-GPU exchange error                */
+};
+
+/* POD parameters; defaults (flipb200_default_params) equal the literals of fluid.cc. */
+typedef struct {
+  int32_t nx, ny, nz;        /* nodes per axis; 121 (box [-60,60], fluid.cc:1159)            */
+  int32_t ox, oy, oz;        /* index of reference coordinate 0; 60                           */
+  int32_t wall;              /* solid shell thickness; 2 <=> |c| > 58 (fluid.cc:1264), >= 1   */
+  int32_t relax_div;         /* 10: velUpdate(dt/10) (fluid.cc:1475)                          */
+  double  dx, rho;           /* 1, 1 (fluid.cc:1358,1471)                                     */
+  double  gx, gy, gz;        /* gravity (0,-10,0) (fluid.cc:1357)                             */
+  double  dt_max;            /* 0.1 (fluid.cc:1490)                                           */
+  double  relax_tol;         /* 0.1 (fluid.cc:1484)                                           */
+  double  restitution;       /* e = 0 (fluid.cc:974)                                          */
+  double  flip_ratio;        /* 1.0: pure FLIP (fluid.cc:981); only 1.0 is implemented        */
+  double  pcg_tol;           /* 2.220446049250313e-16 (Eigen IterativeSolverBase.h:363)       */
+  int32_t pcg_max_iter;      /* <0 => 2*n_fluid (IterativeSolverBase.h:283)                   */
+  int32_t max_passes;        /* safety cap on the do..while loop (reference: unbounded); 200  */
+  int32_t precond;           /* 0 = Jacobi; 1 = multigrid V-cycle (if built)                  */
+  int32_t device;            /* CUDA device ordinal; <0 => current device                     */
+  int64_t max_particles;     /* capacity to reserve; 0 => grow on set_particles               */
+} flipb200_params;
+
+/* per-step statistics (the reference prints none of these except dt and error) */
+typedef struct {
+  int32_t passes;            /* relaxation passes K of the do..while (fluid.cc:1457-1484)     */
+  int32_t n_fluid;           /* numActive (fluid.cc:1395-1433)                                */
+  int32_t pcg_iters_total;   /* sum of cg.iterations() over the passes                        */
+  int32_t pcg_iters_last;
+  double  last_error;        /* error printed at fluid.cc:1499                                */
+  double  dt_out;            /* dt returned by FLIPadvect (fluid.cc:992-999)                  */
+  double  max_speed;         /* maxSpeed (fluid.cc:976-991)                                   */
+  double  pcg_rel_resid;     /* sqrt(|r|^2/|b|^2) of the last solve (cg.error())              */
+  /* device-timed phases, milliseconds (CUDA events on the ctx stream) */
+  float   ms_sort, ms_p2g, ms_grid, ms_pcg, ms_g2p, ms_total;
+  int64_t launches;          /* kernels launched by this call                                 */
+} flipb200_stats;
+
+typedef struct flipb200_ctx flipb200_ctx;
+
+void        flipb200_default_params(flipb200_params*);
+const char* flipb200_strerror(int status);
+int         flipb200_version(void);
+
+/* Scene: replaces the grid construction of main(), fluid.cc:1157-1246, and the solid shell loop
+ * :1256-1331.  solid_host: nx*ny*nz bytes (non-zero = solid obstacle) or NULL; the shell of
+ * thickness `wall` is always made solid, as the reference does. */
+int  flipb200_create (const flipb200_params*, const uint8_t* solid_host, flipb200_ctx**);
+void flipb200_destroy(flipb200_ctx*);
+
+/* PointList state (fluid.cc:804-813, add :841).  Host SoA arrays are copied. */
+int  flipb200_set_particles(flipb200_ctx*, const double* px, const double* py, const double* pz,
+                            const double* vx, const double* vy, const double* vz, int64_t n);
+int  flipb200_get_particles(flipb200_ctx*, double* px, double* py, double* pz,
+                            double* vx, double* vy, double* vz, int64_t cap, int64_t* n);
+int  flipb200_num_particles(flipb200_ctx*, int64_t* n);
+/* Device-side seeding (the role of UniformPointScatter at fluid.cc:1348-1350, stratified):
+ * exactly 8 particles per voxel of the index box [lo,hi] (inclusive), zero velocity. */
+int  flipb200_seed_box(flipb200_ctx*, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
+
+/* One time step == the loop body fluid.cc:1378-1490 with device-resident particles.
+ * dt_inout: in = dt used by the solve (fluid.cc:1469-1475), out = FLIPadvect's dt (:1490). */
+int  flipb200_step(flipb200_ctx*, double* dt_inout, flipb200_stats*);
+/* Same step through HOST buffers (what the reference's main() holds): uploads the six
+ * particle arrays, steps, downloads them and (optionally) the fp32 output grid
+ * (outputGrid, fluid.cc:1434-1451; nx*ny*nz floats or NULL). */
+int  flipb200_step_host(flipb200_ctx*, double* px, double* py, double* pz,
+                        double* vx, double* vy, double* vz, int64_t n,
+                        double* dt_inout, float* output_grid, flipb200_stats*);
+
+/* Stage-level entry points (one per seam of the reference's step loop; used by parity tests). */
+int  flipb200_p2g(flipb200_ctx*);                                /* vels.fill(0) :1378 + PointList::P2Gtransfer :1106-1148 (+ interpolate :843-882 fused) */
+int  flipb200_classify(flipb200_ctx*, int32_t* n_fluid);         /* main :1388-1448 (+ velBeforeUpdate copy :1455) */
+int  flipb200_rhs_div(flipb200_ctx*, double dt, double* b_norm2);/* setRHS :414-479 + setDiver :566-610 (+ b of setA2 :535) */
+int  flipb200_pcg_solve(flipb200_ctx*, double dt, int32_t* iters, double* rel_resid); /* setA :304-412, setA2 :481-541, cg.compute/solve :1473-1474 */
+int  flipb200_vel_update(flipb200_ctx*, double dt_sub);          /* velUpdate :612-703 */
+int  flipb200_relax_error(flipb200_ctx*, double dt, double* error); /* :1477-1483 (setRHS, setDiver, setOnlyB, norm ratio) */
+int  flipb200_g2p_advect(flipb200_ctx*, double* dt_out);         /* PointList::FLIPadvect :972-1038 */
+
+/* Grid access for tests / output.  Double grids: 8 bytes per node; W/B float; FLAGS uint8. */
+enum {
+  FLIPB200_GRID_U = 0, FLIPB200_GRID_V = 1, FLIPB200_GRID_W = 2,     /* vels (Vec3dGrid, fluid.cc:1240), double */
+  FLIPB200_GRID_UB = 3, FLIPB200_GRID_VB = 4, FLIPB200_GRID_WB = 5,  /* velBeforeUpdate (:1455), double          */
+  FLIPB200_GRID_P = 6,                                               /* pressure scattered to the grid, double   */
+  FLIPB200_GRID_WEIGHT = 7,                                          /* weights == containerGrid == outputGrid off solids, float (:809,1157,1161) */
+  FLIPB200_GRID_B = 8,                                               /* diver (= b), float (:1231)               */
+  FLIPB200_GRID_FLAGS = 9                                            /* uint8: bit0..5 solid nbr (-x,+x,-y,+y,-z,+z), bit6 fluid row, bit7 solid */
+};
+int  flipb200_get_grid(flipb200_ctx*, int which, void* host_out, size_t bytes);
+int  flipb200_set_grid(flipb200_ctx*, int which, const void* host_in, size_t bytes);
+
+/* Micro-benchmark hooks (bench.py roofline lines): run `iters` PCG iterations / kernels on the
+ * current system without convergence exit and return the average device time per launch. */
+enum { FLIPB200_KERNEL_SPMV = 0, FLIPB200_KERNEL_PCG_ITER = 1, FLIPB200_KERNEL_P2G = 2,
+       FLIPB200_KERNEL_G2P = 3, FLIPB200_KERNEL_SORT = 4 };
+int  flipb200_time_kernel(flipb200_ctx*, int which, int32_t iters, float* ms_per_launch, int64_t* units);
+
+/* Pinned host memory helpers for the e2e path (cudaHostAlloc / cudaFreeHost). */
+int  flipb200_host_alloc(void** ptr, size_t bytes);
+int  flipb200_host_free(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLIPB200_H */
