@@ -1,0 +1,281 @@
+#!/usr/bin/env python
+"""bench.py -- FLIP particle-steps/s (BASELINE.json metric) on N GPUs of one node.
+
+  python bench.py --gpus N --steps K --warmup W            # CUDA path (this repo)
+  python bench.py --impl reference --gpus N --steps K ...  # CPU oracle arm (reference's Eigen solve)
+
+A "step" is one pass of the hot path (fluid.cc:1378-1490: sort, P2G, classify, relaxation loop with
+the pressure solves, G2P, advection) over the synthetic dam-break full-tank scene (SURVEY.md 8d,
+fill (i)): n^3 grid, exactly 8 particles per fluid voxel, zero initial velocity.  Default n = 256
+(BASELINE configs[2], the configuration the metric is quoted on; ~127 M particles, fits one B200).
+
+Prints ONE JSON line (rank 0).  `value` = particles x K / device time with inputs resident in HBM;
+`e2e` = the same through flipb200_step_host with pinned HOST buffers (H2D + step + D2H per step);
+`roofline` = the PCG stencil kernel (17 algorithmic bytes per swept node) against the measured HBM
+peak; `cpu_baseline` = the CPU oracle on a bounded sample.  N > 1 currently runs N independent
+replicas of the scene, one per GPU (weak scaling; the z-slab decomposition is not built yet).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "flip_particle_steps_per_s"
+UNIT = "particle-steps/s"
+CPU_SAMPLE_N = 64
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                sm.append(float(s[0])); mx = max(mx, float(s[1]))
+                for nm, v in zip(names, s[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def scene_box(n, nz=None):
+    nz = n if nz is None else nz
+    wall = 2
+    lo = (wall, wall, wall)
+    hi = (n - 1 - wall, n - 1 - wall - 2, nz - 1 - wall)     # full tank with a 2-cell air gap (SURVEY 8d fill (i))
+    return lo, hi
+
+
+def run_cpu_sample(steps, warmup, threads):
+    """The CPU arm: oracle restatement + the reference's Eigen IC-PCG on the same scene family at
+    n = CPU_SAMPLE_N (bounded sample).  Returns (particle-steps/s, description)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    from fluid_simulation_b200 import scenes
+    n = CPU_SAMPLE_N
+    sc = scenes.dam_break(n=n, fill="full")
+    o = oracle_py.Oracle(nx=n, ny=n, nz=n, ox=n // 2, oy=n // 2, oz=n // 2, threads=threads)
+    o.set_particles(sc.pos, sc.vel)
+    dt = 0.1
+    for _ in range(warmup):
+        dt, _st = o.step(dt)
+    t0 = time.perf_counter()
+    iters = passes = 0
+    for _ in range(steps):
+        dt, st = o.step(dt)
+        iters += st.pcg_iters_total; passes += st.passes
+    el = time.perf_counter() - t0
+    kind = "port"   # restated particle/grid loops; the pressure solve IS the reference's own Eigen code
+    desc = (f"dam-break full-tank fill at {n}^3 ({sc.num_particles} particles), {steps} full steps after "
+            f"{warmup} warm-up: oracle restatement of fluid.cc with the reference's vendored Eigen IC-PCG "
+            f"(single-threaded, as run.sh builds it) and OpenMP particle loops on {threads} threads; "
+            f"{passes} relaxation passes, {iters} PCG iterations; generous to the CPU: IC-PCG iterations grow "
+            f"~linearly with n and the restatement drops the reference's ValueAccessor/mutex overhead")
+    return sc.num_particles * steps / el, el / steps * 1e3, kind, desc, o.has_eigen
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="flipb200", choices=["flipb200", "reference"])
+    ap.add_argument("--n", type=int, default=int(os.environ.get("FLIPB200_BENCH_N", "256")))
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--kernel-iters", type=int, default=50)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    n = args.n
+    lo, hi = scene_box(n)
+    particles = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8
+    config = {"workload": f"dam-break FLIP full-tank fill, {n}^3 grid, 8 particles/cell ({particles} particles/GPU), "
+                          f"fp64, Jacobi-PCG to 2.2e-16 (BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}])",
+              "grid": [n, n, n], "particles_per_gpu": particles,
+              "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (z-slab split not built yet)",
+              "l2": "inputs larger than L2 (particle arrays 48 B x particles, grid vectors 8 B x n^3)" if n >= 256
+                    else "working set may fit L2 at this n; no flush between steps"}
+
+    if args.impl == "reference":
+        # Reference arm: the reference's CPU implementation of the path, host cores only.
+        if rank != 0:
+            return 0
+        threads = os.cpu_count() or 1
+        v, ms, kind, desc, has_eigen = run_cpu_sample(args.steps, max(args.warmup, 0), threads)
+        line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": desc,
+                                 "eigen_from_reference": bool(has_eigen)},
+                "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    import fluid_simulation_b200 as fb
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the FLIP path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    f = fb.Flip(nx=n, ny=n, nz=n, ox=n // 2, oy=n // 2, oz=n // 2, device=local_rank, max_particles=particles)
+    f.seed_box(lo, hi, seed=1234 + rank)
+    assert f.num_particles == particles
+    dt = 0.1
+    stats = []
+    for _ in range(args.warmup):
+        dt, st = f.step(dt)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    dev_ms = 0.0
+    launches = 0
+    for _ in range(args.steps):
+        dt, st = f.step(dt)
+        dev_ms += st.ms_total; launches += st.launches
+        stats.append(st.as_dict())
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    # device time: CUDA events on the library's stream (flipb200_stats.ms_total), max over ranks
+    dev_s = max_over_ranks(dev_ms * 1e-3)
+    wall = max_over_ranks(wall)
+    value = world * particles * args.steps / dev_s
+
+    # ---- kernel roofline (dominant kernel: the PCG stencil) ----
+    peak, peak_src = measured_peak_gbs()
+    f.p2g(); f.classify(); f.rhs_div(dt)
+    ms_spmv, nodes = f.time_kernel(fb.KERNEL_SPMV, args.kernel_iters)
+    ms_iter, _ = f.time_kernel(fb.KERNEL_PCG_ITER, args.kernel_iters)
+    ms_p2g, npart = f.time_kernel(fb.KERNEL_P2G, 5)
+    ms_sort, _ = f.time_kernel(fb.KERNEL_SORT, 5)
+    ach = 17.0 * nodes / (ms_spmv * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_spmv (7-pt matrix-free A.p + p.Ap)", "achieved": ach, "peak": peak,
+                "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_node": 17, "swept_nodes": nodes, "us_per_launch": ms_spmv * 1e3}
+    kernels = {
+        "pcg_iteration": {"bytes_per_node": 91, "us": ms_iter * 1e3, "gbs": 91.0 * nodes / (ms_iter * 1e-3) / 1e9,
+                          "frac": 91.0 * nodes / (ms_iter * 1e-3) / 1e9 / peak, "iters_per_s": 1e3 / ms_iter},
+        "p2g": {"bytes_per_particle": 52, "ms": ms_p2g, "gbs": 52.0 * npart / (ms_p2g * 1e-3) / 1e9,
+                "frac": 52.0 * npart / (ms_p2g * 1e-3) / 1e9 / peak},
+        "sort": {"ms": ms_sort},
+    }
+
+    # ---- e2e: the same step through the host-buffer entry point ----
+    e2e = None
+    if not args.no_e2e:
+        pos, vel = None, None
+        arrs, ptrs = [], []
+        for q in range(6):
+            a, p = fb.pinned_empty(particles)
+            arrs.append(a); ptrs.append(p)
+        import ctypes as C
+        m = C.c_int64(0)
+        fb._check(f.lib.flipb200_get_particles(f.h, *[fb._ptr(a) for a in arrs], particles, C.byref(m)), "get")
+        out, outp = fb.pinned_empty(n * n * n, np.float32)
+        dte = dt
+        dte, _ = f.step_host(arrs, dte, output_grid=out)      # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            dte, st = f.step_host(arrs, dte, output_grid=out)
+            launches_e = st.launches
+        barrier()
+        el = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": world * particles * args.steps / el, "unit": UNIT,
+               "h2d_bytes_per_step": 48 * particles, "d2h_bytes_per_step": 48 * particles + 4 * n ** 3,
+               "ms_per_step": el / args.steps * 1e3, "api": "flipb200_step_host (pinned host SoA in/out + outputGrid)"}
+        for p in ptrs + [outp]:
+            fb.pinned_free(p)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        v, ms, kind, desc, has_eigen = run_cpu_sample(1, 1, threads)
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": desc,
+               "eigen_from_reference": bool(has_eigen)}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+                "cpu_baseline": cpu, "kernels": kernels, "wall_ms_per_step": wall / args.steps * 1e3,
+                "per_step": [{k: s[k] for k in ("passes", "pcg_iters_total", "ms_sort", "ms_p2g", "ms_grid", "ms_pcg",
+                                                 "ms_g2p", "ms_total")} for s in stats]}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -66,6 +66,8 @@ struct Particles {
   double* b[6];      // alternate buffers (sort destination)
   uint32_t* key;     // cell key of each particle (base cell of its 2x2x2 support)
   uint32_t* rank;    // arrival rank inside the cell
+  uint32_t* id;      // original index of each particle (only with params.track_ids)
+  uint32_t* id_b;
   int64_t n, cap;
 };
 
@@ -199,5 +201,7 @@ int fb_fetch_scalars(flipb200_ctx* c);
 int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units);
 int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 int fb_reserve_particles(flipb200_ctx* c, int64_t n);
+int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n);
+int fb_download_particles(flipb200_ctx* c, double* const dst[6]);
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }

@@ -23,6 +23,7 @@ void flipb200_default_params(flipb200_params* p) {
   p->max_passes = 200;
   p->precond = 0;
   p->device = -1;
+  p->track_ids = 0;
   p->max_particles = 0;
 }
 
@@ -87,10 +88,56 @@ int fb_reserve_particles(flipb200_ctx* c, int64_t n) {
   uint32_t *nk, *nr;
   CK(cudaMalloc((void**)&nk, ncap * sizeof(uint32_t)));
   CK(cudaMalloc((void**)&nr, ncap * sizeof(uint32_t)));
+  uint32_t *ni = nullptr, *nib = nullptr;
+  if (c->P.track_ids) {
+    CK(cudaMalloc((void**)&ni, ncap * sizeof(uint32_t)));
+    CK(cudaMalloc((void**)&nib, ncap * sizeof(uint32_t)));
+    if (pt.n > 0) CK(cudaMemcpyAsync(ni, pt.id, pt.n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+  }
   CK(cudaStreamSynchronize(c->stream));
   for (int q = 0; q < 6; ++q) { cudaFree(pt.a[q]); cudaFree(pt.b[q]); pt.a[q] = na[q]; pt.b[q] = nb[q]; }
-  cudaFree(pt.key); cudaFree(pt.rank);
-  pt.key = nk; pt.rank = nr; pt.cap = ncap;
+  cudaFree(pt.key); cudaFree(pt.rank); cudaFree(pt.id); cudaFree(pt.id_b);
+  pt.key = nk; pt.rank = nr; pt.id = ni; pt.id_b = nib; pt.cap = ncap;
+  return 0;
+}
+
+__global__ void k_iota(uint32_t* __restrict__ id, int64_t first, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) id[first + i] = (uint32_t)(first + i);
+}
+int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n) {
+  if (!c->P.track_ids || n <= 0) return 0;
+  k_iota<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->pt.id, first, n);
+  CK_LAUNCH(); c->launches++;
+  return 0;
+}
+
+// scatter back to the caller's order: dst[id[i]] = src[i]
+__global__ void k_unpermute(int64_t n, const uint32_t* __restrict__ id,
+                            const double* __restrict__ a0, const double* __restrict__ a1, const double* __restrict__ a2,
+                            const double* __restrict__ a3, const double* __restrict__ a4, const double* __restrict__ a5,
+                            double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
+                            double* __restrict__ b3, double* __restrict__ b4, double* __restrict__ b5) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t d = id[i];
+  b0[d] = a0[i]; b1[d] = a1[i]; b2[d] = a2[i]; b3[d] = a3[i]; b4[d] = a4[i]; b5[d] = a5[i];
+}
+
+// device -> host copy of the six particle arrays (original order when ids are tracked)
+int fb_download_particles(flipb200_ctx* c, double* const dst[6]) {
+  Particles& pt = c->pt;
+  if (pt.n == 0) return 0;
+  double* const* src = pt.a;
+  if (c->P.track_ids) {
+    k_unpermute<<<(unsigned)((pt.n + 255) / 256), 256, 0, c->stream>>>(pt.n, pt.id, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                                                       pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2],
+                                                                       pt.b[3], pt.b[4], pt.b[5]);
+    CK_LAUNCH(); c->launches++;
+    src = pt.b;
+  }
+  for (int q = 0; q < 6; ++q)
+    if (dst[q]) CK(cudaMemcpyAsync(dst[q], src[q], pt.n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   return 0;
 }
 
@@ -177,7 +224,7 @@ void flipb200_destroy(flipb200_ctx* c) {
   cudaFree(c->x); cudaFree(c->r); cudaFree(c->pd); cudaFree(c->Ap);
   cudaFree(c->cell_count); cudaFree(c->cell_start); cudaFree(c->scan_tmp);
   for (int q = 0; q < 6; ++q) { cudaFree(c->pt.a[q]); cudaFree(c->pt.b[q]); }
-  cudaFree(c->pt.key); cudaFree(c->pt.rank);
+  cudaFree(c->pt.key); cudaFree(c->pt.rank); cudaFree(c->pt.id); cudaFree(c->pt.id_b);
   cudaFree(c->ds);
   if (c->hs) cudaFreeHost(c->hs);
   for (int e = 0; e < 8; ++e) if (c->ev[e]) cudaEventDestroy(c->ev[e]);
@@ -195,8 +242,9 @@ int flipb200_set_particles(flipb200_ctx* c, const double* px, const double* py, 
   const double* src[6] = {px, py, pz, vx, vy, vz};
   for (int q = 0; q < 6; ++q)
     if (n) CK(cudaMemcpyAsync(c->pt.a[q], src[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
   c->pt.n = n;
+  if (fb_init_ids(c, 0, n)) return FLIPB200_ERR_CUDA;
+  CK(cudaStreamSynchronize(c->stream));
   c->sorted = false;
   return FLIPB200_OK;
 }
@@ -208,8 +256,7 @@ int flipb200_get_particles(flipb200_ctx* c, double* px, double* py, double* pz, 
   if (cap < c->pt.n) return FLIPB200_ERR_ARG;
   CK(cudaSetDevice(c->device));
   double* dst[6] = {px, py, pz, vx, vy, vz};
-  for (int q = 0; q < 6; ++q)
-    if (dst[q] && c->pt.n) CK(cudaMemcpyAsync(dst[q], c->pt.a[q], c->pt.n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  if (fb_download_particles(c, dst)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   return FLIPB200_OK;
 }

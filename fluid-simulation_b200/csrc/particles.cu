@@ -98,12 +98,14 @@ __global__ void k_reorder(int64_t n, const uint32_t* __restrict__ key, const uin
                           const double* __restrict__ a0, const double* __restrict__ a1, const double* __restrict__ a2,
                           const double* __restrict__ a3, const double* __restrict__ a4, const double* __restrict__ a5,
                           double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
-                          double* __restrict__ b3, double* __restrict__ b4, double* __restrict__ b5) {
+                          double* __restrict__ b3, double* __restrict__ b4, double* __restrict__ b5,
+                          const uint32_t* __restrict__ id, uint32_t* __restrict__ id_b) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   int64_t d = (int64_t)start[key[i]] + rank[i];
   b0[d] = a0[i]; b1[d] = a1[i]; b2[d] = a2[i];
   b3[d] = a3[i]; b4[d] = a4[i]; b5[d] = a5[i];
+  if (id) id_b[d] = id[i];
 }
 
 int fb_sort_particles(flipb200_ctx* c) {
@@ -127,9 +129,10 @@ int fb_sort_particles(flipb200_ctx* c) {
     int blocks = (int)((pt.n + 255) / 256);
     k_reorder<<<blocks, 256, 0, c->stream>>>(pt.n, pt.key, pt.rank, c->cell_start, pt.a[0], pt.a[1], pt.a[2],
                                              pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2], pt.b[3],
-                                             pt.b[4], pt.b[5]);
+                                             pt.b[4], pt.b[5], pt.id, pt.id_b);
     CK_LAUNCH(); c->launches++;
     for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
+    { uint32_t* t = pt.id; pt.id = pt.id_b; pt.id_b = t; }
   }
   c->sorted = true;
   return 0;
@@ -393,6 +396,7 @@ int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint6
   k_seed_box<<<(unsigned)blocks, 256, 0, c->stream>>>(g, lo[0], lo[1], lo[2], dxn, dyn, dzn, seed, base, c->pt.a[0],
                                                       c->pt.a[1], c->pt.a[2], c->pt.a[3], c->pt.a[4], c->pt.a[5]);
   CK_LAUNCH(); c->launches++;
+  if (fb_init_ids(c, base, add)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->pt.n = base + add;
   c->sorted = false;

@@ -95,12 +95,12 @@ int flipb200_step_host(flipb200_ctx* c, double* px, double* py, double* pz, doub
   for (int q = 0; q < 6; ++q)
     if (n) CK(cudaMemcpyAsync(c->pt.a[q], src[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   c->pt.n = n; c->sorted = false;
+  if (fb_init_ids(c, 0, n)) return FLIPB200_ERR_CUDA;
   rc = step_device(c, dt_inout, st);
   if (rc) return rc;
-  // NOTE: particles come back in cell-sorted order (a permutation of the input order); the
-  // reference's particle order carries no meaning (tbb::parallel_for over an unordered list).
-  for (int q = 0; q < 6; ++q)
-    if (n) CK(cudaMemcpyAsync(src[q], c->pt.a[q], n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  // With params.track_ids the arrays come back in the caller's order (the reference never
+  // reorders its PointList); otherwise cell-sorted, i.e. a permutation of the input.
+  if (fb_download_particles(c, src)) return FLIPB200_ERR_CUDA;
   if (output_grid) {
     const Grid& g = c->g;
     CK(cudaMemcpy2DAsync(output_grid, g.nx * sizeof(float), c->wf, g.px * sizeof(float), g.nx * sizeof(float),

@@ -52,6 +52,10 @@ typedef struct {
   int32_t max_passes;        /* safety cap on the do..while loop (reference: unbounded); 200  */
   int32_t precond;           /* 0 = Jacobi; 1 = multigrid V-cycle (if built)                  */
   int32_t device;            /* CUDA device ordinal; <0 => current device                     */
+  int32_t track_ids;         /* 1: carry particle ids through the cell sort so that get_particles /
+                                step_host return the caller's original order (the reference never
+                                reorders its PointList); 0: arrays come back cell-sorted          */
+  int32_t reserved0;
   int64_t max_particles;     /* capacity to reserve; 0 => grow on set_particles               */
 } flipb200_params;
 

@@ -1,0 +1,283 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the CPU oracle on the
+same seeded inputs.  Tolerances are the north_star's: single-step grid velocity and pressure
+rel-L2 <= 1e-5, particle positions after 10 steps rel-L2 <= 1e-4 (fp64).  Integer/byte results
+(cell classification, pass counts) must match exactly."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import rel_l2, oracle_for_scene, random_velocity_scene
+
+pytestmark = pytest.mark.gpu
+
+TOL_GRID = 1e-5      # north_star: single-step grid velocity / pressure rel-L2
+TOL_POS10 = 1e-4     # north_star: positions after 10 steps rel-L2
+
+
+@pytest.fixture(scope="module")
+def scenes():
+    from fluid_simulation_b200 import scenes as s
+    return s
+
+
+def _pair(fb, oracle_mod, sc, **kw):
+    f = fb.Flip.from_scene(sc, track_ids=1, **kw)
+    o = oracle_for_scene(oracle_mod, sc)
+    return f, o
+
+
+def _grids(fb, f, base=0):
+    return np.stack([f.get_grid(base + a) for a in range(3)])
+
+
+def _ogrids(o, base=0):
+    return np.stack([o.dgrid(base + a) for a in range(3)])
+
+
+@pytest.mark.parametrize("mode", ["cell", "particle"])
+def test_p2g_classify(fb, oracle_mod, scenes, mode):
+    """a5/a6/a7: splat + normalise + classification vs the oracle (both P2G kernels)."""
+    sc = random_velocity_scene(scenes)
+    os.environ["FLIPB200_P2G"] = mode
+    try:
+        f, o = _pair(fb, oracle_mod, sc)
+        f.p2g(); nf = f.classify()
+    finally:
+        os.environ.pop("FLIPB200_P2G", None)
+    o.clear_vel(); o.p2g(); no = o.classify()
+    assert nf == no
+    fl = f.get_grid(fb.GRID_FLAGS)
+    assert np.array_equal((fl & fb.FB_FLUID) != 0, o.indices >= 0)          # exact cell classification
+    assert np.array_equal((fl & fb.FB_SOLID) != 0, o.solid == 1)
+    w = f.get_grid(fb.GRID_WEIGHT)
+    assert rel_l2(w, o.fgrid(oracle_mod.F_W)) < 5e-7                         # fp32 storage, order-dependent sum
+    assert rel_l2(w, o.fgrid(oracle_mod.F_CONTAINER)) < 5e-7                 # container := weights (a6 fused away)
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < 1e-6                          # u = sum(cw v)/float(w)
+    assert rel_l2(_grids(fb, f, fb.GRID_UB), _ogrids(o)) < 1e-6              # velBeforeUpdate copy
+
+
+def _inject_oracle_state(fb, oracle_mod, f, o):
+    """Make the device hold exactly the oracle's post-P2G fields so later stages compare bit-tightly."""
+    for a in range(3):
+        f.set_grid(fb.GRID_U + a, o.dgrid(a))
+
+
+def test_rhs_div_pcg_velupdate_relax(fb, oracle_mod, scenes):
+    """a9-a16 stage by stage from identical inputs."""
+    sc = random_velocity_scene(scenes, vscale=2.0)
+    f, o = _pair(fb, oracle_mod, sc)
+    dt = 0.1
+    f.p2g(); f.classify()
+    o.clear_vel(); o.p2g(); o.classify(); o.save_vel_before()
+    _inject_oracle_state(fb, oracle_mod, f, o)
+    # rhs + divergence: float grid, same statement order => bit-exact
+    bn2 = f.rhs_div(dt)
+    o.rhs_div(dt); o.assemble(dt)
+    b = f.get_grid(fb.GRID_B)
+    assert np.array_equal(b, o.fgrid(oracle_mod.F_DIVER))
+    assert bn2 == pytest.approx(float(np.sum(o.b.astype(np.float64) ** 2)), rel=1e-12)
+    # pressure solve: Jacobi-PCG (CUDA) vs the reference's IC-PCG (Eigen), both to eps*|b|
+    it, rel = f.pcg_solve(dt)
+    ito, relo = o.solve()
+    p = f.get_grid(fb.GRID_P)
+    assert rel < 2.220446049250313e-16 and relo < 2.220446049250313e-16     # converged to the reference's tolerance
+    assert rel_l2(p, o.dgrid(oracle_mod.D_P)) < 1e-9
+    assert 0 < it <= 2 * o.num_active
+    # velocity update from identical pressure
+    f.set_grid(fb.GRID_P, o.dgrid(oracle_mod.D_P))
+    f.vel_update(dt / 10); o.vel_update(dt / 10)
+    assert np.array_equal(_grids(fb, f), _ogrids(o))                        # same op order, no FMA => bit-exact
+    # relaxation error
+    e = f.relax_error(dt); eo = o.relax_error(dt)
+    assert e == pytest.approx(eo, rel=1e-12)
+
+
+def test_g2p_advect(fb, oracle_mod, scenes):
+    """a17/a18 from identical grids; includes particles that hit the solid shell."""
+    sc = random_velocity_scene(scenes, n=21, half=7, vscale=6.0)   # fast particles next to the wall (|c|<=8)
+    f, o = _pair(fb, oracle_mod, sc)
+    dt = 0.1
+    f.p2g(); f.classify()
+    o.clear_vel(); o.p2g(); o.classify(); o.save_vel_before()
+    o.rhs_div(dt); o.assemble(dt); o.solve(); o.vel_update(dt / 10)
+    for a in range(3):
+        f.set_grid(fb.GRID_U + a, o.dgrid(a))
+        f.set_grid(fb.GRID_UB + a, o.dgrid(3 + a))
+    dt_g = f.g2p_advect()
+    dt_o = o.flip_advect(dt)
+    assert dt_g == pytest.approx(dt_o, rel=1e-13)
+    pg, vg = f.get_particles(); po, vo = o.get_particles()
+    assert rel_l2(vg, vo) < 1e-12
+    assert rel_l2(pg, po) < 1e-13
+    # the collision branch must have fired for some particles (velocity components zeroed, e = 0)
+    assert np.count_nonzero(vo == 0.0) > 0
+    assert np.array_equal(vg == 0.0, vo == 0.0)
+
+
+def test_single_step_small(fb, oracle_mod, scenes):
+    sc = random_velocity_scene(scenes, vscale=0.5)
+    f, o = _pair(fb, oracle_mod, sc)
+    dt_g, st = f.step(0.1)
+    dt_o, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
+    assert abs(st.last_error - so.last_error) < 1e-6
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+    assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
+    assert dt_g == pytest.approx(dt_o, rel=1e-9)
+    pg, vg = f.get_particles(); po, vo = o.get_particles()
+    assert rel_l2(pg, po) < 1e-7 and rel_l2(vg, vo) < 1e-5
+
+
+def test_ten_steps_small_cube_drop(fb, oracle_mod, scenes):
+    """Miniature of BASELINE config 1 from rest: pass counts (8 at step 0), then 10 steps."""
+    sc = scenes.small_cube_drop(n=25, half=4)
+    f, o = _pair(fb, oracle_mod, sc)
+    dg = do = 0.1
+    for s in range(10):
+        dg, st = f.step(dg)
+        do, so = o.step(do)
+        assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid), f"step {s}"
+        if s == 0:
+            assert st.passes == 8
+            assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+            assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
+    pg, vg = f.get_particles(); po, vo = o.get_particles()
+    assert rel_l2(pg, po) < TOL_POS10
+    assert dg == pytest.approx(do, rel=1e-6)
+
+
+def test_default_scene_single_step(fb, oracle_mod, scenes):
+    """BASELINE config 1 at full size (121^3, 689,210 particles): one step vs the oracle."""
+    sc = scenes.cube_drop_default()
+    f, o = _pair(fb, oracle_mod, sc)
+    dt_g, st = f.step(0.1)
+    dt_o, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid) == (8, so.n_fluid)
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+    assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
+    w = f.get_grid(fb.GRID_WEIGHT)
+    assert rel_l2(w, o.fgrid(oracle_mod.F_OUTPUT)) < 5e-7                   # outputGrid (fluid.cc:1434-1448)
+    pg, vg = f.get_particles(); po, vo = o.get_particles()
+    assert rel_l2(pg, po) < 1e-7
+
+
+def test_hydrostatic_kat(fb):
+    """Analytic KAT (analogue of openvdb/unittest/TestPoissonSolver.cc:215-290): open-top tank at
+    rest, p = rho*|g|*dx*depth exactly when dt is exact in fp32."""
+    n = 13
+    xs = np.arange(2, n - 2) - 6
+    ys = np.arange(2, 8) - 6
+    X, Y, Z = np.meshgrid(xs, ys, xs, indexing="ij")
+    pos = np.stack([X.ravel(), Y.ravel(), Z.ravel()], 1).astype(np.float64)
+    f = fb.Flip(nx=n, ny=n, nz=n, ox=6, oy=6, oz=6)
+    f.set_particles(pos, np.zeros_like(pos))
+    dt = 0.125
+    f.p2g(); assert f.classify() == 9 * 6 * 9
+    f.rhs_div(dt); it, rel = f.pcg_solve(dt)
+    p = f.get_grid(fb.GRID_P)
+    for j in range(2, 8):
+        assert np.allclose(p[2:n - 2, j, 2:n - 2], 10.0 * (8 - j), rtol=1e-12)
+    assert it < 60
+    f.vel_update(dt)
+    for a in range(3):
+        assert np.abs(f.get_grid(fb.GRID_U + a)[:, :8, :]).max() < 1e-12
+
+
+def test_edge_cases(fb, oracle_mod, scenes):
+    # empty particle set: a step is a no-op, error = 0/0 = NaN exits after one pass (fluid.cc:1483-1484)
+    f = fb.Flip(nx=17, ny=17, nz=17, ox=8, oy=8, oz=8)
+    f.set_particles(np.zeros((0, 3)), np.zeros((0, 3)))
+    dt, st = f.step(0.1)
+    assert st.n_fluid == 0 and st.passes == 1 and dt == 0.1
+    # particles outside the box / inside the shell: no grid contribution, free flight (Appendix A.15)
+    pos = np.array([[30.0, 0.2, 0.1], [-7.4, 0.3, 0.2], [0.25, 0.5, -0.75]])
+    vel = np.array([[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.5, -0.5, 0.25]])
+    f.set_particles(pos, vel)
+    o = oracle_mod.Oracle(nx=17, ny=17, nz=17, ox=8, oy=8, oz=8)
+    o.set_particles(pos, vel)
+    f2 = fb.Flip(nx=17, ny=17, nz=17, ox=8, oy=8, oz=8, track_ids=1)
+    f2.set_particles(pos, vel)
+    dg, st = f2.step(0.1); do, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
+    pg, vg = f2.get_particles(); po, vo = o.get_particles()
+    assert rel_l2(pg, po) < 1e-9 and rel_l2(vg, vo) < 1e-7
+
+
+def test_interior_obstacle(fb, oracle_mod, scenes):
+    """Interior solids (the reference's commented-out block scenes, fluid.cc:1303-1345)."""
+    sc = random_velocity_scene(scenes, n=25, half=5, vscale=0.5)
+    solid = np.zeros((25, 25, 25), dtype=np.uint8)
+    solid[10:15, 4:10, 10:15] = 1          # a block under the fluid cube (z,y,x order)
+    f = fb.Flip(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, track_ids=1, solid=solid)
+    f.set_particles(sc.pos, sc.vel)
+    o = oracle_mod.Oracle(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, solid=solid)
+    o.set_particles(sc.pos, sc.vel)
+    dg = do = 0.1
+    for s in range(3):
+        dg, st = f.step(dg); do, so = o.step(do)
+        assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid), s
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+    pg, _ = f.get_particles(); po, _ = o.get_particles()
+    assert rel_l2(pg, po) < 1e-6
+
+
+def test_step_host_matches_step(fb, scenes):
+    """The host-buffer entry point (what the reference's main() would call) == device-resident step."""
+    sc = random_velocity_scene(scenes, vscale=0.5)
+    f1 = fb.Flip.from_scene(sc, track_ids=1)
+    f2 = fb.Flip(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, track_ids=1)
+    d1, s1 = f1.step(0.1)
+    arrs = [np.ascontiguousarray(sc.pos[:, i]) for i in range(3)] + [np.ascontiguousarray(sc.vel[:, i]) for i in range(3)]
+    out = np.zeros((25, 25, 25), dtype=np.float32)
+    d2, s2 = f2.step_host(arrs, 0.1, output_grid=out)
+    assert (s1.passes, s1.n_fluid, d1) == (s2.passes, s2.n_fluid, d2)
+    p1, v1 = f1.get_particles()
+    assert rel_l2(np.stack(arrs[:3], 1), p1) < 1e-12 and rel_l2(np.stack(arrs[3:], 1), v1) < 1e-9
+    assert np.array_equal(out, f2.get_grid(fb.GRID_WEIGHT))
+
+
+def test_seed_box_and_sort_invariants(fb):
+    """Device seeding: exactly 8 particles per voxel, inside their voxel, deterministic in the seed."""
+    f = fb.Flip(nx=33, ny=33, nz=33, ox=16, oy=16, oz=16)
+    f.seed_box((4, 4, 4), (19, 11, 27), seed=7)
+    assert f.num_particles == 16 * 8 * 24 * 8
+    p, v = f.get_particles()
+    vox = np.floor(p + 0.5).astype(int) + 16
+    assert vox.min(0).tolist() == [4, 4, 4] and vox.max(0).tolist() == [19, 11, 27]
+    _, counts = np.unique(vox, axis=0, return_counts=True)
+    assert np.all(counts == 8) and np.all(v == 0)
+    g = fb.Flip(nx=33, ny=33, nz=33, ox=16, oy=16, oz=16)
+    g.seed_box((4, 4, 4), (19, 11, 27), seed=7)
+    assert np.array_equal(g.get_particles()[0], p)
+    # P2G of a uniform velocity field reproduces it on every node that received weight (normalisation)
+    f.set_particles(p, np.tile(np.array([[0.25, -1.5, 3.0]]), (p.shape[0], 1)))
+    f.p2g(); f.classify()
+    w = f.get_grid(fb.GRID_WEIGHT)
+    for a, val in enumerate((0.25, -1.5, 3.0)):
+        u = f.get_grid(fb.GRID_U + a)
+        assert np.allclose(u[w > 0], val, rtol=1e-6)     # float(w) rounding only
+        assert np.all(u[w == 0] == 0)
+
+
+def test_full_size_properties_128(fb):
+    """BASELINE config 2 size (128^3, 8 ppc full tank, 15.0 M particles) through size-independent
+    properties: particle count conservation under the cell sort, hydrostatic pressure at rest
+    (p = rho*|g|*depth within the reference's own fp32-coefficient rounding), and a fluid that
+    stays at rest (max speed after one step bounded by the under-relaxation residual)."""
+    n = 128
+    f = fb.Flip(nx=n, ny=n, nz=n, ox=64, oy=64, oz=64)
+    f.seed_box((2, 2, 2), (125, 123, 125), seed=1234)
+    assert f.num_particles == 124 * 122 * 124 * 8
+    f.p2g(); nf = f.classify()
+    assert nf == 124 * 123 * 124          # every interior node below the free surface (+1 layer reached by the splat)
+    w = f.get_grid(fb.GRID_WEIGHT)
+    assert w.sum(dtype=np.float64) > 0
+    dt = 0.125
+    f.rhs_div(dt); it, rel = f.pcg_solve(dt)
+    assert rel < 2.220446049250313e-16
+    p = f.get_grid(fb.GRID_P)
+    top = 2 + 123                          # first air node index in y
+    col = p[64, 2:top, 64]
+    expect = 10.0 * (top - np.arange(2, top))
+    assert np.allclose(col, expect, rtol=1e-9)
