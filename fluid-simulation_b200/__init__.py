@@ -141,7 +141,6 @@ def pinned_empty(n, dtype=np.float64):
     _check(lib.flipb200_host_alloc(C.byref(p), max(nbytes, 8)), "host_alloc")
     buf = (C.c_char * max(nbytes, 8)).from_address(p.value)
     arr = np.frombuffer(buf, dtype=dtype, count=int(n))
-    arr._flip_pinned = p  # keep the address; freed explicitly by pinned_free
     return arr, p
 
 

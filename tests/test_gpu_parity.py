@@ -95,7 +95,7 @@ def test_rhs_div_pcg_velupdate_relax(fb, oracle_mod, scenes):
 
 def test_g2p_advect(fb, oracle_mod, scenes):
     """a17/a18 from identical grids; includes particles that hit the solid shell."""
-    sc = random_velocity_scene(scenes, n=21, half=7, vscale=6.0)   # fast particles next to the wall (|c|<=8)
+    sc = random_velocity_scene(scenes, n=21, half=8, vscale=6.0)   # fast particles touching the wall (shell at |c| >= 9)
     f, o = _pair(fb, oracle_mod, sc)
     dt = 0.1
     f.p2g(); f.classify()
