@@ -133,6 +133,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--kernel-iters", type=int, default=50)
+    ap.add_argument("--precond", type=int, default=int(os.environ.get("FLIPB200_PRECOND", "0")), help="0 Jacobi, 1 multigrid V-cycle")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -142,7 +143,7 @@ def main():
     lo, hi = scene_box(n)
     particles = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8
     config = {"workload": f"dam-break FLIP full-tank fill, {n}^3 grid, 8 particles/cell ({particles} particles/GPU), "
-                          f"fp64, Jacobi-PCG to 2.2e-16 (BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}])",
+                          f"fp64, {'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 (BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}])",
               "grid": [n, n, n], "particles_per_gpu": particles,
               "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (z-slab split not built yet)",
               "l2": "inputs larger than L2 (particle arrays 48 B x particles, grid vectors 8 B x n^3)" if n >= 256
@@ -185,7 +186,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    f = fb.Flip(nx=n, ny=n, nz=n, ox=n // 2, oy=n // 2, oz=n // 2, device=local_rank, max_particles=particles)
+    f = fb.Flip(nx=n, ny=n, nz=n, ox=n // 2, oy=n // 2, oz=n // 2, device=local_rank, max_particles=particles, precond=args.precond)
     f.seed_box(lo, hi, seed=1234 + rank)
     assert f.num_particles == particles
     dt = 0.1

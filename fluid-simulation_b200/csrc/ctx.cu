@@ -185,6 +185,7 @@ int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb20
   if (alloc_n(c, &c->x, T) || alloc_n(c, &c->r, T) || alloc_n(c, &c->pd, T) || alloc_n(c, &c->Ap, T)) goto fail;
   if (alloc_n(c, &c->cell_count, T + 2) || alloc_n(c, &c->cell_start, T + 2) || alloc_n(c, &c->scan_tmp, T / 2048 + 64)) goto fail;
   if (alloc_n(c, &c->ds, 1)) goto fail;
+  if (fb_mg_alloc(c)) goto fail;
   if (cudaHostAlloc((void**)&c->hs, sizeof(DevScalars), cudaHostAllocDefault) != cudaSuccess) goto fail;
   memset(c->hs, 0, sizeof(DevScalars));
 
@@ -218,6 +219,7 @@ void flipb200_destroy(flipb200_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  fb_mg_free(c);
   cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static);
   for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }
   cudaFree(c->wacc); cudaFree(c->wf); cudaFree(c->bf[0]); cudaFree(c->bf[1]);

@@ -42,7 +42,8 @@ __global__ void k_pcg_reset(DevScalars* ds) {
 // x = 0, r = b, p = M^-1 r, rz[3] = r.p   (Eigen ConjugateGradient.h:43,63,66 with x0 = 0)
 __global__ void __launch_bounds__(PCG_TX * PCG_TY)
 k_pcg_init(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, const float* __restrict__ b,
-           double* __restrict__ x, double* __restrict__ r, double* __restrict__ p, DevScalars* __restrict__ ds) {
+           double* __restrict__ x, double* __restrict__ r, double* __restrict__ p, DevScalars* __restrict__ ds,
+           int mg) {
   __shared__ double sm[32];
   double acc[1] = {0.0};
   for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
@@ -60,9 +61,10 @@ k_pcg_init(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl
         pv = rv * cf.inv[k];
         acc[0] += rv * pv;
       }
-      x[q] = 0.0; r[q] = rv; p[q] = pv;
+      x[q] = 0.0; r[q] = rv; p[q] = mg ? 0.0 : pv;
     }
   }
+  if (mg) return;   // multigrid: z = M^-1 r and r.z come from the V-cycle
   block_sum<1>(acc, sm);
   if (threadIdx.x == 0 && threadIdx.y == 0) atomicAdd(&ds->rz[3], acc[0]);
 }
@@ -101,6 +103,7 @@ k_spmv(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, co
 }
 
 // K2: alpha = rz_old / pAp;  x += alpha p;  r -= alpha Ap;  rr = |r|^2;  rz = r.M^-1 r
+template <bool JAC>
 __global__ void __launch_bounds__(PCG_TX * PCG_TY)
 k_update_xr(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, double* __restrict__ x,
             double* __restrict__ r, const double* __restrict__ p, const double* __restrict__ Ap,
@@ -132,14 +135,14 @@ k_update_xr(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ f
         double rn = r[q] - alpha * Ap[q];              // :74
         x[q] = xn; r[q] = rn;
         acc[0] += rn * rn;                             // :76
-        acc[1] += rn * (rn * cf.inv[k]);               // :80,83
+        if (JAC) acc[1] += rn * (rn * cf.inv[k]);      // :80,83
       }
     }
   }
   block_sum<2>(acc, sm);
   if (threadIdx.x == 0 && threadIdx.y == 0) {
     atomicAdd(&ds->rr[it & 3], acc[0]);
-    atomicAdd(&ds->rz[it & 3], acc[1]);
+    if (JAC) atomicAdd(&ds->rz[it & 3], acc[1]);
   }
 }
 
@@ -178,6 +181,41 @@ k_update_p(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl
   }
 }
 
+// ---- multigrid-preconditioned variant: z = M^-1 r comes from fb_mg_vcycle (mg.cu) ---------------
+// stop test of ConjugateGradient.h:77-78, evaluated before the preconditioner is applied
+__global__ void k_pcg_check(DevScalars* __restrict__ ds, int it, double threshold) {
+  if (ds->pcg_done) return;
+  const double rr = ds->rr[it & 3];
+  if (rr < threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
+}
+
+// p = z + beta p, beta = rz/rz_old (first: p = z).  it = -1 for the initial direction.
+__global__ void __launch_bounds__(PCG_TX * PCG_TY)
+k_update_p_mg(Grid g, Box box, Tiling t, const uint8_t* __restrict__ fl, const double* __restrict__ z,
+              double* __restrict__ p, DevScalars* __restrict__ ds, int it, int max_iter) {
+  if (ds->pcg_done) return;
+  const bool first = it < 0;
+  const bool lead = blockIdx.x == 0 && threadIdx.x == 0 && threadIdx.y == 0;
+  const double beta = first ? 0.0 : ds->rz[it & 3] / ds->rz[(it + 3) & 3];
+  if (lead) {
+    int s = (it + 1) & 3;
+    ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
+    if (!first && it + 1 >= max_iter) {
+      ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = ds->rr[it & 3]; ds->pcg_status = FLIPB200_ERR_NOCONV;
+    }
+  }
+  for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
+    int tx, ty, tz; item_to_tile(t, item, tx, ty, tz);
+    int i = box.x0 + tx * PCG_TX + threadIdx.x, j = box.y0 + ty * PCG_TY + threadIdx.y;
+    if (i >= box.x1 || j >= box.y1) continue;
+    int zs = box.z0 + tz * PCG_ZC, ze = min(zs + PCG_ZC, box.z1);
+    int q = gidx(g, i, j, zs);
+    for (int zz = zs; zz < ze; ++zz, q += g.plane) {
+      if (fl[q] & FB_FLUID) p[q] = first ? z[q] : z[q] + beta * p[q];
+    }
+  }
+}
+
 static void make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
   const double scale = dt / (c->P.rho * c->P.dx * c->P.dx);       // fluid.cc:306
   float acc = 0.0f;
@@ -211,22 +249,48 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   const dim3 blk(PCG_TX, PCG_TY, 1);
   const double bnorm2 = c->hs->bnorm2;             // fetched by fb_rhs_div
   const float* bvec = c->bf[c->bcur];
+  const bool use_mg = c->mg_levels >= 2;
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds);
-  k_pcg_init<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, bvec, c->x, c->r, c->pd, c->ds);
+  k_pcg_init<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, bvec, c->x, c->r, c->pd, c->ds, use_mg ? 1 : 0);
   CK_LAUNCH(); c->launches += 2;
   if (bnorm2 == 0.0) return 0;                     // rhsNorm2 == 0 => x = 0, 0 iterations (ConjugateGradient.h:46-52)
   if (!(bnorm2 == bnorm2)) return FLIPB200_ERR_BREAKDOWN;
   const double tol = c->P.pcg_tol;
   const double threshold = tol * tol * bnorm2;     // :53
   const int max_iter = c->P.pcg_max_iter < 0 ? 2 * c->n_fluid : c->P.pcg_max_iter;   // IterativeSolverBase.h:283
-  const int batch = 32;
+  const int batch = use_mg ? 8 : 32;
   int it = 0;
   bool done = max_iter == 0;
+  if (use_mg && !done) {
+    int rc = fb_mg_setup(c, dt);                   // hierarchy of this step (flags are per step; cheap)
+    if (rc) return rc;
+    rc = fb_mg_vcycle(c, -1);                      // z0 = M^-1 r0, rz[3] = r0.z0
+    if (rc) return rc;
+    k_update_p_mg<<<grid, blk, 0, c->stream>>>(g, b, t, c->flags, c->Ap, c->pd, c->ds, -1, max_iter);
+    c->launches++;
+  }
+  while (!done && use_mg) {
+    int stop = min(it + batch, max_iter);
+    for (; it < stop; ++it) {
+      k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, it, 0);
+      k_update_xr<false><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 0);
+      k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it, threshold);
+      c->launches += 3;
+      int rc = fb_mg_vcycle(c, it);
+      if (rc) return rc;
+      k_update_p_mg<<<grid, blk, 0, c->stream>>>(g, b, t, c->flags, c->Ap, c->pd, c->ds, it, max_iter);
+      c->launches++;
+    }
+    CK_LAUNCH();
+    int rc = fb_fetch_scalars(c);
+    if (rc) return rc;
+    done = c->hs->pcg_done != 0 || it >= max_iter;
+  }
   while (!done) {
     int stop = min(it + batch, max_iter);
     for (; it < stop; ++it) {
       k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, it, 0);
-      k_update_xr<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 0);
+      k_update_xr<true><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 0);
       k_update_p<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->r, c->pd, c->ds, it, max_iter, threshold, 0);
       c->launches += 3;
     }
@@ -252,11 +316,11 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   const int grid = min(t.nitems, c->num_sms * 2);
   const dim3 blk(PCG_TX, PCG_TY, 1);
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds);
-  k_pcg_init<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, c->ds);
+  k_pcg_init<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, c->ds, 0);
   for (int w = 0; w < 3; ++w) {
     k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, w, 1);
     if (which == FLIPB200_KERNEL_PCG_ITER) {
-      k_update_xr<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, w, 1);
+      k_update_xr<true><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, w, 1);
       k_update_p<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->r, c->pd, c->ds, w, 1 << 30, 0.0, 1);
     }
   }
@@ -264,7 +328,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   for (int it = 3; it < 3 + iters; ++it) {
     k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
     if (which == FLIPB200_KERNEL_PCG_ITER) {
-      k_update_xr<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 1);
+      k_update_xr<true><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 1);
       k_update_p<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->r, c->pd, c->ds, it, 1 << 30, 0.0, 1);
     }
   }

@@ -1,0 +1,112 @@
+// sweep.cuh -- the two kernel shapes every grid-side solver kernel is built from.  Both were
+// chosen by measurement on B200 (tools/kbench.cu, 256^3 fp64): all loads unconditional and issued
+// before any use, results masked by the flag byte, two x-nodes per lane.
+//
+//  STREAM shape: block (32,8) = 8 rows x 64 nodes, one z-plane per blockIdx.z, one shot.  A pure
+//                axpy-type update in this shape runs at the device-copy rate (6.7 TB/s counted on its
+//                algorithmic bytes); the earlier z-marching tile loop with a flag test in front of
+//                the loads reached 4.3 TB/s.
+//  STENCIL shape: block (32,4), each lane owns 2 x-nodes, the block marches ST_ZP z-planes keeping
+//                z-1/z/z+1 in registers; x-neighbours come from warp shuffles (lane 0/31 load the
+//                two edge values), y-neighbours are vector loads that hit L1/L2.  7-point A.p runs
+//                at 4.3 TB/s (65.7 us at 256^3) against 2.7 TB/s for one-thread-per-node.
+#pragma once
+#include "common.cuh"
+
+#define ST_BY 4
+#define ST_ZP 4
+#define SW_BY 8
+
+template <typename T> struct Vec2T;
+template <> struct Vec2T<double> { typedef double2 type; };
+template <> struct Vec2T<float> { typedef float2 type; };
+
+template <typename T> __device__ __forceinline__ typename Vec2T<T>::type ld2(const T* p) {
+  return *reinterpret_cast<const typename Vec2T<T>::type*>(p);
+}
+template <typename T> __device__ __forceinline__ void st2(T* p, T a, T b) {
+  typename Vec2T<T>::type v; v.x = a; v.y = b;
+  *reinterpret_cast<typename Vec2T<T>::type*>(p) = v;
+}
+template <typename T> __device__ __forceinline__ typename Vec2T<T>::type zero2() {
+  typename Vec2T<T>::type v; v.x = T(0); v.y = T(0); return v;
+}
+
+// geometry of one sweep over a box of a level
+struct Sweep {
+  Grid g;
+  Box box;
+  int xe;        // exclusive x limit for lanes (even, <= px)
+};
+static inline Sweep make_sweep(const Grid& g, const Box& b) {
+  Sweep s; s.g = g; s.box = b;
+  s.box.x0 = b.x0 & ~1;
+  int xe = (b.x1 + 1) & ~1;
+  s.xe = xe < g.px ? xe : g.px;
+  return s;
+}
+static inline bool sweep_empty(const Sweep& s) {
+  return !(s.box.x1 > s.box.x0 && s.box.y1 > s.box.y0 && s.box.z1 > s.box.z0);
+}
+static inline dim3 stream_grid(const Sweep& s) {
+  return dim3(cdiv(s.xe - s.box.x0, 64), cdiv(s.box.y1 - s.box.y0, SW_BY), s.box.z1 - s.box.z0);
+}
+static inline dim3 stencil_grid(const Sweep& s) {
+  return dim3(cdiv(s.xe - s.box.x0, 64), cdiv(s.box.y1 - s.box.y0, ST_BY), cdiv(s.box.z1 - s.box.z0, ST_ZP));
+}
+#define STREAM_BLOCK dim3(32, SW_BY, 1)
+#define STENCIL_BLOCK dim3(32, ST_BY, 1)
+
+// STREAM prologue: i (even x of this lane), j, k, q and `act`
+#define STREAM_PROLOGUE(S)                                                      \
+  const int i = (S).box.x0 + blockIdx.x * 64 + 2 * threadIdx.x;                 \
+  const int j = (S).box.y0 + blockIdx.y * SW_BY + threadIdx.y;                  \
+  const int k = (S).box.z0 + blockIdx.z;                                        \
+  const bool act = i < (S).xe && j < (S).box.y1;                                \
+  const int q = gidx((S).g, i, j, k);
+
+// Z-marching 7-point neighbourhood for the two nodes (i, i+1) of a lane.
+// Usage:  StencilMarch<T> m; m.begin(S, src); for (z...) { m.load(S, src); ... m.sum0()/sum1()/c0()/c1(); m.advance(); }
+template <typename T>
+struct StencilMarch {
+  typedef typename Vec2T<T>::type V;
+  V pm, pc, pn, ym, yp;
+  T left, right;
+  int i, j, k, q, lane;
+  bool act, jlo, jhi;
+
+  __device__ __forceinline__ bool begin(const Sweep& S, const T* __restrict__ src) {
+    lane = threadIdx.x;
+    i = S.box.x0 + blockIdx.x * 64 + 2 * lane;
+    j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
+    k = S.box.z0 + blockIdx.z * ST_ZP;
+    if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
+    act = i < S.xe;
+    jlo = j > 0; jhi = j < S.g.ny - 1;
+    q = gidx(S.g, i, j, k);
+    pm = (act && k > 0) ? ld2<T>(src + q - S.g.plane) : zero2<T>();
+    pc = act ? ld2<T>(src + q) : zero2<T>();
+    return true;
+  }
+  // issue every load of plane k (call before using the values)
+  __device__ __forceinline__ void load(const Sweep& S, const T* __restrict__ src) {
+    pn = (act && k < S.g.nz - 1) ? ld2<T>(src + q + S.g.plane) : zero2<T>();
+    ym = (act && jlo) ? ld2<T>(src + q - S.g.px) : zero2<T>();
+    yp = (act && jhi) ? ld2<T>(src + q + S.g.px) : zero2<T>();
+    left = __shfl_up_sync(0xffffffffu, pc.y, 1);
+    right = __shfl_down_sync(0xffffffffu, pc.x, 1);
+    if (lane == 0) left = (act && i > 0) ? src[q - 1] : T(0);
+    if (lane == 31) right = (act && i + 2 < S.g.px) ? src[q + 2] : T(0);
+  }
+  __device__ __forceinline__ T c0() const { return pc.x; }
+  __device__ __forceinline__ T c1() const { return pc.y; }
+  __device__ __forceinline__ T sum0() const { return (pm.x + pn.x) + (ym.x + yp.x) + (left + pc.y); }
+  __device__ __forceinline__ T sum1() const { return (pm.y + pn.y) + (ym.y + yp.y) + (pc.x + right); }
+  __device__ __forceinline__ void advance(const Sweep& S) { pm = pc; pc = pn; q += S.g.plane; ++k; }
+};
+
+// block reduction for the (32, BY) shapes: thread (0,0) ends with the sum
+template <int NV>
+__device__ __forceinline__ void block_sum_xy(double (&v)[NV], double* smem /* >= 32*NV */) {
+  block_sum<NV>(v, smem);
+}

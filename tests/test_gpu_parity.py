@@ -281,3 +281,64 @@ def test_full_size_properties_128(fb):
     col = p[64, 2:top, 64]
     expect = 10.0 * (top - np.arange(2, top))
     assert np.allclose(col, expect, rtol=1e-9)
+
+
+# ---- multigrid-preconditioned CG (params.precond = 1) ---------------------------------------------
+def test_mgpcg_solve_matches_reference(fb, oracle_mod, scenes):
+    """Same system, three solvers: Eigen IC-PCG (reference), Jacobi-PCG and MG-PCG (CUDA)."""
+    sc = random_velocity_scene(scenes, n=41, half=12, vscale=2.0)
+    o = oracle_for_scene(oracle_mod, sc)
+    o.clear_vel(); o.p2g(); o.classify(); o.rhs_div(0.1); o.assemble(0.1)
+    ito, relo = o.solve()
+    res = {}
+    for precond in (0, 1):
+        f = fb.Flip.from_scene(sc, precond=precond)
+        f.p2g(); f.classify()
+        for a in range(3):
+            f.set_grid(fb.GRID_U + a, o.dgrid(a))
+        f.rhs_div(0.1)
+        it, rel = f.pcg_solve(0.1)
+        assert rel < 2.220446049250313e-16
+        assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < 1e-9
+        res[precond] = it
+    assert res[1] < 40 and res[1] * 4 < res[0], res     # V-cycle must actually precondition
+
+
+def test_mgpcg_steps(fb, oracle_mod, scenes):
+    """Full steps with the multigrid preconditioner: same pass counts and parity bounds."""
+    sc = scenes.small_cube_drop(n=33, half=6)
+    f = fb.Flip.from_scene(sc, track_ids=1, precond=1)
+    o = oracle_for_scene(oracle_mod, sc)
+    dg = do = 0.1
+    for s in range(10):
+        dg, st = f.step(dg); do, so = o.step(do)
+        assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid), f"step {s}"
+        if s == 0:
+            assert st.passes == 8
+            assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+            assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
+    pg, _ = f.get_particles(); po, _ = o.get_particles()
+    assert rel_l2(pg, po) < TOL_POS10
+
+
+def test_mgpcg_obstacle_and_tank_128(fb, oracle_mod, scenes):
+    # interior obstacle (Neumann inside the domain) through the hierarchy
+    sc = random_velocity_scene(scenes, n=25, half=5, vscale=0.5)
+    solid = np.zeros((25, 25, 25), dtype=np.uint8)
+    solid[10:15, 4:10, 10:15] = 1
+    f = fb.Flip(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, track_ids=1, solid=solid, precond=1)
+    f.set_particles(sc.pos, sc.vel)
+    o = oracle_mod.Oracle(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, solid=solid)
+    o.set_particles(sc.pos, sc.vel)
+    dg, st = f.step(0.1); do, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+    # BASELINE config 2 size: hydrostatic tank at 128^3, analytic answer, iteration count bounded
+    n = 128
+    f = fb.Flip(nx=n, ny=n, nz=n, ox=64, oy=64, oz=64, precond=1)
+    f.seed_box((2, 2, 2), (125, 123, 125), seed=1234)
+    f.p2g(); f.classify()
+    f.rhs_div(0.125); it, rel = f.pcg_solve(0.125)
+    assert rel < 2.220446049250313e-16 and it < 60, (it, rel)
+    p = f.get_grid(fb.GRID_P)
+    assert np.allclose(p[64, 2:125, 64], 10.0 * (125 - np.arange(2, 125)), rtol=1e-9)
