@@ -71,12 +71,14 @@ struct Particles {
   int64_t n, cap;
 };
 
-// One level of the geometric multigrid hierarchy (level 0 aliases the fine-grid arrays).
+// One level of the geometric multigrid hierarchy.  The V-cycle runs in fp32 (it only preconditions
+// the fp64 CG); level 0 shares the fine flags.
 struct MgLevel {
   Grid g;
   Box box;            // sweep box of this step at this level
   uint8_t* flags;     // same encoding as the fine flags (FB_*)
-  double *x, *t, *b;  // solution ping-pong and right-hand side
+  uint8_t* nrm;       // 64 x (sum of the prolongation weights of the non-solid coarse donors), 27..64
+  float *xa, *xb, *b; // solution ping-pong and right-hand side
   double h2inv;       // operator scale: A x = h2inv * (k x_c - sum of fluid neighbours)
 };
 #define MG_MAX_LEVELS 12
@@ -98,7 +100,6 @@ struct flipb200_ctx {
   float  *bf[2];           // diver (= b) ping-pong: [cur] is b of this pass, [cur^1] receives b2
   int     bcur;
   double *x, *r, *pd, *Ap; // PCG vectors (x = pressure on the grid)
-  double *mgx;             // level-0 multigrid scratch (second solution buffer)
   MgLevel mg[MG_MAX_LEVELS];
   int mg_levels;           // 0 => hierarchy not allocated (precond != 1)
   // cell-sort arrays
@@ -215,7 +216,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
 int fb_mg_alloc(flipb200_ctx* c);
 void fb_mg_free(flipb200_ctx* c);
 int fb_mg_setup(flipb200_ctx* c, double dt);                    // per step: coarse flags + boxes
-int fb_mg_vcycle(flipb200_ctx* c, int it);                      // z (= mg[0].t) = M^-1 r, accumulates r.z into ds->rz[it&3]
+int fb_mg_vcycle(flipb200_ctx* c, int it);                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it&3]
 int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 int fb_reserve_particles(flipb200_ctx* c, int64_t n);
 int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n);

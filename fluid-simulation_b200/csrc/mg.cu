@@ -2,7 +2,7 @@
 //
 // The reference preconditions with Eigen's IncompleteCholesky (fluid.cc:1352,1473); the north_star
 // asks for a "Jacobi/IC-free" preconditioner.  Jacobi-PCG needs ~10 n iterations on an n^3 tank
-// (2600 at 256^3); this V-cycle brings that to ~25, independent of n (tools/mg_proto*.py).
+// (2600 at 256^3); this V-cycle brings that to ~25-30, independent of n (tools/mg_proto*.py).
 //
 // Design (after McAdams, Sifakis, Teran 2010, adapted to the reference's cell classes):
 //  * level l+1 cell (I,J,K) covers level-l cells (2I..2I+1, 2J..2J+1, 2K..2K+1); children outside
@@ -12,12 +12,19 @@
 //    of non-solid neighbours (air = Dirichlet 0, solid = Neumann); h2inv_l = scale / 4^l.
 //  * smoother: damped Jacobi (omega = 0.8), 2 pre + 2 post sweeps (symmetric).
 //  * prolongation P: cell-centred trilinear (3/4,1/4 per axis) with the weights of SOLID coarse
-//    cells dropped and the rest renormalised (constant extrapolation at Neumann walls);
+//    cells dropped and the rest renormalised (constant extrapolation at Neumann walls) -- the
+//    normaliser of every fine cell is an integer n64/64 kept in a byte array per level;
 //    restriction R = P^T / 8.  => M^-1 is symmetric positive definite, as CG requires.
-//  * coarsest level (<= 4096 cells): 2x20 Jacobi sweeps in one thread block.
-#include "common.cuh"
+//  * coarsest level (<= 4096 cells): 41 Jacobi sweeps inside one thread block, in shared memory.
+//  * precision: the whole cycle runs in fp32 on a residual scaled to O(1) (the outer CG stays fp64
+//    and converges to the same 2.2e-16; prototype: 23 vs 22 iterations, tools/mg_proto3.py), which
+//    halves the preconditioner's HBM traffic.  r.z is accumulated in fp64 against the fp64 residual.
+// Kernel shapes: sweep.cuh.  Finest-level bytes per node and V-cycle: smooth 13, residual 14,
+// restrict 4.5, prolong 9.5, smooth 13, smooth+dot 21  = 75 B (fp32) vs 91 B for ONE Jacobi-PCG
+// iteration in fp64.
+#include "sweep.cuh"
+#include "pcg.cuh"
 
-#define MG_OMEGA 0.8
 #define MG_COARSE_SWEEPS 40
 #define MG_COARSEST_CELLS 4096
 
@@ -29,46 +36,61 @@ static void mg_level_dims(const Grid& f, Grid* c) {
   c->total = c->plane * c->nz;
 }
 
+static int mg_alloc_level(flipb200_ctx* c, MgLevel& L, bool own_flags) {
+  size_t T = (size_t)L.g.total;
+  if (own_flags) {
+    CK(cudaMalloc((void**)&L.flags, T));
+    CK(cudaMemsetAsync(L.flags, FB_SOLID | FB_SMASK, T, c->stream));
+  }
+  CK(cudaMalloc((void**)&L.nrm, T));
+  CK(cudaMalloc((void**)&L.xa, T * sizeof(float)));
+  CK(cudaMalloc((void**)&L.xb, T * sizeof(float)));
+  CK(cudaMalloc((void**)&L.b, T * sizeof(float)));
+  CK(cudaMemsetAsync(L.nrm, 64, T, c->stream));
+  CK(cudaMemsetAsync(L.xa, 0, T * sizeof(float), c->stream));
+  CK(cudaMemsetAsync(L.xb, 0, T * sizeof(float), c->stream));
+  CK(cudaMemsetAsync(L.b, 0, T * sizeof(float), c->stream));
+  return 0;
+}
+
+__global__ void k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* __restrict__ b,
+                              float* __restrict__ xout, const DevScalars* __restrict__ ds);
+
 int fb_mg_alloc(flipb200_ctx* c) {
   c->mg_levels = 0;
   if (c->P.precond != 1) return 0;
-  MgLevel& L0 = c->mg[0];
-  L0.g = c->g; L0.flags = c->flags; L0.b = c->r; L0.t = c->Ap;
-  CK(cudaMalloc((void**)&c->mgx, (size_t)c->g.total * sizeof(double)));
-  CK(cudaMemsetAsync(c->mgx, 0, (size_t)c->g.total * sizeof(double), c->stream));
-  L0.x = c->mgx;
+  // count levels first: a grid that is already "coarsest" keeps the Jacobi preconditioner
+  Grid f = c->g;
   int nl = 1;
+  Grid dims[MG_MAX_LEVELS]; dims[0] = f;
   while (nl < MG_MAX_LEVELS) {
-    const Grid& f = c->mg[nl - 1].g;
-    if ((int64_t)f.nx * f.ny * f.nz <= MG_COARSEST_CELLS || min(f.nx, min(f.ny, f.nz)) < 4) break;
-    MgLevel& L = c->mg[nl];
-    mg_level_dims(f, &L.g);
-    size_t T = (size_t)L.g.total;
-    CK(cudaMalloc((void**)&L.flags, T));
-    CK(cudaMalloc((void**)&L.x, T * sizeof(double)));
-    CK(cudaMalloc((void**)&L.t, T * sizeof(double)));
-    CK(cudaMalloc((void**)&L.b, T * sizeof(double)));
-    CK(cudaMemsetAsync(L.flags, FB_SOLID | FB_SMASK, T, c->stream));
-    CK(cudaMemsetAsync(L.x, 0, T * sizeof(double), c->stream));
-    CK(cudaMemsetAsync(L.t, 0, T * sizeof(double), c->stream));
-    CK(cudaMemsetAsync(L.b, 0, T * sizeof(double), c->stream));
+    const Grid& p = dims[nl - 1];
+    if ((int64_t)p.nx * p.ny * p.nz <= MG_COARSEST_CELLS || min(p.nx, min(p.ny, p.nz)) < 4) break;
+    mg_level_dims(p, &dims[nl]);
     ++nl;
   }
-  if (nl < 2) { cudaFree(c->mgx); c->mgx = nullptr; nl = 0; }   // grid too small: Jacobi preconditioner
+  if (nl < 2) return 0;
+  c->mg[0].g = c->g; c->mg[0].flags = c->flags;
+  if (mg_alloc_level(c, c->mg[0], false)) return FLIPB200_ERR_CUDA;
+  for (int l = 1; l < nl; ++l) {
+    c->mg[l].g = dims[l];
+    if (mg_alloc_level(c, c->mg[l], true)) return FLIPB200_ERR_CUDA;
+  }
+  CK(cudaFuncSetAttribute(k_mg_coarsest, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
   c->mg_levels = nl;
   return 0;
 }
 
 void fb_mg_free(flipb200_ctx* c) {
-  if (c->mg_levels == 0) return;
-  cudaFree(c->mgx);
-  for (int l = 1; l < c->mg_levels; ++l) {
-    cudaFree(c->mg[l].flags); cudaFree(c->mg[l].x); cudaFree(c->mg[l].t); cudaFree(c->mg[l].b);
+  for (int l = 0; l < c->mg_levels; ++l) {
+    MgLevel& L = c->mg[l];
+    if (l > 0) cudaFree(L.flags);
+    cudaFree(L.nrm); cudaFree(L.xa); cudaFree(L.xb); cudaFree(L.b);
   }
   c->mg_levels = 0;
 }
 
-// ---- per-step hierarchy: coarse cell types, then solid-neighbour masks -------------------------
+// ---- per-step hierarchy: coarse cell types, solid-neighbour masks, prolongation normalisers ----
 __global__ void k_mg_coarsen(Grid gf, Grid gc, const uint8_t* __restrict__ ff, uint8_t* __restrict__ fc) {
   int I = blockIdx.x * blockDim.x + threadIdx.x;
   int J = blockIdx.y * blockDim.y + threadIdx.y;
@@ -106,10 +128,34 @@ __global__ void k_mg_nbrmask(Grid g, uint8_t* __restrict__ fl) {
   if (sol(i, j + 1, k)) m |= FB_SYP;
   if (sol(i, j, k - 1)) m |= FB_SZM;
   if (sol(i, j, k + 1)) m |= FB_SZP;
-  // note: only bits 6/7 of the neighbours are read above and only bits 0..5 (+ bit 6) of this
-  // cell change, so the in-place update is race-free.
+  // only bit 7 of the neighbours is read and it never changes here: the in-place update is safe
   if ((f & FB_FLUID) && m == FB_SMASK) f &= ~FB_FLUID;   // no non-solid neighbour: empty row
   fl[q] = f | m;
+}
+
+// n64 = 64 * sum of the trilinear weights of the non-solid, in-grid coarse donors of a fine cell
+__global__ void k_mg_norm(Grid gf, Box box, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ fc,
+                          uint8_t* __restrict__ nrm) {
+  int i = box.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int j = box.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int k = box.z0 + blockIdx.z;
+  if (i >= box.x1 || j >= box.y1) return;
+  int q = gidx(gf, i, j, k);
+  int n64 = 64;
+  if (ff[q] & FB_FLUID) {
+    n64 = 0;
+    int I = i >> 1, J = j >> 1, K = k >> 1;
+    int sx = (i & 1) ? 1 : -1, sy = (j & 1) ? 1 : -1, sz = (k & 1) ? 1 : -1;
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      int ci = I + ((m & 1) ? sx : 0), cj = J + ((m & 2) ? sy : 0), ck = K + ((m & 4) ? sz : 0);
+      if (!in_box(gc, ci, cj, ck)) continue;
+      if (fc[gidx(gc, ci, cj, ck)] & FB_SOLID) continue;
+      n64 += ((m & 1) ? 1 : 3) * ((m & 2) ? 1 : 3) * ((m & 4) ? 1 : 3);
+    }
+    if (n64 == 0) n64 = 64;   // cannot happen: the parent of a fluid cell is never solid
+  }
+  nrm[q] = (uint8_t)n64;
 }
 
 int fb_mg_setup(flipb200_ctx* c, double dt) {
@@ -117,285 +163,253 @@ int fb_mg_setup(flipb200_ctx* c, double dt) {
   const double scale = dt / (c->P.rho * c->P.dx * c->P.dx);   // fluid.cc:306
   c->mg[0].box = c->box;
   c->mg[0].h2inv = scale;
-  c->mg[0].g = c->g;
+  const dim3 blk(32, 8, 1);
   for (int l = 1; l < c->mg_levels; ++l) {
     MgLevel& F = c->mg[l - 1];
     MgLevel& L = c->mg[l];
-    dim3 blk(32, 8, 1), grd(cdiv(L.g.px, 32), cdiv(L.g.ny, 8), L.g.nz);
+    dim3 grd(cdiv(L.g.px, 32), cdiv(L.g.ny, 8), L.g.nz);
     k_mg_coarsen<<<grd, blk, 0, c->stream>>>(F.g, L.g, F.flags, L.flags);
     k_mg_nbrmask<<<grd, blk, 0, c->stream>>>(L.g, L.flags);
     c->launches += 2;
     L.h2inv = F.h2inv * 0.25;
-    // coarse box: covers the parents of the fine box, +1 cell margin for the prolongation reads
+    // coarse box: the parents of the fine box plus a 1-cell margin (prolongation donors)
     Box b;
     b.x0 = max(0, F.box.x0 / 2 - 1) & ~1; b.y0 = max(0, F.box.y0 / 2 - 1); b.z0 = max(0, F.box.z0 / 2 - 1);
     b.x1 = min(L.g.nx, (F.box.x1 + 1) / 2 + 1); b.y1 = min(L.g.ny, (F.box.y1 + 1) / 2 + 1);
     b.z1 = min(L.g.nz, (F.box.z1 + 1) / 2 + 1);
     if (!(F.box.x1 > F.box.x0)) b = Box{0, 0, 0, 0, 0, 0};
     L.box = b;
+    const Box& fb = F.box;
+    if (fb.x1 > fb.x0 && fb.y1 > fb.y0 && fb.z1 > fb.z0) {
+      dim3 g2(cdiv(fb.x1 - fb.x0, 32), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
+      k_mg_norm<<<g2, blk, 0, c->stream>>>(F.g, fb, L.g, F.flags, L.flags, F.nrm);
+      c->launches++;
+    }
   }
   CK_LAUNCH();
   return 0;
 }
 
-// ---- V-cycle kernels -----------------------------------------------------------------------------
-// All sweep the level's box with one thread per node; non-fluid nodes inside the box are written
-// as 0 so that the 6-neighbour sum needs no masks (same convention as pcg.cu).
-struct MgArgs {
-  Grid g; Box box; double h2inv;
-};
-
-#define MG_NODE_PROLOGUE                                             \
-  int i = a.box.x0 + blockIdx.x * blockDim.x + threadIdx.x;          \
-  int j = a.box.y0 + blockIdx.y * blockDim.y + threadIdx.y;          \
-  int k = a.box.z0 + blockIdx.z;                                     \
-  bool inb = i < a.box.x1 && j < a.box.y1;
-
-// sum of the six neighbours; solid / out-of-grid neighbours (mask bit set) are not loaded: coarse
-// levels have no solid shell, so a fluid cell may sit on the grid boundary.
-__device__ __forceinline__ double mg_nbr_sum(const double* __restrict__ x, int q, const Grid& g, uint8_t f) {
-  double s = 0.0;
-  if (!(f & FB_SXM)) s += x[q - 1];
-  if (!(f & FB_SXP)) s += x[q + 1];
-  if (!(f & FB_SYM)) s += x[q - g.px];
-  if (!(f & FB_SYP)) s += x[q + g.px];
-  if (!(f & FB_SZM)) s += x[q - g.plane];
-  if (!(f & FB_SZP)) s += x[q + g.plane];
-  return s;
-}
-
-// first Jacobi sweep from x = 0:  x = omega D^-1 b
-__global__ void __launch_bounds__(256)
-k_mg_smooth_first(MgArgs a, const uint8_t* __restrict__ fl, const double* __restrict__ b, double* __restrict__ xo,
-                  const DevScalars* __restrict__ ds) {
-  if (ds->pcg_done) return;
-  MG_NODE_PROLOGUE
-  if (!inb) return;
-  int q = gidx(a.g, i, j, k);
-  uint8_t f = fl[q];
-  double v = 0.0;
-  if (f & FB_FLUID) {
-    int kk = 6 - __popc(f & FB_SMASK);
-    v = MG_OMEGA * b[q] / ((double)kk * a.h2inv);
-  }
-  xo[q] = v;
-}
-
-// Jacobi sweep: xo = xi + omega D^-1 (b - A xi);  DOT: also accumulate sum(b * xo) into ds->rz[slot]
+// ---- V-cycle kernels (fp32) --------------------------------------------------------------------
+// damped-Jacobi sweep  xo = xi + w D^-1 (b - A xi)   (STENCIL shape).
+// DOT (last sweep of level 0): also rz[it&3] += sum r64 * xo / sc  -- the CG's r.z in fp64.
 template <bool DOT>
-__global__ void __launch_bounds__(256)
-k_mg_smooth(MgArgs a, const uint8_t* __restrict__ fl, const double* __restrict__ b, const double* __restrict__ xi,
-            double* __restrict__ xo, DevScalars* __restrict__ ds, int slot) {
+__global__ void __launch_bounds__(32 * ST_BY)
+k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
+            const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
+            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it) {
   __shared__ double sm[32];
   if (ds->pcg_done) return;
-  MG_NODE_PROLOGUE
   double acc[1] = {0.0};
-  if (inb) {
-    int q = gidx(a.g, i, j, k);
-    uint8_t f = fl[q];
-    double v = 0.0;
-    if (f & FB_FLUID) {
-      int kk = 6 - __popc(f & FB_SMASK);
-      double xc = xi[q];
-      double s = mg_nbr_sum(xi, q, a.g, f);
-      double bq = b[q];
-      double Ax = a.h2inv * ((double)kk * xc - s);
-      v = xc + MG_OMEGA * (bq - Ax) / ((double)kk * a.h2inv);
-      if (DOT) acc[0] = bq * v;
+  StencilMarch<float> m;
+  if (m.begin(S, xi)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, xi);
+      uchar2 f = make_uchar2(0, 0);
+      float2 bv = make_float2(0.f, 0.f);
+      double2 rv = make_double2(0.0, 0.0);
+      if (m.act) {
+        f = *reinterpret_cast<const uchar2*>(fl + m.q);
+        bv = ld2<float>(b + m.q);
+        if (DOT) rv = ld2<double>(r64 + m.q);
+      }
+      float o0 = 0.f, o1 = 0.f;
+      if (f.x & FB_FLUID) { int kk = 6 - __popc(f.x & FB_SMASK); o0 = m.c0() + mc.winv[kk] * (bv.x - mc.h2inv * ((float)kk * m.c0() - m.sum0())); }
+      if (f.y & FB_FLUID) { int kk = 6 - __popc(f.y & FB_SMASK); o1 = m.c1() + mc.winv[kk] * (bv.y - mc.h2inv * ((float)kk * m.c1() - m.sum1())); }
+      if (m.act) st2<float>(xo + m.q, o0, o1);
+      if (DOT) acc[0] += rv.x * (double)o0 + rv.y * (double)o1;
+      m.advance(S);
     }
-    xo[q] = v;
   }
   if (DOT) {
     block_sum<1>(acc, sm);
-    if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(&ds->rz[slot], acc[0]);
+    if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
+      const double rrp = ds->rr[(it + 3) & 3];
+      atomicAdd(&ds->rz[it & 3], acc[0] * (rrp > 0.0 ? sqrt(rrp) : 1.0));
+    }
   }
 }
 
-// res = b - A x
-__global__ void __launch_bounds__(256)
-k_mg_residual(MgArgs a, const uint8_t* __restrict__ fl, const double* __restrict__ b, const double* __restrict__ x,
-              double* __restrict__ res, const DevScalars* __restrict__ ds) {
+// normalised residual  rn = (b - A x) * 64 / n64   (input of the restriction)
+__global__ void __launch_bounds__(32 * ST_BY)
+k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
+           const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
+           float* __restrict__ rn, const DevScalars* __restrict__ ds) {
   if (ds->pcg_done) return;
-  MG_NODE_PROLOGUE
-  if (!inb) return;
-  int q = gidx(a.g, i, j, k);
-  uint8_t f = fl[q];
-  double v = 0.0;
-  if (f & FB_FLUID) {
-    int kk = 6 - __popc(f & FB_SMASK);
-    double s = mg_nbr_sum(x, q, a.g, f);
-    v = b[q] - a.h2inv * ((double)kk * x[q] - s);
+  StencilMarch<float> m;
+  if (!m.begin(S, x)) return;
+  const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+  for (int z = 0; z < ST_ZP; ++z) {
+    if (m.k >= kend) break;
+    m.load(S, x);
+    uchar2 f = make_uchar2(0, 0), nn = make_uchar2(64, 64);
+    float2 bv = make_float2(0.f, 0.f);
+    if (m.act) {
+      f = *reinterpret_cast<const uchar2*>(fl + m.q);
+      nn = *reinterpret_cast<const uchar2*>(nrm + m.q);
+      bv = ld2<float>(b + m.q);
+    }
+    float o0 = 0.f, o1 = 0.f;
+    if (f.x & FB_FLUID) { int kk = 6 - __popc(f.x & FB_SMASK); o0 = (bv.x - mc.h2inv * ((float)kk * m.c0() - m.sum0())) * (64.f / (float)nn.x); }
+    if (f.y & FB_FLUID) { int kk = 6 - __popc(f.y & FB_SMASK); o1 = (bv.y - mc.h2inv * ((float)kk * m.c1() - m.sum1())) * (64.f / (float)nn.y); }
+    if (m.act) st2<float>(rn + m.q, o0, o1);
+    m.advance(S);
   }
-  res[q] = v;
 }
 
-// per-axis geometry of the transfer stencil: fine cell at offset o in {-1,0,1,2} from 2I has
-// parent I+pr (weight 3/4) and second donor I+sr (weight 1/4)
-__device__ __forceinline__ void mg_axis(int o, int& pr, int& sr) {
-  pr = (o < 0) ? -1 : (o > 1 ? 1 : 0);
-  sr = (o == -1 || o == 2) ? 0 : (o == 0 ? -1 : 1);
-}
-
-// restriction  b_c[I] = (1/8) sum_i P[i,I] res_f[i]  with P's row normalisation (see header)
+// restriction b_c[I] = (1/8) sum_i P[i,I] res_i = (1/512) sum over the 4x4x4 fine cells of
+// {1,3,3,1}^3 weights x rn_i, fused with the coarse level's first Jacobi sweep x1 = w D^-1 b_c.
 __global__ void __launch_bounds__(256)
-k_mg_restrict(MgArgs fa, MgArgs ca, const uint8_t* __restrict__ fc, const double* __restrict__ res,
-              double* __restrict__ bc, const DevScalars* __restrict__ ds) {
+k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
+              const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
+              const DevScalars* __restrict__ ds) {
   if (ds->pcg_done) return;
-  int I = ca.box.x0 + blockIdx.x * blockDim.x + threadIdx.x;
-  int J = ca.box.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  int K = ca.box.z0 + blockIdx.z;
-  if (I >= ca.box.x1 || J >= ca.box.y1) return;
-  int qc = gidx(ca.g, I, J, K);
+  int I = cbox.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int K = cbox.z0 + blockIdx.z;
+  if (I >= cbox.x1 || J >= cbox.y1) return;
+  int qc = gidx(gc, I, J, K);
   uint8_t f = fc[qc];
-  if (!(f & FB_FLUID)) { bc[qc] = 0.0; return; }
-  // non-solid mask of the 3x3x3 coarse neighbourhood
-  unsigned m27 = 0;
+  float sum = 0.f;
+  if (f & FB_FLUID) {
 #pragma unroll
-  for (int dz = -1; dz <= 1; ++dz)
+    for (int oz = -1; oz <= 2; ++oz) {
+      int kf = 2 * K + oz;
+      if (kf < fbox.z0 || kf >= fbox.z1) continue;
+      const float wz = (oz == 0 || oz == 1) ? 3.f : 1.f;
 #pragma unroll
-    for (int dy = -1; dy <= 1; ++dy)
-#pragma unroll
-      for (int dx = -1; dx <= 1; ++dx) {
-        int a = I + dx, b = J + dy, cc = K + dz;
-        bool ns = in_box(ca.g, a, b, cc) && !(fc[gidx(ca.g, a, b, cc)] & FB_SOLID);
-        if (ns) m27 |= 1u << (((dz + 1) * 3 + (dy + 1)) * 3 + (dx + 1));
-      }
-  const bool all = m27 == 0x7FFFFFFu;
-  double sum = 0.0;
-  for (int oz = -1; oz <= 2; ++oz) {
-    int kf = 2 * K + oz;
-    if (kf < fa.box.z0 || kf >= fa.box.z1) continue;
-    int pz, sz; mg_axis(oz, pz, sz);
-    double wz = (oz == 0 || oz == 1) ? 0.75 : 0.25;
-    for (int oy = -1; oy <= 2; ++oy) {
-      int jf = 2 * J + oy;
-      if (jf < fa.box.y0 || jf >= fa.box.y1) continue;
-      int py, sy; mg_axis(oy, py, sy);
-      double wy = (oy == 0 || oy == 1) ? 0.75 : 0.25;
-#pragma unroll
-      for (int ox = -1; ox <= 2; ++ox) {
-        int xf = 2 * I + ox;
-        if (xf < fa.box.x0 || xf >= fa.box.x1) continue;
-        double r = res[gidx(fa.g, xf, jf, kf)];
-        if (r == 0.0) continue;
-        double wx = (ox == 0 || ox == 1) ? 0.75 : 0.25;
-        double w = wx * wy * wz;
-        if (!all) {
-          int px_, sx; mg_axis(ox, px_, sx);
-          double norm = 0.0;
-#pragma unroll
-          for (int t = 0; t < 8; ++t) {
-            int rx = (t & 1) ? sx : px_, ry = (t & 2) ? sy : py, rz = (t & 4) ? sz : pz;
-            double ww = ((t & 1) ? 0.25 : 0.75) * ((t & 2) ? 0.25 : 0.75) * ((t & 4) ? 0.25 : 0.75);
-            if (m27 & (1u << (((rz + 1) * 3 + (ry + 1)) * 3 + (rx + 1)))) norm += ww;
-          }
-          w /= norm;   // norm >= 27/64: the parent of a fluid cell is never solid
-        }
-        sum += w * r;
+      for (int oy = -1; oy <= 2; ++oy) {
+        int jf = 2 * J + oy;
+        if (jf < fbox.y0 || jf >= fbox.y1) continue;
+        const float wyz = wz * ((oy == 0 || oy == 1) ? 3.f : 1.f);
+        const float* row = rn + gidx(gf, 0, jf, kf);
+        int x0 = 2 * I - 1;
+        float a = (x0 >= fbox.x0) ? row[x0] : 0.f;
+        float b1 = row[x0 + 1];
+        float b2 = (x0 + 2 < fbox.x1) ? row[x0 + 2] : 0.f;
+        float d = (x0 + 3 < fbox.x1) ? row[x0 + 3] : 0.f;
+        sum += wyz * ((a + d) + 3.f * (b1 + b2));
       }
     }
   }
-  bc[qc] = 0.125 * sum;
+  float v = sum * (1.f / 512.f);
+  bc[qc] = v;
+  x1c[qc] = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * v : 0.f;
 }
 
-// prolongation + correction:  t_f[i] += sum_I P[i,I] e_c[I]
+// prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells)
 __global__ void __launch_bounds__(256)
-k_mg_prolong(MgArgs a, MgArgs ca, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ fc,
-             const double* __restrict__ ec, double* __restrict__ t, const DevScalars* __restrict__ ds) {
+k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ nrm,
+             const float* __restrict__ ec, float* __restrict__ x, const DevScalars* __restrict__ ds) {
   if (ds->pcg_done) return;
-  MG_NODE_PROLOGUE
-  if (!inb) return;
-  int q = gidx(a.g, i, j, k);
+  int i = fbox.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int k = fbox.z0 + blockIdx.z;
+  if (i >= fbox.x1 || j >= fbox.y1) return;
+  int q = gidx(gf, i, j, k);
   if (!(ff[q] & FB_FLUID)) return;
   int I = i >> 1, J = j >> 1, K = k >> 1;
-  int sx = (i & 1) ? 1 : -1, sy = (j & 1) ? 1 : -1, sz = (k & 1) ? 1 : -1;
-  double norm = 0.0, sum = 0.0;
-#pragma unroll
-  for (int m = 0; m < 8; ++m) {
-    int ci = I + ((m & 1) ? sx : 0), cj = J + ((m & 2) ? sy : 0), ck = K + ((m & 4) ? sz : 0);
-    if (!in_box(ca.g, ci, cj, ck)) continue;
-    int qc = gidx(ca.g, ci, cj, ck);
-    uint8_t f = fc[qc];
-    if (f & FB_SOLID) continue;
-    double w = ((m & 1) ? 0.25 : 0.75) * ((m & 2) ? 0.25 : 0.75) * ((m & 4) ? 0.25 : 0.75);
-    norm += w;
-    if (f & FB_FLUID) sum += w * ec[qc];
-  }
-  t[q] += sum / norm;
+  int I2 = I + ((i & 1) ? 1 : -1), J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((k & 1) ? 1 : -1);
+  const bool xin = I2 >= 0 && I2 < gc.nx, yin = J2 >= 0 && J2 < gc.ny, zin = K2 >= 0 && K2 < gc.nz;
+  I2 = xin ? I2 : I; J2 = yin ? J2 : J; K2 = zin ? K2 : K;
+  const float wx = xin ? 1.f : 0.f, wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
+  const float* p00 = ec + gidx(gc, 0, J, K);
+  const float* p10 = ec + gidx(gc, 0, J2, K);
+  const float* p01 = ec + gidx(gc, 0, J, K2);
+  const float* p11 = ec + gidx(gc, 0, J2, K2);
+  float s = 3.f * (3.f * (3.f * p00[I] + wx * p00[I2]) + wy * (3.f * p10[I] + wx * p10[I2])) +
+            wz * (3.f * (3.f * p01[I] + wx * p01[I2]) + wy * (3.f * p11[I] + wx * p11[I2]));
+  x[q] += s / (float)nrm[q];
 }
 
-// coarsest level: MG_COARSE_SWEEPS+1 damped-Jacobi sweeps in one block; result in L.t
+// coarsest level: MG_COARSE_SWEEPS+1 damped-Jacobi sweeps in ONE block; x lives in shared memory
+// with a zero halo (ping-pong), b / flags of the (<= 4) cells of a thread live in registers.
 __global__ void __launch_bounds__(1024)
-k_mg_coarsest(MgArgs a, const uint8_t* __restrict__ fl, const double* __restrict__ b, double* __restrict__ x,
-              double* __restrict__ t, const DevScalars* __restrict__ ds) {
+k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* __restrict__ b,
+              float* __restrict__ xout, const DevScalars* __restrict__ ds) {
+  extern __shared__ float smx[];
   if (ds->pcg_done) return;
-  const int bx = a.box.x1 - a.box.x0, by = a.box.y1 - a.box.y0, bz = a.box.z1 - a.box.z0;
+  const int bx = S.box.x1 - S.box.x0, by = S.box.y1 - S.box.y0, bz = S.box.z1 - S.box.z0;
   const int n = bx * by * bz;
-  for (int s = 0; s <= MG_COARSE_SWEEPS; ++s) {
-    const double* xi = (s & 1) ? t : x;
-    double* xo = (s & 1) ? x : t;
-    for (int e = threadIdx.x; e < n; e += blockDim.x) {
-      int i = a.box.x0 + e % bx, j = a.box.y0 + (e / bx) % by, k = a.box.z0 + e / (bx * by);
-      int q = gidx(a.g, i, j, k);
+  const int sx = bx + 2, sxy = sx * (by + 2), stot = sxy * (bz + 2);
+  float* A = smx; float* B = smx + stot;
+  for (int e = threadIdx.x; e < 2 * stot; e += blockDim.x) smx[e] = 0.f;
+  float bb[4], wv[4], kf[4]; int sidx[4], gq[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    int e = threadIdx.x + u * 1024;
+    bb[u] = 0.f; wv[u] = 0.f; kf[u] = 0.f; sidx[u] = -1; gq[u] = 0;
+    if (e < n) {
+      int li = e % bx, lj = (e / bx) % by, lk = e / (bx * by);
+      int q = gidx(S.g, S.box.x0 + li, S.box.y0 + lj, S.box.z0 + lk);
       uint8_t f = fl[q];
-      double v = 0.0;
-      if (f & FB_FLUID) {
-        int kk = 6 - __popc(f & FB_SMASK);
-        double d = (double)kk * a.h2inv;
-        if (s == 0) v = MG_OMEGA * b[q] / d;
-        else {
-          double xc = xi[q];
-          double sn = mg_nbr_sum(xi, q, a.g, f);
-          v = xc + MG_OMEGA * (b[q] - a.h2inv * ((double)kk * xc - sn)) / d;
-        }
-      }
-      xo[q] = v;
+      sidx[u] = (lk + 1) * sxy + (lj + 1) * sx + li + 1; gq[u] = q;
+      if (f & FB_FLUID) { int kk = 6 - __popc(f & FB_SMASK); kf[u] = (float)kk; wv[u] = mc.winv[kk]; bb[u] = b[q]; }
+    }
+  }
+  __syncthreads();
+  for (int s = 0; s <= MG_COARSE_SWEEPS; ++s) {
+    const float* xi = (s & 1) ? B : A;
+    float* xo = (s & 1) ? A : B;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (sidx[u] < 0) continue;
+      int q = sidx[u];
+      float xc = xi[q];
+      float sn = (xi[q - 1] + xi[q + 1]) + (xi[q - sx] + xi[q + sx]) + (xi[q - sxy] + xi[q + sxy]);
+      xo[q] = xc + wv[u] * (bb[u] - mc.h2inv * (kf[u] * xc - sn));   // wv = 0 off the fluid cells
     }
     __syncthreads();
   }
+  const float* res = (MG_COARSE_SWEEPS & 1) ? A : B;   // sweep s writes B for even s
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+    if (sidx[u] >= 0) xout[gq[u]] = res[sidx[u]];
 }
 
 // ---- host orchestration ----------------------------------------------------------------------
-static inline MgArgs mg_args(const MgLevel& L) { MgArgs a; a.g = L.g; a.box = L.box; a.h2inv = L.h2inv; return a; }
-static inline bool mg_grid(const MgLevel& L, dim3* grd) {
-  const Box& b = L.box;
-  if (!(b.x1 > b.x0 && b.y1 > b.y0 && b.z1 > b.z0)) return false;
-  *grd = dim3(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 8), b.z1 - b.z0);
-  return true;
-}
-
-// z = M^-1 r : input r = mg[0].b (the CG residual), output mg[0].t; r.z is added to ds->rz[it & 3].
+// z = M^-1 r.  Input: level-0 b (= float(r*sc)) and xa (= first sweep) written by the CG's K2/init;
+// output: level-0 xb (fp32, still scaled by sc); r.z is added to ds->rz[it & 3] in fp64.
 int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const int nl = c->mg_levels;
-  const dim3 blk(32, 8, 1);
-  dim3 grd;
+  const dim3 pblk(32, 8, 1);
+  Sweep S[MG_MAX_LEVELS];
+  MgCoef mc[MG_MAX_LEVELS];
+  for (int l = 0; l < nl; ++l) { S[l] = make_sweep(c->mg[l].g, c->mg[l].box); mc[l] = make_mg_coef(c->mg[l].h2inv); }
+  if (sweep_empty(S[0])) return 0;
   for (int l = 0; l < nl - 1; ++l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
-    if (!mg_grid(L, &grd)) return 0;
-    MgArgs a = mg_args(L), ca = mg_args(C);
-    k_mg_smooth_first<<<grd, blk, 0, c->stream>>>(a, L.flags, L.b, L.x, c->ds);
-    k_mg_smooth<false><<<grd, blk, 0, c->stream>>>(a, L.flags, L.b, L.x, L.t, c->ds, 0);
-    k_mg_residual<<<grd, blk, 0, c->stream>>>(a, L.flags, L.b, L.t, L.x, c->ds);
-    dim3 cg;
-    if (!mg_grid(C, &cg)) return 0;
-    k_mg_restrict<<<cg, blk, 0, c->stream>>>(a, ca, C.flags, L.x, C.b, c->ds);
-    c->launches += 4;
+    const dim3 tg = stencil_grid(S[l]);
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it);
+    k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
+    const Box& cb = C.box;
+    dim3 cg(cdiv(cb.x1 - cb.x0, 32), cdiv(cb.y1 - cb.y0, 8), cb.z1 - cb.z0);
+    k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.box, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds);
+    c->launches += 3;
   }
   {
     MgLevel& L = c->mg[nl - 1];
-    k_mg_coarsest<<<1, 1024, 0, c->stream>>>(mg_args(L), L.flags, L.b, L.x, L.t, c->ds);
+    const Box& b = L.box;
+    size_t smem = 2 * sizeof(float) * (size_t)(b.x1 - b.x0 + 2) * (b.y1 - b.y0 + 2) * (b.z1 - b.z0 + 2);
+    if (smem > 160 * 1024 || (int64_t)(b.x1 - b.x0) * (b.y1 - b.y0) * (b.z1 - b.z0) > 4096) return FLIPB200_ERR_ARG;
+    k_mg_coarsest<<<1, 1024, smem, c->stream>>>(S[nl - 1], mc[nl - 1], L.flags, L.b, L.xb, c->ds);
     c->launches++;
   }
   for (int l = nl - 2; l >= 0; --l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
-    mg_grid(L, &grd);
-    MgArgs a = mg_args(L), ca = mg_args(C);
-    k_mg_prolong<<<grd, blk, 0, c->stream>>>(a, ca, L.flags, C.flags, C.t, L.t, c->ds);
-    k_mg_smooth<false><<<grd, blk, 0, c->stream>>>(a, L.flags, L.b, L.t, L.x, c->ds, 0);
-    if (l == 0) k_mg_smooth<true><<<grd, blk, 0, c->stream>>>(a, L.flags, L.b, L.x, L.t, c->ds, it & 3);
-    else k_mg_smooth<false><<<grd, blk, 0, c->stream>>>(a, L.flags, L.b, L.x, L.t, c->ds, 0);
+    const Box& fb = L.box;
+    dim3 pg(cdiv(fb.x1 - fb.x0, 32), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
+    const dim3 tg = stencil_grid(S[l]);
+    k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds);
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it);
+    if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it);
+    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it);
     c->launches += 3;
   }
   CK_LAUNCH();

@@ -1,4 +1,4 @@
-// pcg.cu -- matrix-free 7-point Jacobi-preconditioned conjugate gradient on the fluid cells.
+// pcg.cu -- matrix-free 7-point preconditioned conjugate gradient on the fluid cells.
 //   replaces: setA fluid.cc:304-412, setA2 :481-541 (never materialised), cg.compute(A) :1473,
 //             p = cg.solve(b) :1474 (Eigen ConjugateGradient.h:26-90 loop, same stop rule).
 // Matrix (from setA): for a fluid cell c with k non-solid neighbours, A_cc = Adiag = k
@@ -6,252 +6,218 @@
 // every fluid neighbour n (:335); air neighbours are Dirichlet 0, solid neighbours Neumann.
 // All vectors hold 0 on non-fluid nodes, so A.p = diag[k]*p_c + off * (sum of the 6 neighbours).
 //
-// One iteration = 3 kernels (algorithmic bytes per swept node, fp64: 17 + 49 + 25 = 91):
-//   K1 k_spmv      Ap = A p,  pAp += p.Ap                       read p 8, flag 1; write Ap 8
-//   K2 k_update_xr x += a p, r -= a Ap, rr += r.r, rz += r.M^-1 r   read x,p,r,Ap 32, flag 1; write x,r 16
-//   K3 k_update_p  p = M^-1 r + b p  (or stop: rr < tol^2 |b|^2)    read r,p 16, flag 1; write p 8
+// Preconditioner M: Jacobi (params.precond = 0) or a multigrid V-cycle in fp32 (precond = 1, mg.cu).
+// One iteration (algorithmic bytes per swept node, fp64 vectors, 1-byte flags):
+//   K1 k_spmv      Ap = A p,  pAp += p.Ap                      read p 8, flag 1; write Ap 8        = 17
+//   K2 k_update_xr x += a p, r -= a Ap, rr += r.r (+ Jacobi: rz += r.M^-1 r;
+//                  + MG: b0 = float(r/|r_prev|), x1 = w D^-1 b0)  read x,p,r,Ap 32, flag 1; write x,r 16 = 49 (+8 MG)
+//   [MG: V-cycle, ~74 B/node on the finest level in fp32, r.z fused into its last sweep]
+//   K3 k_update_p  p = z + beta p  (Jacobi: z = M^-1 r on the fly; stop test)  read r|z,p, flag; write p = 25 (21 MG)
 // Scalars never visit the host inside the loop: dot products land in a 4-slot ring in device
 // memory (slot = iteration & 3), alpha/beta are formed by the consuming kernel, convergence sets
 // ds->pcg_done and the remaining launches of a batch return immediately.
-#include "common.cuh"
+// Kernel shapes: sweep.cuh (STREAM for K2/K3/init, STENCIL for K1).
+#include "sweep.cuh"
+#include "pcg.cuh"
 
-struct PcgCoef {
-  double diag[7];   // Adiag for k = 0..6 non-solid neighbours (fp32-accumulated, widened)
-  double inv[7];    // Jacobi: 1/diag
-  double off;       // (double)(float)(-scale)
-};
-
-#define PCG_TX 64
-#define PCG_TY 8
-#define PCG_ZC 16
-
-struct Tiling { int tiles_x, tiles_y, chunks_z, nitems; };
-
-__device__ __forceinline__ void item_to_tile(const Tiling& t, int item, int& tx, int& ty, int& tz) {
-  tz = item / (t.tiles_x * t.tiles_y);
-  int rem = item - tz * t.tiles_x * t.tiles_y;
-  ty = rem / t.tiles_x;
-  tx = rem - ty * t.tiles_x;
-}
-
-__global__ void k_pcg_reset(DevScalars* ds) {
+__global__ void k_pcg_reset(DevScalars* ds, double bnorm2) {
   for (int s = 0; s < 4; ++s) { ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0; }
+  // |r|^2 of "iteration -1" (= |b|^2): scale of the first preconditioner applications
+  ds->rr[2] = bnorm2; ds->rr[3] = bnorm2;
   ds->pcg_done = 0; ds->pcg_iters = 0; ds->pcg_status = 0; ds->rr_final = 0.0;
 }
 
-// x = 0, r = b, p = M^-1 r, rz[3] = r.p   (Eigen ConjugateGradient.h:43,63,66 with x0 = 0)
-__global__ void __launch_bounds__(PCG_TX * PCG_TY)
-k_pcg_init(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, const float* __restrict__ b,
-           double* __restrict__ x, double* __restrict__ r, double* __restrict__ p, DevScalars* __restrict__ ds,
-           int mg) {
+// x = 0, r = b;  Jacobi: p = M^-1 r, rz[3] = r.p   (Eigen ConjugateGradient.h:43,63,66 with x0 = 0)
+//               MG:     b0 = float(r * sc), x1 = w D^-1 b0  (input of the first V-cycle)
+template <int MODE>
+__global__ void __launch_bounds__(32 * SW_BY)
+k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+           const float* __restrict__ b, double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
+           float* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds) {
   __shared__ double sm[32];
+  STREAM_PROLOGUE(S)
   double acc[1] = {0.0};
-  for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
-    int tx, ty, tz; item_to_tile(t, item, tx, ty, tz);
-    int i = box.x0 + tx * PCG_TX + threadIdx.x, j = box.y0 + ty * PCG_TY + threadIdx.y;
-    if (i >= box.x1 || j >= box.y1) continue;
-    int zs = box.z0 + tz * PCG_ZC, ze = min(zs + PCG_ZC, box.z1);
-    int q = gidx(g, i, j, zs);
-    for (int z = zs; z < ze; ++z, q += g.plane) {
-      uint8_t f = fl[q];
-      double rv = 0.0, pv = 0.0;
-      if (f & FB_FLUID) {
-        int k = 6 - __popc(f & FB_SMASK);
-        rv = (double)b[q];
-        pv = rv * cf.inv[k];
-        acc[0] += rv * pv;
-      }
-      x[q] = 0.0; r[q] = rv; p[q] = mg ? 0.0 : pv;
+  if (act) {
+    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    float2 bv = *reinterpret_cast<const float2*>(b + q);
+    double r0 = (f.x & FB_FLUID) ? (double)bv.x : 0.0, r1 = (f.y & FB_FLUID) ? (double)bv.y : 0.0;
+    int k0 = 6 - __popc(f.x & FB_SMASK), k1 = 6 - __popc(f.y & FB_SMASK);
+    st2<double>(x + q, 0.0, 0.0);
+    st2<double>(r + q, r0, r1);
+    if (MODE == 0) {
+      double p0 = r0 * cf.inv[k0], p1 = r1 * cf.inv[k1];
+      st2<double>(p + q, p0, p1);
+      acc[0] = r0 * p0 + r1 * p1;
+    } else {
+      float s0 = (float)(r0 * sc), s1 = (float)(r1 * sc);
+      st2<float>(b0 + q, s0, s1);
+      st2<float>(x1 + q, cf.winv[k0] * s0, cf.winv[k1] * s1);
+      st2<double>(p + q, 0.0, 0.0);
     }
   }
-  if (mg) return;   // multigrid: z = M^-1 r and r.z come from the V-cycle
-  block_sum<1>(acc, sm);
-  if (threadIdx.x == 0 && threadIdx.y == 0) atomicAdd(&ds->rz[3], acc[0]);
+  if (MODE == 0) {
+    block_sum<1>(acc, sm);
+    if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(&ds->rz[3], acc[0]);
+  }
 }
 
-// K1: Ap = A p and p.Ap.  The block marches along z keeping p(z-1), p(z), p(z+1) in registers, so
-// each p value is fetched from L2/HBM once per column; the four in-plane neighbours hit L1.
-__global__ void __launch_bounds__(PCG_TX * PCG_TY)
-k_spmv(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, const double* __restrict__ p,
-       double* __restrict__ Ap, DevScalars* __restrict__ ds, int it, int noexit) {
+// K1: Ap = A p and p.Ap (STENCIL shape: z-march in registers, x neighbours by shuffle)
+__global__ void __launch_bounds__(32 * ST_BY)
+k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+       const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it, int noexit) {
   __shared__ double sm[32];
   if (!noexit && ds->pcg_done) return;
   double acc[1] = {0.0};
-  for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
-    int tx, ty, tz; item_to_tile(t, item, tx, ty, tz);
-    int i = box.x0 + tx * PCG_TX + threadIdx.x, j = box.y0 + ty * PCG_TY + threadIdx.y;
-    if (i >= box.x1 || j >= box.y1) continue;
-    int zs = box.z0 + tz * PCG_ZC, ze = min(zs + PCG_ZC, box.z1);
-    int q = gidx(g, i, j, zs);
-    double pm = zs > 0 ? p[q - g.plane] : 0.0;
-    double pc = p[q];
-    for (int z = zs; z < ze; ++z, q += g.plane) {
-      double pn = (z + 1 < g.nz) ? p[q + g.plane] : 0.0;
-      uint8_t f = fl[q];
-      if (f & FB_FLUID) {   // fluid cells lie inside the shell: all six neighbours are in the box
-        int k = 6 - __popc(f & FB_SMASK);
-        double s = (pm + pn) + (p[q - 1] + p[q + 1]) + (p[q - g.px] + p[q + g.px]);
-        double ap = cf.diag[k] * pc + cf.off * s;
-        Ap[q] = ap;
-        acc[0] += pc * ap;
-      }
-      pm = pc; pc = pn;
+  StencilMarch<double> m;
+  if (m.begin(S, p)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, p);
+      uchar2 f = m.act ? *reinterpret_cast<const uchar2*>(fl + m.q) : make_uchar2(0, 0);
+      double a0 = 0.0, a1 = 0.0;
+      if (f.x & FB_FLUID) { a0 = cf.diag[6 - __popc(f.x & FB_SMASK)] * m.c0() + cf.off * m.sum0(); acc[0] += m.c0() * a0; }
+      if (f.y & FB_FLUID) { a1 = cf.diag[6 - __popc(f.y & FB_SMASK)] * m.c1() + cf.off * m.sum1(); acc[0] += m.c1() * a1; }
+      if ((f.x | f.y) & FB_FLUID) st2<double>(Ap + m.q, a0, a1);
+      m.advance(S);
     }
   }
   block_sum<1>(acc, sm);
-  if (threadIdx.x == 0 && threadIdx.y == 0) atomicAdd(&ds->pAp[it & 3], acc[0]);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(&ds->pAp[it & 3], acc[0]);
 }
 
-// K2: alpha = rz_old / pAp;  x += alpha p;  r -= alpha Ap;  rr = |r|^2;  rz = r.M^-1 r
-template <bool JAC>
-__global__ void __launch_bounds__(PCG_TX * PCG_TY)
-k_update_xr(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, double* __restrict__ x,
-            double* __restrict__ r, const double* __restrict__ p, const double* __restrict__ Ap,
+// K2: alpha = rz_old / pAp;  x += alpha p;  r -= alpha Ap;  rr = |r|^2
+//     MODE 0 (Jacobi): rz = r.M^-1 r.   MODE 1 (MG): b0 = float(r*sc), x1 = w D^-1 b0 with
+//     sc = 1/|r_prev| so that the fp32 V-cycle works on O(1) numbers whatever |r| has become.
+template <int MODE>
+__global__ void __launch_bounds__(32 * SW_BY)
+k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+            double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
+            const double* __restrict__ Ap, float* __restrict__ b0, float* __restrict__ x1,
             DevScalars* __restrict__ ds, int it, int noexit) {
   __shared__ double sm[64];
   if (!noexit && ds->pcg_done) return;
   const double pAp = ds->pAp[it & 3];
   const double rz_old = ds->rz[(it + 3) & 3];
   if (!noexit && !(pAp > 0.0)) {   // breakdown (also catches NaN)
-    if (blockIdx.x == 0 && threadIdx.x == 0 && threadIdx.y == 0) {
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0) {
       ds->pcg_status = FLIPB200_ERR_BREAKDOWN; ds->pcg_done = 1; ds->pcg_iters = it;
       ds->rr_final = ds->rr[(it + 3) & 3];
     }
     return;
   }
   const double alpha = rz_old / pAp;                   // ConjugateGradient.h:72
+  const double rrp = ds->rr[(it + 3) & 3];
+  const double sc = MODE == 1 ? (rrp > 0.0 ? rsqrt(rrp) : 1.0) : 0.0;
+  STREAM_PROLOGUE(S)
   double acc[2] = {0.0, 0.0};
-  for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
-    int tx, ty, tz; item_to_tile(t, item, tx, ty, tz);
-    int i = box.x0 + tx * PCG_TX + threadIdx.x, j = box.y0 + ty * PCG_TY + threadIdx.y;
-    if (i >= box.x1 || j >= box.y1) continue;
-    int zs = box.z0 + tz * PCG_ZC, ze = min(zs + PCG_ZC, box.z1);
-    int q = gidx(g, i, j, zs);
-    for (int z = zs; z < ze; ++z, q += g.plane) {
-      uint8_t f = fl[q];
-      if (f & FB_FLUID) {
-        int k = 6 - __popc(f & FB_SMASK);
-        double xn = x[q] + alpha * p[q];               // :73
-        double rn = r[q] - alpha * Ap[q];              // :74
-        x[q] = xn; r[q] = rn;
-        acc[0] += rn * rn;                             // :76
-        if (JAC) acc[1] += rn * (rn * cf.inv[k]);      // :80,83
-      }
+  if (act) {
+    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    double2 xv = ld2<double>(x + q), rv = ld2<double>(r + q), pv = ld2<double>(p + q), av = ld2<double>(Ap + q);
+    const bool f0 = f.x & FB_FLUID, f1 = f.y & FB_FLUID;
+    int k0 = 6 - __popc(f.x & FB_SMASK), k1 = 6 - __popc(f.y & FB_SMASK);
+    double r0 = 0.0, r1 = 0.0;
+    if (f0) { xv.x += alpha * pv.x; r0 = rv.x - alpha * av.x; }      // :73-74
+    if (f1) { xv.y += alpha * pv.y; r1 = rv.y - alpha * av.y; }
+    if (f0 | f1) { st2<double>(x + q, xv.x, xv.y); st2<double>(r + q, r0, r1); }
+    acc[0] = r0 * r0 + r1 * r1;                                        // :76
+    if (MODE == 0) acc[1] = r0 * (r0 * cf.inv[k0]) + r1 * (r1 * cf.inv[k1]);   // :80,83
+    else {
+      float s0 = (float)(r0 * sc), s1 = (float)(r1 * sc);
+      st2<float>(b0 + q, s0, s1);
+      st2<float>(x1 + q, cf.winv[k0] * s0, cf.winv[k1] * s1);
     }
   }
   block_sum<2>(acc, sm);
   if (threadIdx.x == 0 && threadIdx.y == 0) {
-    atomicAdd(&ds->rr[it & 3], acc[0]);
-    if (JAC) atomicAdd(&ds->rz[it & 3], acc[1]);
+    if (acc[0] != 0.0) atomicAdd(&ds->rr[it & 3], acc[0]);
+    if (MODE == 0 && acc[1] != 0.0) atomicAdd(&ds->rz[it & 3], acc[1]);
   }
 }
 
-// K3: stop test (ConjugateGradient.h:77-78), beta = rz/rz_old (:84), p = z + beta p (:85)
-__global__ void __launch_bounds__(PCG_TX * PCG_TY)
-k_update_p(Grid g, Box box, Tiling t, PcgCoef cf, const uint8_t* __restrict__ fl, const double* __restrict__ r,
-           double* __restrict__ p, DevScalars* __restrict__ ds, int it, int max_iter, double threshold, int noexit) {
-  if (!noexit && ds->pcg_done) return;
-  const double rr = ds->rr[it & 3];
-  const bool lead = blockIdx.x == 0 && threadIdx.x == 0 && threadIdx.y == 0;
-  if (!noexit && rr < threshold) {
-    if (lead) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
-    return;
-  }
-  const double beta = ds->rz[it & 3] / ds->rz[(it + 3) & 3];
-  if (lead) {
-    int s = (it + 1) & 3;
-    ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
-    if (!noexit && it + 1 >= max_iter) {
-      ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = rr; ds->pcg_status = FLIPB200_ERR_NOCONV;
-    }
-  }
-  for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
-    int tx, ty, tz; item_to_tile(t, item, tx, ty, tz);
-    int i = box.x0 + tx * PCG_TX + threadIdx.x, j = box.y0 + ty * PCG_TY + threadIdx.y;
-    if (i >= box.x1 || j >= box.y1) continue;
-    int zs = box.z0 + tz * PCG_ZC, ze = min(zs + PCG_ZC, box.z1);
-    int q = gidx(g, i, j, zs);
-    for (int z = zs; z < ze; ++z, q += g.plane) {
-      uint8_t f = fl[q];
-      if (f & FB_FLUID) {
-        int k = 6 - __popc(f & FB_SMASK);
-        p[q] = r[q] * cf.inv[k] + beta * p[q];
-      }
-    }
-  }
-}
-
-// ---- multigrid-preconditioned variant: z = M^-1 r comes from fb_mg_vcycle (mg.cu) ---------------
-// stop test of ConjugateGradient.h:77-78, evaluated before the preconditioner is applied
+// stop test of ConjugateGradient.h:77-78 (MG path: evaluated before the preconditioner is applied)
 __global__ void k_pcg_check(DevScalars* __restrict__ ds, int it, double threshold) {
   if (ds->pcg_done) return;
   const double rr = ds->rr[it & 3];
   if (rr < threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
 }
 
-// p = z + beta p, beta = rz/rz_old (first: p = z).  it = -1 for the initial direction.
-__global__ void __launch_bounds__(PCG_TX * PCG_TY)
-k_update_p_mg(Grid g, Box box, Tiling t, const uint8_t* __restrict__ fl, const double* __restrict__ z,
-              double* __restrict__ p, DevScalars* __restrict__ ds, int it, int max_iter) {
-  if (ds->pcg_done) return;
+// K3: beta = rz/rz_old (:84), p = z + beta p (:85).
+//     MODE 0: z = M^-1 r (Jacobi) on the fly, includes the stop test.
+//     MODE 1: z = zf / sc from the V-cycle (fp32, scaled); it = -1 sets the first direction p = z.
+template <int MODE>
+__global__ void __launch_bounds__(32 * SW_BY)
+k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+           const double* __restrict__ r, const float* __restrict__ zf, double* __restrict__ p,
+           DevScalars* __restrict__ ds, int it, int max_iter, double threshold, int noexit) {
+  if (!noexit && ds->pcg_done) return;
+  const bool lead = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0;
   const bool first = it < 0;
-  const bool lead = blockIdx.x == 0 && threadIdx.x == 0 && threadIdx.y == 0;
+  const double rr = first ? 0.0 : ds->rr[it & 3];
+  if (MODE == 0 && !noexit && rr < threshold) {
+    if (lead) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
+    return;
+  }
   const double beta = first ? 0.0 : ds->rz[it & 3] / ds->rz[(it + 3) & 3];
+  const double rrp = ds->rr[(it + 3) & 3];
+  const double invsc = MODE == 1 ? (rrp > 0.0 ? sqrt(rrp) : 1.0) : 0.0;
   if (lead) {
     int s = (it + 1) & 3;
     ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
-    if (!first && it + 1 >= max_iter) {
-      ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = ds->rr[it & 3]; ds->pcg_status = FLIPB200_ERR_NOCONV;
+    if (!noexit && !first && it + 1 >= max_iter) {
+      ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = rr; ds->pcg_status = FLIPB200_ERR_NOCONV;
     }
   }
-  for (int item = blockIdx.x; item < t.nitems; item += gridDim.x) {
-    int tx, ty, tz; item_to_tile(t, item, tx, ty, tz);
-    int i = box.x0 + tx * PCG_TX + threadIdx.x, j = box.y0 + ty * PCG_TY + threadIdx.y;
-    if (i >= box.x1 || j >= box.y1) continue;
-    int zs = box.z0 + tz * PCG_ZC, ze = min(zs + PCG_ZC, box.z1);
-    int q = gidx(g, i, j, zs);
-    for (int zz = zs; zz < ze; ++zz, q += g.plane) {
-      if (fl[q] & FB_FLUID) p[q] = first ? z[q] : z[q] + beta * p[q];
-    }
+  STREAM_PROLOGUE(S)
+  if (!act) return;
+  uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+  double2 pv = ld2<double>(p + q);
+  double z0, z1;
+  if (MODE == 0) {
+    double2 rv = ld2<double>(r + q);
+    z0 = rv.x * cf.inv[6 - __popc(f.x & FB_SMASK)]; z1 = rv.y * cf.inv[6 - __popc(f.y & FB_SMASK)];
+  } else {
+    float2 zv = ld2<float>(zf + q);
+    z0 = (double)zv.x * invsc; z1 = (double)zv.y * invsc;
+  }
+  if ((f.x | f.y) & FB_FLUID) {
+    double p0 = (f.x & FB_FLUID) ? z0 + beta * pv.x : 0.0;
+    double p1 = (f.y & FB_FLUID) ? z1 + beta * pv.y : 0.0;
+    st2<double>(p + q, p0, p1);
   }
 }
 
-static void make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
+void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
   const double scale = dt / (c->P.rho * c->P.dx * c->P.dx);       // fluid.cc:306
   float acc = 0.0f;
-  cf->diag[0] = 0.0; cf->inv[0] = 0.0;
+  cf->diag[0] = 0.0; cf->inv[0] = 0.0; cf->winv[0] = 0.f;
   for (int k = 1; k <= 6; ++k) {
     acc = (float)((double)acc + scale);                           // daccessor.setValue(c, getValue(c) + scale), :333
     cf->diag[k] = (double)acc;
     cf->inv[k] = 1.0 / (double)acc;
+    cf->winv[k] = (float)(MG_OMEGA / (k * scale));
   }
   cf->off = (double)(float)(-1 * scale);                          // :335
 }
 
-static Tiling make_tiling(const Box& b) {
-  Tiling t;
-  t.tiles_x = cdiv(b.x1 - b.x0, PCG_TX);
-  t.tiles_y = cdiv(b.y1 - b.y0, PCG_TY);
-  t.chunks_z = cdiv(b.z1 - b.z0, PCG_ZC);
-  t.nitems = t.tiles_x * t.tiles_y * t.chunks_z;
-  return t;
-}
-
 int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
-  const Grid& g = c->g;
-  const Box& b = c->box;
   if (iters_out) *iters_out = 0;
   if (rel_out) *rel_out = 0.0;
-  if (c->n_fluid == 0 || !(b.x1 > b.x0)) return 0;
-  PcgCoef cf; make_coef(c, dt, &cf);
-  Tiling t = make_tiling(b);
-  const int grid = min(t.nitems, c->num_sms * 2);
-  const dim3 blk(PCG_TX, PCG_TY, 1);
+  const Sweep S = make_sweep(c->g, c->box);
+  if (c->n_fluid == 0 || sweep_empty(S)) return 0;
+  PcgCoef cf; fb_make_coef(c, dt, &cf);
+  const dim3 sg = stream_grid(S), tg = stencil_grid(S);
   const double bnorm2 = c->hs->bnorm2;             // fetched by fb_rhs_div
   const float* bvec = c->bf[c->bcur];
   const bool use_mg = c->mg_levels >= 2;
-  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds);
-  k_pcg_init<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, bvec, c->x, c->r, c->pd, c->ds, use_mg ? 1 : 0);
+  MgLevel& L0 = c->mg[0];
+  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2);
+  if (use_mg)
+    k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, L0.b, L0.xa,
+                                                      bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds);
+  else
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds);
   CK_LAUNCH(); c->launches += 2;
   if (bnorm2 == 0.0) return 0;                     // rhsNorm2 == 0 => x = 0, 0 iterations (ConjugateGradient.h:46-52)
   if (!(bnorm2 == bnorm2)) return FLIPB200_ERR_BREAKDOWN;
@@ -266,33 +232,26 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     if (rc) return rc;
     rc = fb_mg_vcycle(c, -1);                      // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
-    k_update_p_mg<<<grid, blk, 0, c->stream>>>(g, b, t, c->flags, c->Ap, c->pd, c->ds, -1, max_iter);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, max_iter, threshold, 0);
     c->launches++;
-  }
-  while (!done && use_mg) {
-    int stop = min(it + batch, max_iter);
-    for (; it < stop; ++it) {
-      k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, it, 0);
-      k_update_xr<false><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 0);
-      k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it, threshold);
-      c->launches += 3;
-      int rc = fb_mg_vcycle(c, it);
-      if (rc) return rc;
-      k_update_p_mg<<<grid, blk, 0, c->stream>>>(g, b, t, c->flags, c->Ap, c->pd, c->ds, it, max_iter);
-      c->launches++;
-    }
-    CK_LAUNCH();
-    int rc = fb_fetch_scalars(c);
-    if (rc) return rc;
-    done = c->hs->pcg_done != 0 || it >= max_iter;
   }
   while (!done) {
     int stop = min(it + batch, max_iter);
     for (; it < stop; ++it) {
-      k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, it, 0);
-      k_update_xr<true><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 0);
-      k_update_p<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->r, c->pd, c->ds, it, max_iter, threshold, 0);
-      c->launches += 3;
+      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 0);
+      if (use_mg) {
+        k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it, 0);
+        k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it, threshold);
+        c->launches += 3;
+        int rc = fb_mg_vcycle(c, it);
+        if (rc) return rc;
+        k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it, max_iter, threshold, 0);
+        c->launches++;
+      } else {
+        k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it, 0);
+        k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it, max_iter, threshold, 0);
+        c->launches += 3;
+      }
     }
     CK_LAUNCH();
     int rc = fb_fetch_scalars(c);
@@ -305,40 +264,49 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   return 0;   // hitting max_iter is reported through iters == max_iter, as Eigen does
 }
 
-// Timing hook: `iters` launches of K1 alone (which == SPMV) or of the whole 3-kernel iteration
-// (which == PCG_ITER) on the current system, no convergence exit.  units = swept nodes per launch.
+// Timing hook: `iters` launches of K1 alone (which == SPMV) or of one whole PCG iteration
+// (which == PCG_ITER; includes the V-cycle when precond = 1) on the current system, no convergence
+// exit.  units = swept nodes per launch.
 int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units) {
-  const Grid& g = c->g;
-  const Box& b = c->box;
-  if (!(b.x1 > b.x0)) return FLIPB200_ERR_STATE;
-  PcgCoef cf; make_coef(c, c->P.dt_max, &cf);
-  Tiling t = make_tiling(b);
-  const int grid = min(t.nitems, c->num_sms * 2);
-  const dim3 blk(PCG_TX, PCG_TY, 1);
-  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds);
-  k_pcg_init<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, c->ds, 0);
-  for (int w = 0; w < 3; ++w) {
-    k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, w, 1);
-    if (which == FLIPB200_KERNEL_PCG_ITER) {
-      k_update_xr<true><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, w, 1);
-      k_update_p<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->r, c->pd, c->ds, w, 1 << 30, 0.0, 1);
-    }
+  const Sweep S = make_sweep(c->g, c->box);
+  if (sweep_empty(S)) return FLIPB200_ERR_STATE;
+  PcgCoef cf; fb_make_coef(c, c->P.dt_max, &cf);
+  const dim3 sg = stream_grid(S), tg = stencil_grid(S);
+  const bool use_mg = c->mg_levels >= 2 && which == FLIPB200_KERNEL_PCG_ITER;
+  MgLevel& L0 = c->mg[0];
+  const double bn = c->hs->bnorm2 > 0.0 ? c->hs->bnorm2 : 1.0;
+  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn);
+  if (use_mg) {
+    k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds);
+    int rc = fb_mg_setup(c, c->P.dt_max); if (rc) return rc;
+    rc = fb_mg_vcycle(c, -1); if (rc) return rc;
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1 << 30, 0.0, 1);
+  } else {
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds);
   }
-  CK(cudaEventRecord(c->ev[6], c->stream));
-  for (int it = 3; it < 3 + iters; ++it) {
-    k_spmv<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
-    if (which == FLIPB200_KERNEL_PCG_ITER) {
-      k_update_xr<true><<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->x, c->r, c->pd, c->Ap, c->ds, it, 1);
-      k_update_p<<<grid, blk, 0, c->stream>>>(g, b, t, cf, c->flags, c->r, c->pd, c->ds, it, 1 << 30, 0.0, 1);
+  const int64_t l0 = c->launches;
+  for (int it = 0; it < 3 + iters; ++it) {
+    if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
+    k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
+    c->launches++;
+    if (which != FLIPB200_KERNEL_PCG_ITER) continue;
+    if (use_mg) {
+      k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it, 1);
+      int rc = fb_mg_vcycle(c, it); if (rc) return rc;
+      k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it, 1 << 30, 0.0, 1);
+    } else {
+      k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it, 1);
+      k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it, 1 << 30, 0.0, 1);
     }
+    c->launches += 2;
   }
+  (void)l0;
   CK(cudaEventRecord(c->ev[7], c->stream));
   CK(cudaStreamSynchronize(c->stream));
   CK_LAUNCH();
   float e = 0.f;
   CK(cudaEventElapsedTime(&e, c->ev[6], c->ev[7]));
   *ms = e / iters;
-  *units = (int64_t)(b.x1 - b.x0) * (b.y1 - b.y0) * (b.z1 - b.z0);
-  c->launches += (which == FLIPB200_KERNEL_PCG_ITER ? 3 : 1) * (iters + 3) + 2;
+  *units = (int64_t)(S.box.x1 - S.box.x0) * (S.box.y1 - S.box.y0) * (S.box.z1 - S.box.z0);
   return 0;
 }

@@ -1,0 +1,23 @@
+// pcg.cuh -- coefficient tables shared by pcg.cu and mg.cu
+#pragma once
+#include "common.cuh"
+
+struct PcgCoef {
+  double diag[7];   // Adiag for k = 0..6 non-solid neighbours (fp32-accumulated as in setA, widened)
+  double inv[7];    // Jacobi: 1/diag
+  double off;       // (double)(float)(-scale)
+  float winv[7];    // multigrid level 0: omega / (k * h2inv)  (first damped-Jacobi sweep from x = 0)
+};
+
+#define MG_OMEGA 0.8f
+
+// per-level multigrid coefficients (fp32)
+struct MgCoef {
+  float h2inv;      // operator scale of the level
+  float winv[7];    // omega / (k * h2inv)
+};
+static inline MgCoef make_mg_coef(double h2inv) {
+  MgCoef m; m.h2inv = (float)h2inv; m.winv[0] = 0.f;
+  for (int k = 1; k <= 6; ++k) m.winv[k] = (float)(MG_OMEGA / (k * h2inv));
+  return m;
+}
