@@ -57,6 +57,7 @@ struct DevScalars {
   int n_fluid;
   int bbox[6];                       // min x,y,z / max x,y,z of fluid cells
   int pcg_done, pcg_iters, pcg_status;
+  int pcg_it;                        // current iteration (kernels launched from a CUDA graph read it here)
   int n_invalid;                     // particles whose support lies outside the box
   int pad;
 };
@@ -112,6 +113,7 @@ struct flipb200_ctx {
   DevScalars* hs;          // pinned host mirror
   Box box;                 // sweep box of this step
   int n_fluid;
+  int last_iters;          // iterations of the previous solve (sizes the first launch batch)
   int stage;               // bookkeeping for stage-level calls
   cudaEvent_t ev[8];
   int64_t launches;

@@ -197,9 +197,10 @@ template <bool DOT>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
             const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
-            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it) {
+            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg) {
   __shared__ double sm[32];
   if (ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
   double acc[1] = {0.0};
   StencilMarch<float> m;
   if (m.begin(S, xi)) {
@@ -263,71 +264,103 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
 
 // restriction b_c[I] = (1/8) sum_i P[i,I] res_i = (1/512) sum over the 4x4x4 fine cells of
 // {1,3,3,1}^3 weights x rn_i, fused with the coarse level's first Jacobi sweep x1 = w D^-1 b_c.
+// One lane per coarse cell: the lane loads its two children of each of the 16 fine rows as one
+// float2 (coalesced across the warp) and gets the two outer taps from its neighbours by shuffle.
 __global__ void __launch_bounds__(256)
 k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
               const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
               const DevScalars* __restrict__ ds) {
   if (ds->pcg_done) return;
-  int I = cbox.x0 + blockIdx.x * blockDim.x + threadIdx.x;
-  int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  int K = cbox.z0 + blockIdx.z;
-  if (I >= cbox.x1 || J >= cbox.y1) return;
-  int qc = gidx(gc, I, J, K);
-  uint8_t f = fc[qc];
+  const int lane = threadIdx.x;
+  const int I = cbox.x0 + blockIdx.x * 32 + lane;
+  const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int K = cbox.z0 + blockIdx.z;
+  if (J >= cbox.y1) return;                         // whole warp
+  const bool in = I < cbox.x1;
+  const int xf = 2 * I;                             // children xf, xf+1
+  const bool c0 = in && xf >= fbox.x0 && xf < fbox.x1, c1 = in && xf + 1 >= fbox.x0 && xf + 1 < fbox.x1;
+  const bool both = c0 && c1;
+  const bool eL = xf - 1 >= fbox.x0 && xf - 1 < fbox.x1, eR = xf + 2 >= fbox.x0 && xf + 2 < fbox.x1;
   float sum = 0.f;
-  if (f & FB_FLUID) {
 #pragma unroll
-    for (int oz = -1; oz <= 2; ++oz) {
-      int kf = 2 * K + oz;
-      if (kf < fbox.z0 || kf >= fbox.z1) continue;
-      const float wz = (oz == 0 || oz == 1) ? 3.f : 1.f;
+  for (int oz = -1; oz <= 2; ++oz) {
+    const int kf = 2 * K + oz;
+    const bool zin = kf >= fbox.z0 && kf < fbox.z1;
+    const float wz = (oz == 0 || oz == 1) ? 3.f : 1.f;
 #pragma unroll
-      for (int oy = -1; oy <= 2; ++oy) {
-        int jf = 2 * J + oy;
-        if (jf < fbox.y0 || jf >= fbox.y1) continue;
-        const float wyz = wz * ((oy == 0 || oy == 1) ? 3.f : 1.f);
-        const float* row = rn + gidx(gf, 0, jf, kf);
-        int x0 = 2 * I - 1;
-        float a = (x0 >= fbox.x0) ? row[x0] : 0.f;
-        float b1 = row[x0 + 1];
-        float b2 = (x0 + 2 < fbox.x1) ? row[x0 + 2] : 0.f;
-        float d = (x0 + 3 < fbox.x1) ? row[x0 + 3] : 0.f;
-        sum += wyz * ((a + d) + 3.f * (b1 + b2));
-      }
+    for (int oy = -1; oy <= 2; ++oy) {
+      const int jf = 2 * J + oy;
+      const bool rin = zin && jf >= fbox.y0 && jf < fbox.y1;   // warp-uniform
+      if (!rin) continue;
+      const float wyz = wz * ((oy == 0 || oy == 1) ? 3.f : 1.f);
+      const float* row = rn + gidx(gf, 0, jf, kf);
+      float2 v = make_float2(0.f, 0.f);
+      if (both) v = *reinterpret_cast<const float2*>(row + xf);
+      else { if (c0) v.x = row[xf]; if (c1) v.y = row[xf + 1]; }
+      float a = __shfl_up_sync(0xffffffffu, v.y, 1), d = __shfl_down_sync(0xffffffffu, v.x, 1);
+      if (lane == 0) a = (in && eL) ? row[xf - 1] : 0.f;
+      if (lane == 31) d = (in && eR) ? row[xf + 2] : 0.f;
+      sum += wyz * ((a + d) + 3.f * (v.x + v.y));
     }
   }
-  float v = sum * (1.f / 512.f);
+  if (!in) return;
+  const int qc = gidx(gc, I, J, K);
+  const uint8_t f = fc[qc];
+  const float v = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
   bc[qc] = v;
   x1c[qc] = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * v : 0.f;
 }
 
-// prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells)
+// prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells).
+// One lane per coarse column I = two fine nodes (2I, 2I+1): the four coarse rows that feed this
+// fine row are loaded coalesced and combined, the x-neighbours I-1 / I+1 come by shuffle.
 __global__ void __launch_bounds__(256)
 k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ nrm,
              const float* __restrict__ ec, float* __restrict__ x, const DevScalars* __restrict__ ds) {
   if (ds->pcg_done) return;
-  int i = fbox.x0 + blockIdx.x * blockDim.x + threadIdx.x;
-  int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  int k = fbox.z0 + blockIdx.z;
-  if (i >= fbox.x1 || j >= fbox.y1) return;
-  int q = gidx(gf, i, j, k);
-  if (!(ff[q] & FB_FLUID)) return;
-  int I = i >> 1, J = j >> 1, K = k >> 1;
-  int I2 = I + ((i & 1) ? 1 : -1), J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((k & 1) ? 1 : -1);
-  const bool xin = I2 >= 0 && I2 < gc.nx, yin = J2 >= 0 && J2 < gc.ny, zin = K2 >= 0 && K2 < gc.nz;
-  I2 = xin ? I2 : I; J2 = yin ? J2 : J; K2 = zin ? K2 : K;
-  const float wx = xin ? 1.f : 0.f, wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
+  const int lane = threadIdx.x;
+  const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
+  const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = fbox.z0 + blockIdx.z;
+  if (j >= fbox.y1) return;                         // whole warp
+  const int I = i >> 1, J = j >> 1, K = k >> 1;
+  int J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((k & 1) ? 1 : -1);
+  const bool yin = J2 >= 0 && J2 < gc.ny, zin = K2 >= 0 && K2 < gc.nz;
+  J2 = yin ? J2 : J; K2 = zin ? K2 : K;
+  const float wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
   const float* p00 = ec + gidx(gc, 0, J, K);
   const float* p10 = ec + gidx(gc, 0, J2, K);
   const float* p01 = ec + gidx(gc, 0, J, K2);
   const float* p11 = ec + gidx(gc, 0, J2, K2);
-  float s = 3.f * (3.f * (3.f * p00[I] + wx * p00[I2]) + wy * (3.f * p10[I] + wx * p10[I2])) +
-            wz * (3.f * (3.f * p01[I] + wx * p01[I2]) + wy * (3.f * p11[I] + wx * p11[I2]));
-  x[q] += s / (float)nrm[q];
+  auto comb = [&](int ii) -> float {                // y/z-combined coarse value of column ii (weights 3|1)
+    return 3.f * (3.f * p00[ii] + wy * p10[ii]) + wz * (3.f * p01[ii] + wy * p11[ii]);
+  };
+  const bool cin = I < gc.nx;
+  const float E = cin ? comb(I) : 0.f;
+  float EL = __shfl_up_sync(0xffffffffu, E, 1), ER = __shfl_down_sync(0xffffffffu, E, 1);
+  if (lane == 0) EL = (I - 1 >= 0 && I - 1 < gc.nx) ? comb(I - 1) : 0.f;
+  if (lane == 31) ER = (I + 1 < gc.nx) ? comb(I + 1) : 0.f;
+  if (I - 1 < 0) EL = 0.f;
+  if (I + 1 >= gc.nx) ER = 0.f;
+  const int xe = min(gf.px, (fbox.x1 + 1) & ~1);
+  if (i >= xe) return;
+  const int q = gidx(gf, i, j, k);
+  const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);
+  if (!((f.x | f.y) & FB_FLUID)) return;
+  const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
+  float2 xv = *reinterpret_cast<const float2*>(x + q);
+  if (f.x & FB_FLUID) xv.x += (3.f * E + EL) / (float)nn.x;     // node 2I   : donors I (3) and I-1 (1)
+  if (f.y & FB_FLUID) xv.y += (3.f * E + ER) / (float)nn.y;     // node 2I+1 : donors I (3) and I+1 (1)
+  *reinterpret_cast<float2*>(x + q) = xv;
 }
 
-// coarsest level: MG_COARSE_SWEEPS+1 damped-Jacobi sweeps in ONE block; x lives in shared memory
-// with a zero halo (ping-pong), b / flags of the (<= 4) cells of a thread live in registers.
+// coarsest level (<= 4096 cells) in ONE block: 40 steps of the Chebyshev semi-iteration on the
+// Jacobi-scaled operator D^-1 A (spectrum inside [MG_CHEB_LMIN, 2]) -- a fixed polynomial, hence
+// still a symmetric linear preconditioner, and close to an exact coarse solve (22 vs 27 outer
+// iterations against 41 plain Jacobi sweeps, tools/mg_proto4.py).  The search direction d lives
+// in shared memory with a zero halo (ping-pong); x, r of the (<= 4) cells of a thread in registers.
+#define MG_CHEB_STEPS 40
+#define MG_CHEB_LMIN 0.005f
 __global__ void __launch_bounds__(1024)
 k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* __restrict__ b,
               float* __restrict__ xout, const DevScalars* __restrict__ ds) {
@@ -338,37 +371,50 @@ k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* _
   const int sx = bx + 2, sxy = sx * (by + 2), stot = sxy * (bz + 2);
   float* A = smx; float* B = smx + stot;
   for (int e = threadIdx.x; e < 2 * stot; e += blockDim.x) smx[e] = 0.f;
-  float bb[4], wv[4], kf[4]; int sidx[4], gq[4];
+  const float lmax = 2.f, lmin = MG_CHEB_LMIN;
+  const float theta = 0.5f * (lmax + lmin), delta = 0.5f * (lmax - lmin), sigma = theta / delta;
+  float xr[4], rr[4], kinv[4]; int sidx[4], gq[4];
+  __syncthreads();
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
     int e = threadIdx.x + u * 1024;
-    bb[u] = 0.f; wv[u] = 0.f; kf[u] = 0.f; sidx[u] = -1; gq[u] = 0;
+    xr[u] = 0.f; rr[u] = 0.f; kinv[u] = 0.f; sidx[u] = -1; gq[u] = 0;
     if (e < n) {
       int li = e % bx, lj = (e / bx) % by, lk = e / (bx * by);
       int q = gidx(S.g, S.box.x0 + li, S.box.y0 + lj, S.box.z0 + lk);
       uint8_t f = fl[q];
       sidx[u] = (lk + 1) * sxy + (lj + 1) * sx + li + 1; gq[u] = q;
-      if (f & FB_FLUID) { int kk = 6 - __popc(f & FB_SMASK); kf[u] = (float)kk; wv[u] = mc.winv[kk]; bb[u] = b[q]; }
+      if (f & FB_FLUID) {
+        int kk = 6 - __popc(f & FB_SMASK);
+        kinv[u] = 1.f / (float)kk;
+        rr[u] = b[q] * kinv[u] / mc.h2inv;          // r0 = D^-1 b
+        A[sidx[u]] = rr[u] / theta;                 // d0
+      }
     }
   }
   __syncthreads();
-  for (int s = 0; s <= MG_COARSE_SWEEPS; ++s) {
-    const float* xi = (s & 1) ? B : A;
-    float* xo = (s & 1) ? A : B;
+  float rho = 1.f / sigma;
+  for (int s = 0; s < MG_CHEB_STEPS; ++s) {
+    const float* di = (s & 1) ? B : A;
+    float* dn = (s & 1) ? A : B;
+    const float rho_new = 1.f / (2.f * sigma - rho);
+    const float c1 = rho_new * rho, c2 = 2.f * rho_new / delta;
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      if (sidx[u] < 0) continue;
-      int q = sidx[u];
-      float xc = xi[q];
-      float sn = (xi[q - 1] + xi[q + 1]) + (xi[q - sx] + xi[q + sx]) + (xi[q - sxy] + xi[q + sxy]);
-      xo[q] = xc + wv[u] * (bb[u] - mc.h2inv * (kf[u] * xc - sn));   // wv = 0 off the fluid cells
+      if (sidx[u] < 0 || kinv[u] == 0.f) continue;
+      const int q = sidx[u];
+      const float dc = di[q];
+      const float sn = (di[q - 1] + di[q + 1]) + (di[q - sx] + di[q + sx]) + (di[q - sxy] + di[q + sxy]);
+      xr[u] += dc;
+      rr[u] -= dc - sn * kinv[u];                   // r -= D^-1 A d
+      dn[q] = c1 * dc + c2 * rr[u];
     }
+    rho = rho_new;
     __syncthreads();
   }
-  const float* res = (MG_COARSE_SWEEPS & 1) ? A : B;   // sweep s writes B for even s
 #pragma unroll
   for (int u = 0; u < 4; ++u)
-    if (sidx[u] >= 0) xout[gq[u]] = res[sidx[u]];
+    if (sidx[u] >= 0) xout[gq[u]] = xr[u];
 }
 
 // ---- host orchestration ----------------------------------------------------------------------
@@ -404,7 +450,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const Box& fb = L.box;
-    dim3 pg(cdiv(fb.x1 - fb.x0, 32), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
+    dim3 pg(cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
     const dim3 tg = stencil_grid(S[l]);
     k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds);
     k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it);

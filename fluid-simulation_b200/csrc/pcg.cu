@@ -19,12 +19,13 @@
 // Kernel shapes: sweep.cuh (STREAM for K2/K3/init, STENCIL for K1).
 #include "sweep.cuh"
 #include "pcg.cuh"
+#include <stdlib.h>
 
 __global__ void k_pcg_reset(DevScalars* ds, double bnorm2) {
   for (int s = 0; s < 4; ++s) { ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0; }
   // |r|^2 of "iteration -1" (= |b|^2): scale of the first preconditioner applications
   ds->rr[2] = bnorm2; ds->rr[3] = bnorm2;
-  ds->pcg_done = 0; ds->pcg_iters = 0; ds->pcg_status = 0; ds->rr_final = 0.0;
+  ds->pcg_done = 0; ds->pcg_iters = 0; ds->pcg_status = 0; ds->rr_final = 0.0; ds->pcg_it = 0;
 }
 
 // x = 0, r = b;  Jacobi: p = M^-1 r, rz[3] = r.p   (Eigen ConjugateGradient.h:43,63,66 with x0 = 0)
@@ -64,9 +65,10 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
 // K1: Ap = A p and p.Ap (STENCIL shape: z-march in registers, x neighbours by shuffle)
 __global__ void __launch_bounds__(32 * ST_BY)
 k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
-       const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it, int noexit) {
+       const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit) {
   __shared__ double sm[32];
   if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
   double acc[1] = {0.0};
   StencilMarch<double> m;
   if (m.begin(S, p)) {
@@ -95,9 +97,10 @@ __global__ void __launch_bounds__(32 * SW_BY)
 k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
             double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
             const double* __restrict__ Ap, float* __restrict__ b0, float* __restrict__ x1,
-            DevScalars* __restrict__ ds, int it, int noexit) {
+            DevScalars* __restrict__ ds, int it_arg, int noexit) {
   __shared__ double sm[64];
   if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
   const double pAp = ds->pAp[it & 3];
   const double rz_old = ds->rz[(it + 3) & 3];
   if (!noexit && !(pAp > 0.0)) {   // breakdown (also catches NaN)
@@ -137,8 +140,9 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
 }
 
 // stop test of ConjugateGradient.h:77-78 (MG path: evaluated before the preconditioner is applied)
-__global__ void k_pcg_check(DevScalars* __restrict__ ds, int it, double threshold) {
+__global__ void k_pcg_check(DevScalars* __restrict__ ds, int it_arg, double threshold) {
   if (ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
   const double rr = ds->rr[it & 3];
   if (rr < threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
 }
@@ -150,8 +154,9 @@ template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
            const double* __restrict__ r, const float* __restrict__ zf, double* __restrict__ p,
-           DevScalars* __restrict__ ds, int it, int max_iter, double threshold, int noexit) {
+           DevScalars* __restrict__ ds, int it_arg, double threshold, int noexit) {
   if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
   const bool lead = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0;
   const bool first = it < 0;
   const double rr = first ? 0.0 : ds->rr[it & 3];
@@ -162,13 +167,6 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   const double beta = first ? 0.0 : ds->rz[it & 3] / ds->rz[(it + 3) & 3];
   const double rrp = ds->rr[(it + 3) & 3];
   const double invsc = MODE == 1 ? (rrp > 0.0 ? sqrt(rrp) : 1.0) : 0.0;
-  if (lead) {
-    int s = (it + 1) & 3;
-    ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
-    if (!noexit && !first && it + 1 >= max_iter) {
-      ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = rr; ds->pcg_status = FLIPB200_ERR_NOCONV;
-    }
-  }
   STREAM_PROLOGUE(S)
   if (!act) return;
   uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
@@ -188,6 +186,19 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   }
 }
 
+// end of an iteration: clear the ring slot the next iteration accumulates into, enforce the
+// iteration limit (IterativeSolverBase.h:283) and advance the device-side iteration counter
+__global__ void k_pcg_advance(DevScalars* __restrict__ ds, int it_arg, int max_iter, int noexit) {
+  if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
+  const int s = (it + 1) & 3;
+  ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
+  if (!noexit && it >= 0 && it + 1 >= max_iter) {
+    ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = ds->rr[it & 3]; ds->pcg_status = FLIPB200_ERR_NOCONV;
+  }
+  if (it >= 0) ds->pcg_it = it + 1;
+}
+
 void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
   const double scale = dt / (c->P.rho * c->P.dx * c->P.dx);       // fluid.cc:306
   float acc = 0.0f;
@@ -201,13 +212,56 @@ void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
   cf->off = (double)(float)(-1 * scale);                          // :335
 }
 
+// one CG iteration on the stream (it_arg = explicit iteration or IT_DEV for graph replay)
+static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int it_arg, int max_iter,
+                             double threshold, int noexit) {
+  const dim3 sg = stream_grid(S), tg = stencil_grid(S);
+  MgLevel& L0 = c->mg[0];
+  k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit);
+  if (use_mg) {
+    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit);
+    if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg, threshold); c->launches++; }
+    int rc = fb_mg_vcycle(c, it_arg);
+    if (rc) return rc;
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, threshold, noexit);
+  } else {
+    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit);
+    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, threshold, noexit);
+  }
+  k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, max_iter, noexit);
+  c->launches += 4;
+  return 0;
+}
+
+// The iteration is captured once per solve into a CUDA graph (36 kernels with the V-cycle, most of
+// them launch-latency bound on the coarse levels) and replayed; kernels read the iteration number
+// from ds->pcg_it.  FLIPB200_NO_GRAPH=1 falls back to plain launches.
+struct IterGraph {
+  cudaGraph_t g = nullptr; cudaGraphExec_t e = nullptr; int64_t kernels = 0;
+  void destroy() { if (e) cudaGraphExecDestroy(e); if (g) cudaGraphDestroy(g); e = nullptr; g = nullptr; }
+};
+static int capture_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int max_iter,
+                             double threshold, int noexit, IterGraph* G) {
+  const char* ng = getenv("FLIPB200_NO_GRAPH");
+  if (ng && ng[0] == '1') return 1;
+  if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return 1; }
+  const int64_t l0 = c->launches;
+  int rc = enqueue_iteration(c, S, cf, use_mg, IT_DEV, max_iter, threshold, noexit);
+  G->kernels = c->launches - l0;
+  c->launches = l0;
+  cudaError_t e = cudaStreamEndCapture(c->stream, &G->g);
+  if (rc || e != cudaSuccess || !G->g) { cudaGetLastError(); G->destroy(); return 1; }
+  if (cudaGraphInstantiate(&G->e, G->g, 0) != cudaSuccess) { cudaGetLastError(); G->destroy(); return 1; }
+  return 0;
+}
+
 int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (iters_out) *iters_out = 0;
   if (rel_out) *rel_out = 0.0;
   const Sweep S = make_sweep(c->g, c->box);
   if (c->n_fluid == 0 || sweep_empty(S)) return 0;
   PcgCoef cf; fb_make_coef(c, dt, &cf);
-  const dim3 sg = stream_grid(S), tg = stencil_grid(S);
+  const dim3 sg = stream_grid(S);
   const double bnorm2 = c->hs->bnorm2;             // fetched by fb_rhs_div
   const float* bvec = c->bf[c->bcur];
   const bool use_mg = c->mg_levels >= 2;
@@ -224,40 +278,40 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   const double tol = c->P.pcg_tol;
   const double threshold = tol * tol * bnorm2;     // :53
   const int max_iter = c->P.pcg_max_iter < 0 ? 2 * c->n_fluid : c->P.pcg_max_iter;   // IterativeSolverBase.h:283
-  const int batch = use_mg ? 8 : 32;
-  int it = 0;
   bool done = max_iter == 0;
   if (use_mg && !done) {
     int rc = fb_mg_setup(c, dt);                   // hierarchy of this step (flags are per step; cheap)
     if (rc) return rc;
     rc = fb_mg_vcycle(c, -1);                      // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, max_iter, threshold, 0);
-    c->launches++;
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, threshold, 0);
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, max_iter, 0);
+    c->launches += 2;
   }
+  IterGraph G;
+  const bool graph = !done && capture_iteration(c, S, cf, use_mg, max_iter, threshold, 0, &G) == 0;
+  // first batch: about as many iterations as the previous solve needed, then small batches
+  int batch = c->last_iters > 4 ? c->last_iters - 1 : (use_mg ? 8 : 32);
+  int it = 0;
   while (!done) {
     int stop = min(it + batch, max_iter);
     for (; it < stop; ++it) {
-      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 0);
-      if (use_mg) {
-        k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it, 0);
-        k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it, threshold);
-        c->launches += 3;
-        int rc = fb_mg_vcycle(c, it);
-        if (rc) return rc;
-        k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it, max_iter, threshold, 0);
-        c->launches++;
+      if (graph) {
+        if (cudaGraphLaunch(G.e, c->stream) != cudaSuccess) { G.destroy(); return FLIPB200_ERR_CUDA; }
+        c->launches += G.kernels;
       } else {
-        k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it, 0);
-        k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it, max_iter, threshold, 0);
-        c->launches += 3;
+        int rc = enqueue_iteration(c, S, cf, use_mg, it, max_iter, threshold, 0);
+        if (rc) { G.destroy(); return rc; }
       }
     }
-    CK_LAUNCH();
-    int rc = fb_fetch_scalars(c);
-    if (rc) return rc;
+    cudaError_t le = cudaGetLastError();
+    int rc = le == cudaSuccess ? fb_fetch_scalars(c) : FLIPB200_ERR_CUDA;
+    if (rc) { G.destroy(); return rc; }
     done = c->hs->pcg_done != 0 || it >= max_iter;
+    batch = use_mg ? 2 : 8;
   }
+  G.destroy();
+  c->last_iters = c->hs->pcg_iters;
   if (iters_out) *iters_out = c->hs->pcg_iters;
   if (rel_out) *rel_out = sqrt(c->hs->rr_final / bnorm2);          // cg.error(), ConjugateGradient.h:88
   if (c->hs->pcg_status == FLIPB200_ERR_BREAKDOWN) return FLIPB200_ERR_BREAKDOWN;
@@ -280,29 +334,30 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds);
     int rc = fb_mg_setup(c, c->P.dt_max); if (rc) return rc;
     rc = fb_mg_vcycle(c, -1); if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1 << 30, 0.0, 1);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 0.0, 1);
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1 << 30, 1);
   } else {
     k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds);
   }
-  const int64_t l0 = c->launches;
+  IterGraph G;
+  bool graph = false;
+  if (which == FLIPB200_KERNEL_PCG_ITER) graph = capture_iteration(c, S, cf, use_mg, 1 << 30, 0.0, 1, &G) == 0;
   for (int it = 0; it < 3 + iters; ++it) {
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
-    k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
-    c->launches++;
-    if (which != FLIPB200_KERNEL_PCG_ITER) continue;
-    if (use_mg) {
-      k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it, 1);
-      int rc = fb_mg_vcycle(c, it); if (rc) return rc;
-      k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it, 1 << 30, 0.0, 1);
+    if (which != FLIPB200_KERNEL_PCG_ITER) {
+      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
+      c->launches++;
+    } else if (graph) {
+      if (cudaGraphLaunch(G.e, c->stream) != cudaSuccess) { G.destroy(); return FLIPB200_ERR_CUDA; }
+      c->launches += G.kernels;
     } else {
-      k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it, 1);
-      k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it, 1 << 30, 0.0, 1);
+      int rc = enqueue_iteration(c, S, cf, use_mg, it, 1 << 30, 0.0, 1);
+      if (rc) return rc;
     }
-    c->launches += 2;
   }
-  (void)l0;
   CK(cudaEventRecord(c->ev[7], c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  G.destroy();
   CK_LAUNCH();
   float e = 0.f;
   CK(cudaEventElapsedTime(&e, c->ev[6], c->ev[7]));

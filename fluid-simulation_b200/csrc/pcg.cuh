@@ -21,3 +21,7 @@ static inline MgCoef make_mg_coef(double h2inv) {
   for (int k = 1; k <= 6; ++k) m.winv[k] = (float)(MG_OMEGA / (k * h2inv));
   return m;
 }
+
+// kernels take the iteration number as an argument, or IT_DEV to read it from ds->pcg_it (graph replay)
+#define IT_DEV (-1000)
+__device__ __forceinline__ int pcg_iter(const DevScalars* ds, int it_arg) { return it_arg == IT_DEV ? ds->pcg_it : it_arg; }
