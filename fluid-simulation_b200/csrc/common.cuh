@@ -57,6 +57,7 @@ struct DevScalars {
   int n_fluid;
   int bbox[6];                       // min x,y,z / max x,y,z of fluid cells
   int pcg_done, pcg_iters, pcg_status;
+  int pcg_max_iter;                  // iteration limit of the current solve
   int pcg_it;                        // current iteration (kernels launched from a CUDA graph read it here)
   int n_invalid;                     // particles whose support lies outside the box
   int pad;
@@ -114,6 +115,10 @@ struct flipb200_ctx {
   Box box;                 // sweep box of this step
   int n_fluid;
   int last_iters;          // iterations of the previous solve (sizes the first launch batch)
+  bool mg_dirty;           // cell classes changed since the hierarchy was built (set by classify)
+  // cached CUDA graph of one PCG iteration; valid while box / dt / mode are unchanged
+  cudaGraph_t it_graph; cudaGraphExec_t it_exec; int64_t it_kernels;
+  Box it_box; double it_dt; int it_mode;
   int stage;               // bookkeeping for stage-level calls
   cudaEvent_t ev[8];
   int64_t launches;
@@ -215,6 +220,7 @@ int fb_cell_delta(flipb200_ctx* c);
 int fb_g2p_advect(flipb200_ctx* c);
 int fb_fetch_scalars(flipb200_ctx* c);
 int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units);
+void fb_graph_invalidate(flipb200_ctx* c);
 int fb_mg_alloc(flipb200_ctx* c);
 void fb_mg_free(flipb200_ctx* c);
 int fb_mg_setup(flipb200_ctx* c, double dt);                    // per step: coarse flags + boxes

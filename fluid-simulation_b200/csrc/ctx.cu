@@ -219,6 +219,7 @@ void flipb200_destroy(flipb200_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  fb_graph_invalidate(c);
   fb_mg_free(c);
   cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static);
   for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }

@@ -102,6 +102,7 @@ int fb_classify(flipb200_ctx* c) {
   }
   c->box = b;
   c->bcur = 0;
+  c->mg_dirty = true;
   return 0;
 }
 

@@ -167,11 +167,12 @@ int fb_mg_setup(flipb200_ctx* c, double dt) {
   for (int l = 1; l < c->mg_levels; ++l) {
     MgLevel& F = c->mg[l - 1];
     MgLevel& L = c->mg[l];
+    L.h2inv = F.h2inv * 0.25;
+    if (!c->mg_dirty) continue;                     // same cell classes as the previous solve of this step
     dim3 grd(cdiv(L.g.px, 32), cdiv(L.g.ny, 8), L.g.nz);
     k_mg_coarsen<<<grd, blk, 0, c->stream>>>(F.g, L.g, F.flags, L.flags);
     k_mg_nbrmask<<<grd, blk, 0, c->stream>>>(L.g, L.flags);
     c->launches += 2;
-    L.h2inv = F.h2inv * 0.25;
     // coarse box: the parents of the fine box plus a 1-cell margin (prolongation donors)
     Box b;
     b.x0 = max(0, F.box.x0 / 2 - 1) & ~1; b.y0 = max(0, F.box.y0 / 2 - 1); b.z0 = max(0, F.box.z0 / 2 - 1);
@@ -186,6 +187,7 @@ int fb_mg_setup(flipb200_ctx* c, double dt) {
       c->launches++;
     }
   }
+  c->mg_dirty = false;
   CK_LAUNCH();
   return 0;
 }
@@ -277,38 +279,41 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
   const int K = cbox.z0 + blockIdx.z;
   if (J >= cbox.y1) return;                         // whole warp
   const bool in = I < cbox.x1;
+  // the fine sweeps write pairs over [fx0, fxe): everything in that x-range is fresh (0 off the fluid)
+  const int fx0 = fbox.x0 & ~1, fxe = min(gf.px, (fbox.x1 + 1) & ~1);
   const int xf = 2 * I;                             // children xf, xf+1
-  const bool c0 = in && xf >= fbox.x0 && xf < fbox.x1, c1 = in && xf + 1 >= fbox.x0 && xf + 1 < fbox.x1;
-  const bool both = c0 && c1;
-  const bool eL = xf - 1 >= fbox.x0 && xf - 1 < fbox.x1, eR = xf + 2 >= fbox.x0 && xf + 2 < fbox.x1;
+  const bool cv = in && xf >= fx0 && xf < fxe;
+  const bool eL = in && xf - 1 >= fx0 && xf - 1 < fxe, eR = in && xf + 2 >= fx0 && xf + 2 < fxe;
+  const int xc = cv ? xf : fx0;                     // clamped (value discarded when !cv)
+  // issue all 16 row loads first (rows outside the fine box are clamped and get weight 0)
+  float2 v[16]; float ea[16], ed[16], w[16];
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const int oz = (t >> 2) - 1, oy = (t & 3) - 1;
+    const int kf = 2 * K + oz, jf = 2 * J + oy;
+    const bool rin = kf >= fbox.z0 && kf < fbox.z1 && jf >= fbox.y0 && jf < fbox.y1;
+    const int kc = min(max(kf, fbox.z0), fbox.z1 - 1), jc = min(max(jf, fbox.y0), fbox.y1 - 1);
+    const float* row = rn + gidx(gf, 0, jc, kc);
+    w[t] = rin ? (((oz == 0 || oz == 1) ? 3.f : 1.f) * ((oy == 0 || oy == 1) ? 3.f : 1.f)) : 0.f;
+    v[t] = *reinterpret_cast<const float2*>(row + xc);
+    ea[t] = (lane == 0 && eL) ? row[xf - 1] : 0.f;
+    ed[t] = (lane == 31 && eR) ? row[xf + 2] : 0.f;
+  }
   float sum = 0.f;
 #pragma unroll
-  for (int oz = -1; oz <= 2; ++oz) {
-    const int kf = 2 * K + oz;
-    const bool zin = kf >= fbox.z0 && kf < fbox.z1;
-    const float wz = (oz == 0 || oz == 1) ? 3.f : 1.f;
-#pragma unroll
-    for (int oy = -1; oy <= 2; ++oy) {
-      const int jf = 2 * J + oy;
-      const bool rin = zin && jf >= fbox.y0 && jf < fbox.y1;   // warp-uniform
-      if (!rin) continue;
-      const float wyz = wz * ((oy == 0 || oy == 1) ? 3.f : 1.f);
-      const float* row = rn + gidx(gf, 0, jf, kf);
-      float2 v = make_float2(0.f, 0.f);
-      if (both) v = *reinterpret_cast<const float2*>(row + xf);
-      else { if (c0) v.x = row[xf]; if (c1) v.y = row[xf + 1]; }
-      float a = __shfl_up_sync(0xffffffffu, v.y, 1), d = __shfl_down_sync(0xffffffffu, v.x, 1);
-      if (lane == 0) a = (in && eL) ? row[xf - 1] : 0.f;
-      if (lane == 31) d = (in && eR) ? row[xf + 2] : 0.f;
-      sum += wyz * ((a + d) + 3.f * (v.x + v.y));
-    }
+  for (int t = 0; t < 16; ++t) {
+    float vx = cv ? v[t].x : 0.f, vy = cv ? v[t].y : 0.f;
+    float a = __shfl_up_sync(0xffffffffu, vy, 1), d = __shfl_down_sync(0xffffffffu, vx, 1);
+    if (lane == 0) a = ea[t];
+    if (lane == 31) d = ed[t];
+    sum += w[t] * ((a + d) + 3.f * (vx + vy));
   }
   if (!in) return;
   const int qc = gidx(gc, I, J, K);
   const uint8_t f = fc[qc];
-  const float v = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
-  bc[qc] = v;
-  x1c[qc] = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * v : 0.f;
+  const float r = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
+  bc[qc] = r;
+  x1c[qc] = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * r : 0.f;
 }
 
 // prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells).
@@ -345,12 +350,12 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
   const int xe = min(gf.px, (fbox.x1 + 1) & ~1);
   if (i >= xe) return;
   const int q = gidx(gf, i, j, k);
-  const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);
-  if (!((f.x | f.y) & FB_FLUID)) return;
+  const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);      // three independent loads in flight
   const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
   float2 xv = *reinterpret_cast<const float2*>(x + q);
-  if (f.x & FB_FLUID) xv.x += (3.f * E + EL) / (float)nn.x;     // node 2I   : donors I (3) and I-1 (1)
-  if (f.y & FB_FLUID) xv.y += (3.f * E + ER) / (float)nn.y;     // node 2I+1 : donors I (3) and I+1 (1)
+  if (!((f.x | f.y) & FB_FLUID)) return;
+  if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
+  if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
   *reinterpret_cast<float2*>(x + q) = xv;
 }
 

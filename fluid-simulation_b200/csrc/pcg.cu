@@ -21,7 +21,8 @@
 #include "pcg.cuh"
 #include <stdlib.h>
 
-__global__ void k_pcg_reset(DevScalars* ds, double bnorm2) {
+__global__ void k_pcg_reset(DevScalars* ds, double bnorm2, double threshold, int max_iter) {
+  ds->threshold = threshold; ds->pcg_max_iter = max_iter;
   for (int s = 0; s < 4; ++s) { ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0; }
   // |r|^2 of "iteration -1" (= |b|^2): scale of the first preconditioner applications
   ds->rr[2] = bnorm2; ds->rr[3] = bnorm2;
@@ -140,11 +141,11 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
 }
 
 // stop test of ConjugateGradient.h:77-78 (MG path: evaluated before the preconditioner is applied)
-__global__ void k_pcg_check(DevScalars* __restrict__ ds, int it_arg, double threshold) {
+__global__ void k_pcg_check(DevScalars* __restrict__ ds, int it_arg) {
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   const double rr = ds->rr[it & 3];
-  if (rr < threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
+  if (rr < ds->threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
 }
 
 // K3: beta = rz/rz_old (:84), p = z + beta p (:85).
@@ -154,13 +155,13 @@ template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
            const double* __restrict__ r, const float* __restrict__ zf, double* __restrict__ p,
-           DevScalars* __restrict__ ds, int it_arg, double threshold, int noexit) {
+           DevScalars* __restrict__ ds, int it_arg, int noexit) {
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   const bool lead = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0;
   const bool first = it < 0;
   const double rr = first ? 0.0 : ds->rr[it & 3];
-  if (MODE == 0 && !noexit && rr < threshold) {
+  if (MODE == 0 && !noexit && rr < ds->threshold) {
     if (lead) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
     return;
   }
@@ -188,11 +189,12 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
 
 // end of an iteration: clear the ring slot the next iteration accumulates into, enforce the
 // iteration limit (IterativeSolverBase.h:283) and advance the device-side iteration counter
-__global__ void k_pcg_advance(DevScalars* __restrict__ ds, int it_arg, int max_iter, int noexit) {
+__global__ void k_pcg_advance(DevScalars* __restrict__ ds, int it_arg, int noexit) {
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   const int s = (it + 1) & 3;
   ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
+  const int max_iter = ds->pcg_max_iter;
   if (!noexit && it >= 0 && it + 1 >= max_iter) {
     ds->pcg_done = 1; ds->pcg_iters = max_iter; ds->rr_final = ds->rr[it & 3]; ds->pcg_status = FLIPB200_ERR_NOCONV;
   }
@@ -213,46 +215,53 @@ void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
 }
 
 // one CG iteration on the stream (it_arg = explicit iteration or IT_DEV for graph replay)
-static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int it_arg, int max_iter,
-                             double threshold, int noexit) {
+static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int it_arg, int noexit) {
   const dim3 sg = stream_grid(S), tg = stencil_grid(S);
   MgLevel& L0 = c->mg[0];
   k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit);
   if (use_mg) {
     k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit);
-    if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg, threshold); c->launches++; }
+    if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg); c->launches++; }
     int rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, threshold, noexit);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit);
   } else {
     k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit);
-    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, threshold, noexit);
+    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, noexit);
   }
-  k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, max_iter, noexit);
+  k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, noexit);
   c->launches += 4;
   return 0;
 }
 
-// The iteration is captured once per solve into a CUDA graph (36 kernels with the V-cycle, most of
-// them launch-latency bound on the coarse levels) and replayed; kernels read the iteration number
-// from ds->pcg_it.  FLIPB200_NO_GRAPH=1 falls back to plain launches.
-struct IterGraph {
-  cudaGraph_t g = nullptr; cudaGraphExec_t e = nullptr; int64_t kernels = 0;
-  void destroy() { if (e) cudaGraphExecDestroy(e); if (g) cudaGraphDestroy(g); e = nullptr; g = nullptr; }
-};
-static int capture_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int max_iter,
-                             double threshold, int noexit, IterGraph* G) {
+// The iteration is captured into a CUDA graph (36 kernels with the V-cycle, most of them
+// launch-latency bound on the coarse levels) and replayed; kernels read the iteration number, the
+// threshold and the iteration limit from DevScalars, so the graph stays valid across solves and steps
+// until the sweep box, dt or the mode change.  FLIPB200_NO_GRAPH=1 falls back to plain launches.
+void fb_graph_invalidate(flipb200_ctx* c) {
+  if (c->it_exec) cudaGraphExecDestroy(c->it_exec);
+  if (c->it_graph) cudaGraphDestroy(c->it_graph);
+  c->it_exec = nullptr; c->it_graph = nullptr;
+}
+static bool same_box(const Box& a, const Box& b) {
+  return a.x0 == b.x0 && a.y0 == b.y0 && a.z0 == b.z0 && a.x1 == b.x1 && a.y1 == b.y1 && a.z1 == b.z1;
+}
+static bool get_iteration_graph(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, double dt, int noexit) {
   const char* ng = getenv("FLIPB200_NO_GRAPH");
-  if (ng && ng[0] == '1') return 1;
-  if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return 1; }
+  if (ng && ng[0] == '1') return false;
+  const int mode = (use_mg ? 1 : 0) | (noexit ? 2 : 0);
+  if (c->it_exec && same_box(c->it_box, c->box) && c->it_dt == dt && c->it_mode == mode) return true;
+  fb_graph_invalidate(c);
+  if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
   const int64_t l0 = c->launches;
-  int rc = enqueue_iteration(c, S, cf, use_mg, IT_DEV, max_iter, threshold, noexit);
-  G->kernels = c->launches - l0;
+  int rc = enqueue_iteration(c, S, cf, use_mg, IT_DEV, noexit);
+  c->it_kernels = c->launches - l0;
   c->launches = l0;
-  cudaError_t e = cudaStreamEndCapture(c->stream, &G->g);
-  if (rc || e != cudaSuccess || !G->g) { cudaGetLastError(); G->destroy(); return 1; }
-  if (cudaGraphInstantiate(&G->e, G->g, 0) != cudaSuccess) { cudaGetLastError(); G->destroy(); return 1; }
-  return 0;
+  cudaError_t e = cudaStreamEndCapture(c->stream, &c->it_graph);
+  if (rc || e != cudaSuccess || !c->it_graph) { cudaGetLastError(); fb_graph_invalidate(c); return false; }
+  if (cudaGraphInstantiate(&c->it_exec, c->it_graph, 0) != cudaSuccess) { cudaGetLastError(); fb_graph_invalidate(c); return false; }
+  c->it_box = c->box; c->it_dt = dt; c->it_mode = mode;
+  return true;
 }
 
 int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
@@ -266,7 +275,10 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   const float* bvec = c->bf[c->bcur];
   const bool use_mg = c->mg_levels >= 2;
   MgLevel& L0 = c->mg[0];
-  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2);
+  const double tol = c->P.pcg_tol;
+  const double threshold = tol * tol * bnorm2;     // ConjugateGradient.h:53
+  const int max_iter = c->P.pcg_max_iter < 0 ? 2 * c->n_fluid : c->P.pcg_max_iter;   // IterativeSolverBase.h:283
+  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2, threshold, max_iter);
   if (use_mg)
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, L0.b, L0.xa,
                                                       bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds);
@@ -275,21 +287,17 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   CK_LAUNCH(); c->launches += 2;
   if (bnorm2 == 0.0) return 0;                     // rhsNorm2 == 0 => x = 0, 0 iterations (ConjugateGradient.h:46-52)
   if (!(bnorm2 == bnorm2)) return FLIPB200_ERR_BREAKDOWN;
-  const double tol = c->P.pcg_tol;
-  const double threshold = tol * tol * bnorm2;     // :53
-  const int max_iter = c->P.pcg_max_iter < 0 ? 2 * c->n_fluid : c->P.pcg_max_iter;   // IterativeSolverBase.h:283
   bool done = max_iter == 0;
   if (use_mg && !done) {
-    int rc = fb_mg_setup(c, dt);                   // hierarchy of this step (flags are per step; cheap)
+    int rc = fb_mg_setup(c, dt);                   // hierarchy: rebuilt only when the cell classes changed
     if (rc) return rc;
     rc = fb_mg_vcycle(c, -1);                      // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, threshold, 0);
-    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, max_iter, 0);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 0);
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 0);
     c->launches += 2;
   }
-  IterGraph G;
-  const bool graph = !done && capture_iteration(c, S, cf, use_mg, max_iter, threshold, 0, &G) == 0;
+  const bool graph = !done && get_iteration_graph(c, S, cf, use_mg, dt, 0);
   // first batch: about as many iterations as the previous solve needed, then small batches
   int batch = c->last_iters > 4 ? c->last_iters - 1 : (use_mg ? 8 : 32);
   int it = 0;
@@ -297,20 +305,19 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     int stop = min(it + batch, max_iter);
     for (; it < stop; ++it) {
       if (graph) {
-        if (cudaGraphLaunch(G.e, c->stream) != cudaSuccess) { G.destroy(); return FLIPB200_ERR_CUDA; }
-        c->launches += G.kernels;
+        if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }
+        c->launches += c->it_kernels;
       } else {
-        int rc = enqueue_iteration(c, S, cf, use_mg, it, max_iter, threshold, 0);
-        if (rc) { G.destroy(); return rc; }
+        int rc = enqueue_iteration(c, S, cf, use_mg, it, 0);
+        if (rc) return rc;
       }
     }
     cudaError_t le = cudaGetLastError();
     int rc = le == cudaSuccess ? fb_fetch_scalars(c) : FLIPB200_ERR_CUDA;
-    if (rc) { G.destroy(); return rc; }
+    if (rc) return rc;
     done = c->hs->pcg_done != 0 || it >= max_iter;
     batch = use_mg ? 2 : 8;
   }
-  G.destroy();
   c->last_iters = c->hs->pcg_iters;
   if (iters_out) *iters_out = c->hs->pcg_iters;
   if (rel_out) *rel_out = sqrt(c->hs->rr_final / bnorm2);          // cg.error(), ConjugateGradient.h:88
@@ -324,40 +331,39 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
 int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units) {
   const Sweep S = make_sweep(c->g, c->box);
   if (sweep_empty(S)) return FLIPB200_ERR_STATE;
-  PcgCoef cf; fb_make_coef(c, c->P.dt_max, &cf);
+  const double dt = c->P.dt_max;
+  PcgCoef cf; fb_make_coef(c, dt, &cf);
   const dim3 sg = stream_grid(S), tg = stencil_grid(S);
   const bool use_mg = c->mg_levels >= 2 && which == FLIPB200_KERNEL_PCG_ITER;
   MgLevel& L0 = c->mg[0];
   const double bn = c->hs->bnorm2 > 0.0 ? c->hs->bnorm2 : 1.0;
-  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn);
+  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn, 0.0, 1 << 30);
   if (use_mg) {
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds);
-    int rc = fb_mg_setup(c, c->P.dt_max); if (rc) return rc;
+    int rc = fb_mg_setup(c, dt); if (rc) return rc;
     rc = fb_mg_vcycle(c, -1); if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 0.0, 1);
-    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1 << 30, 1);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1);
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1);
   } else {
     k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds);
   }
-  IterGraph G;
   bool graph = false;
-  if (which == FLIPB200_KERNEL_PCG_ITER) graph = capture_iteration(c, S, cf, use_mg, 1 << 30, 0.0, 1, &G) == 0;
+  if (which == FLIPB200_KERNEL_PCG_ITER) graph = get_iteration_graph(c, S, cf, use_mg, dt, 1);
   for (int it = 0; it < 3 + iters; ++it) {
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
       k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
       c->launches++;
     } else if (graph) {
-      if (cudaGraphLaunch(G.e, c->stream) != cudaSuccess) { G.destroy(); return FLIPB200_ERR_CUDA; }
-      c->launches += G.kernels;
+      if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }
+      c->launches += c->it_kernels;
     } else {
-      int rc = enqueue_iteration(c, S, cf, use_mg, it, 1 << 30, 0.0, 1);
+      int rc = enqueue_iteration(c, S, cf, use_mg, it, 1);
       if (rc) return rc;
     }
   }
   CK(cudaEventRecord(c->ev[7], c->stream));
   CK(cudaStreamSynchronize(c->stream));
-  G.destroy();
   CK_LAUNCH();
   float e = 0.f;
   CK(cudaEventElapsedTime(&e, c->ev[6], c->ev[7]));
