@@ -133,7 +133,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--kernel-iters", type=int, default=50)
-    ap.add_argument("--precond", type=int, default=int(os.environ.get("FLIPB200_PRECOND", "0")), help="0 Jacobi, 1 multigrid V-cycle")
+    ap.add_argument("--precond", type=int, default=int(os.environ.get("FLIPB200_PRECOND", "1")), help="0 Jacobi, 1 multigrid V-cycle")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))

@@ -21,7 +21,7 @@ void flipb200_default_params(flipb200_params* p) {
   p->pcg_tol = 2.220446049250313e-16;   // NumTraits<double>::epsilon(), IterativeSolverBase.h:363
   p->pcg_max_iter = -1;
   p->max_passes = 200;
-  p->precond = 0;
+  p->precond = 1;                // multigrid V-cycle (IC-free); 0 = Jacobi
   p->device = -1;
   p->track_ids = 0;
   p->max_particles = 0;

@@ -294,6 +294,76 @@ k_g2p(Grid g, int64_t n, const uint8_t* __restrict__ fl,
   }
 }
 
+// Cell-ordered G2P: one thread per base cell.  The 8 x 3 cell-centred deltas (and which of the 8
+// nodes lie inside the shell) are loaded once per cell and reused by all of its particles, so the
+// gather costs 24 loads per cell instead of 24 per particle.  Requires cell-sorted particles.
+__global__ void __launch_bounds__(128)
+k_g2p_cell(Grid g, const int32_t* __restrict__ start,
+           const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+           double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
+           const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
+           DevScalars* __restrict__ ds) {
+  __shared__ double red[4];
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  int k = blockIdx.z;
+  double speed = 0.0;
+  int s = 0, e = 0, q = 0;
+  if (i <= g.nx - 2 && j <= g.ny - 2 && k <= g.nz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
+  if (s < e) {
+    double ddx[8], ddy[8], ddz[8];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
+      int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+      bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
+      ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
+    }
+    unsigned inmask = 0;
+#pragma unroll
+    for (int m = 0; m < 8; ++m)
+      if (inside_shell(g, i + (m & 1), j + ((m >> 1) & 1), k + ((m >> 2) & 1))) inmask |= 1u << m;
+    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+    for (int n = s; n < e; ++n) {
+      double x = px[n], y = py[n], z = pz[n];
+      double a = vx[n], b = vy[n], cc = vz[n];
+      double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+      double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+      double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+      double wsum = 0, dx = 0, dy = 0, dz = 0;
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+        if (inmask & (1u << m)) wsum += cw;
+        dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
+      }
+      if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; vx[n] = a; vy[n] = b; vz[n] = cc; }   // fluid.cc:258-262, 981
+      speed = fmax(speed, sqrt(a * a + b * b + cc * cc));      // fluid.cc:982
+    }
+  }
+  speed = warp_max(speed);
+  int tid = threadIdx.x + blockDim.x * threadIdx.y, lane = tid & 31, w = tid >> 5;
+  if (lane == 0) red[w] = speed;
+  __syncthreads();
+  if (tid == 0) {
+    double m = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
+    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
+  }
+}
+
+// particles of the trailing "outside" bucket: no grid contact, but their speed counts (fluid.cc:982)
+__global__ void k_speed_tail(const int32_t* __restrict__ start, int total, int64_t n, const double* __restrict__ vx,
+                             const double* __restrict__ vy, const double* __restrict__ vz, DevScalars* __restrict__ ds) {
+  double speed = 0.0;
+  for (int64_t t = (int64_t)start[total] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    double a = vx[t], b = vy[t], cc = vz[t];
+    speed = fmax(speed, sqrt(a * a + b * b + cc * cc));
+  }
+  speed = warp_max(speed);
+  if ((threadIdx.x & 31) == 0 && speed > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(speed));
+}
+
 __device__ __forceinline__ bool solid_at(const Grid& g, const uint8_t* __restrict__ fl, int i, int j, int k) {
   return in_box(g, i, j, k) && (fl[gidx(g, i, j, k)] & FB_SOLID);
 }
@@ -343,9 +413,21 @@ int fb_g2p_advect(flipb200_ctx* c) {
   c->launches++;
   int blocks = (int)((pt.n + 255) / 256);
   if (blocks == 0) blocks = 1;
-  k_g2p<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                       c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
-  CK_LAUNCH(); c->launches++;
+  const char* mode = getenv("FLIPB200_G2P");
+  if (c->sorted && pt.n > 0 && !(mode && mode[0] == 'p')) {
+    dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.nz - 1);
+    k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                           c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+    c->launches++;
+    // the trailing bucket (key == total) holds the particles outside the box (usually none)
+    k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, pt.n, pt.a[3], pt.a[4], pt.a[5], c->ds);
+    c->launches++;
+  } else {
+    k_g2p<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                         c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+    c->launches++;
+  }
+  CK_LAUNCH();
   k_advect<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
                                           pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds);
   CK_LAUNCH(); c->launches++;

@@ -50,7 +50,7 @@ typedef struct {
   double  pcg_tol;           /* 2.220446049250313e-16 (Eigen IterativeSolverBase.h:363)       */
   int32_t pcg_max_iter;      /* <0 => 2*n_fluid (IterativeSolverBase.h:283)                   */
   int32_t max_passes;        /* safety cap on the do..while loop (reference: unbounded); 200  */
-  int32_t precond;           /* 0 = Jacobi; 1 = multigrid V-cycle (if built)                  */
+  int32_t precond;           /* 1 = multigrid V-cycle in fp32 (default); 0 = Jacobi           */
   int32_t device;            /* CUDA device ordinal; <0 => current device                     */
   int32_t track_ids;         /* 1: carry particle ids through the cell sort so that get_particles /
                                 step_host return the caller's original order (the reference never

@@ -93,8 +93,10 @@ def test_rhs_div_pcg_velupdate_relax(fb, oracle_mod, scenes):
     assert e == pytest.approx(eo, rel=1e-12)
 
 
-def test_g2p_advect(fb, oracle_mod, scenes):
-    """a17/a18 from identical grids; includes particles that hit the solid shell."""
+@pytest.mark.parametrize("mode", ["cell", "particle"])
+def test_g2p_advect(fb, oracle_mod, scenes, mode, monkeypatch):
+    """a17/a18 from identical grids; includes particles that hit the solid shell (both G2P kernels)."""
+    monkeypatch.setenv("FLIPB200_G2P", mode)
     sc = random_velocity_scene(scenes, n=21, half=8, vscale=6.0)   # fast particles touching the wall (shell at |c| >= 9)
     f, o = _pair(fb, oracle_mod, sc)
     dt = 0.1
@@ -115,9 +117,10 @@ def test_g2p_advect(fb, oracle_mod, scenes):
     assert np.array_equal(vg == 0.0, vo == 0.0)
 
 
-def test_single_step_small(fb, oracle_mod, scenes):
+@pytest.mark.parametrize("precond", [0, 1])
+def test_single_step_small(fb, oracle_mod, scenes, precond):
     sc = random_velocity_scene(scenes, vscale=0.5)
-    f, o = _pair(fb, oracle_mod, sc)
+    f, o = _pair(fb, oracle_mod, sc, precond=precond)
     dt_g, st = f.step(0.1)
     dt_o, so = o.step(0.1)
     assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
