@@ -59,7 +59,25 @@ def build(force=False, verbose=False):
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError("link failed")
+    build_host()
     return LIB
+
+
+VDB_LIB = os.path.join(HERE, "libflipvdb.so")
+
+
+def build_host():
+    """Host-side pieces that need no GPU: the self-contained VDB-224 writer (used by the C++ driver
+    and, through this small shared library, by the tests)."""
+    src = os.path.join(HERE, "host", "vdb_writer.cc")
+    hdr = os.path.join(HERE, "host", "vdb_writer.h")
+    if _stale(VDB_LIB, [src, hdr]):
+        cmd = ["/usr/bin/g++", "-std=c++11", "-O2", "-fPIC", "-shared", "-o", VDB_LIB, src, "-lz"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("vdb writer build failed")
+    return VDB_LIB
 
 
 if __name__ == "__main__":
