@@ -62,6 +62,8 @@ EXPORTS = [
     "flipb200_rhs_div", "flipb200_pcg_solve", "flipb200_vel_update", "flipb200_relax_error",
     "flipb200_g2p_advect", "flipb200_get_grid", "flipb200_set_grid", "flipb200_time_kernel",
     "flipb200_host_alloc", "flipb200_host_free",
+    "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
+    "flipb200_comm_init_local", "flipb200_get_particle_ids",
 ]
 
 _lib = None
@@ -110,8 +112,21 @@ def load():
     lib.flipb200_time_kernel.argtypes = [vp, C.c_int, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int64)]
     lib.flipb200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     lib.flipb200_host_free.argtypes = [vp]
+    lib.flipb200_create_slab.argtypes = [C.POINTER(Params), vp, C.c_int32, C.c_int32, C.POINTER(vp)]
+    lib.flipb200_slab_range.argtypes = [vp, ip, ip]
+    lib.flipb200_comm_unique_id.argtypes = [vp]
+    lib.flipb200_comm_init_nccl.argtypes = [vp, vp]
+    lib.flipb200_comm_init_local.argtypes = [vp, C.c_int32]
+    lib.flipb200_get_particle_ids.argtypes = [vp, vp, C.c_int64]
     _lib = lib
     return lib
+
+
+def comm_unique_id():
+    """128-byte NCCL unique id (call on rank 0, broadcast to the other ranks)."""
+    buf = (C.c_char * 128)()
+    _check(load().flipb200_comm_unique_id(buf), "comm_unique_id")
+    return bytes(buf)
 
 
 def default_params(**kw):
@@ -151,20 +166,43 @@ def pinned_free(p):
 class Flip:
     """One simulation context on one GPU.  Grid arrays are (nz, ny, nx) numpy arrays (x fastest)."""
 
-    def __init__(self, params=None, solid=None, **kw):
+    def __init__(self, params=None, solid=None, rank=0, world=1, **kw):
+        """world > 1: this context is z-slab `rank` of `world` (connect with comm_init_* before use)."""
         self.lib = load()
         self.params = params if params is not None else default_params(**kw)
-        self.shape = (self.params.nz, self.params.ny, self.params.nx)
-        self.N = int(np.prod(self.shape))
+        self.rank, self.world = rank, world
+        gshape = (self.params.nz, self.params.ny, self.params.nx)
         sp = None
         if solid is not None:
             self._solid = np.ascontiguousarray(solid, dtype=np.uint8).reshape(-1)
-            if self._solid.size != self.N:
+            if self._solid.size != int(np.prod(gshape)):
                 raise ValueError("solid must have nx*ny*nz entries")
             sp = _ptr(self._solid)
         h = C.c_void_p()
-        _check(self.lib.flipb200_create(C.byref(self.params), sp, C.byref(h)), "flipb200_create")
+        if world == 1:
+            _check(self.lib.flipb200_create(C.byref(self.params), sp, C.byref(h)), "flipb200_create")
+        else:
+            _check(self.lib.flipb200_create_slab(C.byref(self.params), sp, rank, world, C.byref(h)), "flipb200_create_slab")
         self.h = h
+        z0, z1 = C.c_int32(0), C.c_int32(0)
+        _check(self.lib.flipb200_slab_range(self.h, C.byref(z0), C.byref(z1)), "slab_range")
+        self.z0, self.z1 = z0.value, z1.value
+        self.shape = (self.z1 - self.z0, self.params.ny, self.params.nx)     # owned planes
+        self.N = int(np.prod(self.shape))
+
+    # ---- z-slab plumbing ----
+    def comm_init_local(self, group_id):
+        _check(self.lib.flipb200_comm_init_local(self.h, group_id), "comm_init_local")
+
+    def comm_init_nccl(self, unique_id):
+        buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
+        _check(self.lib.flipb200_comm_init_nccl(self.h, buf), "comm_init_nccl")
+
+    def get_particle_ids(self):
+        n = self.num_particles
+        ids = np.empty(n, dtype=np.uint32)
+        _check(self.lib.flipb200_get_particle_ids(self.h, _ptr(ids), n), "get_particle_ids")
+        return ids
 
     @classmethod
     def from_scene(cls, scene, **kw):

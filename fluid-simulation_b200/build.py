@@ -12,7 +12,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libflipb200.so")
-SOURCES = ["ctx.cu", "particles.cu", "grid.cu", "pcg.cu", "mg.cu", "step.cu"]
+SOURCES = ["ctx.cu", "particles.cu", "grid.cu", "pcg.cu", "mg.cu", "step.cu", "comm.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -54,7 +54,7 @@ def build(force=False, verbose=False):
                 raise RuntimeError("nvcc failed: " + cmd[-3])
     if force or jobs or _stale(LIB, objs):
         cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
-                                                      "-ccbin", "/usr/bin/g++", "-lcudart"]
+                                                      "-ccbin", "/usr/bin/g++", "-lcudart", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)

@@ -1,0 +1,407 @@
+// comm.cu -- exchanges of the z-slab decomposition.  The reference is single-process
+// (its only parallelism is tbb::parallel_for over particles, fluid.cc:845-1126); this is new design.
+//
+// Two transports behind the same five primitives (halo fill, P2G ghost sum, all-reduce, plane
+// all-gather, particle migration):
+//   NCCL   one process per GPU (torch.distributed / mpirun bootstrap hands the 128-byte unique id
+//          through flipb200_comm_init_nccl); point-to-point ncclSend/ncclRecv pairs between z
+//          neighbours and small ncclAllReduce calls, all enqueued on the ctx stream so they can
+//          be captured into the CUDA graph of the PCG iteration.  libnccl.so.2 is dlopen'ed on
+//          first use: a single-GPU user of libflipb200.so needs no NCCL at all.
+//   LOCAL  several ranks as host threads of ONE process (any devices, also all on one GPU): each
+//          primitive is stream-sync + host barrier + cudaMemcpyAsync pulls.  Slow by design; it
+//          exists so that the slab logic (ghost planes, distributed V-cycle, migration) is
+//          parity-tested on a single GPU (tests/test_gpu_slab.py).
+#include "common.cuh"
+#include <dlfcn.h>
+#include <string.h>
+#include <stdlib.h>
+#include <mutex>
+#include <condition_variable>
+#include <map>
+#include <nccl.h>
+
+#define MAXR 16
+
+// ---- NCCL entry points (dlsym) -----------------------------------------------------------------
+struct NcclApi {
+  void* h;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*GroupStart)();
+  ncclResult_t (*GroupEnd)();
+  const char* (*GetErrorString)(ncclResult_t);
+};
+static NcclApi g_nccl;
+static std::mutex g_nccl_mu;
+
+static bool nccl_load() {
+  std::lock_guard<std::mutex> lk(g_nccl_mu);
+  if (g_nccl.h) return true;
+  const char* names[] = {getenv("FLIPB200_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+  void* h = nullptr;
+  for (const char* n : names) {
+    if (!n || !n[0]) continue;
+    h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (h) break;
+  }
+  if (!h) { fprintf(stderr, "flipb200: cannot dlopen libnccl.so.2: %s\n", dlerror()); return false; }
+#define SYM(field, name)                                                   \
+  *(void**)(&g_nccl.field) = dlsym(h, name);                               \
+  if (!g_nccl.field) { fprintf(stderr, "flipb200: %s missing in NCCL\n", name); return false; }
+  SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
+  SYM(Send, "ncclSend") SYM(Recv, "ncclRecv") SYM(AllReduce, "ncclAllReduce") SYM(Broadcast, "ncclBroadcast")
+  SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd") SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+  g_nccl.h = h;
+  return true;
+}
+
+// ---- LOCAL transport: ranks are threads of this process ----------------------------------------
+struct LocalGroup {
+  int world = 0, joined = 0;
+  std::mutex mu;
+  std::condition_variable cv;
+  int waiting = 0; unsigned phase = 0;
+  flipb200_ctx* member[MAXR] = {};
+  void* ptr[MAXR][8] = {};             // published device pointers of the current primitive
+  Grid grid[MAXR];
+  int64_t cnt[MAXR][4] = {};
+  unsigned char red[MAXR][128] = {};   // all-reduce staging (host)
+  void barrier() {
+    std::unique_lock<std::mutex> lk(mu);
+    unsigned ph = phase;
+    if (++waiting == world) { waiting = 0; ++phase; cv.notify_all(); }
+    else cv.wait(lk, [&] { return phase != ph; });
+  }
+};
+static std::map<int, LocalGroup*> g_groups;
+static std::mutex g_groups_mu;
+
+struct Comm {
+  int kind;            // 1 NCCL, 2 LOCAL
+  ncclComm_t nc;
+  LocalGroup* lg;
+};
+
+#define NC(call)                                                                                    \
+  do {                                                                                              \
+    ncclResult_t r__ = (call);                                                                      \
+    if (r__ != ncclSuccess) {                                                                       \
+      snprintf(c->errmsg, sizeof(c->errmsg), "%s:%d NCCL %s", __FILE__, __LINE__, g_nccl.GetErrorString(r__)); \
+      fprintf(stderr, "flipb200: %s\n", c->errmsg);                                                 \
+      return FLIPB200_ERR_COMM;                                                                     \
+    }                                                                                               \
+  } while (0)
+
+extern "C" {
+
+int flipb200_comm_unique_id(void* id128) {
+  if (!id128) return FLIPB200_ERR_ARG;
+  if (!nccl_load()) return FLIPB200_ERR_COMM;
+  ncclUniqueId id;
+  if (g_nccl.GetUniqueId(&id) != ncclSuccess) return FLIPB200_ERR_COMM;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  memcpy(id128, &id, 128);
+  return FLIPB200_OK;
+}
+
+int flipb200_comm_init_nccl(flipb200_ctx* c, const void* id128) {
+  if (!c || !id128) return FLIPB200_ERR_ARG;
+  if (c->world == 1) return FLIPB200_OK;
+  if (c->comm) return FLIPB200_ERR_STATE;
+  if (!nccl_load()) return FLIPB200_ERR_COMM;
+  CK(cudaSetDevice(c->device));
+  ncclUniqueId id; memcpy(&id, id128, 128);
+  Comm* cm = (Comm*)calloc(1, sizeof(Comm));
+  cm->kind = 1;
+  ncclResult_t r = g_nccl.CommInitRank(&cm->nc, c->world, id, c->rank);
+  if (r != ncclSuccess) {
+    fprintf(stderr, "flipb200: ncclCommInitRank: %s\n", g_nccl.GetErrorString(r));
+    free(cm);
+    return FLIPB200_ERR_COMM;
+  }
+  c->comm = cm;
+  return FLIPB200_OK;
+}
+
+int flipb200_comm_init_local(flipb200_ctx* c, int group_id) {
+  if (!c) return FLIPB200_ERR_ARG;
+  if (c->world == 1) return FLIPB200_OK;
+  if (c->comm || c->world > MAXR) return FLIPB200_ERR_STATE;
+  std::lock_guard<std::mutex> lk(g_groups_mu);
+  LocalGroup*& g = g_groups[group_id];
+  if (!g) { g = new LocalGroup(); g->world = c->world; }
+  if (g->world != c->world || g->member[c->rank]) return FLIPB200_ERR_ARG;
+  g->member[c->rank] = c; g->joined++;
+  Comm* cm = (Comm*)calloc(1, sizeof(Comm));
+  cm->kind = 2; cm->lg = g;
+  c->comm = cm;
+  return FLIPB200_OK;
+}
+
+}  // extern "C"
+
+void fb_comm_free(flipb200_ctx* c) {
+  if (!c->comm) return;
+  if (c->comm->kind == 1 && g_nccl.h) g_nccl.CommDestroy(c->comm->nc);
+  if (c->comm->kind == 2) {
+    std::lock_guard<std::mutex> lk(g_groups_mu);
+    LocalGroup* g = c->comm->lg;
+    g->member[c->rank] = nullptr;
+    if (--g->joined == 0) {
+      for (auto it = g_groups.begin(); it != g_groups.end(); ++it)
+        if (it->second == g) { g_groups.erase(it); break; }
+      delete g;
+    }
+  }
+  free(c->comm);
+  c->comm = nullptr;
+}
+
+static inline bool comm_missing(flipb200_ctx* c) {
+  if (c->comm) return false;
+  snprintf(c->errmsg, sizeof(c->errmsg), "slab context used before flipb200_comm_init_*");
+  fprintf(stderr, "flipb200: %s\n", c->errmsg);
+  return true;
+}
+
+int fb_comm_barrier(flipb200_ctx* c) {
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  CK(cudaStreamSynchronize(c->stream));
+  if (c->comm->kind == 2) c->comm->lg->barrier();
+  return 0;
+}
+
+// ---- halo fill ---------------------------------------------------------------------------------
+int fb_halo_fill(flipb200_ctx* c, const Grid& g, void* base, size_t elem, int nlo, int nhi) {
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  const bool up = c->rank + 1 < c->world, dn = c->rank > 0;
+  const size_t pb = (size_t)g.plane * elem;
+  char* b = (char*)base;
+  if (c->comm->kind == 1) {
+    ncclComm_t nc = c->comm->nc;
+    NC(g_nccl.GroupStart());
+    if (up) {
+      if (nlo) NC(g_nccl.Send(b + (size_t)(g.k1 - nlo) * pb, nlo * pb, ncclChar, c->rank + 1, nc, c->stream));
+      if (nhi) NC(g_nccl.Recv(b + (size_t)g.k1 * pb, nhi * pb, ncclChar, c->rank + 1, nc, c->stream));
+    }
+    if (dn) {
+      if (nhi) NC(g_nccl.Send(b + (size_t)g.k0 * pb, nhi * pb, ncclChar, c->rank - 1, nc, c->stream));
+      if (nlo) NC(g_nccl.Recv(b + (size_t)(g.k0 - nlo) * pb, nlo * pb, ncclChar, c->rank - 1, nc, c->stream));
+    }
+    NC(g_nccl.GroupEnd());
+    return 0;
+  }
+  LocalGroup* lg = c->comm->lg;
+  lg->ptr[c->rank][0] = base; lg->grid[c->rank] = g;
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  if (dn && nlo) {
+    const Grid& pg = lg->grid[c->rank - 1];
+    CK(cudaMemcpyAsync(b + (size_t)(g.k0 - nlo) * pb, (char*)lg->ptr[c->rank - 1][0] + (size_t)(pg.k1 - nlo) * pb,
+                       nlo * pb, cudaMemcpyDefault, c->stream));
+  }
+  if (up && nhi) {
+    const Grid& pg = lg->grid[c->rank + 1];
+    CK(cudaMemcpyAsync(b + (size_t)g.k1 * pb, (char*)lg->ptr[c->rank + 1][0] + (size_t)pg.k0 * pb, nhi * pb,
+                       cudaMemcpyDefault, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  return 0;
+}
+
+// ---- P2G ghost sum -------------------------------------------------------------------------------
+__global__ void k_add_planes(int n, const double* __restrict__ src, double* __restrict__ d0, double* __restrict__ d1,
+                             double* __restrict__ d2, double* __restrict__ d3) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  d0[i] += src[i]; d1[i] += src[n + i]; d2[i] += src[2 * n + i]; d3[i] += src[3 * n + i];
+}
+
+int fb_halo_sum_up(flipb200_ctx* c, double* const arr[4]) {
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  const Grid& g = c->g;
+  const bool up = c->rank + 1 < c->world, dn = c->rank > 0;
+  const size_t pn = (size_t)g.plane, pb = pn * sizeof(double);
+  if (c->comm->kind == 1) {
+    ncclComm_t nc = c->comm->nc;
+    NC(g_nccl.GroupStart());
+    for (int a = 0; a < 4; ++a) {
+      if (up) NC(g_nccl.Send(arr[a] + (size_t)g.k1 * pn, pn, ncclDouble, c->rank + 1, nc, c->stream));
+      if (dn) NC(g_nccl.Recv(c->halo_tmp + a * pn, pn, ncclDouble, c->rank - 1, nc, c->stream));
+    }
+    NC(g_nccl.GroupEnd());
+  } else {
+    LocalGroup* lg = c->comm->lg;
+    for (int a = 0; a < 4; ++a) lg->ptr[c->rank][a] = arr[a];
+    lg->grid[c->rank] = g;
+    CK(cudaStreamSynchronize(c->stream));
+    lg->barrier();
+    if (dn) {
+      const Grid& pg = lg->grid[c->rank - 1];
+      for (int a = 0; a < 4; ++a)
+        CK(cudaMemcpyAsync(c->halo_tmp + a * pn, (double*)lg->ptr[c->rank - 1][a] + (size_t)pg.k1 * pn, pb,
+                           cudaMemcpyDefault, c->stream));
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    lg->barrier();
+  }
+  if (dn) {
+    const size_t o = (size_t)g.k0 * pn;
+    k_add_planes<<<cdiv(g.plane, 256), 256, 0, c->stream>>>(g.plane, c->halo_tmp, arr[0] + o, arr[1] + o, arr[2] + o,
+                                                            arr[3] + o);
+    CK_LAUNCH(); c->launches++;
+  }
+  return 0;
+}
+
+// ---- all-reduce (in place, device memory, <= 16 elements) ---------------------------------------
+template <typename T>
+static void host_reduce(T* out, const unsigned char (*in)[128], int world, int count, int op) {
+  for (int e = 0; e < count; ++e) {
+    T v = ((const T*)in[0])[e];
+    for (int r = 1; r < world; ++r) {
+      T w = ((const T*)in[r])[e];
+      v = op == FB_SUM ? v + w : (op == FB_MIN ? (w < v ? w : v) : (w > v ? w : v));
+    }
+    out[e] = v;
+  }
+}
+
+int fb_allreduce(flipb200_ctx* c, void* dev, int count, int type, int op) {
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  const size_t esz = type == FB_I32 ? 4 : 8;
+  if (count < 1 || count * esz > 128) return FLIPB200_ERR_ARG;
+  if (c->comm->kind == 1) {
+    const ncclDataType_t t = type == FB_F64 ? ncclDouble : (type == FB_I32 ? ncclInt32 : ncclUint64);
+    const ncclRedOp_t o = op == FB_SUM ? ncclSum : (op == FB_MIN ? ncclMin : ncclMax);
+    NC(g_nccl.AllReduce(dev, dev, (size_t)count, t, o, c->comm->nc, c->stream));
+    return 0;
+  }
+  LocalGroup* lg = c->comm->lg;
+  CK(cudaMemcpyAsync(lg->red[c->rank], dev, count * esz, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  unsigned char out[128];
+  if (type == FB_F64) host_reduce<double>((double*)out, lg->red, c->world, count, op);
+  else if (type == FB_I32) host_reduce<int32_t>((int32_t*)out, lg->red, c->world, count, op);
+  else host_reduce<unsigned long long>((unsigned long long*)out, lg->red, c->world, count, op);
+  CK(cudaMemcpyAsync(dev, out, count * esz, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  return 0;
+}
+
+// ---- all-gather of the owned planes of a replicated grid ----------------------------------------
+int fb_allgather_planes(flipb200_ctx* c, const Grid& gg, void* base, size_t elem, const int* zs) {
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  const size_t pb = (size_t)gg.plane * elem;
+  char* b = (char*)base;
+  if (c->comm->kind == 1) {
+    NC(g_nccl.GroupStart());
+    for (int r = 0; r < c->world; ++r) {
+      const size_t n = (size_t)(zs[r + 1] - zs[r]) * pb;
+      if (n) NC(g_nccl.Broadcast(b + (size_t)zs[r] * pb, b + (size_t)zs[r] * pb, n, ncclChar, r, c->comm->nc, c->stream));
+    }
+    NC(g_nccl.GroupEnd());
+    return 0;
+  }
+  LocalGroup* lg = c->comm->lg;
+  lg->ptr[c->rank][0] = base;
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  for (int r = 0; r < c->world; ++r) {
+    const size_t n = (size_t)(zs[r + 1] - zs[r]) * pb;
+    if (r == c->rank || !n) continue;
+    CK(cudaMemcpyAsync(b + (size_t)zs[r] * pb, (char*)lg->ptr[r][0] + (size_t)zs[r] * pb, n, cudaMemcpyDefault, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  return 0;
+}
+
+// ---- particle migration --------------------------------------------------------------------------
+// index 0 = the lower neighbour (rank-1), 1 = the upper neighbour (rank+1)
+int fb_comm_exchange_counts(flipb200_ctx* c, const int64_t send[2], int64_t recv[2]) {
+  recv[0] = recv[1] = 0;
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  const bool up = c->rank + 1 < c->world, dn = c->rank > 0;
+  if (c->comm->kind == 1) {
+    // staged through DevScalars::part (idle outside the PCG): [0..1] send, [2..3] receive
+    double h[4] = {(double)send[0], (double)send[1], 0.0, 0.0};
+    CK(cudaMemcpyAsync(c->ds->part, h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
+    ncclComm_t nc = c->comm->nc;
+    NC(g_nccl.GroupStart());
+    if (dn) { NC(g_nccl.Send(&c->ds->part[0], 1, ncclDouble, c->rank - 1, nc, c->stream));
+              NC(g_nccl.Recv(&c->ds->part[2], 1, ncclDouble, c->rank - 1, nc, c->stream)); }
+    if (up) { NC(g_nccl.Send(&c->ds->part[1], 1, ncclDouble, c->rank + 1, nc, c->stream));
+              NC(g_nccl.Recv(&c->ds->part[3], 1, ncclDouble, c->rank + 1, nc, c->stream)); }
+    NC(g_nccl.GroupEnd());
+    CK(cudaMemcpyAsync(h, c->ds->part, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    recv[0] = (int64_t)h[2]; recv[1] = (int64_t)h[3];
+    CK(cudaMemsetAsync(c->ds->part, 0, sizeof(h), c->stream));
+    return 0;
+  }
+  LocalGroup* lg = c->comm->lg;
+  lg->cnt[c->rank][0] = send[0]; lg->cnt[c->rank][1] = send[1];
+  lg->barrier();
+  if (dn) recv[0] = lg->cnt[c->rank - 1][1];
+  if (up) recv[1] = lg->cnt[c->rank + 1][0];
+  lg->barrier();
+  return 0;
+}
+
+int fb_comm_exchange_particles(flipb200_ctx* c, int narr, void* const src[], void* const dst[], const size_t elem[],
+                               const int64_t send_off[2], const int64_t send_n[2],
+                               const int64_t recv_off[2], const int64_t recv_n[2]) {
+  if (c->world == 1) return 0;
+  if (comm_missing(c)) return FLIPB200_ERR_COMM;
+  if (narr > 8) return FLIPB200_ERR_ARG;
+  const bool up = c->rank + 1 < c->world, dn = c->rank > 0;
+  if (c->comm->kind == 1) {
+    ncclComm_t nc = c->comm->nc;
+    NC(g_nccl.GroupStart());
+    for (int a = 0; a < narr; ++a) {
+      char* s = (char*)src[a]; char* d = (char*)dst[a];
+      if (dn && send_n[0]) NC(g_nccl.Send(s + send_off[0] * elem[a], send_n[0] * elem[a], ncclChar, c->rank - 1, nc, c->stream));
+      if (up && send_n[1]) NC(g_nccl.Send(s + send_off[1] * elem[a], send_n[1] * elem[a], ncclChar, c->rank + 1, nc, c->stream));
+      if (dn && recv_n[0]) NC(g_nccl.Recv(d + recv_off[0] * elem[a], recv_n[0] * elem[a], ncclChar, c->rank - 1, nc, c->stream));
+      if (up && recv_n[1]) NC(g_nccl.Recv(d + recv_off[1] * elem[a], recv_n[1] * elem[a], ncclChar, c->rank + 1, nc, c->stream));
+    }
+    NC(g_nccl.GroupEnd());
+    return 0;
+  }
+  LocalGroup* lg = c->comm->lg;
+  for (int a = 0; a < narr; ++a) lg->ptr[c->rank][a] = src[a];
+  lg->cnt[c->rank][2] = send_off[0]; lg->cnt[c->rank][3] = send_off[1];
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  for (int a = 0; a < narr; ++a) {
+    char* d = (char*)dst[a];
+    if (dn && recv_n[0])   // the lower neighbour's "up" bucket
+      CK(cudaMemcpyAsync(d + recv_off[0] * elem[a], (char*)lg->ptr[c->rank - 1][a] + lg->cnt[c->rank - 1][3] * elem[a],
+                         recv_n[0] * elem[a], cudaMemcpyDefault, c->stream));
+    if (up && recv_n[1])   // the upper neighbour's "down" bucket
+      CK(cudaMemcpyAsync(d + recv_off[1] * elem[a], (char*)lg->ptr[c->rank + 1][a] + lg->cnt[c->rank + 1][2] * elem[a],
+                         recv_n[1] * elem[a], cudaMemcpyDefault, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  lg->barrier();
+  return 0;
+}
+
+bool fb_comm_capturable(flipb200_ctx* c) { return c->world == 1 || (c->comm && c->comm->kind == 1); }

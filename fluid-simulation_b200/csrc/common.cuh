@@ -12,26 +12,37 @@
 // `px` (multiple of 32 elements => every row of an 8-byte array starts 256-byte aligned, rows of
 // the 1-byte flag array 32-byte aligned), then y, then z:  idx = (k*ny + j)*px + i.
 // z is the slowest index so that z-slabs and ghost planes are contiguous (multi-GPU split).
+//
+// Multi-GPU: the box is cut into z-slabs.  A rank's arrays hold its owned planes
+// [k0, k1) plus SLAB_GHOST ghost planes on either side (also past the ends of the global box,
+// where they are inert), so every kernel indexes a slab exactly like a whole grid; `kg0` is the
+// global z index of local plane 0 and `gnz` the global plane count.  Single GPU: kg0 = 0,
+// gnz = nz, k0 = 0, k1 = nz.
 // ---------------------------------------------------------------------------------------------
+#define SLAB_GHOST 2
 struct Grid {
-  int nx, ny, nz;   // nodes per axis
+  int nx, ny, nz;   // nodes per axis held in the local arrays (nz includes ghost planes)
   int px;           // row pitch in elements
-  int ox, oy, oz;   // index of reference coordinate 0
+  int ox, oy, oz;   // local index of reference coordinate 0
   int wall;         // solid shell thickness
   int plane;        // px*ny
   int total;        // px*ny*nz  (< 2^31, checked at create)
+  int kg0;          // global z index of local plane 0 (negative on rank 0 of a slab split)
+  int gnz;          // global number of z planes
+  int k0, k1;       // owned local planes [k0, k1)
 };
 
 __host__ __device__ __forceinline__ int gidx(const Grid& g, int i, int j, int k) {
   return (k * g.ny + j) * g.px + i;
 }
+// inside the GLOBAL box and inside the local arrays
 __host__ __device__ __forceinline__ bool in_box(const Grid& g, int i, int j, int k) {
-  return i >= 0 && j >= 0 && k >= 0 && i < g.nx && j < g.ny && k < g.nz;
+  return i >= 0 && j >= 0 && k >= 0 && i < g.nx && j < g.ny && k < g.nz && k + g.kg0 >= 0 && k + g.kg0 < g.gnz;
 }
 // isWithinBounds(c, 58) of fluid.cc:38-45 in index space: inside the solid shell
 __host__ __device__ __forceinline__ bool inside_shell(const Grid& g, int i, int j, int k) {
-  return i >= g.wall && j >= g.wall && k >= g.wall && i <= g.nx - 1 - g.wall &&
-         j <= g.ny - 1 - g.wall && k <= g.nz - 1 - g.wall;
+  return i >= g.wall && j >= g.wall && k + g.kg0 >= g.wall && i <= g.nx - 1 - g.wall &&
+         j <= g.ny - 1 - g.wall && k + g.kg0 <= g.gnz - 1 - g.wall;
 }
 
 // flag byte per node
@@ -61,7 +72,13 @@ struct DevScalars {
   int pcg_it;                        // current iteration (kernels launched from a CUDA graph read it here)
   int n_invalid;                     // particles whose support lies outside the box
   int pad;
+  // z-slab runs: kernels accumulate this rank's share of the current dot products here; after the
+  // all-reduce k_pcg_publish moves the sum into the ring slot (single GPU: straight into the ring)
+  double part[4];                    // [0] p.Ap  [1] r.z  [2] r.r
 };
+#define PART_PAP 0
+#define PART_RZ 1
+#define PART_RR 2
 
 struct Particles {
   double* a[6];      // px,py,pz,vx,vy,vz  (current, cell-sorted after sort)
@@ -76,8 +93,12 @@ struct Particles {
 // One level of the geometric multigrid hierarchy.  The V-cycle runs in fp32 (it only preconditions
 // the fp64 CG); level 0 shares the fine flags.
 struct MgLevel {
-  Grid g;
-  Box box;            // sweep box of this step at this level
+  Grid g;             // z-slab runs: a slab with ghost planes on the distributed levels, the whole grid on the replicated ones
+  bool dist;          // level is slab-distributed (needs halo fills); false: every rank holds the whole level
+  int zs[17];         // first global plane of every rank at this level (+ end)
+  Box gbox;           // sweep box over the whole domain (z in global planes of the level)
+  Box boxe;           // `box` extended into the ghost planes the global box covers (input range of the restriction)
+  Box box;            // sweep box of this step at this level (local planes)
   uint8_t* flags;     // same encoding as the fine flags (FB_*)
   uint8_t* nrm;       // 64 x (sum of the prolongation weights of the non-solid coarse donors), 27..64
   float *xa, *xb, *b; // solution ping-pong and right-hand side
@@ -85,9 +106,17 @@ struct MgLevel {
 };
 #define MG_MAX_LEVELS 12
 
+struct Comm;   // comm.cu: NCCL (one process per GPU) or in-process threaded ranks (tests)
+
 struct flipb200_ctx {
   flipb200_params P;
-  Grid g;
+  Grid g;                  // local grid (a z-slab with ghost planes when world > 1)
+  int rank, world;         // z-slab decomposition; world == 1: the whole box
+  int gz0, gz1;            // owned global planes [gz0, gz1)
+  int zsplit[17];          // global first plane of every rank (+ end), level 0
+  Comm* comm;
+  int slab_align;          // log2 of the alignment of the slab boundaries (mg.cu: distributed levels)
+  double* halo_tmp;        // 4 planes of doubles: receive buffer of the P2G ghost sum
   int device;
   int num_sms;
   cudaStream_t stream;
@@ -104,15 +133,18 @@ struct flipb200_ctx {
   double *x, *r, *pd, *Ap; // PCG vectors (x = pressure on the grid)
   MgLevel mg[MG_MAX_LEVELS];
   int mg_levels;           // 0 => hierarchy not allocated (precond != 1)
+  int mg_nd;               // levels [0, mg_nd) are slab-distributed, [mg_nd, mg_levels) replicated (0 when world == 1)
   // cell-sort arrays
   int32_t* cell_count;     // total+2 entries (last bucket: invalid particles)
   int32_t* cell_start;
   int32_t* scan_tmp;
   Particles pt;
+  int64_t n_sorted;        // particles [0, n_sorted) are in cell order; [n_sorted, n) arrived by migration this step
   bool sorted;             // particle arrays are in cell order and cell_start is valid
   DevScalars* ds;          // device
   DevScalars* hs;          // pinned host mirror
-  Box box;                 // sweep box of this step
+  Box box;                 // sweep box of this step (local planes, clipped to the owned range)
+  Box gbox;                // the same box over the whole domain (z in GLOBAL planes); == box when world == 1
   int n_fluid;
   int last_iters;          // iterations of the previous solve (sizes the first launch batch)
   bool mg_dirty;           // cell classes changed since the hierarchy was built (set by classify)
@@ -224,10 +256,32 @@ void fb_graph_invalidate(flipb200_ctx* c);
 int fb_mg_alloc(flipb200_ctx* c);
 void fb_mg_free(flipb200_ctx* c);
 int fb_mg_setup(flipb200_ctx* c, double dt);                    // per step: coarse flags + boxes
-int fb_mg_vcycle(flipb200_ctx* c, int it);                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it&3]
+int fb_mg_vcycle(flipb200_ctx* c, int it);
+void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg);     // part[] -> ring slots after an all-reduce                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it&3]
 int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 int fb_reserve_particles(flipb200_ctx* c, int64_t n);
-int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n);
+int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n, int64_t id0);
+int fb_sort_particles_ex(flipb200_ctx* c, int filter);
 int fb_download_particles(flipb200_ctx* c, double* const dst[6]);
+int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int world, flipb200_ctx** out);
+
+// ---- z-slab exchanges (comm.cu); every call is a no-op returning 0 when world == 1 -------------
+enum { FB_F64 = 0, FB_I32 = 1, FB_U64 = 2 };
+enum { FB_SUM = 0, FB_MIN = 1, FB_MAX = 2 };
+// fill my ghost planes from the neighbours' owned planes: nlo planes below k0, nhi planes above k1
+int fb_halo_fill(flipb200_ctx* c, const Grid& g, void* base, size_t elem, int nlo, int nhi);
+// P2G ghost sum: my upper ghost plane k1 of each array is added into the upper neighbour's plane k0
+int fb_halo_sum_up(flipb200_ctx* c, double* const arr[4]);
+int fb_allreduce(flipb200_ctx* c, void* dev, int count, int type, int op);
+// every rank ends with all owned planes of a REPLICATED (global) grid; zs[r] = first plane of rank r
+int fb_allgather_planes(flipb200_ctx* c, const Grid& gglobal, void* base, size_t elem, const int* zs);
+// exchange the particles of the trailing down / up buckets with the neighbours (particles.cu)
+int fb_comm_exchange_counts(flipb200_ctx* c, const int64_t send[2], int64_t recv[2]);
+int fb_comm_exchange_particles(flipb200_ctx* c, int narr, void* const src[], void* const dst[], const size_t elem[],
+                               const int64_t send_off[2], const int64_t send_n[2],
+                               const int64_t recv_off[2], const int64_t recv_n[2]);
+void fb_comm_free(flipb200_ctx* c);
+int fb_comm_barrier(flipb200_ctx* c);
+bool fb_comm_capturable(flipb200_ctx* c);   // exchanges can be recorded into a CUDA graph (NCCL or single GPU)
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }

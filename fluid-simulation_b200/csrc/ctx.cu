@@ -51,7 +51,7 @@ __global__ void k_static_flags(Grid g, const uint8_t* __restrict__ solid, uint8_
   int k = blockIdx.z;
   if (i >= g.px || j >= g.ny) return;
   int q = gidx(g, i, j, k);
-  if (i >= g.nx) { fl[q] = FB_SOLID | FB_SMASK; return; }   // pitch padding: inert
+  if (i >= g.nx || k + g.kg0 < 0 || k + g.kg0 >= g.gnz) { fl[q] = FB_SOLID | FB_SMASK; return; }   // pitch padding / ghost planes past the box: inert
   auto sol = [&](int a, int b, int cc) -> bool {
     return in_box(g, a, b, cc) && solid[gidx(g, a, b, cc)] != 0;   // out of box: VDB background => not solid
   };
@@ -101,13 +101,14 @@ int fb_reserve_particles(flipb200_ctx* c, int64_t n) {
   return 0;
 }
 
-__global__ void k_iota(uint32_t* __restrict__ id, int64_t first, int64_t n) {
+__global__ void k_iota(uint32_t* __restrict__ id, int64_t first, int64_t n, int64_t id0) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) id[first + i] = (uint32_t)(first + i);
+  if (i < n) id[first + i] = (uint32_t)(id0 + i);
 }
-int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n) {
+// ids of the particles [first, first+n) := id0, id0+1, ...
+int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n, int64_t id0) {
   if (!c->P.track_ids || n <= 0) return 0;
-  k_iota<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->pt.id, first, n);
+  k_iota<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->pt.id, first, n, id0);
   CK_LAUNCH(); c->launches++;
   return 0;
 }
@@ -129,7 +130,7 @@ int fb_download_particles(flipb200_ctx* c, double* const dst[6]) {
   Particles& pt = c->pt;
   if (pt.n == 0) return 0;
   double* const* src = pt.a;
-  if (c->P.track_ids) {
+  if (c->P.track_ids && c->world == 1) {   // slab contexts return local order; ids via flipb200_get_particle_ids
     k_unpermute<<<(unsigned)((pt.n + 255) / 256), 256, 0, c->stream>>>(pt.n, pt.id, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
                                                                        pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2],
                                                                        pt.b[3], pt.b[4], pt.b[5]);
@@ -141,9 +142,23 @@ int fb_download_particles(flipb200_ctx* c, double* const dst[6]) {
   return 0;
 }
 
-extern "C" {
+// z-slab split: first owned plane of every rank, aligned to 2^a so that `a` multigrid levels
+// coarsen without crossing a slab boundary (mg.cu); every slab keeps >= 2 planes on level a.
+static int slab_split(int nz, int world, int* zs, int* align_log2) {
+  if (world == 1) { zs[0] = 0; zs[1] = nz; *align_log2 = 0; return 0; }
+  const int base = nz / world;
+  if (base < 4) return -1;
+  int a = 0;
+  while (a < 6 && (4 << a) <= base) ++a;     // 2^(a+1) <= base
+  const int A = 1 << a;
+  for (int r = 0; r < world; ++r) zs[r] = (int)((int64_t)r * nz / world) & ~(A - 1);
+  zs[world] = nz;
+  for (int r = 0; r < world; ++r) if (zs[r + 1] - zs[r] < 2 * A) return -1;
+  *align_log2 = a;
+  return 0;
+}
 
-int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb200_ctx** out) {
+int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int world, flipb200_ctx** out) {
   if (!p || !out) return FLIPB200_ERR_ARG;
   *out = nullptr;
   if (p->nx < 2 * p->wall + 2 || p->ny < 2 * p->wall + 2 || p->nz < 2 * p->wall + 2) return FLIPB200_ERR_ARG;
@@ -152,6 +167,9 @@ int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb20
   flipb200_ctx* c = (flipb200_ctx*)calloc(1, sizeof(flipb200_ctx));
   if (!c) return FLIPB200_ERR_ARG;
   c->P = *p;
+  c->rank = rank; c->world = world;
+  if (slab_split(p->nz, world, c->zsplit, &c->slab_align)) { free(c); return FLIPB200_ERR_ARG; }
+  c->gz0 = c->zsplit[rank]; c->gz1 = c->zsplit[rank + 1];
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     fprintf(stderr, "flipb200: no CUDA device -- this library has no CPU fallback\n");
@@ -169,12 +187,14 @@ int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb20
   for (int e = 0; e < 8; ++e) CK(cudaEventCreate(&c->ev[e]));
 
   Grid& g = c->g;
-  g.nx = p->nx; g.ny = p->ny; g.nz = p->nz;
+  const int gh = world > 1 ? SLAB_GHOST : 0;
+  g.nx = p->nx; g.ny = p->ny; g.nz = (c->gz1 - c->gz0) + 2 * gh;
   g.px = (p->nx + 31) & ~31;
-  g.ox = p->ox; g.oy = p->oy; g.oz = p->oz;
+  g.kg0 = c->gz0 - gh; g.gnz = p->nz; g.k0 = gh; g.k1 = g.nz - gh;
+  g.ox = p->ox; g.oy = p->oy; g.oz = p->oz - g.kg0;
   g.wall = p->wall;
   int64_t plane = (int64_t)g.px * g.ny, total = plane * g.nz;
-  if (total >= (int64_t)2147483647 - 4) { flipb200_destroy(c); return FLIPB200_ERR_ARG; }
+  if (total >= (int64_t)2147483647 - 8) { flipb200_destroy(c); return FLIPB200_ERR_ARG; }
   g.plane = (int)plane; g.total = (int)total;
   const size_t T = (size_t)total;
 
@@ -183,29 +203,34 @@ int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb20
     if (alloc_n(c, &c->u[a], T) || alloc_n(c, &c->ub[a], T)) goto fail;
   if (alloc_n(c, &c->wacc, T) || alloc_n(c, &c->wf, T) || alloc_n(c, &c->bf[0], T) || alloc_n(c, &c->bf[1], T)) goto fail;
   if (alloc_n(c, &c->x, T) || alloc_n(c, &c->r, T) || alloc_n(c, &c->pd, T) || alloc_n(c, &c->Ap, T)) goto fail;
-  if (alloc_n(c, &c->cell_count, T + 2) || alloc_n(c, &c->cell_start, T + 2) || alloc_n(c, &c->scan_tmp, T / 2048 + 64)) goto fail;
+  if (alloc_n(c, &c->cell_count, T + 8) || alloc_n(c, &c->cell_start, T + 8) || alloc_n(c, &c->scan_tmp, T / 2048 + 64)) goto fail;
   if (alloc_n(c, &c->ds, 1)) goto fail;
+  if (world > 1 && alloc_n(c, &c->halo_tmp, 4 * (size_t)plane)) goto fail;
   if (fb_mg_alloc(c)) goto fail;
   if (cudaHostAlloc((void**)&c->hs, sizeof(DevScalars), cudaHostAllocDefault) != cudaSuccess) goto fail;
   memset(c->hs, 0, sizeof(DevScalars));
 
   {
-    // solid mask with the shell forced solid (fluid.cc:1264-1266), laid out with the row pitch
+    // solid mask with the shell forced solid (fluid.cc:1264-1266), laid out with the row pitch;
+    // ghost planes carry the neighbours' values (the mask is static, every rank has the whole box)
     std::vector<uint8_t> h(T, 0);
-    for (int k = 0; k < g.nz; ++k)
+    for (int k = 0; k < g.nz; ++k) {
+      const int kk = k + g.kg0;
+      if (kk < 0 || kk >= g.gnz) continue;
       for (int j = 0; j < g.ny; ++j)
         for (int i = 0; i < g.nx; ++i) {
           bool s = !inside_shell(g, i, j, k);
-          if (!s && solid_host) s = solid_host[((size_t)k * g.ny + j) * g.nx + i] != 0;
+          if (!s && solid_host) s = solid_host[((size_t)kk * g.ny + j) * g.nx + i] != 0;
           h[gidx(g, i, j, k)] = s ? 1 : 0;
         }
+    }
     if (cudaMemcpyAsync(c->solid, h.data(), T, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) goto fail;
     dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.nz);
     k_static_flags<<<grd, blk, 0, c->stream>>>(g, c->solid, c->flags_static);
     if (cudaMemcpyAsync(c->flags, c->flags_static, T, cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) goto fail;
     if (cudaStreamSynchronize(c->stream) != cudaSuccess) goto fail;
   }
-  c->box = Box{0, 0, 0, g.nx, g.ny, g.nz};
+  c->box = Box{0, 0, g.k0, g.nx, g.ny, g.k1};
   if (p->max_particles > 0 && fb_reserve_particles(c, p->max_particles)) goto fail;
   *out = c;
   return FLIPB200_OK;
@@ -215,12 +240,36 @@ fail:
   return FLIPB200_ERR_CUDA;
 }
 
+extern "C" {
+
+int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb200_ctx** out) {
+  return fb_create(p, solid_host, 0, 1, out);
+}
+
+// One z-slab of the box: rank `rank` of `world` owns the global planes reported by
+// flipb200_slab_range; params and solid_host describe the WHOLE box on every rank.  The context is
+// usable after flipb200_comm_init_nccl / _local.  New design: the reference is single-process.
+int flipb200_create_slab(const flipb200_params* p, const uint8_t* solid_host, int32_t rank, int32_t world,
+                         flipb200_ctx** out) {
+  if (world < 1 || world > 16 || rank < 0 || rank >= world) return FLIPB200_ERR_ARG;
+  return fb_create(p, solid_host, rank, world, out);
+}
+
+int flipb200_slab_range(flipb200_ctx* c, int32_t* z0, int32_t* z1) {
+  if (!c) return FLIPB200_ERR_ARG;
+  if (z0) *z0 = c->gz0;
+  if (z1) *z1 = c->gz1;
+  return FLIPB200_OK;
+}
+
 void flipb200_destroy(flipb200_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   fb_graph_invalidate(c);
   fb_mg_free(c);
+  fb_comm_free(c);
+  cudaFree(c->halo_tmp);
   cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static);
   for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }
   cudaFree(c->wacc); cudaFree(c->wf); cudaFree(c->bf[0]); cudaFree(c->bf[1]);
@@ -246,9 +295,26 @@ int flipb200_set_particles(flipb200_ctx* c, const double* px, const double* py, 
   for (int q = 0; q < 6; ++q)
     if (n) CK(cudaMemcpyAsync(c->pt.a[q], src[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   c->pt.n = n;
-  if (fb_init_ids(c, 0, n)) return FLIPB200_ERR_CUDA;
+  if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->sorted = false;
+  if (c->world > 1) {
+    // every rank is handed the whole scene and keeps the particles whose base plane it owns
+    int rc = fb_sort_particles_ex(c, 1);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  return FLIPB200_OK;
+}
+
+/* ids of the particles in the order flipb200_get_particles returns them on a slab context (index
+ * into the arrays given to flipb200_set_particles; needs params.track_ids) */
+int flipb200_get_particle_ids(flipb200_ctx* c, uint32_t* ids, int64_t cap) {
+  if (!c || !ids || cap < c->pt.n) return FLIPB200_ERR_ARG;
+  if (!c->P.track_ids) return FLIPB200_ERR_STATE;
+  CK(cudaSetDevice(c->device));
+  if (c->pt.n) CK(cudaMemcpyAsync(ids, c->pt.id, c->pt.n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
   return FLIPB200_OK;
 }
 
@@ -286,11 +352,11 @@ int flipb200_get_grid(flipb200_ctx* c, int which, void* host_out, size_t bytes) 
   if (!c || !host_out) return FLIPB200_ERR_ARG;
   void* d; size_t esz;
   if (grid_ptr(c, which, &d, &esz)) return FLIPB200_ERR_ARG;
-  const Grid& g = c->g;
-  if (bytes != (size_t)g.nx * g.ny * g.nz * esz) return FLIPB200_ERR_ARG;
+  const Grid& g = c->g;   // a slab returns its owned planes [gz0, gz1)
+  if (bytes != (size_t)g.nx * g.ny * (g.k1 - g.k0) * esz) return FLIPB200_ERR_ARG;
   CK(cudaSetDevice(c->device));
-  CK(cudaMemcpy2DAsync(host_out, g.nx * esz, d, g.px * esz, g.nx * esz, (size_t)g.ny * g.nz,
-                       cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpy2DAsync(host_out, g.nx * esz, (char*)d + (size_t)g.k0 * g.plane * esz, g.px * esz, g.nx * esz,
+                       (size_t)g.ny * (g.k1 - g.k0), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   return FLIPB200_OK;
 }
@@ -300,10 +366,10 @@ int flipb200_set_grid(flipb200_ctx* c, int which, const void* host_in, size_t by
   void* d; size_t esz;
   if (grid_ptr(c, which, &d, &esz)) return FLIPB200_ERR_ARG;
   const Grid& g = c->g;
-  if (bytes != (size_t)g.nx * g.ny * g.nz * esz) return FLIPB200_ERR_ARG;
+  if (bytes != (size_t)g.nx * g.ny * (g.k1 - g.k0) * esz) return FLIPB200_ERR_ARG;
   CK(cudaSetDevice(c->device));
-  CK(cudaMemcpy2DAsync(d, g.px * esz, host_in, g.nx * esz, g.nx * esz, (size_t)g.ny * g.nz,
-                       cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpy2DAsync((char*)d + (size_t)g.k0 * g.plane * esz, g.px * esz, host_in, g.nx * esz, g.nx * esz,
+                       (size_t)g.ny * (g.k1 - g.k0), cudaMemcpyHostToDevice, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   return FLIPB200_OK;
 }

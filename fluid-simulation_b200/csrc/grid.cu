@@ -22,7 +22,7 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
   __shared__ int sred[7][8];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = blockIdx.z;
+  int k = g.k0 + blockIdx.z;                      // owned planes
   int cnt = 0, mnx = 1 << 30, mny = 1 << 30, mnz = 1 << 30, mxx = -1, mxy = -1, mxz = -1;
   if (i < g.nx && j < g.ny) {
     int q = gidx(g, i, j, k);
@@ -42,7 +42,7 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
     bool fluid = !(f & FB_SOLID) && w > 0.0f && (f & FB_SMASK) != FB_SMASK;
     if (fluid) {
       f |= FB_FLUID; cnt = 1;
-      mnx = mxx = i; mny = mxy = j; mnz = mxz = k;
+      mnx = mxx = i; mny = mxy = j; mnz = mxz = k + g.kg0;   // bbox in GLOBAL planes
     }
     fl[q] = f;
   }
@@ -84,23 +84,42 @@ __global__ void k_reset_classify(DevScalars* ds) {
 int fb_classify(flipb200_ctx* c) {
   const Grid& g = c->g;
   k_reset_classify<<<1, 1, 0, c->stream>>>(c->ds);
-  dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.nz);
+  dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.k1 - g.k0);
   k_classify<<<grd, blk, 0, c->stream>>>(g, c->wacc, c->wf, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1],
                                          c->ub[2], c->x, c->flags_static, c->flags, c->ds);
   CK_LAUNCH(); c->launches += 2;
-  int rc = fb_fetch_scalars(c);
+  int rc;
+  if (c->world > 1) {
+    // global cell count and bounding box; ghost planes of what the neighbours' stencils read
+    if ((rc = fb_allreduce(c, &c->ds->n_fluid, 1, FB_I32, FB_SUM))) return rc;
+    if ((rc = fb_allreduce(c, &c->ds->bbox[0], 3, FB_I32, FB_MIN))) return rc;
+    if ((rc = fb_allreduce(c, &c->ds->bbox[3], 3, FB_I32, FB_MAX))) return rc;
+    if ((rc = fb_halo_fill(c, g, c->flags, 1, 1, 1))) return rc;
+    if ((rc = fb_halo_fill(c, g, c->u[2], sizeof(double), 0, 1))) return rc;    // u_z[c+e_z] of setRHS/setDiver/getVelocity
+    if ((rc = fb_halo_fill(c, g, c->ub[2], sizeof(double), 0, 1))) return rc;
+    // pressure ghosts start at 0 like the owned planes
+    CK(cudaMemsetAsync(c->x, 0, (size_t)g.k0 * g.plane * sizeof(double), c->stream));
+    CK(cudaMemsetAsync(c->x + (size_t)g.k1 * g.plane, 0, (size_t)(g.nz - g.k1) * g.plane * sizeof(double), c->stream));
+  }
+  rc = fb_fetch_scalars(c);
   if (rc) return rc;
   c->n_fluid = c->hs->n_fluid;
-  Box b;
+  Box b, gb;
   if (c->n_fluid == 0) {
-    b = Box{0, 0, 0, 0, 0, 0};
+    b = Box{0, 0, 0, 0, 0, 0}; gb = b;
   } else {
     const int* bb = c->hs->bbox;
-    b.x0 = max(0, bb[0] - 2) & ~31;            // rows stay sector/line aligned
-    b.y0 = max(0, bb[1] - 2); b.z0 = max(0, bb[2] - 2);
-    b.x1 = min(g.nx, bb[3] + 3); b.y1 = min(g.ny, bb[4] + 3); b.z1 = min(g.nz, bb[5] + 3);
+    gb.x0 = max(0, bb[0] - 2) & ~31;            // rows stay sector/line aligned
+    gb.y0 = max(0, bb[1] - 2); gb.z0 = max(0, bb[2] - 2);
+    gb.x1 = min(g.nx, bb[3] + 3); gb.y1 = min(g.ny, bb[4] + 3); gb.z1 = min(g.gnz, bb[5] + 3);
+    b = gb;
+    // this rank sweeps the part of the global box that lies in its owned planes (local indices);
+    // a rank the box does not reach sweeps one inert plane so that every rank launches the same kernels
+    b.z0 = max(gb.z0, c->gz0) - g.kg0; b.z1 = min(gb.z1, c->gz1) - g.kg0;
+    if (b.z1 <= b.z0) { b.z0 = g.k0; b.z1 = g.k0 + 1; }
   }
   c->box = b;
+  c->gbox = gb;
   c->bcur = 0;
   c->mg_dirty = true;
   return 0;
@@ -189,6 +208,8 @@ int fb_rhs_div(flipb200_ctx* c, double dt, int mode) {
     CK_LAUNCH(); c->launches++;
   }
   if (mode == 1) c->bcur ^= 1;
+  int rc = fb_allreduce(c, &c->ds->bnorm2, 3, FB_F64, FB_SUM);   // bnorm2, err_num, err_den are adjacent
+  if (rc) return rc;
   return fb_fetch_scalars(c);
 }
 
@@ -248,6 +269,8 @@ int fb_vel_update(flipb200_ctx* c, double dt_sub) {
   const Grid& g = c->g;
   const Box& b = c->box;
   if (!(b.x1 > b.x0 && b.y1 > b.y0 && b.z1 > b.z0)) return 0;
+  int rc = fb_halo_fill(c, g, c->x, sizeof(double), 1, 0);             // p of the cell below my first plane
+  if (rc) return rc;
   int tiles_x = cdiv(b.x1 - b.x0, 32), tiles_y = cdiv(b.y1 - b.y0, 8);
   int nitems = tiles_x * tiles_y * (b.z1 - b.z0);
   int grid = min(nitems, c->num_sms * 8);
@@ -256,7 +279,7 @@ int fb_vel_update(flipb200_ctx* c, double dt_sub) {
                                                        c->u[1], c->u[2], scale, c->P.gx * dt_sub, c->P.gy * dt_sub,
                                                        c->P.gz * dt_sub);   // g = gravity*dt, :638
   CK_LAUNCH(); c->launches++;
-  return 0;
+  return fb_halo_fill(c, g, c->u[2], sizeof(double), 0, 1);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -270,7 +293,7 @@ k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u
              double* __restrict__ d0, double* __restrict__ d1, double* __restrict__ d2) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = blockIdx.z;
+  int k = g.k0 + blockIdx.z;                      // owned planes
   if (i >= g.px || j >= g.ny) return;
   int q = gidx(g, i, j, k);
   double a = 0.0, b = 0.0, cc = 0.0;
@@ -284,9 +307,12 @@ k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u
 
 int fb_cell_delta(flipb200_ctx* c) {
   const Grid& g = c->g;
-  dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.nz);
+  dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.k1 - g.k0);
   k_cell_delta<<<grd, blk, 0, c->stream>>>(g, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->r, c->pd,
                                            c->Ap);
   CK_LAUNCH(); c->launches++;
+  // particles of my top base plane read the deltas of plane k1
+  double* dc[3] = {c->r, c->pd, c->Ap};
+  for (int a = 0; a < 3; ++a) { int rc = fb_halo_fill(c, g, dc[a], sizeof(double), 0, 1); if (rc) return rc; }
   return 0;
 }

@@ -28,12 +28,16 @@
 #define MG_COARSE_SWEEPS 40
 #define MG_COARSEST_CELLS 4096
 
+#define MG_REPLICATED_CELLS (1 << 18)   // z-slab runs: levels with at most this many cells are solved on every rank
+
+// dimensions of the whole level below `f` (f: whole-domain dimensions of the finer level)
 static void mg_level_dims(const Grid& f, Grid* c) {
-  c->nx = (f.nx + 1) / 2; c->ny = (f.ny + 1) / 2; c->nz = (f.nz + 1) / 2;
+  c->nx = (f.nx + 1) / 2; c->ny = (f.ny + 1) / 2; c->nz = (f.gnz + 1) / 2;
   c->px = (c->nx + 31) & ~31;
   c->ox = c->oy = c->oz = 0; c->wall = 0;
   c->plane = c->px * c->ny;
   c->total = c->plane * c->nz;
+  c->kg0 = 0; c->gnz = c->nz; c->k0 = 0; c->k1 = c->nz;
 }
 
 static int mg_alloc_level(flipb200_ctx* c, MgLevel& L, bool own_flags) {
@@ -57,10 +61,10 @@ __global__ void k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl
                               float* __restrict__ xout, const DevScalars* __restrict__ ds);
 
 int fb_mg_alloc(flipb200_ctx* c) {
-  c->mg_levels = 0;
+  c->mg_levels = 0; c->mg_nd = 0;
   if (c->P.precond != 1) return 0;
-  // count levels first: a grid that is already "coarsest" keeps the Jacobi preconditioner
-  Grid f = c->g;
+  // count levels first (whole-domain dimensions): a grid that is already "coarsest" keeps the Jacobi preconditioner
+  Grid f = c->g; f.nz = f.gnz;
   int nl = 1;
   Grid dims[MG_MAX_LEVELS]; dims[0] = f;
   while (nl < MG_MAX_LEVELS) {
@@ -70,14 +74,34 @@ int fb_mg_alloc(flipb200_ctx* c) {
     ++nl;
   }
   if (nl < 2) return 0;
-  c->mg[0].g = c->g; c->mg[0].flags = c->flags;
-  if (mg_alloc_level(c, c->mg[0], false)) return FLIPB200_ERR_CUDA;
-  for (int l = 1; l < nl; ++l) {
-    c->mg[l].g = dims[l];
-    if (mg_alloc_level(c, c->mg[l], true)) return FLIPB200_ERR_CUDA;
+  // z-slab runs: how many levels stay distributed.  Slab boundaries are multiples of 2^slab_align
+  // and level nd is written plane-aligned too, so nd <= slab_align; the first level small enough
+  // to replicate ends the distributed part.
+  int nd = 0;
+  if (c->world > 1) {
+    nd = 1;
+    while (nd < c->slab_align && nd < nl - 1 && (int64_t)dims[nd].nx * dims[nd].ny * dims[nd].nz > MG_REPLICATED_CELLS) ++nd;
+    const char* e = getenv("FLIPB200_MG_ND");
+    if (e && e[0]) { int v = atoi(e); nd = max(1, min(v, min(c->slab_align, nl - 1))); }
+    if (c->slab_align < 1) return FLIPB200_ERR_ARG;
+  }
+  for (int l = 0; l < nl; ++l) {
+    MgLevel& L = c->mg[l];
+    L.dist = l < nd;
+    for (int r = 0; r < c->world; ++r) L.zs[r] = c->zsplit[r] >> l;
+    L.zs[c->world] = dims[l].nz;
+    if (l == 0) { L.g = c->g; L.flags = c->flags; }
+    else if (L.dist) {
+      Grid g = dims[l];
+      const int own = L.zs[c->rank + 1] - L.zs[c->rank];
+      g.gnz = dims[l].nz; g.nz = own + 2 * SLAB_GHOST; g.kg0 = L.zs[c->rank] - SLAB_GHOST;
+      g.k0 = SLAB_GHOST; g.k1 = SLAB_GHOST + own; g.total = g.plane * g.nz;
+      L.g = g;
+    } else L.g = dims[l];
+    if (mg_alloc_level(c, L, l > 0)) return FLIPB200_ERR_CUDA;
   }
   CK(cudaFuncSetAttribute(k_mg_coarsest, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-  c->mg_levels = nl;
+  c->mg_levels = nl; c->mg_nd = nd;
   return 0;
 }
 
@@ -91,18 +115,20 @@ void fb_mg_free(flipb200_ctx* c) {
 }
 
 // ---- per-step hierarchy: coarse cell types, solid-neighbour masks, prolongation normalisers ----
-__global__ void k_mg_coarsen(Grid gf, Grid gc, const uint8_t* __restrict__ ff, uint8_t* __restrict__ fc) {
+// Sweeps the coarse planes [K0, K0 + gridDim.z) (local indices of gc).  Slab runs: the children of an
+// owned coarse plane are owned fine planes (slab boundaries are aligned, ctx.cu slab_split).
+__global__ void k_mg_coarsen(Grid gf, Grid gc, int K0, const uint8_t* __restrict__ ff, uint8_t* __restrict__ fc) {
   int I = blockIdx.x * blockDim.x + threadIdx.x;
   int J = blockIdx.y * blockDim.y + threadIdx.y;
-  int K = blockIdx.z;
+  int K = K0 + blockIdx.z;
   if (I >= gc.px || J >= gc.ny) return;
   int q = gidx(gc, I, J, K);
   if (I >= gc.nx) { fc[q] = FB_SOLID; return; }
   bool any_air = false, any_fluid = false;
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
-    int i = 2 * I + (m & 1), j = 2 * J + ((m >> 1) & 1), k = 2 * K + (m >> 2);
-    if (i < gf.nx && j < gf.ny && k < gf.nz) {
+    int i = 2 * I + (m & 1), j = 2 * J + ((m >> 1) & 1), k = 2 * (K + gc.kg0) + (m >> 2) - gf.kg0;
+    if (i < gf.nx && j < gf.ny && k + gf.kg0 < gf.gnz) {
       uint8_t f = ff[gidx(gf, i, j, k)];
       if (f & FB_FLUID) any_fluid = true;
       else if (!(f & FB_SOLID)) any_air = true;
@@ -111,10 +137,10 @@ __global__ void k_mg_coarsen(Grid gf, Grid gc, const uint8_t* __restrict__ ff, u
   fc[q] = any_air ? 0 : (any_fluid ? FB_FLUID : FB_SOLID);
 }
 
-__global__ void k_mg_nbrmask(Grid g, uint8_t* __restrict__ fl) {
+__global__ void k_mg_nbrmask(Grid g, int K0, uint8_t* __restrict__ fl) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = blockIdx.z;
+  int k = K0 + blockIdx.z;
   if (i >= g.nx || j >= g.ny) return;
   int q = gidx(g, i, j, k);
   auto sol = [&](int a, int b, int cc) -> bool {
@@ -144,8 +170,9 @@ __global__ void k_mg_norm(Grid gf, Box box, Grid gc, const uint8_t* __restrict__
   int n64 = 64;
   if (ff[q] & FB_FLUID) {
     n64 = 0;
-    int I = i >> 1, J = j >> 1, K = k >> 1;
-    int sx = (i & 1) ? 1 : -1, sy = (j & 1) ? 1 : -1, sz = (k & 1) ? 1 : -1;
+    const int kg = k + gf.kg0;                       // global fine plane
+    int I = i >> 1, J = j >> 1, K = (kg >> 1) - gc.kg0;
+    int sx = (i & 1) ? 1 : -1, sy = (j & 1) ? 1 : -1, sz = (kg & 1) ? 1 : -1;
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       int ci = I + ((m & 1) ? sx : 0), cj = J + ((m & 2) ? sy : 0), ck = K + ((m & 4) ? sz : 0);
@@ -158,28 +185,54 @@ __global__ void k_mg_norm(Grid gf, Box box, Grid gc, const uint8_t* __restrict__
   nrm[q] = (uint8_t)n64;
 }
 
+// local sweep boxes of a level from its whole-domain box
+static void mg_local_boxes(const flipb200_ctx* c, MgLevel& L) {
+  const Box& gb = L.gbox;
+  L.box = gb; L.boxe = gb;
+  if (!L.dist || !(gb.x1 > gb.x0)) return;
+  const int z0 = L.zs[c->rank], z1 = L.zs[c->rank + 1], kg0 = L.g.kg0;
+  L.box.z0 = max(gb.z0, z0) - kg0; L.box.z1 = min(gb.z1, z1) - kg0;
+  L.boxe.z0 = max(gb.z0, z0 - 1) - kg0; L.boxe.z1 = min(gb.z1, z1 + 1) - kg0;
+  if (L.box.z1 <= L.box.z0) {          // the box does not reach this slab: one inert plane (uniform launches)
+    L.box.z0 = L.g.k0; L.box.z1 = L.g.k0 + 1;
+    L.boxe = L.box;
+  }
+}
+
 int fb_mg_setup(flipb200_ctx* c, double dt) {
   if (c->mg_levels == 0) return 0;
   const double scale = dt / (c->P.rho * c->P.dx * c->P.dx);   // fluid.cc:306
+  c->mg[0].gbox = c->gbox;
   c->mg[0].box = c->box;
+  mg_local_boxes(c, c->mg[0]);
   c->mg[0].h2inv = scale;
   const dim3 blk(32, 8, 1);
+  int rc;
   for (int l = 1; l < c->mg_levels; ++l) {
     MgLevel& F = c->mg[l - 1];
     MgLevel& L = c->mg[l];
     L.h2inv = F.h2inv * 0.25;
     if (!c->mg_dirty) continue;                     // same cell classes as the previous solve of this step
-    dim3 grd(cdiv(L.g.px, 32), cdiv(L.g.ny, 8), L.g.nz);
-    k_mg_coarsen<<<grd, blk, 0, c->stream>>>(F.g, L.g, F.flags, L.flags);
-    k_mg_nbrmask<<<grd, blk, 0, c->stream>>>(L.g, L.flags);
-    c->launches += 2;
+    // cell types: this rank coarsens the planes whose children it owns ...
+    const int K0 = (F.dist ? L.zs[c->rank] : 0) - L.g.kg0;
+    const int nK = F.dist ? L.zs[c->rank + 1] - L.zs[c->rank] : L.g.gnz;
+    k_mg_coarsen<<<dim3(cdiv(L.g.px, 32), cdiv(L.g.ny, 8), nK), blk, 0, c->stream>>>(F.g, L.g, K0, F.flags, L.flags);
+    c->launches++;
+    // ... and gets the rest: ghost planes from the z neighbours, or every plane of a replicated level
+    if (L.dist) { if ((rc = fb_halo_fill(c, L.g, L.flags, 1, 1, 1))) return rc; }
+    else if (F.dist) { if ((rc = fb_allgather_planes(c, L.g, L.flags, 1, L.zs))) return rc; }
+    const int M0 = L.dist ? L.g.k0 : 0, nM = L.dist ? L.g.k1 - L.g.k0 : L.g.nz;
+    k_mg_nbrmask<<<dim3(cdiv(L.g.px, 32), cdiv(L.g.ny, 8), nM), blk, 0, c->stream>>>(L.g, M0, L.flags);
+    c->launches++;
     // coarse box: the parents of the fine box plus a 1-cell margin (prolongation donors)
     Box b;
-    b.x0 = max(0, F.box.x0 / 2 - 1) & ~1; b.y0 = max(0, F.box.y0 / 2 - 1); b.z0 = max(0, F.box.z0 / 2 - 1);
-    b.x1 = min(L.g.nx, (F.box.x1 + 1) / 2 + 1); b.y1 = min(L.g.ny, (F.box.y1 + 1) / 2 + 1);
-    b.z1 = min(L.g.nz, (F.box.z1 + 1) / 2 + 1);
-    if (!(F.box.x1 > F.box.x0)) b = Box{0, 0, 0, 0, 0, 0};
-    L.box = b;
+    const Box& fg = F.gbox;
+    b.x0 = max(0, fg.x0 / 2 - 1) & ~1; b.y0 = max(0, fg.y0 / 2 - 1); b.z0 = max(0, fg.z0 / 2 - 1);
+    b.x1 = min(L.g.nx, (fg.x1 + 1) / 2 + 1); b.y1 = min(L.g.ny, (fg.y1 + 1) / 2 + 1);
+    b.z1 = min(L.g.gnz, (fg.z1 + 1) / 2 + 1);
+    if (!(fg.x1 > fg.x0)) b = Box{0, 0, 0, 0, 0, 0};
+    L.gbox = b;
+    mg_local_boxes(c, L);
     const Box& fb = F.box;
     if (fb.x1 > fb.x0 && fb.y1 > fb.y0 && fb.z1 > fb.z0) {
       dim3 g2(cdiv(fb.x1 - fb.x0, 32), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
@@ -199,7 +252,7 @@ template <bool DOT>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
             const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
-            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg) {
+            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg, int dist) {
   __shared__ double sm[32];
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
@@ -231,7 +284,7 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
       const double rrp = ds->rr[(it + 3) & 3];
-      atomicAdd(&ds->rz[it & 3], acc[0] * (rrp > 0.0 ? sqrt(rrp) : 1.0));
+      atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[0] * (rrp > 0.0 ? sqrt(rrp) : 1.0));
     }
   }
 }
@@ -290,7 +343,7 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
 #pragma unroll
   for (int t = 0; t < 16; ++t) {
     const int oz = (t >> 2) - 1, oy = (t & 3) - 1;
-    const int kf = 2 * K + oz, jf = 2 * J + oy;
+    const int kf = 2 * (K + gc.kg0) + oz - gf.kg0, jf = 2 * J + oy;
     const bool rin = kf >= fbox.z0 && kf < fbox.z1 && jf >= fbox.y0 && jf < fbox.y1;
     const int kc = min(max(kf, fbox.z0), fbox.z1 - 1), jc = min(max(jf, fbox.y0), fbox.y1 - 1);
     const float* row = rn + gidx(gf, 0, jc, kc);
@@ -328,9 +381,10 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = fbox.z0 + blockIdx.z;
   if (j >= fbox.y1) return;                         // whole warp
-  const int I = i >> 1, J = j >> 1, K = k >> 1;
-  int J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((k & 1) ? 1 : -1);
-  const bool yin = J2 >= 0 && J2 < gc.ny, zin = K2 >= 0 && K2 < gc.nz;
+  const int kg = k + gf.kg0;                         // global fine plane
+  const int I = i >> 1, J = j >> 1, K = (kg >> 1) - gc.kg0;
+  int J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((kg & 1) ? 1 : -1);
+  const bool yin = J2 >= 0 && J2 < gc.ny, zin = K2 + gc.kg0 >= 0 && K2 + gc.kg0 < gc.gnz;
   J2 = yin ? J2 : J; K2 = zin ? K2 : K;
   const float wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
   const float* p00 = ec + gidx(gc, 0, J, K);
@@ -425,8 +479,13 @@ k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* _
 // ---- host orchestration ----------------------------------------------------------------------
 // z = M^-1 r.  Input: level-0 b (= float(r*sc)) and xa (= first sweep) written by the CG's K2/init;
 // output: level-0 xb (fp32, still scaled by sc); r.z is added to ds->rz[it & 3] in fp64.
+// z-slab runs: on the distributed levels every sweep is preceded by a one-plane halo
+// fill of its input; the first replicated level is assembled with an all-gather of the restricted
+// residual and solved redundantly by every rank; r.z is all-reduced at the end.
+#define HALO(L, arr) do { if ((L).dist) { int rc__ = fb_halo_fill(c, (L).g, (arr), sizeof(float), 1, 1); if (rc__) return rc__; } } while (0)
 int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const int nl = c->mg_levels;
+  const int dist = c->world > 1 ? 1 : 0;
   const dim3 pblk(32, 8, 1);
   Sweep S[MG_MAX_LEVELS];
   MgCoef mc[MG_MAX_LEVELS];
@@ -436,11 +495,24 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const dim3 tg = stencil_grid(S[l]);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it);
+    HALO(L, L.xa);
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist);
+    HALO(L, L.xb);
     k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
-    const Box& cb = C.box;
-    dim3 cg(cdiv(cb.x1 - cb.x0, 32), cdiv(cb.y1 - cb.y0, 8), cb.z1 - cb.z0);
-    k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.box, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds);
+    HALO(L, L.xa);
+    Box cb = C.box;
+    if (L.dist && !C.dist) {            // this rank restricts into the planes whose children it owns
+      cb.z0 = max(C.gbox.z0, C.zs[c->rank]); cb.z1 = min(C.gbox.z1, C.zs[c->rank + 1]);
+    }
+    if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0) {
+      dim3 cg(cdiv(cb.x1 - cb.x0, 32), cdiv(cb.y1 - cb.y0, 8), cb.z1 - cb.z0);
+      k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds);
+    }
+    if (L.dist && !C.dist) {
+      int rc = fb_allgather_planes(c, C.g, C.b, sizeof(float), C.zs);
+      if (!rc) rc = fb_allgather_planes(c, C.g, C.xa, sizeof(float), C.zs);
+      if (rc) return rc;
+    }
     c->launches += 3;
   }
   {
@@ -457,12 +529,20 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     const Box& fb = L.box;
     dim3 pg(cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
     const dim3 tg = stencil_grid(S[l]);
+    HALO(C, C.xb);
     k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it);
-    if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it);
-    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it);
+    HALO(L, L.xb);
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist);
+    HALO(L, L.xa);
+    if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist);
+    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist);
     c->launches += 3;
   }
   CK_LAUNCH();
+  if (dist) {
+    int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
+    if (rc) return rc;
+    fb_pcg_publish(c, 1 << PART_RZ, it);
+  }
   return 0;
 }

@@ -11,20 +11,25 @@
 // the trailing bucket `total`.  Counting sort: histogram (atomic, returns the in-cell rank),
 // exclusive scan, scatter.
 // ---------------------------------------------------------------------------------------------
+// z-slabs: a particle belongs to the rank that owns its base plane; base planes below / above the
+// owned range go to the buckets total+1 (lower neighbour) / total+2 (upper neighbour).
 __device__ __forceinline__ uint32_t particle_key(const Grid& g, double x, double y, double z) {
   // guard against NaN / huge coordinates before the int conversion
   if (!(fabs(x) < 1.0e9) || !(fabs(y) < 1.0e9) || !(fabs(z) < 1.0e9)) return (uint32_t)g.total;
   int bi = base_cell(x, g.ox), bj = base_cell(y, g.oy), bk = base_cell(z, g.oz);
-  if (bi < 0 || bj < 0 || bk < 0 || bi > g.nx - 2 || bj > g.ny - 2 || bk > g.nz - 2) return (uint32_t)g.total;
+  if (bi < 0 || bj < 0 || bk + g.kg0 < 0 || bi > g.nx - 2 || bj > g.ny - 2 || bk + g.kg0 > g.gnz - 2) return (uint32_t)g.total;
+  if (bk < g.k0) return (uint32_t)g.total + 1u;
+  if (bk >= g.k1) return (uint32_t)g.total + 2u;
   return (uint32_t)gidx(g, bi, bj, bk);
 }
 
 __global__ void k_key_count(Grid g, int64_t n, const double* __restrict__ px, const double* __restrict__ py,
                             const double* __restrict__ pz, uint32_t* __restrict__ key,
-                            uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
+                            uint32_t* __restrict__ rank, int32_t* __restrict__ count, int drop_outside) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t kx = particle_key(g, px[i], py[i], pz[i]);
+  if (drop_outside && kx == (uint32_t)g.total) kx = (uint32_t)g.total + 1u;   // slab filter: rank 0 keeps the strays
   key[i] = kx;
   rank[i] = (uint32_t)atomicAdd(&count[kx], 1);
 }
@@ -108,14 +113,17 @@ __global__ void k_reorder(int64_t n, const uint32_t* __restrict__ key, const uin
   if (id) id_b[d] = id[i];
 }
 
-int fb_sort_particles(flipb200_ctx* c) {
+// filter != 0 (slab contexts, after set_particles with the whole scene): keep what this rank owns,
+// drop the rest without any exchange.
+int fb_sort_particles_ex(flipb200_ctx* c, int filter) {
   const Grid& g = c->g;
   Particles& pt = c->pt;
-  const int nb = g.total + 1;                 // buckets incl. the trailing "outside" bucket
+  const int nb = g.total + 3;                 // cells + "outside the box" + "to lower rank" + "to upper rank"
   CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(nb + 1) * sizeof(int32_t), c->stream));
   if (pt.n > 0) {
     int blocks = (int)((pt.n + 255) / 256);
-    k_key_count<<<blocks, 256, 0, c->stream>>>(g, pt.n, pt.a[0], pt.a[1], pt.a[2], pt.key, pt.rank, c->cell_count);
+    k_key_count<<<blocks, 256, 0, c->stream>>>(g, pt.n, pt.a[0], pt.a[1], pt.a[2], pt.key, pt.rank, c->cell_count,
+                                               (filter && c->rank != 0) ? 1 : 0);
     CK_LAUNCH(); c->launches++;
   }
   // scan nb+1 entries so that cell_start[nb] == n
@@ -134,9 +142,38 @@ int fb_sort_particles(flipb200_ctx* c) {
     for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
     { uint32_t* t = pt.id; pt.id = pt.id_b; pt.id_b = t; }
   }
+  c->n_sorted = pt.n;
   c->sorted = true;
+  if (c->world == 1) return 0;
+  // ---- migration: the two trailing buckets leave, the neighbours' arrive as an
+  // unsorted tail [n_sorted, n) that this step's P2G / G2P handle particle by particle.
+  int32_t s3[3];
+  CK(cudaMemcpyAsync(s3, c->cell_start + g.total + 1, sizeof(s3), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  const int64_t n_keep = s3[0];
+  const int64_t send_n[2] = {s3[1] - s3[0], s3[2] - s3[1]};
+  c->n_sorted = n_keep;
+  if (filter) { pt.n = n_keep; return 0; }
+  int64_t recv_n[2];
+  int rc = fb_comm_exchange_counts(c, send_n, recv_n);
+  if (rc) return rc;
+  const int64_t nnew = n_keep + recv_n[0] + recv_n[1];
+  if (nnew >= (int64_t)2147483647) return FLIPB200_ERR_ARG;
+  if ((rc = fb_reserve_particles(c, nnew > pt.n ? nnew : pt.n))) return rc;
+  void* src[8]; void* dst[8]; size_t elem[8]; int na = 0;
+  for (int q = 0; q < 6; ++q) { src[na] = pt.a[q]; dst[na] = pt.b[q]; elem[na] = sizeof(double); ++na; }
+  if (c->P.track_ids) { src[na] = pt.id; dst[na] = pt.id_b; elem[na] = sizeof(uint32_t); ++na; }
+  const int64_t send_off[2] = {n_keep, n_keep + send_n[0]};
+  const int64_t recv_off[2] = {0, recv_n[0]};
+  if ((rc = fb_comm_exchange_particles(c, na, src, dst, elem, send_off, send_n, recv_off, recv_n))) return rc;
+  const int64_t nr = recv_n[0] + recv_n[1];
+  if (nr > 0)
+    for (int a = 0; a < na; ++a)
+      CK(cudaMemcpyAsync((char*)src[a] + n_keep * elem[a], dst[a], nr * elem[a], cudaMemcpyDeviceToDevice, c->stream));
+  pt.n = nnew;
   return 0;
 }
+int fb_sort_particles(flipb200_ctx* c) { return fb_sort_particles_ex(c, 0); }
 
 // ---------------------------------------------------------------------------------------------
 // P2G.  One thread per base cell: every particle of the cell touches the same 2x2x2 nodes, so
@@ -153,7 +190,7 @@ k_p2g_cell(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __
   int i = box.x0 + blockIdx.x * blockDim.x + threadIdx.x;
   int j = box.y0 + blockIdx.y * blockDim.y + threadIdx.y;
   int k = box.z0 + blockIdx.z;
-  if (i >= box.x1 || j >= box.y1 || i > g.nx - 2 || j > g.ny - 2 || k > g.nz - 2) return;
+  if (i >= box.x1 || j >= box.y1 || i > g.nx - 2 || j > g.ny - 2 || k + g.kg0 > g.gnz - 2) return;
   int q = gidx(g, i, j, k);
   int s = start[q], e = start[q + 1];
   if (s == e) return;
@@ -194,7 +231,7 @@ __global__ void k_p2g_particle(Grid g, int64_t n, const uint8_t* __restrict__ fl
   if (t >= n) return;
   double x = px[t], y = py[t], z = pz[t];
   uint32_t key = particle_key(g, x, y, z);
-  if (key == (uint32_t)g.total) return;
+  if (key >= (uint32_t)g.total) return;
   int q = (int)key;
   int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
   double a = vx[t], b = vy[t], cc = vz[t];
@@ -223,9 +260,9 @@ int fb_p2g(flipb200_ctx* c) {
   CK(cudaMemsetAsync(c->wacc, 0, T * sizeof(double), c->stream));
   for (int a = 0; a < 3; ++a) CK(cudaMemsetAsync(c->u[a], 0, T * sizeof(double), c->stream));
   Particles& pt = c->pt;
-  if (pt.n == 0) return 0;
   const char* mode = getenv("FLIPB200_P2G");
-  if (mode && mode[0] == 'p') {
+  if (mode && mode[0] == 'p' && c->world == 1) {
+    if (pt.n == 0) return 0;
     int blocks = (int)((pt.n + 127) / 128);
     k_p2g_particle<<<blocks, 128, 0, c->stream>>>(g, pt.n, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
                                                   pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
@@ -233,12 +270,23 @@ int fb_p2g(flipb200_ctx* c) {
     return 0;
   }
   if (!c->sorted) { int rc = fb_sort_particles(c); if (rc) return rc; }
-  Box b{0, 0, 0, g.nx - 1, g.ny - 1, g.nz - 1};
-  dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
-  k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                         pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
-  CK_LAUNCH(); c->launches++;
-  return 0;
+  if (c->n_sorted > 0) {
+    Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
+    dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
+    k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                           pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    CK_LAUNCH(); c->launches++;
+  }
+  if (pt.n > c->n_sorted) {   // particles that migrated in this step (unsorted tail)
+    const int64_t o = c->n_sorted, m = pt.n - o;
+    k_p2g_particle<<<(unsigned)((m + 127) / 128), 128, 0, c->stream>>>(g, m, c->flags_static, pt.a[0] + o, pt.a[1] + o,
+                                                                      pt.a[2] + o, pt.a[3] + o, pt.a[4] + o, pt.a[5] + o,
+                                                                      c->wacc, c->u[0], c->u[1], c->u[2]);
+    CK_LAUNCH(); c->launches++;
+  }
+  // nodes of plane k1 belong to the upper neighbour: add my contributions there
+  double* arr[4] = {c->wacc, c->u[0], c->u[1], c->u[2]};
+  return fb_halo_sum_up(c, arr);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -261,7 +309,7 @@ k_g2p(Grid g, int64_t n, const uint8_t* __restrict__ fl,
     double x = px[t], y = py[t], z = pz[t];
     double a = vx[t], b = vy[t], cc = vz[t];
     uint32_t key = particle_key(g, x, y, z);
-    if (key != (uint32_t)g.total) {
+    if (key < (uint32_t)g.total) {
       int q = (int)key;
       int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
       const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
@@ -306,10 +354,10 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
   __shared__ double red[4];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = blockIdx.z;
+  int k = g.k0 + blockIdx.z;
   double speed = 0.0;
   int s = 0, e = 0, q = 0;
-  if (i <= g.nx - 2 && j <= g.ny - 2 && k <= g.nz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
+  if (i <= g.nx - 2 && j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
   if (s < e) {
     double ddx[8], ddy[8], ddz[8];
 #pragma unroll
@@ -352,7 +400,7 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
 }
 
 // particles of the trailing "outside" bucket: no grid contact, but their speed counts (fluid.cc:982)
-__global__ void k_speed_tail(const int32_t* __restrict__ start, int total, int64_t n, const double* __restrict__ vx,
+__global__ void k_speed_tail(const int32_t* __restrict__ start, int total, int64_t n /* = n_sorted */, const double* __restrict__ vx,
                              const double* __restrict__ vy, const double* __restrict__ vz, DevScalars* __restrict__ ds) {
   double speed = 0.0;
   for (int64_t t = (int64_t)start[total] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n;
@@ -414,20 +462,31 @@ int fb_g2p_advect(flipb200_ctx* c) {
   int blocks = (int)((pt.n + 255) / 256);
   if (blocks == 0) blocks = 1;
   const char* mode = getenv("FLIPB200_G2P");
-  if (c->sorted && pt.n > 0 && !(mode && mode[0] == 'p')) {
-    dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.nz - 1);
-    k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                           c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
-    c->launches++;
-    // the trailing bucket (key == total) holds the particles outside the box (usually none)
-    k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, pt.n, pt.a[3], pt.a[4], pt.a[5], c->ds);
-    c->launches++;
+  if (c->sorted && !(mode && mode[0] == 'p' && c->world == 1)) {
+    if (c->n_sorted > 0) {
+      dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
+      k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                             c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+      c->launches++;
+      // the trailing bucket (key == total) holds the particles outside the box (usually none)
+      k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, c->n_sorted, pt.a[3], pt.a[4], pt.a[5], c->ds);
+      c->launches++;
+    }
+    if (pt.n > c->n_sorted) {   // migrated-in tail
+      const int64_t o = c->n_sorted, m = pt.n - o;
+      k_g2p<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(g, m, c->flags, pt.a[0] + o, pt.a[1] + o, pt.a[2] + o,
+                                                               pt.a[3] + o, pt.a[4] + o, pt.a[5] + o, c->r, c->pd, c->Ap, c->ds);
+      c->launches++;
+    }
   } else {
     k_g2p<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
                                          c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
     c->launches++;
   }
   CK_LAUNCH();
+  // maxSpeed is a global max (fluid.cc:976-991): every rank advects with the same dt
+  int rc = fb_allreduce(c, &c->ds->max_speed_bits, 1, FB_U64, FB_MAX);
+  if (rc) return rc;
   k_advect<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
                                           pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds);
   CK_LAUNCH(); c->launches++;
@@ -448,37 +507,44 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 __device__ __forceinline__ double u01(uint64_t h) {   // (0,1) open
   return ((double)(h >> 11) + 0.5) * (1.0 / 9007199254740992.0);
 }
-__global__ void k_seed_box(Grid g, int lx, int ly, int lz, int dxn, int dyn, int dzn, uint64_t seed, int64_t base,
-                           double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+// t0: index of the first (voxel, sub-cell) pair this launch seeds within the WHOLE box, so that a
+// z-slab rank draws exactly the jitters the single-GPU run draws for the same voxels.
+__global__ void k_seed_box(Grid g, int lx, int ly, int lz, int dxn, int dyn, int64_t t0, int64_t count, uint64_t seed,
+                           int64_t base, double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
                            double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t nvox = (int64_t)dxn * dyn * dzn;
-  if (t >= nvox * 8) return;
+  int64_t tl = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (tl >= count) return;
+  const int64_t t = t0 + tl;
   int64_t v = t >> 3; int sub = (int)(t & 7);
   int i = (int)(v % dxn), j = (int)((v / dxn) % dyn), k = (int)(v / ((int64_t)dxn * dyn));
   uint64_t h = splitmix64(seed ^ (uint64_t)t * 0xD1B54A32D192ED03ull);
   double jx = u01(h); h = splitmix64(h); double jy = u01(h); h = splitmix64(h); double jz = u01(h);
-  int64_t o = base + t;
+  int64_t o = base + tl;
   px[o] = (double)(lx + i - g.ox) - 0.5 + ((sub & 1) + jx) * 0.5;
   py[o] = (double)(ly + j - g.oy) - 0.5 + (((sub >> 1) & 1) + jy) * 0.5;
-  pz[o] = (double)(lz + k - g.oz) - 0.5 + (((sub >> 2) & 1) + jz) * 0.5;
+  pz[o] = (double)(lz + k - g.oz) - 0.5 + (((sub >> 2) & 1) + jz) * 0.5;   // lz, g.oz: local plane indices
   vx[o] = 0.0; vy[o] = 0.0; vz[o] = 0.0;
 }
 
+// lo/hi are GLOBAL voxel indices; a slab seeds the voxels of its owned planes (the first sort moves
+// the particles whose base plane belongs to a neighbour).
 int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed) {
   const Grid& g = c->g;
   int dxn = hi[0] - lo[0] + 1, dyn = hi[1] - lo[1] + 1, dzn = hi[2] - lo[2] + 1;
   if (dxn <= 0 || dyn <= 0 || dzn <= 0) return FLIPB200_ERR_ARG;
-  int64_t add = (int64_t)dxn * dyn * dzn * 8;
+  const int zl = lo[2] > c->gz0 ? lo[2] : c->gz0, zh = hi[2] < c->gz1 - 1 ? hi[2] : c->gz1 - 1;
+  if (zh < zl) return 0;
+  const int64_t per_plane = (int64_t)dxn * dyn * 8;
+  const int64_t t0 = (int64_t)(zl - lo[2]) * per_plane, add = (int64_t)(zh - zl + 1) * per_plane;
   int64_t base = c->pt.n;
   if (base + add >= (int64_t)2147483647) return FLIPB200_ERR_ARG;
   int rc = fb_reserve_particles(c, base + add);
   if (rc) return rc;
   int64_t blocks = (add + 255) / 256;
-  k_seed_box<<<(unsigned)blocks, 256, 0, c->stream>>>(g, lo[0], lo[1], lo[2], dxn, dyn, dzn, seed, base, c->pt.a[0],
-                                                      c->pt.a[1], c->pt.a[2], c->pt.a[3], c->pt.a[4], c->pt.a[5]);
+  k_seed_box<<<(unsigned)blocks, 256, 0, c->stream>>>(g, lo[0], lo[1], lo[2] - g.kg0, dxn, dyn, t0, add, seed, base,
+                                                      c->pt.a[0], c->pt.a[1], c->pt.a[2], c->pt.a[3], c->pt.a[4], c->pt.a[5]);
   CK_LAUNCH(); c->launches++;
-  if (fb_init_ids(c, base, add)) return FLIPB200_ERR_CUDA;
+  if (fb_init_ids(c, base, add, c->world > 1 ? t0 : base)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->pt.n = base + add;
   c->sorted = false;

@@ -27,6 +27,7 @@ __global__ void k_pcg_reset(DevScalars* ds, double bnorm2, double threshold, int
   // |r|^2 of "iteration -1" (= |b|^2): scale of the first preconditioner applications
   ds->rr[2] = bnorm2; ds->rr[3] = bnorm2;
   ds->pcg_done = 0; ds->pcg_iters = 0; ds->pcg_status = 0; ds->rr_final = 0.0; ds->pcg_it = 0;
+  for (int s = 0; s < 4; ++s) ds->part[s] = 0.0;
 }
 
 // x = 0, r = b;  Jacobi: p = M^-1 r, rz[3] = r.p   (Eigen ConjugateGradient.h:43,63,66 with x0 = 0)
@@ -35,7 +36,7 @@ template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
            const float* __restrict__ b, double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
-           float* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds) {
+           float* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds, int dist) {
   __shared__ double sm[32];
   STREAM_PROLOGUE(S)
   double acc[1] = {0.0};
@@ -59,14 +60,15 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   }
   if (MODE == 0) {
     block_sum<1>(acc, sm);
-    if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(&ds->rz[3], acc[0]);
+    if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[3], acc[0]);
   }
 }
 
 // K1: Ap = A p and p.Ap (STENCIL shape: z-march in registers, x neighbours by shuffle)
 __global__ void __launch_bounds__(32 * ST_BY)
 k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
-       const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit) {
+       const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit,
+       int dist) {
   __shared__ double sm[32];
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
@@ -87,7 +89,7 @@ k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, cons
     }
   }
   block_sum<1>(acc, sm);
-  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(&ds->pAp[it & 3], acc[0]);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_PAP] : &ds->pAp[it & 3], acc[0]);
 }
 
 // K2: alpha = rz_old / pAp;  x += alpha p;  r -= alpha Ap;  rr = |r|^2
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(32 * SW_BY)
 k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
             double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
             const double* __restrict__ Ap, float* __restrict__ b0, float* __restrict__ x1,
-            DevScalars* __restrict__ ds, int it_arg, int noexit) {
+            DevScalars* __restrict__ ds, int it_arg, int noexit, int dist) {
   __shared__ double sm[64];
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
@@ -135,8 +137,8 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
   }
   block_sum<2>(acc, sm);
   if (threadIdx.x == 0 && threadIdx.y == 0) {
-    if (acc[0] != 0.0) atomicAdd(&ds->rr[it & 3], acc[0]);
-    if (MODE == 0 && acc[1] != 0.0) atomicAdd(&ds->rz[it & 3], acc[1]);
+    if (acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RR] : &ds->rr[it & 3], acc[0]);
+    if (MODE == 0 && acc[1] != 0.0) atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[1]);
   }
 }
 
@@ -146,6 +148,20 @@ __global__ void k_pcg_check(DevScalars* __restrict__ ds, int it_arg) {
   const int it = pcg_iter(ds, it_arg);
   const double rr = ds->rr[it & 3];
   if (rr < ds->threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
+}
+
+// z-slab runs: after the all-reduce of ds->part[], move the global sums into the ring slot of this
+// iteration and clear the partials (it = -1 addresses slot 3, the "previous" slot of iteration 0).
+__global__ void k_pcg_publish(DevScalars* __restrict__ ds, int mask, int it_arg) {
+  const int it = pcg_iter(ds, it_arg);
+  const int s = it & 3;
+  if (mask & (1 << PART_PAP)) { ds->pAp[s] = ds->part[PART_PAP]; ds->part[PART_PAP] = 0.0; }
+  if (mask & (1 << PART_RZ)) { ds->rz[s] = ds->part[PART_RZ]; ds->part[PART_RZ] = 0.0; }
+  if (mask & (1 << PART_RR)) { ds->rr[s] = ds->part[PART_RR]; ds->part[PART_RR] = 0.0; }
+}
+void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg) {
+  k_pcg_publish<<<1, 1, 0, c->stream>>>(c->ds, mask, it_arg);
+  c->launches++;
 }
 
 // K3: beta = rz/rz_old (:84), p = z + beta p (:85).
@@ -214,19 +230,36 @@ void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
   cf->off = (double)(float)(-1 * scale);                          // :335
 }
 
-// one CG iteration on the stream (it_arg = explicit iteration or IT_DEV for graph replay)
+// one CG iteration on the stream (it_arg = explicit iteration or IT_DEV for graph replay).
+// z-slab runs add: a one-plane halo fill of the search direction before A.p and an all-reduce +
+// publish after every kernel that ends in a dot product.
 static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int it_arg, int noexit) {
   const dim3 sg = stream_grid(S), tg = stencil_grid(S);
   MgLevel& L0 = c->mg[0];
-  k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit);
+  const int dist = c->world > 1 ? 1 : 0;
+  int rc;
+  if ((rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1))) return rc;
+  k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist);
+  if (dist) {
+    if ((rc = fb_allreduce(c, &c->ds->part[PART_PAP], 1, FB_F64, FB_SUM))) return rc;
+    fb_pcg_publish(c, 1 << PART_PAP, it_arg);
+  }
   if (use_mg) {
-    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit);
+    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist);
+    if (dist) {
+      if ((rc = fb_allreduce(c, &c->ds->part[PART_RR], 1, FB_F64, FB_SUM))) return rc;
+      fb_pcg_publish(c, 1 << PART_RR, it_arg);
+    }
     if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg); c->launches++; }
-    int rc = fb_mg_vcycle(c, it_arg);
+    rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit);
   } else {
-    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit);
+    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit, dist);
+    if (dist) {
+      if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 2, FB_F64, FB_SUM))) return rc;   // r.z and r.r are adjacent
+      fb_pcg_publish(c, (1 << PART_RZ) | (1 << PART_RR), it_arg);
+    }
     k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, noexit);
   }
   k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, noexit);
@@ -249,10 +282,11 @@ static bool same_box(const Box& a, const Box& b) {
 static bool get_iteration_graph(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, double dt, int noexit) {
   const char* ng = getenv("FLIPB200_NO_GRAPH");
   if (ng && ng[0] == '1') return false;
+  if (!fb_comm_capturable(c)) return false;      // in-process test transport synchronises on the host
   const int mode = (use_mg ? 1 : 0) | (noexit ? 2 : 0);
   if (c->it_exec && same_box(c->it_box, c->box) && c->it_dt == dt && c->it_mode == mode) return true;
   fb_graph_invalidate(c);
-  if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
+  if (cudaStreamBeginCapture(c->stream, c->world > 1 ? cudaStreamCaptureModeRelaxed : cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
   const int64_t l0 = c->launches;
   int rc = enqueue_iteration(c, S, cf, use_mg, IT_DEV, noexit);
   c->it_kernels = c->launches - l0;
@@ -274,6 +308,7 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   const double bnorm2 = c->hs->bnorm2;             // fetched by fb_rhs_div
   const float* bvec = c->bf[c->bcur];
   const bool use_mg = c->mg_levels >= 2;
+  const int dist = c->world > 1 ? 1 : 0;
   MgLevel& L0 = c->mg[0];
   const double tol = c->P.pcg_tol;
   const double threshold = tol * tol * bnorm2;     // ConjugateGradient.h:53
@@ -281,9 +316,15 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2, threshold, max_iter);
   if (use_mg)
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, L0.b, L0.xa,
-                                                      bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds);
-  else
-    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds);
+                                                      bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds, dist);
+  else {
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist);
+    if (dist) {
+      int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
+      if (rc) return rc;
+      fb_pcg_publish(c, 1 << PART_RZ, -1);
+    }
+  }
   CK_LAUNCH(); c->launches += 2;
   if (bnorm2 == 0.0) return 0;                     // rhsNorm2 == 0 => x = 0, 0 iterations (ConjugateGradient.h:46-52)
   if (!(bnorm2 == bnorm2)) return FLIPB200_ERR_BREAKDOWN;
@@ -335,24 +376,30 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   PcgCoef cf; fb_make_coef(c, dt, &cf);
   const dim3 sg = stream_grid(S), tg = stencil_grid(S);
   const bool use_mg = c->mg_levels >= 2 && which == FLIPB200_KERNEL_PCG_ITER;
+  const int dist = c->world > 1 ? 1 : 0;
   MgLevel& L0 = c->mg[0];
   const double bn = c->hs->bnorm2 > 0.0 ? c->hs->bnorm2 : 1.0;
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn, 0.0, 1 << 30);
   if (use_mg) {
-    k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds);
+    k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds, dist);
     int rc = fb_mg_setup(c, dt); if (rc) return rc;
     rc = fb_mg_vcycle(c, -1); if (rc) return rc;
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1);
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1);
   } else {
-    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds);
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist);
+    if (dist) {
+      int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
+      if (rc) return rc;
+      fb_pcg_publish(c, 1 << PART_RZ, -1);
+    }
   }
   bool graph = false;
   if (which == FLIPB200_KERNEL_PCG_ITER) graph = get_iteration_graph(c, S, cf, use_mg, dt, 1);
   for (int it = 0; it < 3 + iters; ++it) {
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
-      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1);
+      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1, 0);
       c->launches++;
     } else if (graph) {
       if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }

@@ -95,7 +95,8 @@ int flipb200_step_host(flipb200_ctx* c, double* px, double* py, double* pz, doub
   for (int q = 0; q < 6; ++q)
     if (n) CK(cudaMemcpyAsync(c->pt.a[q], src[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   c->pt.n = n; c->sorted = false;
-  if (fb_init_ids(c, 0, n)) return FLIPB200_ERR_CUDA;
+  if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
+  if (c->world > 1) return FLIPB200_ERR_STATE;   // slab contexts: set_particles / step / get_particles per rank
   rc = step_device(c, dt_inout, st);
   if (rc) return rc;
   // With params.track_ids the arrays come back in the caller's order (the reference never

@@ -86,6 +86,25 @@ int         flipb200_version(void);
 int  flipb200_create (const flipb200_params*, const uint8_t* solid_host, flipb200_ctx**);
 void flipb200_destroy(flipb200_ctx*);
 
+/* ---- multi-GPU: z-slab decomposition (no counterpart in the reference, which is single-process;
+ * its only parallelism is tbb::parallel_for over particles, fluid.cc:845-1126) -------------------
+ * One context per GPU / process.  `params` and `solid_host` describe the WHOLE box on every rank;
+ * rank r owns the planes [z0, z1) reported by flipb200_slab_range plus ghost planes.  After
+ * create_slab the ranks must be connected with ONE of:
+ *   flipb200_comm_init_nccl  -- one process per GPU: rank 0 calls flipb200_comm_unique_id and ships
+ *                               the 128 bytes to the others (torch.distributed / MPI / a file);
+ *   flipb200_comm_init_local -- all ranks are host threads of one process (tests, also on one GPU).
+ * Every per-step call (step, p2g, classify, ...) is then COLLECTIVE: all ranks call it, in the same
+ * order.  Particles: set_particles takes the whole scene on every rank and keeps what the rank
+ * owns; seed_box seeds the rank's part of a global box; get_particles / get_grid return the
+ * rank's particles / owned planes.  step_host is not available on slab contexts. */
+int  flipb200_create_slab(const flipb200_params*, const uint8_t* solid_host, int32_t rank, int32_t world, flipb200_ctx**);
+int  flipb200_slab_range(flipb200_ctx*, int32_t* z0, int32_t* z1);
+int  flipb200_comm_unique_id(void* id128);                         /* ncclGetUniqueId, 128 bytes */
+int  flipb200_comm_init_nccl(flipb200_ctx*, const void* id128);    /* ncclCommInitRank(world, id, rank) */
+int  flipb200_comm_init_local(flipb200_ctx*, int32_t group_id);
+int  flipb200_get_particle_ids(flipb200_ctx*, uint32_t* ids, int64_t cap);   /* needs params.track_ids */
+
 /* PointList state (fluid.cc:804-813, add :841).  Host SoA arrays are copied. */
 int  flipb200_set_particles(flipb200_ctx*, const double* px, const double* py, const double* pz,
                             const double* vx, const double* vy, const double* vz, int64_t n);
