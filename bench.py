@@ -12,8 +12,12 @@ fill (i)): n^3 grid, exactly 8 particles per fluid voxel, zero initial velocity.
 Prints ONE JSON line (rank 0).  `value` = particles x K / device time with inputs resident in HBM;
 `e2e` = the same through flipb200_step_host with pinned HOST buffers (H2D + step + D2H per step);
 `roofline` = the PCG stencil kernel (17 algorithmic bytes per swept node) against the measured HBM
-peak; `cpu_baseline` = the CPU oracle on a bounded sample.  N > 1 currently runs N independent
-replicas of the scene, one per GPU (weak scaling; the z-slab decomposition is not built yet).
+peak; `cpu_baseline` = the CPU oracle on a bounded sample.
+
+N > 1 (torchrun, one rank per GPU): ONE tank of n x n x (n*N) nodes cut into N z-slabs (SURVEY.md
+8e) -- weak scaling, every GPU owns an n^3 block and ~the same particles; ghost planes, PCG dot
+products and particle migration go over the library's own NCCL communicator.  `value` counts the
+particles of the whole tank; time = max over ranks of the device time of the K collective steps.
 """
 import argparse
 import json
@@ -129,7 +133,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="flipb200", choices=["flipb200", "reference"])
-    ap.add_argument("--n", type=int, default=int(os.environ.get("FLIPB200_BENCH_N", "256")))
+    ap.add_argument("--grid-n", dest="n", type=int, default=int(os.environ.get("FLIPB200_BENCH_N", "256")))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--kernel-iters", type=int, default=50)
@@ -140,12 +144,15 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     n = args.n
-    lo, hi = scene_box(n)
-    particles = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8
-    config = {"workload": f"dam-break FLIP full-tank fill, {n}^3 grid, 8 particles/cell ({particles} particles/GPU), "
-                          f"fp64, {'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 (BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}])",
-              "grid": [n, n, n], "particles_per_gpu": particles,
-              "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (z-slab split not built yet)",
+    nzg = n * world                                    # weak scaling: an n^3 block per GPU, stacked along z
+    lo, hi = scene_box(n, nz=nzg)
+    total_particles = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8
+    particles = total_particles // world
+    config = {"workload": f"dam-break FLIP full-tank fill, {n}x{n}x{nzg} grid, 8 particles/cell ({total_particles} particles, "
+                          f"~{particles}/GPU), fp64, {'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 "
+                          f"(BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}]" + (" per GPU" if world > 1 else "") + ")",
+              "grid": [n, n, nzg], "particles_per_gpu": particles, "particles_total": total_particles,
+              "parallelism": "single GPU" if world == 1 else f"{world} z-slabs of {n} planes, NCCL halo exchange + PCG all-reduces + particle migration",
               "l2": "inputs larger than L2 (particle arrays 48 B x particles, grid vectors 8 B x n^3)" if n >= 256
                     else "working set may fit L2 at this n; no flush between steps"}
 
@@ -173,6 +180,7 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from fluid_simulation_b200 import dist as fdist
 
     def barrier():
         if world > 1:
@@ -186,9 +194,11 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    f = fb.Flip(nx=n, ny=n, nz=n, ox=n // 2, oy=n // 2, oz=n // 2, device=local_rank, max_particles=particles, precond=args.precond)
-    f.seed_box(lo, hi, seed=1234 + rank)
-    assert f.num_particles == particles
+    f = fdist.create_slab_flip(fb, rank, world, device=local_rank, nx=n, ny=n, nz=nzg, ox=n // 2, oy=n // 2, oz=nzg // 2,
+                               max_particles=int(particles * 1.06) + 4096, precond=args.precond)
+    f.seed_box(lo, hi, seed=1234)
+    if world == 1:
+        assert f.num_particles == particles
     dt = 0.1
     stats = []
     for _ in range(args.warmup):
@@ -209,7 +219,7 @@ def main():
     # device time: CUDA events on the library's stream (flipb200_stats.ms_total), max over ranks
     dev_s = max_over_ranks(dev_ms * 1e-3)
     wall = max_over_ranks(wall)
-    value = world * particles * args.steps / dev_s
+    value = total_particles * args.steps / dev_s
 
     # ---- kernel roofline (dominant kernel: the PCG stencil) ----
     peak, peak_src = measured_peak_gbs()
@@ -233,27 +243,39 @@ def main():
     # ---- e2e: the same step through the host-buffer entry point ----
     e2e = None
     if not args.no_e2e:
-        pos, vel = None, None
+        import ctypes as C
+        nloc = f.num_particles
+        cap = nloc + nloc // 16 + 4096 if world > 1 else nloc
         arrs, ptrs = [], []
         for q in range(6):
-            a, p = fb.pinned_empty(particles)
+            a, p = fb.pinned_empty(cap)
             arrs.append(a); ptrs.append(p)
-        import ctypes as C
         m = C.c_int64(0)
-        fb._check(f.lib.flipb200_get_particles(f.h, *[fb._ptr(a) for a in arrs], particles, C.byref(m)), "get")
-        out, outp = fb.pinned_empty(n * n * n, np.float32)
+        fb._check(f.lib.flipb200_get_particles(f.h, *[fb._ptr(a) for a in arrs], cap, C.byref(m)), "get")
+        out, outp = fb.pinned_empty(f.N, np.float32)          # this rank's planes of outputGrid
         dte = dt
-        dte, _ = f.step_host(arrs, dte, output_grid=out)      # warm-up
+
+        def host_step(nl, d):
+            if world == 1:
+                d, st_ = f.step_host(arrs, d, output_grid=out)
+                return nl, d
+            d, st_, nl = f.step_host_slab(arrs, nl, d, output_grid=out)
+            return nl, d
+
+        nloc, dte = host_step(nloc, dte)                       # warm-up
         barrier()
         t0 = time.perf_counter()
+        moved = 0
         for _ in range(args.steps):
-            dte, st = f.step_host(arrs, dte, output_grid=out)
-            launches_e = st.launches
+            moved += nloc
+            nloc, dte = host_step(nloc, dte)
         barrier()
         el = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": world * particles * args.steps / el, "unit": UNIT,
-               "h2d_bytes_per_step": 48 * particles, "d2h_bytes_per_step": 48 * particles + 4 * n ** 3,
-               "ms_per_step": el / args.steps * 1e3, "api": "flipb200_step_host (pinned host SoA in/out + outputGrid)"}
+        e2e = {"value": total_particles * args.steps / el, "unit": UNIT,
+               "h2d_bytes_per_step": 48 * total_particles, "d2h_bytes_per_step": 48 * total_particles + 4 * n * n * nzg,
+               "ms_per_step": el / args.steps * 1e3,
+               "api": ("flipb200_step_host" if world == 1 else "flipb200_step_host_slab per rank") +
+                      " (pinned host SoA in/out + outputGrid)"}
         for p in ptrs + [outp]:
             fb.pinned_free(p)
 

@@ -63,7 +63,7 @@ EXPORTS = [
     "flipb200_g2p_advect", "flipb200_get_grid", "flipb200_set_grid", "flipb200_time_kernel",
     "flipb200_host_alloc", "flipb200_host_free",
     "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
-    "flipb200_comm_init_local", "flipb200_get_particle_ids",
+    "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab",
 ]
 
 _lib = None
@@ -118,6 +118,8 @@ def load():
     lib.flipb200_comm_init_nccl.argtypes = [vp, vp]
     lib.flipb200_comm_init_local.argtypes = [vp, C.c_int32]
     lib.flipb200_get_particle_ids.argtypes = [vp, vp, C.c_int64]
+    lib.flipb200_step_host_slab.argtypes = [vp] + [vp] * 6 + [C.c_int64, C.c_int64, C.POINTER(C.c_int64), dp, vp,
+                                                              C.POINTER(Stats)]
     _lib = lib
     return lib
 
@@ -262,6 +264,15 @@ class Flip:
         _check(self.lib.flipb200_step_host(self.h, *[_ptr(x) for x in arrays], n, C.byref(d),
                                            _ptr(output_grid), C.byref(st)), "step_host")
         return d.value, st
+
+    def step_host_slab(self, arrays, n, dt, output_grid=None):
+        """Slab version of step_host: arrays hold capacity >= n entries; returns (dt, stats, n_out)."""
+        d = C.c_double(dt)
+        st = Stats()
+        m = C.c_int64(0)
+        _check(self.lib.flipb200_step_host_slab(self.h, *[_ptr(x) for x in arrays], n, arrays[0].size, C.byref(m),
+                                                C.byref(d), _ptr(output_grid), C.byref(st)), "step_host_slab")
+        return d.value, st, m.value
 
     # ---- stages ----
     def p2g(self):

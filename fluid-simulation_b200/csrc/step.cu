@@ -83,32 +83,48 @@ int flipb200_step(flipb200_ctx* c, double* dt_inout, flipb200_stats* st) {
   return step_device(c, dt_inout, st);
 }
 
-int flipb200_step_host(flipb200_ctx* c, double* px, double* py, double* pz, double* vx, double* vy, double* vz,
-                       int64_t n, double* dt_inout, float* output_grid, flipb200_stats* st) {
-  if (!c || !dt_inout || n < 0) return FLIPB200_ERR_ARG;
+static int step_host_impl(flipb200_ctx* c, double* const arr[6], int64_t n, int64_t cap, int64_t* n_out,
+                          double* dt_inout, float* output_grid, flipb200_stats* st) {
+  if (!c || !dt_inout || n < 0 || cap < n) return FLIPB200_ERR_ARG;
   CK(cudaSetDevice(c->device));
   if (n >= (int64_t)2147483647) return FLIPB200_ERR_ARG;
   c->pt.n = 0;
   int rc = fb_reserve_particles(c, n);
   if (rc) return rc;
-  double* src[6] = {px, py, pz, vx, vy, vz};
   for (int q = 0; q < 6; ++q)
-    if (n) CK(cudaMemcpyAsync(c->pt.a[q], src[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    if (n) CK(cudaMemcpyAsync(c->pt.a[q], arr[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   c->pt.n = n; c->sorted = false;
   if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
-  if (c->world > 1) return FLIPB200_ERR_STATE;   // slab contexts: set_particles / step / get_particles per rank
   rc = step_device(c, dt_inout, st);
   if (rc) return rc;
   // With params.track_ids the arrays come back in the caller's order (the reference never
-  // reorders its PointList); otherwise cell-sorted, i.e. a permutation of the input.
-  if (fb_download_particles(c, src)) return FLIPB200_ERR_CUDA;
+  // reorders its PointList); otherwise cell-sorted, i.e. a permutation of the input.  On a slab the
+  // rank's particle set itself changes (migration): *n_out particles come back, cell-sorted.
+  if (n_out) *n_out = c->pt.n;
+  if (c->pt.n > cap) return FLIPB200_ERR_ARG;
+  if (fb_download_particles(c, arr)) return FLIPB200_ERR_CUDA;
   if (output_grid) {
     const Grid& g = c->g;
-    CK(cudaMemcpy2DAsync(output_grid, g.nx * sizeof(float), c->wf, g.px * sizeof(float), g.nx * sizeof(float),
-                         (size_t)g.ny * g.nz, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpy2DAsync(output_grid, g.nx * sizeof(float), c->wf + (size_t)g.k0 * g.plane, g.px * sizeof(float),
+                         g.nx * sizeof(float), (size_t)g.ny * (g.k1 - g.k0), cudaMemcpyDeviceToHost, c->stream));
   }
   CK(cudaStreamSynchronize(c->stream));
   return FLIPB200_OK;
+}
+
+int flipb200_step_host(flipb200_ctx* c, double* px, double* py, double* pz, double* vx, double* vy, double* vz,
+                       int64_t n, double* dt_inout, float* output_grid, flipb200_stats* st) {
+  if (c && c->world > 1) return FLIPB200_ERR_STATE;   // slab contexts: flipb200_step_host_slab
+  double* arr[6] = {px, py, pz, vx, vy, vz};
+  return step_host_impl(c, arr, n, n, nullptr, dt_inout, output_grid, st);
+}
+
+int flipb200_step_host_slab(flipb200_ctx* c, double* px, double* py, double* pz, double* vx, double* vy, double* vz,
+                            int64_t n, int64_t cap, int64_t* n_out, double* dt_inout, float* output_grid,
+                            flipb200_stats* st) {
+  if (!n_out) return FLIPB200_ERR_ARG;
+  double* arr[6] = {px, py, pz, vx, vy, vz};
+  return step_host_impl(c, arr, n, cap, n_out, dt_inout, output_grid, st);
 }
 
 int flipb200_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed) {

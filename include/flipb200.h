@@ -104,6 +104,12 @@ int  flipb200_comm_unique_id(void* id128);                         /* ncclGetUni
 int  flipb200_comm_init_nccl(flipb200_ctx*, const void* id128);    /* ncclCommInitRank(world, id, rank) */
 int  flipb200_comm_init_local(flipb200_ctx*, int32_t group_id);
 int  flipb200_get_particle_ids(flipb200_ctx*, uint32_t* ids, int64_t cap);   /* needs params.track_ids */
+/* flipb200_step_host for a slab (collective): the rank uploads ITS n particles (every base plane
+ * must be owned by the rank or an adjacent one), steps, and gets back the *n_out particles it owns
+ * after migration (host arrays hold `cap` entries) and, optionally, its owned planes of outputGrid. */
+int  flipb200_step_host_slab(flipb200_ctx*, double* px, double* py, double* pz, double* vx, double* vy, double* vz,
+                             int64_t n, int64_t cap, int64_t* n_out, double* dt_inout, float* output_grid,
+                             flipb200_stats*);
 
 /* PointList state (fluid.cc:804-813, add :841).  Host SoA arrays are copied. */
 int  flipb200_set_particles(flipb200_ctx*, const double* px, const double* py, const double* pz,
