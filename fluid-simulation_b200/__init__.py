@@ -63,7 +63,7 @@ EXPORTS = [
     "flipb200_g2p_advect", "flipb200_get_grid", "flipb200_set_grid", "flipb200_time_kernel",
     "flipb200_host_alloc", "flipb200_host_free",
     "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
-    "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab",
+    "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab", "flipb200_halo_mode",
 ]
 
 _lib = None
@@ -118,6 +118,7 @@ def load():
     lib.flipb200_comm_init_nccl.argtypes = [vp, vp]
     lib.flipb200_comm_init_local.argtypes = [vp, C.c_int32]
     lib.flipb200_get_particle_ids.argtypes = [vp, vp, C.c_int64]
+    lib.flipb200_halo_mode.argtypes = [vp]
     lib.flipb200_step_host_slab.argtypes = [vp] + [vp] * 6 + [C.c_int64, C.c_int64, C.POINTER(C.c_int64), dp, vp,
                                                               C.POINTER(Stats)]
     _lib = lib
@@ -199,6 +200,10 @@ class Flip:
     def comm_init_nccl(self, unique_id):
         buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
         _check(self.lib.flipb200_comm_init_nccl(self.h, buf), "comm_init_nccl")
+
+    @property
+    def halo_mode(self):
+        return self.lib.flipb200_halo_mode(self.h)
 
     def get_particle_ids(self):
         n = self.num_particles

@@ -404,4 +404,151 @@ int fb_comm_exchange_particles(flipb200_ctx* c, int narr, void* const src[], voi
   return 0;
 }
 
+extern "C" int flipb200_halo_mode(flipb200_ctx* c) { return c ? c->halo.mode : FLIPB200_ERR_ARG; }
+
 bool fb_comm_capturable(flipb200_ctx* c) { return c->world == 1 || (c->comm && c->comm->kind == 1); }
+
+// ---- ghost pushes fused into the PCG kernels (halo.cuh) -------------------------------------------
+#include "halo.cuh"
+
+static bool link_active(const flipb200_ctx* c, const MgLevel& L, int dir) {
+  if (!L.dist) return false;
+  const Box& gb = L.gbox;
+  if (!(gb.x1 > gb.x0 && gb.z1 > gb.z0)) return false;
+  if (dir == 0) { if (c->rank == 0) return false; const int zb = L.zs[c->rank]; return gb.z0 < zb && gb.z1 > zb; }
+  if (c->rank + 1 >= c->world) return false;
+  const int zb = L.zs[c->rank + 1];
+  return gb.z0 < zb && gb.z1 > zb;       // the sweep box straddles the slab boundary: both sides sweep their boundary plane
+}
+
+// Describe one launch: it consumes array (lin, ain) -- ghost planes pushed by the neighbours' latest
+// producer of that array -- and/or produces array (lout, aout).  -1 = none.  kdn / kup: first / last
+// owned plane in the index space of the sweep; nb: blocks per boundary plane.
+PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, size_t elem_out, int kdn, int kup, int nb) {
+  PeerHalo h = halo_off();
+  HaloState& hs = c->halo;
+  if (hs.mode == 0) return h;
+  h.mode = hs.mode; h.kdn = kdn; h.kup = kup; h.nb = nb;
+  h.my_flags = hs.flags; h.cnt = hs.flags + 2;
+  h.sig_dn = hs.peer_flags[0] ? hs.peer_flags[0] + 1 : nullptr;
+  h.sig_up = hs.peer_flags[1] ? hs.peer_flags[1] + 0 : nullptr;
+  if (ain >= 0) {
+    const MgLevel& L = c->mg[lin];
+    h.wait_dn = link_active(c, L, 0); h.wait_up = link_active(c, L, 1);
+    h.wrel_dn = h.wrel_up = (int)(hs.last_prod[lin][ain] - hs.seg_base);
+  }
+  if (aout >= 0) {
+    const MgLevel& L = c->mg[lout];
+    h.push_dn = link_active(c, L, 0); h.push_up = link_active(c, L, 1);
+    h.srel = (int)(hs.abs_seq - hs.seg_base);
+    hs.last_prod[lout][aout] = hs.abs_seq;
+    hs.abs_seq++;
+    const Grid& g = L.g;
+    const size_t pb = (size_t)g.plane * elem_out;
+    if (h.push_dn) {       // lower neighbour's upper ghost plane k1' <- my plane k0
+      const int k1p = SLAB_GHOST + (L.zs[c->rank] - L.zs[c->rank - 1]);
+      h.dst_dn = (char*)hs.peer[0][lout][aout] + ((ptrdiff_t)k1p - g.k0) * (ptrdiff_t)pb;
+    }
+    if (h.push_up)         // upper neighbour's lower ghost plane k0' - 1 <- my plane k1 - 1
+      h.dst_up = (char*)hs.peer[1][lout][aout] + ((ptrdiff_t)(SLAB_GHOST - 1) - (g.k1 - 1)) * (ptrdiff_t)pb;
+  }
+  return h;
+}
+
+// where a halo copy used to be: nothing to do with device flags; the in-process transport orders
+// producers and consumers with its host barrier
+int fb_halo_point(flipb200_ctx* c) {
+  if (c->halo.mode == 1) return fb_comm_barrier(c);
+  return 0;
+}
+
+// exchange `n` bytes with both neighbours over NCCL (setup only): out_dn/out_up receive theirs
+static int nccl_swap_bytes(flipb200_ctx* c, const void* mine, void* from_dn, void* from_up, size_t n) {
+  char* d = nullptr;
+  CK(cudaMalloc((void**)&d, 3 * n));
+  CK(cudaMemcpyAsync(d, mine, n, cudaMemcpyHostToDevice, c->stream));
+  const bool up = c->rank + 1 < c->world, dn = c->rank > 0;
+  ncclComm_t nc = c->comm->nc;
+  NC(g_nccl.GroupStart());
+  if (dn) { NC(g_nccl.Send(d, n, ncclChar, c->rank - 1, nc, c->stream)); NC(g_nccl.Recv(d + n, n, ncclChar, c->rank - 1, nc, c->stream)); }
+  if (up) { NC(g_nccl.Send(d, n, ncclChar, c->rank + 1, nc, c->stream)); NC(g_nccl.Recv(d + 2 * n, n, ncclChar, c->rank + 1, nc, c->stream)); }
+  NC(g_nccl.GroupEnd());
+  if (dn) CK(cudaMemcpyAsync(from_dn, d + n, n, cudaMemcpyDeviceToHost, c->stream));
+  if (up) CK(cudaMemcpyAsync(from_up, d + 2 * n, n, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  cudaFree(d);
+  return 0;
+}
+
+// Map the neighbours' exchanged arrays.  NCCL transport: cudaIpc handles travel over NCCL itself;
+// in-process transport: the other contexts' pointers are directly usable (one address space).
+// FLIPB200_FUSED_HALO=0 keeps the separate halo copies.
+int fb_halo_setup(flipb200_ctx* c) {
+  HaloState& hs = c->halo;
+  hs.mode = 0;
+  if (c->world == 1 || !c->comm || c->mg_levels < 2 || c->mg_nd < 1) return 0;
+  const char* e = getenv("FLIPB200_FUSED_HALO");
+  if (e && e[0] == '0') return 0;
+  CK(cudaMalloc((void**)&hs.flags, 4 * sizeof(unsigned)));
+  CK(cudaMemsetAsync(hs.flags, 0, 4 * sizeof(unsigned), c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  const int nd = c->mg_nd;
+  // my exported pointers: flags, pd, then (xa, xb) of every distributed level
+  void* mine[2 + 2 * MG_MAX_LEVELS]; int n = 0;
+  mine[n++] = hs.flags; mine[n++] = c->pd;
+  for (int l = 0; l < nd; ++l) { mine[n++] = c->mg[l].xa; mine[n++] = c->mg[l].xb; }
+  void* theirs[2][2 + 2 * MG_MAX_LEVELS] = {};
+  const bool up = c->rank + 1 < c->world, dn = c->rank > 0;
+  if (c->comm->kind == 2) {
+    LocalGroup* lg = c->comm->lg;
+    lg->barrier();                                   // every rank has allocated its arrays
+    for (int dir = 0; dir < 2; ++dir) {
+      if (!(dir ? up : dn)) continue;
+      flipb200_ctx* o = lg->member[c->rank + (dir ? 1 : -1)];
+      if (!o || o->mg_nd != nd) return FLIPB200_ERR_STATE;
+      int m = 0;
+      // the neighbour may not have run its own setup yet: its flag block is published below
+      theirs[dir][m++] = nullptr; theirs[dir][m++] = o->pd;
+      for (int l = 0; l < nd; ++l) { theirs[dir][m++] = o->mg[l].xa; theirs[dir][m++] = o->mg[l].xb; }
+    }
+    hs.mode = 1;                                     // flags unused: host barriers order the kernels
+  } else {
+    cudaIpcMemHandle_t hm[2 + 2 * MG_MAX_LEVELS], hd[2 + 2 * MG_MAX_LEVELS], hu[2 + 2 * MG_MAX_LEVELS];
+    memset(hm, 0, sizeof(hm));
+    bool ok = true;
+    for (int i = 0; i < n; ++i) if (cudaIpcGetMemHandle(&hm[i], mine[i]) != cudaSuccess) { ok = false; cudaGetLastError(); }
+    unsigned char okb = ok ? 1 : 0;
+    memcpy(&hm[n], &okb, 1);                         // slot n carries the "handles valid" byte
+    int rc = nccl_swap_bytes(c, hm, hd, hu, sizeof(cudaIpcMemHandle_t) * (n + 1));
+    if (rc) return rc;
+    for (int dir = 0; dir < 2 && ok; ++dir) {
+      if (!(dir ? up : dn)) continue;
+      cudaIpcMemHandle_t* hh = dir ? hu : hd;
+      if (*(unsigned char*)&hh[n] != 1) { ok = false; break; }
+      for (int i = 0; i < n; ++i)
+        if (cudaIpcOpenMemHandle(&theirs[dir][i], hh[i], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+          fprintf(stderr, "flipb200: cudaIpcOpenMemHandle failed (%s): ghost planes go through NCCL copies\n",
+                  cudaGetErrorString(cudaGetLastError()));
+          ok = false; break;
+        }
+    }
+    // all ranks must agree on the mode
+    int* flag = nullptr; int hflag = ok ? 1 : 0;
+    CK(cudaMalloc((void**)&flag, sizeof(int)));
+    CK(cudaMemcpyAsync(flag, &hflag, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    NC(g_nccl.AllReduce(flag, flag, 1, ncclInt32, ncclMin, c->comm->nc, c->stream));
+    CK(cudaMemcpyAsync(&hflag, flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    cudaFree(flag);
+    if (!hflag) return 0;
+    hs.mode = 2;
+  }
+  for (int dir = 0; dir < 2; ++dir) {
+    int m = 0;
+    hs.peer_flags[dir] = (unsigned*)theirs[dir][m++];
+    hs.peer[dir][0][HA_PD] = theirs[dir][m++];
+    for (int l = 0; l < nd; ++l) { hs.peer[dir][l][HA_XA] = theirs[dir][m++]; hs.peer[dir][l][HA_XB] = theirs[dir][m++]; }
+  }
+  hs.abs_seq = 1; hs.seg_base = 1;
+  return 0;
+}

@@ -75,6 +75,8 @@ struct DevScalars {
   // z-slab runs: kernels accumulate this rank's share of the current dot products here; after the
   // all-reduce k_pcg_publish moves the sum into the ring slot (single GPU: straight into the ring)
   double part[4];                    // [0] p.Ap  [1] r.z  [2] r.r
+  int halo_base;                     // sequence number base of the fused ghost-plane pushes (halo.cuh)
+  int pad2;
 };
 #define PART_PAP 0
 #define PART_RZ 1
@@ -104,9 +106,21 @@ struct MgLevel {
   float *xa, *xb, *b; // solution ping-pong and right-hand side
   double h2inv;       // operator scale: A x = h2inv * (k x_c - sum of fluid neighbours)
 };
-#define MG_MAX_LEVELS 12
 
+#define MG_MAX_LEVELS 12
 struct Comm;   // comm.cu: NCCL (one process per GPU) or in-process threaded ranks (tests)
+
+// host state of the ghost-plane pushes fused into the PCG kernels (halo.cuh, comm.cu)
+enum { HA_XA = 0, HA_XB = 1, HA_PD = 2 };
+struct HaloState {
+  int mode;                          // 0 off (halo copies), 1 push + host barrier (in-process ranks), 2 push + device flags
+  unsigned* flags;                   // device: [0..1] flags written by the lower / upper neighbour, [2..3] block counters
+  unsigned* peer_flags[2];           // the neighbours' flag blocks (peer mappings): [0] lower, [1] upper
+  void* peer[2][MG_MAX_LEVELS][3];   // the neighbours' arrays: [dir][level][HA_*]
+  long long abs_seq;                 // producer kernels enqueued so far
+  long long seg_base;                // host mirror of DevScalars::halo_base for the segment being enqueued
+  long long last_prod[MG_MAX_LEVELS][3];
+};
 
 struct flipb200_ctx {
   flipb200_params P;
@@ -117,6 +131,8 @@ struct flipb200_ctx {
   Comm* comm;
   int slab_align;          // log2 of the alignment of the slab boundaries (mg.cu: distributed levels)
   double* halo_tmp;        // 4 planes of doubles: receive buffer of the P2G ghost sum
+  HaloState halo;
+  bool halo_ready;         // fb_halo_setup has run (lazily, at the first collective solve)
   int device;
   int num_sms;
   cudaStream_t stream;
@@ -149,8 +165,8 @@ struct flipb200_ctx {
   int last_iters;          // iterations of the previous solve (sizes the first launch batch)
   bool mg_dirty;           // cell classes changed since the hierarchy was built (set by classify)
   // cached CUDA graph of one PCG iteration; valid while box / dt / mode are unchanged
-  cudaGraph_t it_graph; cudaGraphExec_t it_exec; int64_t it_kernels;
-  Box it_box; double it_dt; int it_mode;
+  cudaGraph_t it_graph; cudaGraphExec_t it_exec; int64_t it_kernels; int it_nprod;
+  Box it_box, it_gbox; double it_dt; int it_mode;
   int stage;               // bookkeeping for stage-level calls
   cudaEvent_t ev[8];
   int64_t launches;
@@ -282,6 +298,8 @@ int fb_comm_exchange_particles(flipb200_ctx* c, int narr, void* const src[], voi
                                const int64_t recv_off[2], const int64_t recv_n[2]);
 void fb_comm_free(flipb200_ctx* c);
 int fb_comm_barrier(flipb200_ctx* c);
-bool fb_comm_capturable(flipb200_ctx* c);   // exchanges can be recorded into a CUDA graph (NCCL or single GPU)
+bool fb_comm_capturable(flipb200_ctx* c);
+int fb_halo_setup(flipb200_ctx* c);
+int fb_halo_point(flipb200_ctx* c);          // a place where a halo copy used to be (host barrier of the test transport)
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }

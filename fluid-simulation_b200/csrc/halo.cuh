@@ -1,0 +1,115 @@
+// halo.cuh -- ghost-plane exchange FUSED into the producing kernels (z-slab runs).
+//
+// Inside the PCG iteration every sweep of a distributed level needs one ghost plane of its input
+// from each z neighbour (~20 exchanges per iteration with the V-cycle).  As separate NCCL
+// send/recv launches they cost ~14 us each, a third of the iteration.  Here the kernel that
+// PRODUCES an exchanged array also stores its two boundary planes straight into the neighbours'
+// ghost planes through NVLink peer mappings (cudaIpc), and the kernel that CONSUMES the array makes
+// only its boundary blocks wait on a flag -- interior blocks run while the planes are in flight.
+//
+//   producer block that owns boundary plane kdn / kup:   st.global to the peer pointer, then
+//       __threadfence_system, block counter; the LAST boundary block release-stores the sequence
+//       number of this producer kernel into the neighbour's flag word.
+//   consumer block that reads ghost plane kdn-1 / kup+1: thread 0 acquire-spins until the flag
+//       reaches the sequence number of the latest producer of that array (bounded: a time-out sets
+//       ds->pcg_status = FLIPB200_ERR_COMM instead of hanging the GPU).
+//
+// Sequence numbers: every producer launch gets the next number; all ranks launch the same kernels
+// in the same order, so "my producer #s" pairs with "the neighbour's producer #s".  Kernels read
+// seq = ds->halo_base + rel (rel is a launch constant), which keeps a captured CUDA graph valid:
+// k_pcg_advance adds the number of producers of the iteration to halo_base.
+// Write-after-read safety (a push must not overwrite a ghost plane the neighbour still reads) follows
+// from the ping-pong of xa/xb: the blocks that push array X have first waited on the neighbour's
+// producer of their own input, which runs after the neighbour's last reader of X.
+//
+// mode 0: off (separate halo copies);  mode 1: push only, the host barrier of the in-process test
+// transport orders producers and consumers;  mode 2: push + device flags (one process per GPU).
+#pragma once
+#include "sweep.cuh"
+#include <string.h>
+
+struct PeerHalo {
+  int mode;
+  int kdn, kup;              // planes (sweep index space) whose blocks are the boundary blocks: first / last owned
+  int wait_dn, wait_up;      // consumer side: wait for the lower / upper neighbour's producer
+  int push_dn, push_up;      // producer side: push + signal to the lower / upper neighbour
+  int wrel_dn, wrel_up;      // seq to wait for   = ds->halo_base + wrel
+  int srel;                  // seq to signal     = ds->halo_base + srel
+  int nb;                    // boundary blocks per direction (gridDim.x * gridDim.y)
+  void* dst_dn;              // peer array rebased so that MY element index addresses the peer's ghost plane
+  void* dst_up;
+  unsigned* my_flags;        // [0] written by the lower neighbour, [1] by the upper neighbour
+  unsigned* sig_dn;          // lower neighbour's my_flags[1]
+  unsigned* sig_up;          // upper neighbour's my_flags[0]
+  unsigned* cnt;             // [2] block counters (own memory)
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+#define HALO_SPIN_LIMIT (4000000000ll)   // ~2 s of SM clocks
+
+// Call at kernel start (after the uniform early exits), by ALL threads of the block.
+// bdn / bup: this block reads the ghost plane below kdn / above kup.
+__device__ __forceinline__ void halo_wait(const PeerHalo& H, DevScalars* ds, bool bdn, bool bup) {
+  if (H.mode != 2) return;
+  const bool w0 = bdn && H.wait_dn, w1 = bup && H.wait_up;
+  if (!(w0 || w1)) return;
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  if (tid == 0) {
+    const unsigned base = (unsigned)ds->halo_base;
+    const long long t0 = clock64();
+    if (w0) {
+      const unsigned need = base + (unsigned)H.wrel_dn;
+      while ((int)(ld_acquire_sys(&H.my_flags[0]) - need) < 0)
+        if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
+    }
+    if (w1) {
+      const unsigned need = base + (unsigned)H.wrel_up;
+      while ((int)(ld_acquire_sys(&H.my_flags[1]) - need) < 0)
+        if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
+    }
+  }
+  __syncthreads();
+}
+
+// Store the pair (v0, v1) written at element q of plane k into the neighbours' ghost planes.
+template <typename T>
+__device__ __forceinline__ void halo_push2(const PeerHalo& H, int q, int k, T v0, T v1) {
+  if (H.mode == 0) return;
+  if (H.push_dn && k == H.kdn) st2<T>(reinterpret_cast<T*>(H.dst_dn) + q, v0, v1);
+  if (H.push_up && k == H.kup) st2<T>(reinterpret_cast<T*>(H.dst_up) + q, v0, v1);
+}
+template <typename T>
+__device__ __forceinline__ void halo_push1(const PeerHalo& H, int q, int k, T v) {
+  if (H.mode == 0) return;
+  if (H.push_dn && k == H.kdn) reinterpret_cast<T*>(H.dst_dn)[q] = v;
+  if (H.push_up && k == H.kup) reinterpret_cast<T*>(H.dst_up)[q] = v;
+}
+
+// Call at kernel end by ALL threads of every block (no early returns before it).
+// bdn / bup: this block owns (part of) boundary plane kdn / kup.
+__device__ __forceinline__ void halo_signal(const PeerHalo& H, DevScalars* ds, bool bdn, bool bup) {
+  if (H.mode != 2) return;
+  const bool s0 = bdn && H.push_dn, s1 = bup && H.push_up;
+  if (!(s0 || s1)) return;
+  __threadfence_system();            // my peer stores are visible system-wide before the flag
+  __syncthreads();
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  if (tid == 0) {
+    const unsigned seq = (unsigned)ds->halo_base + (unsigned)H.srel;
+    if (s0 && atomicAdd(&H.cnt[0], 1u) == (unsigned)H.nb - 1u) { H.cnt[0] = 0u; __threadfence_system(); st_release_sys(H.sig_dn, seq); }
+    if (s1 && atomicAdd(&H.cnt[1], 1u) == (unsigned)H.nb - 1u) { H.cnt[1] = 0u; __threadfence_system(); st_release_sys(H.sig_up, seq); }
+  }
+}
+
+// host (comm.cu): describe one launch as consumer of (lin, ain) and/or producer of (lout, aout)
+PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, size_t elem_out, int kdn, int kup, int nb);
+
+static inline PeerHalo halo_off() { PeerHalo h; memset(&h, 0, sizeof(h)); return h; }

@@ -24,6 +24,7 @@
 // iteration in fp64.
 #include "sweep.cuh"
 #include "pcg.cuh"
+#include "halo.cuh"
 
 #define MG_COARSE_SWEEPS 40
 #define MG_COARSEST_CELLS 4096
@@ -252,10 +253,14 @@ template <bool DOT>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
             const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
-            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg, int dist) {
+            const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg, int dist,
+            const __grid_constant__ PeerHalo H) {
   __shared__ double sm[32];
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
+  const int kz0 = S.box.z0 + blockIdx.z * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
+  halo_wait(H, ds, bdn, bup);
   double acc[1] = {0.0};
   StencilMarch<float> m;
   if (m.begin(S, xi)) {
@@ -275,11 +280,12 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
       float o0 = 0.f, o1 = 0.f;
       if (f.x & FB_FLUID) { int kk = 6 - __popc(f.x & FB_SMASK); o0 = m.c0() + mc.winv[kk] * (bv.x - mc.h2inv * ((float)kk * m.c0() - m.sum0())); }
       if (f.y & FB_FLUID) { int kk = 6 - __popc(f.y & FB_SMASK); o1 = m.c1() + mc.winv[kk] * (bv.y - mc.h2inv * ((float)kk * m.c1() - m.sum1())); }
-      if (m.act) st2<float>(xo + m.q, o0, o1);
+      if (m.act) { st2<float>(xo + m.q, o0, o1); halo_push2<float>(H, m.q, m.k, o0, o1); }
       if (DOT) acc[0] += rv.x * (double)o0 + rv.y * (double)o1;
       m.advance(S);
     }
   }
+  halo_signal(H, ds, bdn, bup);
   if (DOT) {
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
@@ -293,28 +299,33 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
            const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
-           float* __restrict__ rn, const DevScalars* __restrict__ ds) {
+           float* __restrict__ rn, DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
+  const int kz0 = S.box.z0 + blockIdx.z * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
+  halo_wait(H, ds, bdn, bup);
   StencilMarch<float> m;
-  if (!m.begin(S, x)) return;
-  const int kend = min(m.k + ST_ZP, S.box.z1);
+  if (m.begin(S, x)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
 #pragma unroll
-  for (int z = 0; z < ST_ZP; ++z) {
-    if (m.k >= kend) break;
-    m.load(S, x);
-    uchar2 f = make_uchar2(0, 0), nn = make_uchar2(64, 64);
-    float2 bv = make_float2(0.f, 0.f);
-    if (m.act) {
-      f = *reinterpret_cast<const uchar2*>(fl + m.q);
-      nn = *reinterpret_cast<const uchar2*>(nrm + m.q);
-      bv = ld2<float>(b + m.q);
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, x);
+      uchar2 f = make_uchar2(0, 0), nn = make_uchar2(64, 64);
+      float2 bv = make_float2(0.f, 0.f);
+      if (m.act) {
+        f = *reinterpret_cast<const uchar2*>(fl + m.q);
+        nn = *reinterpret_cast<const uchar2*>(nrm + m.q);
+        bv = ld2<float>(b + m.q);
+      }
+      float o0 = 0.f, o1 = 0.f;
+      if (f.x & FB_FLUID) { int kk = 6 - __popc(f.x & FB_SMASK); o0 = (bv.x - mc.h2inv * ((float)kk * m.c0() - m.sum0())) * (64.f / (float)nn.x); }
+      if (f.y & FB_FLUID) { int kk = 6 - __popc(f.y & FB_SMASK); o1 = (bv.y - mc.h2inv * ((float)kk * m.c1() - m.sum1())) * (64.f / (float)nn.y); }
+      if (m.act) { st2<float>(rn + m.q, o0, o1); halo_push2<float>(H, m.q, m.k, o0, o1); }
+      m.advance(S);
     }
-    float o0 = 0.f, o1 = 0.f;
-    if (f.x & FB_FLUID) { int kk = 6 - __popc(f.x & FB_SMASK); o0 = (bv.x - mc.h2inv * ((float)kk * m.c0() - m.sum0())) * (64.f / (float)nn.x); }
-    if (f.y & FB_FLUID) { int kk = 6 - __popc(f.y & FB_SMASK); o1 = (bv.y - mc.h2inv * ((float)kk * m.c1() - m.sum1())) * (64.f / (float)nn.y); }
-    if (m.act) st2<float>(rn + m.q, o0, o1);
-    m.advance(S);
   }
+  halo_signal(H, ds, bdn, bup);
 }
 
 // restriction b_c[I] = (1/8) sum_i P[i,I] res_i = (1/512) sum over the 4x4x4 fine cells of
@@ -324,49 +335,55 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
 __global__ void __launch_bounds__(256)
 k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
               const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
-              const DevScalars* __restrict__ ds) {
+              DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
   const int K = cbox.z0 + blockIdx.z;
-  if (J >= cbox.y1) return;                         // whole warp
-  const bool in = I < cbox.x1;
-  // the fine sweeps write pairs over [fx0, fxe): everything in that x-range is fresh (0 off the fluid)
-  const int fx0 = fbox.x0 & ~1, fxe = min(gf.px, (fbox.x1 + 1) & ~1);
-  const int xf = 2 * I;                             // children xf, xf+1
-  const bool cv = in && xf >= fx0 && xf < fxe;
-  const bool eL = in && xf - 1 >= fx0 && xf - 1 < fxe, eR = in && xf + 2 >= fx0 && xf + 2 < fxe;
-  const int xc = cv ? xf : fx0;                     // clamped (value discarded when !cv)
-  // issue all 16 row loads first (rows outside the fine box are clamped and get weight 0)
-  float2 v[16]; float ea[16], ed[16], w[16];
+  halo_wait(H, ds, K == H.kdn, K == H.kup);         // boundary coarse planes read the fine ghost planes
+  if (J < cbox.y1) {                                // whole warp
+    const bool in = I < cbox.x1;
+    // the fine sweeps write pairs over [fx0, fxe): everything in that x-range is fresh (0 off the fluid)
+    const int fx0 = fbox.x0 & ~1, fxe = min(gf.px, (fbox.x1 + 1) & ~1);
+    const int xf = 2 * I;                             // children xf, xf+1
+    const bool cv = in && xf >= fx0 && xf < fxe;
+    const bool eL = in && xf - 1 >= fx0 && xf - 1 < fxe, eR = in && xf + 2 >= fx0 && xf + 2 < fxe;
+    const int xc = cv ? xf : fx0;                     // clamped (value discarded when !cv)
+    // issue all 16 row loads first (rows outside the fine box are clamped and get weight 0)
+    float2 v[16]; float ea[16], ed[16], w[16];
 #pragma unroll
-  for (int t = 0; t < 16; ++t) {
-    const int oz = (t >> 2) - 1, oy = (t & 3) - 1;
-    const int kf = 2 * (K + gc.kg0) + oz - gf.kg0, jf = 2 * J + oy;
-    const bool rin = kf >= fbox.z0 && kf < fbox.z1 && jf >= fbox.y0 && jf < fbox.y1;
-    const int kc = min(max(kf, fbox.z0), fbox.z1 - 1), jc = min(max(jf, fbox.y0), fbox.y1 - 1);
-    const float* row = rn + gidx(gf, 0, jc, kc);
-    w[t] = rin ? (((oz == 0 || oz == 1) ? 3.f : 1.f) * ((oy == 0 || oy == 1) ? 3.f : 1.f)) : 0.f;
-    v[t] = *reinterpret_cast<const float2*>(row + xc);
-    ea[t] = (lane == 0 && eL) ? row[xf - 1] : 0.f;
-    ed[t] = (lane == 31 && eR) ? row[xf + 2] : 0.f;
-  }
-  float sum = 0.f;
+    for (int t = 0; t < 16; ++t) {
+      const int oz = (t >> 2) - 1, oy = (t & 3) - 1;
+      const int kf = 2 * (K + gc.kg0) + oz - gf.kg0, jf = 2 * J + oy;
+      const bool rin = kf >= fbox.z0 && kf < fbox.z1 && jf >= fbox.y0 && jf < fbox.y1;
+      const int kc = min(max(kf, fbox.z0), fbox.z1 - 1), jc = min(max(jf, fbox.y0), fbox.y1 - 1);
+      const float* row = rn + gidx(gf, 0, jc, kc);
+      w[t] = rin ? (((oz == 0 || oz == 1) ? 3.f : 1.f) * ((oy == 0 || oy == 1) ? 3.f : 1.f)) : 0.f;
+      v[t] = *reinterpret_cast<const float2*>(row + xc);
+      ea[t] = (lane == 0 && eL) ? row[xf - 1] : 0.f;
+      ed[t] = (lane == 31 && eR) ? row[xf + 2] : 0.f;
+    }
+    float sum = 0.f;
 #pragma unroll
-  for (int t = 0; t < 16; ++t) {
-    float vx = cv ? v[t].x : 0.f, vy = cv ? v[t].y : 0.f;
-    float a = __shfl_up_sync(0xffffffffu, vy, 1), d = __shfl_down_sync(0xffffffffu, vx, 1);
-    if (lane == 0) a = ea[t];
-    if (lane == 31) d = ed[t];
-    sum += w[t] * ((a + d) + 3.f * (vx + vy));
+    for (int t = 0; t < 16; ++t) {
+      float vx = cv ? v[t].x : 0.f, vy = cv ? v[t].y : 0.f;
+      float a = __shfl_up_sync(0xffffffffu, vy, 1), d = __shfl_down_sync(0xffffffffu, vx, 1);
+      if (lane == 0) a = ea[t];
+      if (lane == 31) d = ed[t];
+      sum += w[t] * ((a + d) + 3.f * (vx + vy));
+    }
+    if (in) {
+      const int qc = gidx(gc, I, J, K);
+      const uint8_t f = fc[qc];
+      const float r = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
+      const float x1 = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * r : 0.f;
+      bc[qc] = r;
+      x1c[qc] = x1;
+      halo_push1<float>(H, qc, K, x1);
+    }
   }
-  if (!in) return;
-  const int qc = gidx(gc, I, J, K);
-  const uint8_t f = fc[qc];
-  const float r = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
-  bc[qc] = r;
-  x1c[qc] = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * r : 0.f;
+  halo_signal(H, ds, K == H.kdn, K == H.kup);
 }
 
 // prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells).
@@ -374,43 +391,50 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
 // fine row are loaded coalesced and combined, the x-neighbours I-1 / I+1 come by shuffle.
 __global__ void __launch_bounds__(256)
 k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ nrm,
-             const float* __restrict__ ec, float* __restrict__ x, const DevScalars* __restrict__ ds) {
+             const float* __restrict__ ec, float* __restrict__ x, DevScalars* __restrict__ ds,
+             const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
   const int k = fbox.z0 + blockIdx.z;
-  if (j >= fbox.y1) return;                         // whole warp
-  const int kg = k + gf.kg0;                         // global fine plane
-  const int I = i >> 1, J = j >> 1, K = (kg >> 1) - gc.kg0;
-  int J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((kg & 1) ? 1 : -1);
-  const bool yin = J2 >= 0 && J2 < gc.ny, zin = K2 + gc.kg0 >= 0 && K2 + gc.kg0 < gc.gnz;
-  J2 = yin ? J2 : J; K2 = zin ? K2 : K;
-  const float wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
-  const float* p00 = ec + gidx(gc, 0, J, K);
-  const float* p10 = ec + gidx(gc, 0, J2, K);
-  const float* p01 = ec + gidx(gc, 0, J, K2);
-  const float* p11 = ec + gidx(gc, 0, J2, K2);
-  auto comb = [&](int ii) -> float {                // y/z-combined coarse value of column ii (weights 3|1)
-    return 3.f * (3.f * p00[ii] + wy * p10[ii]) + wz * (3.f * p01[ii] + wy * p11[ii]);
-  };
-  const bool cin = I < gc.nx;
-  const float E = cin ? comb(I) : 0.f;
-  float EL = __shfl_up_sync(0xffffffffu, E, 1), ER = __shfl_down_sync(0xffffffffu, E, 1);
-  if (lane == 0) EL = (I - 1 >= 0 && I - 1 < gc.nx) ? comb(I - 1) : 0.f;
-  if (lane == 31) ER = (I + 1 < gc.nx) ? comb(I + 1) : 0.f;
-  if (I - 1 < 0) EL = 0.f;
-  if (I + 1 >= gc.nx) ER = 0.f;
-  const int xe = min(gf.px, (fbox.x1 + 1) & ~1);
-  if (i >= xe) return;
-  const int q = gidx(gf, i, j, k);
-  const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);      // three independent loads in flight
-  const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
-  float2 xv = *reinterpret_cast<const float2*>(x + q);
-  if (!((f.x | f.y) & FB_FLUID)) return;
-  if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
-  if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
-  *reinterpret_cast<float2*>(x + q) = xv;
+  halo_wait(H, ds, k == H.kdn, k == H.kup);         // boundary fine planes read the coarse ghost planes
+  if (j < fbox.y1) {                                // whole warp
+    const int kg = k + gf.kg0;                         // global fine plane
+    const int I = i >> 1, J = j >> 1, K = (kg >> 1) - gc.kg0;
+    int J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((kg & 1) ? 1 : -1);
+    const bool yin = J2 >= 0 && J2 < gc.ny, zin = K2 + gc.kg0 >= 0 && K2 + gc.kg0 < gc.gnz;
+    J2 = yin ? J2 : J; K2 = zin ? K2 : K;
+    const float wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
+    const float* p00 = ec + gidx(gc, 0, J, K);
+    const float* p10 = ec + gidx(gc, 0, J2, K);
+    const float* p01 = ec + gidx(gc, 0, J, K2);
+    const float* p11 = ec + gidx(gc, 0, J2, K2);
+    auto comb = [&](int ii) -> float {                // y/z-combined coarse value of column ii (weights 3|1)
+      return 3.f * (3.f * p00[ii] + wy * p10[ii]) + wz * (3.f * p01[ii] + wy * p11[ii]);
+    };
+    const bool cin = I < gc.nx;
+    const float E = cin ? comb(I) : 0.f;
+    float EL = __shfl_up_sync(0xffffffffu, E, 1), ER = __shfl_down_sync(0xffffffffu, E, 1);
+    if (lane == 0) EL = (I - 1 >= 0 && I - 1 < gc.nx) ? comb(I - 1) : 0.f;
+    if (lane == 31) ER = (I + 1 < gc.nx) ? comb(I + 1) : 0.f;
+    if (I - 1 < 0) EL = 0.f;
+    if (I + 1 >= gc.nx) ER = 0.f;
+    const int xe = min(gf.px, (fbox.x1 + 1) & ~1);
+    if (i < xe) {
+      const int q = gidx(gf, i, j, k);
+      const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);      // three independent loads in flight
+      const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
+      float2 xv = *reinterpret_cast<const float2*>(x + q);
+      if ((f.x | f.y) & FB_FLUID) {
+        if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
+        if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
+        *reinterpret_cast<float2*>(x + q) = xv;
+        halo_push2<float>(H, q, k, xv.x, xv.y);
+      }
+    }
+  }
+  halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
 // coarsest level (<= 4096 cells) in ONE block: 40 steps of the Chebyshev semi-iteration on the
@@ -482,31 +506,43 @@ k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* _
 // z-slab runs: on the distributed levels every sweep is preceded by a one-plane halo
 // fill of its input; the first replicated level is assembled with an all-gather of the restricted
 // residual and solved redundantly by every rank; r.z is all-reduced at the end.
-#define HALO(L, arr) do { if ((L).dist) { int rc__ = fb_halo_fill(c, (L).g, (arr), sizeof(float), 1, 1); if (rc__) return rc__; } } while (0)
+// Ghost planes of `arr` before a sweep reads them: a copy (NCCL / in-process pulls), or -- with the
+// pushes fused into the producing kernels (halo.cuh) -- nothing but the test transport's host barrier.
+#define HALO(L, arr) do { if ((L).dist) { int rc__ = fused ? fb_halo_point(c) : fb_halo_fill(c, (L).g, (arr), sizeof(float), 1, 1); if (rc__) return rc__; } } while (0)
 int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const int nl = c->mg_levels;
   const int dist = c->world > 1 ? 1 : 0;
+  const bool fused = c->halo.mode != 0;
   const dim3 pblk(32, 8, 1);
   Sweep S[MG_MAX_LEVELS];
   MgCoef mc[MG_MAX_LEVELS];
   for (int l = 0; l < nl; ++l) { S[l] = make_sweep(c->mg[l].g, c->mg[l].box); mc[l] = make_mg_coef(c->mg[l].h2inv); }
   if (sweep_empty(S[0])) return 0;
+  const size_t F = sizeof(float);
   for (int l = 0; l < nl - 1; ++l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const dim3 tg = stencil_grid(S[l]);
+    const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(L, L.xa);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist);
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+                                                            fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     HALO(L, L.xb);
-    k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
+    k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
+                                                    fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     HALO(L, L.xa);
     Box cb = C.box;
+    int ck0 = C.g.k0, ck1 = C.g.k1 - 1;          // boundary planes in the coarse index space
     if (L.dist && !C.dist) {            // this rank restricts into the planes whose children it owns
       cb.z0 = max(C.gbox.z0, C.zs[c->rank]); cb.z1 = min(C.gbox.z1, C.zs[c->rank + 1]);
+      ck0 = C.zs[c->rank]; ck1 = C.zs[c->rank + 1] - 1;
     }
-    if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0) {
-      dim3 cg(cdiv(cb.x1 - cb.x0, 32), cdiv(cb.y1 - cb.y0, 8), cb.z1 - cb.z0);
-      k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds);
+    {
+      // the sequence number is taken even when this rank has nothing to restrict
+      dim3 cg(max(1, cdiv(cb.x1 - cb.x0, 32)), max(1, cdiv(cb.y1 - cb.y0, 8)), max(1, cb.z1 - cb.z0));
+      PeerHalo H = fb_halo_make(c, l, HA_XA, C.dist ? l + 1 : -1, C.dist ? HA_XA : -1, F, ck0, ck1, cg.x * cg.y);
+      if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0)
+        k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, H);
     }
     if (L.dist && !C.dist) {
       int rc = fb_allgather_planes(c, C.g, C.b, sizeof(float), C.zs);
@@ -529,13 +565,19 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     const Box& fb = L.box;
     dim3 pg(cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
     const dim3 tg = stencil_grid(S[l]);
+    const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(C, C.xb);
-    k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds);
+    k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds,
+                                             fb_halo_make(c, C.dist ? l + 1 : -1, C.dist ? HA_XB : -1, l, HA_XB, F, k0, k1, pg.x * pg.y));
     HALO(L, L.xb);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist);
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+                                                            fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     HALO(L, L.xa);
-    if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist);
-    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist);
+    // the last sweep's output is read through ghosts only as the coarse correction of the level above
+    if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
+                                                                       fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
+    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+                                                                 fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     c->launches += 3;
   }
   CK_LAUNCH();

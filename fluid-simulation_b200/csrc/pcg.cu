@@ -19,10 +19,11 @@
 // Kernel shapes: sweep.cuh (STREAM for K2/K3/init, STENCIL for K1).
 #include "sweep.cuh"
 #include "pcg.cuh"
+#include "halo.cuh"
 #include <stdlib.h>
 
-__global__ void k_pcg_reset(DevScalars* ds, double bnorm2, double threshold, int max_iter) {
-  ds->threshold = threshold; ds->pcg_max_iter = max_iter;
+__global__ void k_pcg_reset(DevScalars* ds, double bnorm2, double threshold, int max_iter, int halo_base) {
+  ds->threshold = threshold; ds->pcg_max_iter = max_iter; ds->halo_base = halo_base;
   for (int s = 0; s < 4; ++s) { ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0; }
   // |r|^2 of "iteration -1" (= |b|^2): scale of the first preconditioner applications
   ds->rr[2] = bnorm2; ds->rr[3] = bnorm2;
@@ -36,7 +37,8 @@ template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
            const float* __restrict__ b, double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
-           float* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds, int dist) {
+           float* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds, int dist,
+           const __grid_constant__ PeerHalo H) {
   __shared__ double sm[32];
   STREAM_PROLOGUE(S)
   double acc[1] = {0.0};
@@ -55,6 +57,7 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
       float s0 = (float)(r0 * sc), s1 = (float)(r1 * sc);
       st2<float>(b0 + q, s0, s1);
       st2<float>(x1 + q, cf.winv[k0] * s0, cf.winv[k1] * s1);
+      halo_push2<float>(H, q, k, cf.winv[k0] * s0, cf.winv[k1] * s1);
       st2<double>(p + q, 0.0, 0.0);
     }
   }
@@ -62,16 +65,21 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[3], acc[0]);
   }
+  if (MODE == 1) halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
 // K1: Ap = A p and p.Ap (STENCIL shape: z-march in registers, x neighbours by shuffle)
 __global__ void __launch_bounds__(32 * ST_BY)
 k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
        const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit,
-       int dist) {
+       int dist, const __grid_constant__ PeerHalo H) {
   __shared__ double sm[32];
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
+  {
+    const int kz0 = S.box.z0 + blockIdx.z * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+    halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
+  }
   double acc[1] = {0.0};
   StencilMarch<double> m;
   if (m.begin(S, p)) {
@@ -100,7 +108,7 @@ __global__ void __launch_bounds__(32 * SW_BY)
 k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
             double* __restrict__ x, double* __restrict__ r, const double* __restrict__ p,
             const double* __restrict__ Ap, float* __restrict__ b0, float* __restrict__ x1,
-            DevScalars* __restrict__ ds, int it_arg, int noexit, int dist) {
+            DevScalars* __restrict__ ds, int it_arg, int noexit, int dist, const __grid_constant__ PeerHalo H) {
   __shared__ double sm[64];
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
@@ -133,6 +141,7 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
       float s0 = (float)(r0 * sc), s1 = (float)(r1 * sc);
       st2<float>(b0 + q, s0, s1);
       st2<float>(x1 + q, cf.winv[k0] * s0, cf.winv[k1] * s1);
+      halo_push2<float>(H, q, k, cf.winv[k0] * s0, cf.winv[k1] * s1);
     }
   }
   block_sum<2>(acc, sm);
@@ -140,6 +149,7 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
     if (acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RR] : &ds->rr[it & 3], acc[0]);
     if (MODE == 0 && acc[1] != 0.0) atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[1]);
   }
+  if (MODE == 1) halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
 // stop test of ConjugateGradient.h:77-78 (MG path: evaluated before the preconditioner is applied)
@@ -171,7 +181,7 @@ template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
            const double* __restrict__ r, const float* __restrict__ zf, double* __restrict__ p,
-           DevScalars* __restrict__ ds, int it_arg, int noexit) {
+           DevScalars* __restrict__ ds, int it_arg, int noexit, const __grid_constant__ PeerHalo H) {
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   const bool lead = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0;
@@ -185,28 +195,30 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   const double rrp = ds->rr[(it + 3) & 3];
   const double invsc = MODE == 1 ? (rrp > 0.0 ? sqrt(rrp) : 1.0) : 0.0;
   STREAM_PROLOGUE(S)
-  if (!act) return;
-  uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
-  double2 pv = ld2<double>(p + q);
-  double z0, z1;
-  if (MODE == 0) {
-    double2 rv = ld2<double>(r + q);
-    z0 = rv.x * cf.inv[6 - __popc(f.x & FB_SMASK)]; z1 = rv.y * cf.inv[6 - __popc(f.y & FB_SMASK)];
-  } else {
-    float2 zv = ld2<float>(zf + q);
-    z0 = (double)zv.x * invsc; z1 = (double)zv.y * invsc;
+  if (act) {
+    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    double2 pv = ld2<double>(p + q);
+    double z0, z1;
+    if (MODE == 0) {
+      double2 rv = ld2<double>(r + q);
+      z0 = rv.x * cf.inv[6 - __popc(f.x & FB_SMASK)]; z1 = rv.y * cf.inv[6 - __popc(f.y & FB_SMASK)];
+    } else {
+      float2 zv = ld2<float>(zf + q);
+      z0 = (double)zv.x * invsc; z1 = (double)zv.y * invsc;
+    }
+    const double p0 = (f.x & FB_FLUID) ? z0 + beta * pv.x : 0.0;
+    const double p1 = (f.y & FB_FLUID) ? z1 + beta * pv.y : 0.0;
+    if ((f.x | f.y) & FB_FLUID) st2<double>(p + q, p0, p1);
+    halo_push2<double>(H, q, k, p0, p1);          // the neighbours' ghost planes see 0 off the fluid cells
   }
-  if ((f.x | f.y) & FB_FLUID) {
-    double p0 = (f.x & FB_FLUID) ? z0 + beta * pv.x : 0.0;
-    double p1 = (f.y & FB_FLUID) ? z1 + beta * pv.y : 0.0;
-    st2<double>(p + q, p0, p1);
-  }
+  halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
 // end of an iteration: clear the ring slot the next iteration accumulates into, enforce the
 // iteration limit (IterativeSolverBase.h:283) and advance the device-side iteration counter
-__global__ void k_pcg_advance(DevScalars* __restrict__ ds, int it_arg, int noexit) {
+__global__ void k_pcg_advance(DevScalars* __restrict__ ds, int it_arg, int noexit, int nprod) {
   if (!noexit && ds->pcg_done) return;
+  ds->halo_base += nprod;                      // fused ghost pushes: sequence base of the next segment (halo.cuh)
   const int it = pcg_iter(ds, it_arg);
   const int s = (it + 1) & 3;
   ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0;
@@ -233,19 +245,39 @@ void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
 // one CG iteration on the stream (it_arg = explicit iteration or IT_DEV for graph replay).
 // z-slab runs add: a one-plane halo fill of the search direction before A.p and an all-reduce +
 // publish after every kernel that ends in a dot product.
+// bookkeeping of the fused ghost pushes (halo.cuh): a "segment" is what runs between two
+// k_pcg_advance launches; sequence numbers inside kernels are relative to its base.
+static inline int halo_seg_close(flipb200_ctx* c) {
+  HaloState& hs = c->halo;
+  const int n = (int)(hs.abs_seq - hs.seg_base);
+  hs.seg_base = hs.abs_seq;
+  return n;
+}
+static inline void halo_replayed(flipb200_ctx* c, int n) {   // a captured iteration ran again: shift the host mirror
+  HaloState& hs = c->halo;
+  if (hs.mode == 0) return;
+  hs.abs_seq += n; hs.seg_base += n;
+  for (int l = 0; l < MG_MAX_LEVELS; ++l) for (int a = 0; a < 3; ++a) hs.last_prod[l][a] += n;
+}
+
 static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, int it_arg, int noexit) {
   const dim3 sg = stream_grid(S), tg = stencil_grid(S);
   MgLevel& L0 = c->mg[0];
   const int dist = c->world > 1 ? 1 : 0;
+  const bool fused = use_mg && c->halo.mode != 0;
+  const int k0 = c->g.k0, k1 = c->g.k1 - 1;
   int rc;
-  if ((rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1))) return rc;
-  k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist);
+  if (fused) rc = fb_halo_point(c); else rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1);
+  if (rc) return rc;
+  k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist,
+                                              fused ? fb_halo_make(c, 0, HA_PD, -1, -1, 0, k0, k1, tg.x * tg.y) : halo_off());
   if (dist) {
     if ((rc = fb_allreduce(c, &c->ds->part[PART_PAP], 1, FB_F64, FB_SUM))) return rc;
     fb_pcg_publish(c, 1 << PART_PAP, it_arg);
   }
   if (use_mg) {
-    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist);
+    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
+                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     if (dist) {
       if ((rc = fb_allreduce(c, &c->ds->part[PART_RR], 1, FB_F64, FB_SUM))) return rc;
       fb_pcg_publish(c, 1 << PART_RR, it_arg);
@@ -253,16 +285,17 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg); c->launches++; }
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit,
+                                                      fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
   } else {
-    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit, dist);
+    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit, dist, halo_off());
     if (dist) {
       if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 2, FB_F64, FB_SUM))) return rc;   // r.z and r.r are adjacent
       fb_pcg_publish(c, (1 << PART_RZ) | (1 << PART_RR), it_arg);
     }
-    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, noexit);
+    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, noexit, halo_off());
   }
-  k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, noexit);
+  k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, noexit, halo_seg_close(c));
   c->launches += 4;
   return 0;
 }
@@ -284,17 +317,19 @@ static bool get_iteration_graph(flipb200_ctx* c, const Sweep& S, const PcgCoef& 
   if (ng && ng[0] == '1') return false;
   if (!fb_comm_capturable(c)) return false;      // in-process test transport synchronises on the host
   const int mode = (use_mg ? 1 : 0) | (noexit ? 2 : 0);
-  if (c->it_exec && same_box(c->it_box, c->box) && c->it_dt == dt && c->it_mode == mode) return true;
+  if (c->it_exec && same_box(c->it_box, c->box) && same_box(c->it_gbox, c->gbox) && c->it_dt == dt && c->it_mode == mode) return true;
   fb_graph_invalidate(c);
   if (cudaStreamBeginCapture(c->stream, c->world > 1 ? cudaStreamCaptureModeRelaxed : cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return false; }
   const int64_t l0 = c->launches;
+  const long long seq0 = c->halo.abs_seq;
   int rc = enqueue_iteration(c, S, cf, use_mg, IT_DEV, noexit);
+  c->it_nprod = (int)(c->halo.abs_seq - seq0);      // producers per iteration (the capture itself did not run them)
   c->it_kernels = c->launches - l0;
   c->launches = l0;
   cudaError_t e = cudaStreamEndCapture(c->stream, &c->it_graph);
   if (rc || e != cudaSuccess || !c->it_graph) { cudaGetLastError(); fb_graph_invalidate(c); return false; }
   if (cudaGraphInstantiate(&c->it_exec, c->it_graph, 0) != cudaSuccess) { cudaGetLastError(); fb_graph_invalidate(c); return false; }
-  c->it_box = c->box; c->it_dt = dt; c->it_mode = mode;
+  c->it_box = c->box; c->it_gbox = c->gbox; c->it_dt = dt; c->it_mode = mode;
   return true;
 }
 
@@ -313,12 +348,25 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   const double tol = c->P.pcg_tol;
   const double threshold = tol * tol * bnorm2;     // ConjugateGradient.h:53
   const int max_iter = c->P.pcg_max_iter < 0 ? 2 * c->n_fluid : c->P.pcg_max_iter;   // IterativeSolverBase.h:283
-  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2, threshold, max_iter);
+  if (c->world > 1 && !c->halo_ready) {            // first collective solve: map the neighbours' arrays (halo.cuh)
+    int rc = fb_halo_setup(c);
+    if (rc) return rc;
+    c->halo_ready = true;
+  }
+  const bool fused = use_mg && c->halo.mode != 0;
+  const int k0 = c->g.k0, k1 = c->g.k1 - 1;
+  if (use_mg) {
+    int rc = fb_mg_setup(c, dt);                   // hierarchy: rebuilt only when the cell classes changed
+    if (rc) return rc;
+  }
+  c->halo.seg_base = c->halo.abs_seq;
+  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2, threshold, max_iter, (int)c->halo.seg_base);
   if (use_mg)
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, L0.b, L0.xa,
-                                                      bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds, dist);
+                                                      bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds, dist,
+                                                      fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
   else {
-    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist);
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist, halo_off());
     if (dist) {
       int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
       if (rc) return rc;
@@ -330,12 +378,11 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (!(bnorm2 == bnorm2)) return FLIPB200_ERR_BREAKDOWN;
   bool done = max_iter == 0;
   if (use_mg && !done) {
-    int rc = fb_mg_setup(c, dt);                   // hierarchy: rebuilt only when the cell classes changed
+    int rc = fb_mg_vcycle(c, -1);                  // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
-    rc = fb_mg_vcycle(c, -1);                      // z0 = M^-1 r0, rz[3] = r0.z0
-    if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 0);
-    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 0);
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 0,
+                                                      fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 0, halo_seg_close(c));
     c->launches += 2;
   }
   const bool graph = !done && get_iteration_graph(c, S, cf, use_mg, dt, 0);
@@ -348,6 +395,7 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
       if (graph) {
         if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }
         c->launches += c->it_kernels;
+        halo_replayed(c, c->it_nprod);
       } else {
         int rc = enqueue_iteration(c, S, cf, use_mg, it, 0);
         if (rc) return rc;
@@ -363,6 +411,7 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (iters_out) *iters_out = c->hs->pcg_iters;
   if (rel_out) *rel_out = sqrt(c->hs->rr_final / bnorm2);          // cg.error(), ConjugateGradient.h:88
   if (c->hs->pcg_status == FLIPB200_ERR_BREAKDOWN) return FLIPB200_ERR_BREAKDOWN;
+  if (c->hs->pcg_status == FLIPB200_ERR_COMM) return FLIPB200_ERR_COMM;     // a ghost-plane wait timed out (halo.cuh)
   return 0;   // hitting max_iter is reported through iters == max_iter, as Eigen does
 }
 
@@ -379,15 +428,25 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   const int dist = c->world > 1 ? 1 : 0;
   MgLevel& L0 = c->mg[0];
   const double bn = c->hs->bnorm2 > 0.0 ? c->hs->bnorm2 : 1.0;
-  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn, 0.0, 1 << 30);
+  if (c->world > 1 && !c->halo_ready) {
+    int rc = fb_halo_setup(c);
+    if (rc) return rc;
+    c->halo_ready = true;
+  }
+  const bool fused = use_mg && c->halo.mode != 0;
+  const int k0 = c->g.k0, k1 = c->g.k1 - 1;
+  if (use_mg) { int rc = fb_mg_setup(c, dt); if (rc) return rc; }
+  c->halo.seg_base = c->halo.abs_seq;
+  k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn, 0.0, 1 << 30, (int)c->halo.seg_base);
   if (use_mg) {
-    k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds, dist);
-    int rc = fb_mg_setup(c, dt); if (rc) return rc;
-    rc = fb_mg_vcycle(c, -1); if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1);
-    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1);
+    k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds, dist,
+                                                      fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
+    int rc = fb_mg_vcycle(c, -1); if (rc) return rc;
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1,
+                                                      fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1, halo_seg_close(c));
   } else {
-    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist);
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist, halo_off());
     if (dist) {
       int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
       if (rc) return rc;
@@ -399,11 +458,12 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   for (int it = 0; it < 3 + iters; ++it) {
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
-      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1, 0);
+      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1, 0, halo_off());
       c->launches++;
     } else if (graph) {
       if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }
       c->launches += c->it_kernels;
+      halo_replayed(c, c->it_nprod);
     } else {
       int rc = enqueue_iteration(c, S, cf, use_mg, it, 1);
       if (rc) return rc;

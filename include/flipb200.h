@@ -104,6 +104,10 @@ int  flipb200_comm_unique_id(void* id128);                         /* ncclGetUni
 int  flipb200_comm_init_nccl(flipb200_ctx*, const void* id128);    /* ncclCommInitRank(world, id, rank) */
 int  flipb200_comm_init_local(flipb200_ctx*, int32_t group_id);
 int  flipb200_get_particle_ids(flipb200_ctx*, uint32_t* ids, int64_t cap);   /* needs params.track_ids */
+/* how the PCG ghost planes travel, known after the first solve: 0 = separate copies (NCCL send/recv),
+ * 1 = pushed by the producing kernels + host barrier (in-process ranks), 2 = pushed over NVLink peer
+ * mappings with device-side flags (one process per GPU; csrc/halo.cuh) */
+int  flipb200_halo_mode(flipb200_ctx*);
 /* flipb200_step_host for a slab (collective): the rank uploads ITS n particles (every base plane
  * must be owned by the rank or an adjacent one), steps, and gets back the *n_out particles it owns
  * after migration (host arrays hold `cap` entries) and, optionally, its owned planes of outputGrid. */

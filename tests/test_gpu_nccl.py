@@ -15,8 +15,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _worker(rank, world, port, nsteps, no_graph, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
-    if no_graph:
+    if no_graph & 1:
         os.environ["FLIPB200_NO_GRAPH"] = "1"
+    if no_graph & 2:
+        os.environ["FLIPB200_FUSED_HALO"] = "0"
     for p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
     import torch
@@ -47,6 +49,7 @@ def _worker(rank, world, port, nsteps, no_graph, q):
             log.append(rec)
         p, v = f.get_particles()
         ids = f.get_particle_ids()
+        assert f.halo_mode == (0 if os.environ.get("FLIPB200_FUSED_HALO") == "0" else 2), f.halo_mode
         parts = [None] * world
         dist.gather_object((ids, p, v, f.get_grid(fb.GRID_P), log), parts if rank == 0 else None, dst=0)
         if rank == 0:
@@ -68,7 +71,7 @@ def _worker(rank, world, port, nsteps, no_graph, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("no_graph", [0, 1])
+@pytest.mark.parametrize("no_graph", [0, 1, 2])   # bit 0: no CUDA graph, bit 1: NCCL halo copies instead of fused pushes
 def test_nccl_slabs_match_single(no_graph):
     import torch
     ngpu = torch.cuda.device_count()

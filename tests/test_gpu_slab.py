@@ -86,8 +86,11 @@ def moving_scene(scenes, n=32, seed=5):
     return sc
 
 
-@pytest.mark.parametrize("world,precond", [(2, 1), (4, 1), (2, 0)])
-def test_slab_steps_match_single(fb, scenes, world, precond):
+@pytest.mark.parametrize("world,precond,fused", [(2, 1, 1), (4, 1, 1), (2, 1, 0), (2, 0, 1)])
+def test_slab_steps_match_single(fb, scenes, world, precond, fused, monkeypatch):
+    """fused=1: ghost planes are pushed by the producing kernels (halo.cuh; here ordered by the host
+    barrier of the in-process transport); fused=0: separate halo copies."""
+    monkeypatch.setenv("FLIPB200_FUSED_HALO", str(fused))
     sc = moving_scene(scenes, n=32)
     nsteps = 6
     f1 = fb.Flip.from_scene(sc, track_ids=1, precond=precond)
@@ -113,6 +116,7 @@ def test_slab_steps_match_single(fb, scenes, world, precond):
         for a in range(3):
             assert rel_l2(gather_grid(fs, fb.GRID_U + a), f1.get_grid(fb.GRID_U + a)) < 1e-9, (step, a)
         assert rel_l2(gather_grid(fs, fb.GRID_P), f1.get_grid(fb.GRID_P)) < 1e-8, step
+    assert all(f.halo_mode == (1 if (fused and precond == 1) else 0) for f in fs)
     p1, v1 = f1.get_particles()
     ps, vs = gather_particles(fs, sc.num_particles)
     assert rel_l2(ps, p1) < 1e-10 and rel_l2(vs, v1) < 1e-9
