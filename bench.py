@@ -221,6 +221,7 @@ def main():
     wall = max_over_ranks(wall)
     value = total_particles * args.steps / dev_s
 
+    config["engine"] = f.debug_info()
     # ---- kernel roofline (dominant kernel: the PCG stencil) ----
     peak, peak_src = measured_peak_gbs()
     f.p2g(); f.classify(); f.rhs_div(dt)

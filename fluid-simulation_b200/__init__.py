@@ -63,7 +63,7 @@ EXPORTS = [
     "flipb200_g2p_advect", "flipb200_get_grid", "flipb200_set_grid", "flipb200_time_kernel",
     "flipb200_host_alloc", "flipb200_host_free",
     "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
-    "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab", "flipb200_halo_mode",
+    "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab", "flipb200_halo_mode", "flipb200_debug_info",
 ]
 
 _lib = None
@@ -119,6 +119,7 @@ def load():
     lib.flipb200_comm_init_local.argtypes = [vp, C.c_int32]
     lib.flipb200_get_particle_ids.argtypes = [vp, vp, C.c_int64]
     lib.flipb200_halo_mode.argtypes = [vp]
+    lib.flipb200_debug_info.argtypes = [vp, ip]
     lib.flipb200_step_host_slab.argtypes = [vp] + [vp] * 6 + [C.c_int64, C.c_int64, C.POINTER(C.c_int64), dp, vp,
                                                               C.POINTER(Stats)]
     _lib = lib
@@ -200,6 +201,13 @@ class Flip:
     def comm_init_nccl(self, unique_id):
         buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
         _check(self.lib.flipb200_comm_init_nccl(self.h, buf), "comm_init_nccl")
+
+    def debug_info(self):
+        out = (C.c_int32 * 8)()
+        _check(self.lib.flipb200_debug_info(self.h, out), "debug_info")
+        keys = ["halo_mode", "iteration_graph", "mg_levels", "mg_distributed_levels", "kernels_per_iteration",
+                "pushing_kernels_per_iteration", "rank", "world"]
+        return dict(zip(keys, list(out)))
 
     @property
     def halo_mode(self):

@@ -405,6 +405,14 @@ int fb_comm_exchange_particles(flipb200_ctx* c, int narr, void* const src[], voi
 }
 
 extern "C" int flipb200_halo_mode(flipb200_ctx* c) { return c ? c->halo.mode : FLIPB200_ERR_ARG; }
+// diagnostics for bench.py: [0] halo mode [1] PCG iteration replayed from a CUDA graph [2] multigrid levels
+// [3] distributed levels [4] kernels per iteration [5] ghost-pushing kernels per iteration [6] rank [7] world
+extern "C" int flipb200_debug_info(flipb200_ctx* c, int32_t* out8) {
+  if (!c || !out8) return FLIPB200_ERR_ARG;
+  out8[0] = c->halo.mode; out8[1] = c->it_exec ? 1 : 0; out8[2] = c->mg_levels; out8[3] = c->mg_nd;
+  out8[4] = (int32_t)c->it_kernels; out8[5] = c->it_nprod; out8[6] = c->rank; out8[7] = c->world;
+  return FLIPB200_OK;
+}
 
 bool fb_comm_capturable(flipb200_ctx* c) { return c->world == 1 || (c->comm && c->comm->kind == 1); }
 

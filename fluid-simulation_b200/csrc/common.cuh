@@ -108,6 +108,17 @@ struct MgLevel {
 };
 
 #define MG_MAX_LEVELS 12
+// FLIPB200_PROFILE_ITER=1: stage-by-stage CUDA-event timing of the PCG iteration inside
+// flipb200_time_kernel(PCG_ITER) (plain launches, one stream sync per iteration); printed to stderr.
+#define PROF_MAX 96
+struct IterProf {
+  bool on;
+  int n;                       // marks of the current iteration
+  cudaEvent_t ev[PROF_MAX];
+  const char* name[PROF_MAX];
+  double acc[PROF_MAX];
+  int iters;
+};
 struct Comm;   // comm.cu: NCCL (one process per GPU) or in-process threaded ranks (tests)
 
 // host state of the ghost-plane pushes fused into the PCG kernels (halo.cuh, comm.cu)
@@ -132,6 +143,7 @@ struct flipb200_ctx {
   int slab_align;          // log2 of the alignment of the slab boundaries (mg.cu: distributed levels)
   double* halo_tmp;        // 4 planes of doubles: receive buffer of the P2G ghost sum
   HaloState halo;
+  IterProf* prof;
   bool halo_ready;         // fb_halo_setup has run (lazily, at the first collective solve)
   int device;
   int num_sms;
@@ -302,4 +314,12 @@ bool fb_comm_capturable(flipb200_ctx* c);
 int fb_halo_setup(flipb200_ctx* c);
 int fb_halo_point(flipb200_ctx* c);          // a place where a halo copy used to be (host barrier of the test transport)
 
+static inline void fb_prof(flipb200_ctx* c, const char* name) {
+  IterProf* p = c->prof;
+  if (!p || !p->on || p->n >= PROF_MAX) return;
+  if (!p->ev[p->n]) cudaEventCreate(&p->ev[p->n]);
+  p->name[p->n] = name;
+  cudaEventRecord(p->ev[p->n], c->stream);
+  p->n++;
+}
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }

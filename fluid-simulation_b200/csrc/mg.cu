@@ -29,7 +29,7 @@
 #define MG_COARSE_SWEEPS 40
 #define MG_COARSEST_CELLS 4096
 
-#define MG_REPLICATED_CELLS (1 << 18)   // z-slab runs: levels with at most this many cells are solved on every rank
+#define MG_REPLICATED_CELLS (1 << 19)   // z-slab runs: levels with at most this many cells are solved on every rank
 
 // dimensions of the whole level below `f` (f: whole-domain dimensions of the finer level)
 static void mg_level_dims(const Grid& f, Grid* c) {
@@ -258,7 +258,7 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
   __shared__ double sm[32];
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
-  const int kz0 = S.box.z0 + blockIdx.z * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   halo_wait(H, ds, bdn, bup);
   double acc[1] = {0.0};
@@ -301,7 +301,7 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
            const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
            float* __restrict__ rn, DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
-  const int kz0 = S.box.z0 + blockIdx.z * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   halo_wait(H, ds, bdn, bup);
   StencilMarch<float> m;
@@ -340,7 +340,7 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K = cbox.z0 + blockIdx.z;
+  const int K = cbox.z0 + zperm(blockIdx.z, gridDim.z);
   halo_wait(H, ds, K == H.kdn, K == H.kup);         // boundary coarse planes read the fine ghost planes
   if (J < cbox.y1) {                                // whole warp
     const bool in = I < cbox.x1;
@@ -397,7 +397,7 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = fbox.z0 + blockIdx.z;
+  const int k = fbox.z0 + zperm(blockIdx.z, gridDim.z);
   halo_wait(H, ds, k == H.kdn, k == H.kup);         // boundary fine planes read the coarse ghost planes
   if (j < fbox.y1) {                                // whole warp
     const int kg = k + gf.kg0;                         // global fine plane
@@ -527,9 +527,11 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     HALO(L, L.xa);
     k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
                                                             fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
+    fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
     k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
                                                     fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    fb_prof(c, l == 0 ? "L0 halo+resid" : (l == 1 ? "L1 halo+resid" : "L2+ halo+resid"));
     HALO(L, L.xa);
     Box cb = C.box;
     int ck0 = C.g.k0, ck1 = C.g.k1 - 1;          // boundary planes in the coarse index space
@@ -544,10 +546,12 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
       if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0)
         k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, H);
     }
+    fb_prof(c, l == 0 ? "L0 halo+restrict" : (l == 1 ? "L1 halo+restrict" : "L2+ halo+restrict"));
     if (L.dist && !C.dist) {
       int rc = fb_allgather_planes(c, C.g, C.b, sizeof(float), C.zs);
       if (!rc) rc = fb_allgather_planes(c, C.g, C.xa, sizeof(float), C.zs);
       if (rc) return rc;
+      fb_prof(c, "allgather b, xa");
     }
     c->launches += 3;
   }
@@ -558,6 +562,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     if (smem > 160 * 1024 || (int64_t)(b.x1 - b.x0) * (b.y1 - b.y0) * (b.z1 - b.z0) > 4096) return FLIPB200_ERR_ARG;
     k_mg_coarsest<<<1, 1024, smem, c->stream>>>(S[nl - 1], mc[nl - 1], L.flags, L.b, L.xb, c->ds);
     c->launches++;
+    fb_prof(c, "coarsest");
   }
   for (int l = nl - 2; l >= 0; --l) {
     MgLevel& L = c->mg[l];
@@ -569,15 +574,18 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     HALO(C, C.xb);
     k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds,
                                              fb_halo_make(c, C.dist ? l + 1 : -1, C.dist ? HA_XB : -1, l, HA_XB, F, k0, k1, pg.x * pg.y));
+    fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
     k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
                                                             fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
     HALO(L, L.xa);
     // the last sweep's output is read through ghosts only as the coarse correction of the level above
     if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
                                                                        fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
     else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
                                                                  fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
+    fb_prof(c, l == 0 ? "L0 halo+smooth (post 2)" : (l == 1 ? "L1 halo+smooth (post 2)" : "L2+ halo+smooth (post 2)"));
     c->launches += 3;
   }
   CK_LAUNCH();
@@ -586,5 +594,6 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     if (rc) return rc;
     fb_pcg_publish(c, 1 << PART_RZ, it);
   }
+  fb_prof(c, "allreduce rz");
   return 0;
 }

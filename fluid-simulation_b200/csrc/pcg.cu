@@ -77,7 +77,7 @@ k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, cons
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   {
-    const int kz0 = S.box.z0 + blockIdx.z * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
     halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
   }
   double acc[1] = {0.0};
@@ -267,22 +267,28 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   const bool fused = use_mg && c->halo.mode != 0;
   const int k0 = c->g.k0, k1 = c->g.k1 - 1;
   int rc;
+  fb_prof(c, "start");
   if (fused) rc = fb_halo_point(c); else rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1);
   if (rc) return rc;
+  fb_prof(c, "halo pd");
   k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist,
                                               fused ? fb_halo_make(c, 0, HA_PD, -1, -1, 0, k0, k1, tg.x * tg.y) : halo_off());
+  fb_prof(c, "k_spmv");
   if (dist) {
     if ((rc = fb_allreduce(c, &c->ds->part[PART_PAP], 1, FB_F64, FB_SUM))) return rc;
     fb_pcg_publish(c, 1 << PART_PAP, it_arg);
   }
+  fb_prof(c, "allreduce pAp");
   if (use_mg) {
     k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
+    fb_prof(c, "k_update_xr");
     if (dist) {
       if ((rc = fb_allreduce(c, &c->ds->part[PART_RR], 1, FB_F64, FB_SUM))) return rc;
       fb_pcg_publish(c, 1 << PART_RR, it_arg);
     }
     if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg); c->launches++; }
+    fb_prof(c, "allreduce rr");
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit,
@@ -295,6 +301,7 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     }
     k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, noexit, halo_off());
   }
+  fb_prof(c, "k_update_p");
   k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, noexit, halo_seg_close(c));
   c->launches += 4;
   return 0;
@@ -454,8 +461,12 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     }
   }
   bool graph = false;
-  if (which == FLIPB200_KERNEL_PCG_ITER) graph = get_iteration_graph(c, S, cf, use_mg, dt, 1);
+  const char* pe = getenv("FLIPB200_PROFILE_ITER");
+  const bool prof = pe && pe[0] == '1' && which == FLIPB200_KERNEL_PCG_ITER;
+  if (prof && !c->prof) c->prof = (IterProf*)calloc(1, sizeof(IterProf));
+  if (which == FLIPB200_KERNEL_PCG_ITER && !prof) graph = get_iteration_graph(c, S, cf, use_mg, dt, 1);
   for (int it = 0; it < 3 + iters; ++it) {
+    if (prof && it >= 3) { c->prof->on = true; c->prof->n = 0; }
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
       k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1, 0, halo_off());
@@ -468,6 +479,22 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
       int rc = enqueue_iteration(c, S, cf, use_mg, it, 1);
       if (rc) return rc;
     }
+    if (prof && it >= 3) {
+      IterProf* p = c->prof;
+      p->on = false;
+      CK(cudaStreamSynchronize(c->stream));
+      for (int m = 1; m < p->n; ++m) { float t = 0.f; cudaEventElapsedTime(&t, p->ev[m - 1], p->ev[m]); p->acc[m] += t; }
+      p->iters++;
+    }
+  }
+  if (prof && c->prof->iters > 0) {
+    IterProf* p = c->prof;
+    double tot = 0.0;
+    for (int m = 1; m < p->n; ++m) tot += p->acc[m] / p->iters;
+    fprintf(stderr, "flipb200 rank %d: PCG iteration profile over %d iterations (plain launches), total %.1f us\n", c->rank, p->iters, tot * 1e3);
+    for (int m = 1; m < p->n; ++m) fprintf(stderr, "  r%d %-28s %8.1f us\n", c->rank, p->name[m], p->acc[m] / p->iters * 1e3);
+    for (int m = 0; m < PROF_MAX; ++m) p->acc[m] = 0.0;
+    p->iters = 0;
   }
   CK(cudaEventRecord(c->ev[7], c->stream));
   CK(cudaStreamSynchronize(c->stream));

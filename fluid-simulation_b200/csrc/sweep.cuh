@@ -57,11 +57,16 @@ static inline dim3 stencil_grid(const Sweep& s) {
 #define STREAM_BLOCK dim3(32, SW_BY, 1)
 #define STENCIL_BLOCK dim3(32, ST_BY, 1)
 
+// Block z index -> plane (chunk) index: the first and the last chunk of the sweep are issued FIRST.
+// z-slab runs push those boundary planes to the neighbours (halo.cuh); doing them at the start of
+// the kernel hides the NVLink signalling latency behind the interior of the sweep.
+__device__ __forceinline__ int zperm(int bz, int nz) { return bz == 0 ? 0 : (bz == 1 ? nz - 1 : bz - 1); }
+
 // STREAM prologue: i (even x of this lane), j, k, q and `act`
 #define STREAM_PROLOGUE(S)                                                      \
   const int i = (S).box.x0 + blockIdx.x * 64 + 2 * threadIdx.x;                 \
   const int j = (S).box.y0 + blockIdx.y * SW_BY + threadIdx.y;                  \
-  const int k = (S).box.z0 + blockIdx.z;                                        \
+  const int k = (S).box.z0 + zperm(blockIdx.z, gridDim.z);                      \
   const bool act = i < (S).xe && j < (S).box.y1;                                \
   const int q = gidx((S).g, i, j, k);
 
@@ -79,7 +84,7 @@ struct StencilMarch {
     lane = threadIdx.x;
     i = S.box.x0 + blockIdx.x * 64 + 2 * lane;
     j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
-    k = S.box.z0 + blockIdx.z * ST_ZP;
+    k = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP;
     if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
     act = i < S.xe;
     jlo = j > 0; jhi = j < S.g.ny - 1;
