@@ -67,7 +67,7 @@ class ClockSampler:
                     self.samples.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.25)
 
     def start(self):
         self._t = threading.Thread(target=self._run, daemon=True)
@@ -203,9 +203,12 @@ def main():
     stats = []
     for _ in range(args.warmup):
         dt, st = f.step(dt)
+    # one sampler for the job (rank 0, its own GPU): concurrent nvidia-smi polls from every rank
+    # serialise on the driver and perturb the step they are meant to observe
     sampler = ClockSampler(local_rank)
     barrier()
-    sampler.start()
+    if rank == 0 and not os.environ.get("FLIPB200_BENCH_NOSMI"):
+        sampler.start()
     t0 = time.perf_counter()
     dev_ms = 0.0
     launches = 0
