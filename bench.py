@@ -233,8 +233,16 @@ def main():
     ms_p2g, npart = f.time_kernel(fb.KERNEL_P2G, 5)
     ms_sort, _ = f.time_kernel(fb.KERNEL_SORT, 5)
     ach = 17.0 * nodes / (ms_spmv * 1e-3) / 1e9
+    traffic = None          # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu capture
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_spmv"]
+        if tj["grid"] == [n, n, n]:
+            traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": "k_spmv (7-pt matrix-free A.p + p.Ap)", "achieved": ach, "peak": peak,
-                "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu, per launch)" if traffic else None,
+                "algorithmic_bytes": 17 * nodes, "peak_source": peak_src,
                 "algorithmic_bytes_per_node": 17, "swept_nodes": nodes, "us_per_launch": ms_spmv * 1e3}
     kernels = {
         "pcg_iteration": {"bytes_per_node": 91, "us": ms_iter * 1e3, "gbs": 91.0 * nodes / (ms_iter * 1e-3) / 1e9,

@@ -10,7 +10,7 @@
 //    any child is fluid, else SOLID.
 //  * operator on every level: rediscretised 7-point, A x = h2inv*(k x_c - sum fluid nbrs), k = number
 //    of non-solid neighbours (air = Dirichlet 0, solid = Neumann); h2inv_l = scale / 4^l.
-//  * smoother: damped Jacobi (omega = 0.8), 2 pre + 2 post sweeps (symmetric).
+//  * smoother: damped Jacobi, 2 pre sweeps with weights (0.6, 1.7) + 2 post sweeps in the reversed order (symmetric).
 //  * prolongation P: cell-centred trilinear (3/4,1/4 per axis) with the weights of SOLID coarse
 //    cells dropped and the rest renormalised (constant extrapolation at Neumann walls) -- the
 //    normaliser of every fine cell is an integer n64/64 kept in a byte array per level;
@@ -258,7 +258,7 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
   __shared__ double sm[32];
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
-  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   halo_wait(H, ds, bdn, bup);
   double acc[1] = {0.0};
@@ -301,7 +301,7 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
            const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
            float* __restrict__ rn, DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
-  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   halo_wait(H, ds, bdn, bup);
   StencilMarch<float> m;
@@ -340,7 +340,7 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K = cbox.z0 + zperm(blockIdx.z, gridDim.z);
+  const int K = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode);
   halo_wait(H, ds, K == H.kdn, K == H.kup);         // boundary coarse planes read the fine ghost planes
   if (J < cbox.y1) {                                // whole warp
     const bool in = I < cbox.x1;
@@ -397,7 +397,7 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = fbox.z0 + zperm(blockIdx.z, gridDim.z);
+  const int k = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode);
   halo_wait(H, ds, k == H.kdn, k == H.kup);         // boundary fine planes read the coarse ghost planes
   if (j < fbox.y1) {                                // whole warp
     const int kg = k + gf.kg0;                         // global fine plane
@@ -515,8 +515,11 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const bool fused = c->halo.mode != 0;
   const dim3 pblk(32, 8, 1);
   Sweep S[MG_MAX_LEVELS];
-  MgCoef mc[MG_MAX_LEVELS];
-  for (int l = 0; l < nl; ++l) { S[l] = make_sweep(c->mg[l].g, c->mg[l].box); mc[l] = make_mg_coef(c->mg[l].h2inv); }
+  MgCoef mc[MG_MAX_LEVELS], mc2[MG_MAX_LEVELS];   // mc: weight W1 (first pre-sweep, last post-sweep), mc2: W2
+  for (int l = 0; l < nl; ++l) {
+    S[l] = make_sweep(c->mg[l].g, c->mg[l].box);
+    mc[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA1); mc2[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA2);
+  }
   if (sweep_empty(S[0])) return 0;
   const size_t F = sizeof(float);
   for (int l = 0; l < nl - 1; ++l) {
@@ -525,7 +528,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     const dim3 tg = stencil_grid(S[l]);
     const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(L, L.xa);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
                                                             fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
@@ -576,7 +579,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
                                              fb_halo_make(c, C.dist ? l + 1 : -1, C.dist ? HA_XB : -1, l, HA_XB, F, k0, k1, pg.x * pg.y));
     fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
                                                             fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
     HALO(L, L.xa);

@@ -221,6 +221,94 @@ k_p2g_cell(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Row-staged variants (FLIPB200_P2G=row / FLIPB200_G2P=row; parity-tested, not the default).  A warp owns 32 consecutive base cells of one x-row; because the
+// particles are cell-sorted, the particles of those cells are ONE contiguous range of the SoA arrays.
+// The warp streams that range into shared memory with 8-byte cp.async (fully coalesced, no
+// registers held while the loads fly), then every lane walks the particles of its own cell out of
+// shared memory and accumulates in registers exactly like the per-cell kernels.  The per-cell
+// kernels issue one dependent 8-byte load per lane and iteration with a 64-byte stride between
+// lanes (ncu: 25 % occupancy, 37 % DRAM utilisation, LSU wavefronts 66 %, fp64 pipe 40 %).  Measured on
+// B200 at 256^3 / 8 ppc the staged kernels are NOT faster (P2G 2.68 vs 2.45 ms): with 128 registers and 55 KB
+// of shared memory per block only 12 warps are resident and the fp64 pipe starves during the load phases.  Shared-memory index t of a
+// chunk is padded to t + t/8: with ~8 particles per cell the lanes' walks start 8 apart, which
+// would put them on two banks.
+// ---------------------------------------------------------------------------------------------
+#define ROW_CH 256                                   // particles per staged chunk
+#define ROW_PAD(t) ((t) + ((t) >> 3))
+#define ROW_STRIDE (ROW_CH + ROW_CH / 8 + 2)         // doubles per attribute and warp
+#define ROW_WARPS 4
+#define ROW_SMEM(nattr) ((size_t)ROW_WARPS * (nattr) * ROW_STRIDE * sizeof(double))
+
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+__global__ void __launch_bounds__(32 * ROW_WARPS)
+k_p2g_row(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
+          const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+          const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+          double* __restrict__ wacc, double* __restrict__ ux, double* __restrict__ uy, double* __restrict__ uz) {
+  extern __shared__ double rsm[];
+  const int lane = threadIdx.x;
+  double* sm = rsm + (size_t)threadIdx.y * 6 * ROW_STRIDE;
+  const int i = box.x0 + blockIdx.x * 32 + lane;
+  const int j = box.y0 + blockIdx.y * ROW_WARPS + threadIdx.y;
+  const int k = box.z0 + blockIdx.z;
+  if (j >= box.y1 || j > g.ny - 2 || k + g.kg0 > g.gnz - 2) return;          // whole warp
+  const bool valid = i < box.x1 && i <= g.nx - 2;
+  const int q0 = gidx(g, box.x0 + blockIdx.x * 32, j, k);
+  const int q = q0 + lane;
+  int s = 0, e = 0;
+  if (valid) { s = start[q]; e = start[q + 1]; }
+  const unsigned vm = __ballot_sync(0xffffffffu, valid);
+  if (vm == 0) return;
+  const int S = __shfl_sync(0xffffffffu, s, 0), E = __shfl_sync(0xffffffffu, e, 31 - __clz(vm));
+  if (E == S) return;
+  double aw[8], ax[8], ay[8], az[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { aw[m] = 0; ax[m] = 0; ay[m] = 0; az[m] = 0; }
+  const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+  for (int cs = S; cs < E; cs += ROW_CH) {
+    const int cn = min(ROW_CH, E - cs);
+    for (int t = lane; t < cn; t += 32) {
+      const int u = ROW_PAD(t);
+      cp_async8(sm + 0 * ROW_STRIDE + u, px + cs + t); cp_async8(sm + 1 * ROW_STRIDE + u, py + cs + t);
+      cp_async8(sm + 2 * ROW_STRIDE + u, pz + cs + t); cp_async8(sm + 3 * ROW_STRIDE + u, vx + cs + t);
+      cp_async8(sm + 4 * ROW_STRIDE + u, vy + cs + t); cp_async8(sm + 5 * ROW_STRIDE + u, vz + cs + t);
+    }
+    cp_async_wait_all();
+    __syncwarp();
+    const int n0 = max(s, cs), n1 = min(e, cs + cn);
+    for (int n = n0; n < n1; ++n) {
+      const int u = ROW_PAD(n - cs);
+      double x = sm[u], y = sm[ROW_STRIDE + u], z = sm[2 * ROW_STRIDE + u];
+      double a = sm[3 * ROW_STRIDE + u], b = sm[4 * ROW_STRIDE + u], cc = sm[5 * ROW_STRIDE + u];
+      double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+      double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+      double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);   // (sx*sy)*sz, fluid.cc:291
+        aw[m] += cw; ax[m] += cw * a; ay[m] += cw * b; az[m] += cw * cc;
+      }
+    }
+    __syncwarp();
+  }
+  if (s == e) return;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+    if (fl[qq] & FB_SOLID) continue;            // fluid.cc:288
+    atomicAdd(&wacc[qq], aw[m]);
+    atomicAdd(&ux[qq], ax[m]);
+    atomicAdd(&uy[qq], ay[m]);
+    atomicAdd(&uz[qq], az[m]);
+  }
+}
+
 // Reference-shaped variant: one thread per particle, 32 atomics each.  Kept as the cross-check of
 // the cell kernel (FLIPB200_P2G=particle) and as the path for unsorted input.
 __global__ void k_p2g_particle(Grid g, int64_t n, const uint8_t* __restrict__ fl,
@@ -273,8 +361,16 @@ int fb_p2g(flipb200_ctx* c) {
   if (c->n_sorted > 0) {
     Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
     dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
-    k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                           pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    if (!(mode && mode[0] == 'r'))   // default: per-cell kernel; FLIPB200_P2G=row: shared-memory staged variant (measured 9 % slower at 8 ppc)
+      k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                             pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    else {
+      static bool attr_set = false;
+      if (!attr_set) { CK(cudaFuncSetAttribute(k_p2g_row, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROW_SMEM(6))); attr_set = true; }
+      k_p2g_row<<<grd, dim3(32, ROW_WARPS, 1), ROW_SMEM(6), c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1],
+                                                                         pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->wacc, c->u[0],
+                                                                         c->u[1], c->u[2]);
+    }
     CK_LAUNCH(); c->launches++;
   }
   if (pt.n > c->n_sorted) {   // particles that migrated in this step (unsorted tail)
@@ -399,6 +495,94 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
   }
 }
 
+// Row-staged G2P (see k_p2g_row): positions and velocities of a row's particles are staged in
+// shared memory with coalesced cp.async, every lane updates the particles of its own cell there, and
+// the new velocities go back to HBM with coalesced stores.
+__global__ void __launch_bounds__(32 * ROW_WARPS)
+k_g2p_row(Grid g, const int32_t* __restrict__ start,
+          const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+          double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
+          const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
+          DevScalars* __restrict__ ds) {
+  extern __shared__ double rsm[];
+  __shared__ double red[ROW_WARPS];
+  const int lane = threadIdx.x;
+  double* sm = rsm + (size_t)threadIdx.y * 6 * ROW_STRIDE;
+  const int i = blockIdx.x * 32 + lane;
+  const int j = blockIdx.y * ROW_WARPS + threadIdx.y;
+  const int k = g.k0 + blockIdx.z;
+  double speed = 0.0;
+  const bool row = j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2;                 // whole warp
+  const bool valid = row && i <= g.nx - 2;
+  const int q = gidx(g, i, j, k);
+  int s = 0, e = 0;
+  if (valid) { s = start[q]; e = start[q + 1]; }
+  const unsigned vm = __ballot_sync(0xffffffffu, valid);
+  const int S = __shfl_sync(0xffffffffu, s, 0), E = vm ? __shfl_sync(0xffffffffu, e, 31 - __clz(vm | 1u)) : S;
+  if (vm != 0 && E > S) {
+    double ddx[8], ddy[8], ddz[8];
+    unsigned inmask = 0;
+    if (s < e) {
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
+        int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+        bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
+        ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
+        if (in) inmask |= 1u << m;
+      }
+    }
+    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+    for (int cs = S; cs < E; cs += ROW_CH) {
+      const int cn = min(ROW_CH, E - cs);
+      for (int t = lane; t < cn; t += 32) {
+        const int u = ROW_PAD(t);
+        cp_async8(sm + 0 * ROW_STRIDE + u, px + cs + t); cp_async8(sm + 1 * ROW_STRIDE + u, py + cs + t);
+        cp_async8(sm + 2 * ROW_STRIDE + u, pz + cs + t); cp_async8(sm + 3 * ROW_STRIDE + u, vx + cs + t);
+        cp_async8(sm + 4 * ROW_STRIDE + u, vy + cs + t); cp_async8(sm + 5 * ROW_STRIDE + u, vz + cs + t);
+      }
+      cp_async_wait_all();
+      __syncwarp();
+      const int n0 = max(s, cs), n1 = min(e, cs + cn);
+      for (int n = n0; n < n1; ++n) {
+        const int u = ROW_PAD(n - cs);
+        double x = sm[u], y = sm[ROW_STRIDE + u], z = sm[2 * ROW_STRIDE + u];
+        double a = sm[3 * ROW_STRIDE + u], b = sm[4 * ROW_STRIDE + u], cc = sm[5 * ROW_STRIDE + u];
+        double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+        double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+        double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+        double wsum = 0, dx = 0, dy = 0, dz = 0;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+          if (inmask & (1u << m)) wsum += cw;
+          dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
+        }
+        if (wsum != 0.0) {                                           // fluid.cc:258-262, 981
+          a += dx / wsum; b += dy / wsum; cc += dz / wsum;
+          sm[3 * ROW_STRIDE + u] = a; sm[4 * ROW_STRIDE + u] = b; sm[5 * ROW_STRIDE + u] = cc;
+        }
+        speed = fmax(speed, sqrt(a * a + b * b + cc * cc));          // fluid.cc:982
+      }
+      __syncwarp();
+      for (int t = lane; t < cn; t += 32) {
+        const int u = ROW_PAD(t);
+        vx[cs + t] = sm[3 * ROW_STRIDE + u]; vy[cs + t] = sm[4 * ROW_STRIDE + u]; vz[cs + t] = sm[5 * ROW_STRIDE + u];
+      }
+      __syncwarp();
+    }
+  }
+  speed = warp_max(speed);
+  if (lane == 0) red[threadIdx.y] = speed;
+  __syncthreads();
+  if (threadIdx.y == 0 && lane == 0) {
+    double m = red[0];
+#pragma unroll
+    for (int w = 1; w < ROW_WARPS; ++w) m = fmax(m, red[w]);
+    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
+  }
+}
+
 // particles of the trailing "outside" bucket: no grid contact, but their speed counts (fluid.cc:982)
 __global__ void k_speed_tail(const int32_t* __restrict__ start, int total, int64_t n /* = n_sorted */, const double* __restrict__ vx,
                              const double* __restrict__ vy, const double* __restrict__ vz, DevScalars* __restrict__ ds) {
@@ -465,8 +649,15 @@ int fb_g2p_advect(flipb200_ctx* c) {
   if (c->sorted && !(mode && mode[0] == 'p' && c->world == 1)) {
     if (c->n_sorted > 0) {
       dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
-      k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                             c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+      if (!(mode && mode[0] == 'r'))  // default: per-cell kernel; FLIPB200_G2P=row: shared-memory staged variant (measured 3 % slower)
+        k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                               c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+      else {
+        static bool attr_set = false;
+        if (!attr_set) { CK(cudaFuncSetAttribute(k_g2p_row, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROW_SMEM(6))); attr_set = true; }
+        k_g2p_row<<<grd, dim3(32, ROW_WARPS, 1), ROW_SMEM(6), c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                                                           pt.a[4], pt.a[5], c->r, c->pd, c->Ap, c->ds);
+      }
       c->launches++;
       // the trailing bucket (key == total) holds the particles outside the box (usually none)
       k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, c->n_sorted, pt.a[3], pt.a[4], pt.a[5], c->ds);

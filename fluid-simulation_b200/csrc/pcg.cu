@@ -77,7 +77,7 @@ k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, cons
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   {
-    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
     halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
   }
   double acc[1] = {0.0};
@@ -237,7 +237,7 @@ void fb_make_coef(const flipb200_ctx* c, double dt, PcgCoef* cf) {
     acc = (float)((double)acc + scale);                           // daccessor.setValue(c, getValue(c) + scale), :333
     cf->diag[k] = (double)acc;
     cf->inv[k] = 1.0 / (double)acc;
-    cf->winv[k] = (float)(MG_OMEGA / (k * scale));
+    cf->winv[k] = (float)(MG_OMEGA1 / (k * scale));
   }
   cf->off = (double)(float)(-1 * scale);                          // :335
 }

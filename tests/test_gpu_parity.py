@@ -35,7 +35,7 @@ def _ogrids(o, base=0):
     return np.stack([o.dgrid(base + a) for a in range(3)])
 
 
-@pytest.mark.parametrize("mode", ["cell", "particle"])
+@pytest.mark.parametrize("mode", ["row", "cell", "particle"])
 def test_p2g_classify(fb, oracle_mod, scenes, mode):
     """a5/a6/a7: splat + normalise + classification vs the oracle (both P2G kernels)."""
     sc = random_velocity_scene(scenes)
@@ -93,7 +93,7 @@ def test_rhs_div_pcg_velupdate_relax(fb, oracle_mod, scenes):
     assert e == pytest.approx(eo, rel=1e-12)
 
 
-@pytest.mark.parametrize("mode", ["cell", "particle"])
+@pytest.mark.parametrize("mode", ["row", "cell", "particle"])
 def test_g2p_advect(fb, oracle_mod, scenes, mode, monkeypatch):
     """a17/a18 from identical grids; includes particles that hit the solid shell (both G2P kernels)."""
     monkeypatch.setenv("FLIPB200_G2P", mode)
