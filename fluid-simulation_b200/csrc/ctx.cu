@@ -163,7 +163,7 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
   *out = nullptr;
   if (p->nx < 2 * p->wall + 2 || p->ny < 2 * p->wall + 2 || p->nz < 2 * p->wall + 2) return FLIPB200_ERR_ARG;
   if (p->wall < 1 || p->relax_div < 1 || !(p->dx > 0) || !(p->rho > 0)) return FLIPB200_ERR_ARG;
-  if (p->flip_ratio != 1.0) return FLIPB200_ERR_ARG;   // reference runs pure FLIP (fluid.cc:981)
+  if (!(p->flip_ratio >= 0.0 && p->flip_ratio <= 1.0)) return FLIPB200_ERR_ARG;   // 1 = the reference's pure FLIP (fluid.cc:981)
   flipb200_ctx* c = (flipb200_ctx*)calloc(1, sizeof(flipb200_ctx));
   if (!c) return FLIPB200_ERR_ARG;
   c->P = *p;

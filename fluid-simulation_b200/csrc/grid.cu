@@ -286,11 +286,14 @@ int fb_vel_update(flipb200_ctx* c, double dt_sub) {
 // cell-centred FLIP delta for every node inside the shell (CatmullRomFLIP fluid.cc:237-240,252):
 //   dc_a[c] = (u_a[c] + u_a[c+e_a])/2 - (ub_a[c] + ub_a[c+e_a])/2
 // written into the (now idle) PCG vectors r, pd, Ap; zero outside the shell.
+// PIC/FLIP blend (params.flip_ratio = r < 1; the reference runs r = 1): the particle update is
+//   v_p = r (v_p + interp(dc)) + (1 - r) interp(vc),  vc = getVelocity(c, vels)  (clampedCatmullRom :125-207)
+// and interp is linear with the same weights, so the grid carries  r dc + (1 - r) vc  instead.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u1, const double* __restrict__ u2,
              const double* __restrict__ b0, const double* __restrict__ b1, const double* __restrict__ b2,
-             double* __restrict__ d0, double* __restrict__ d1, double* __restrict__ d2) {
+             double* __restrict__ d0, double* __restrict__ d1, double* __restrict__ d2, double ratio) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
   int k = g.k0 + blockIdx.z;                      // owned planes
@@ -301,6 +304,11 @@ k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u
     a = (u0[q] + u0[q + 1]) / 2.0 - (b0[q] + b0[q + 1]) / 2.0;
     b = (u1[q] + u1[q + g.px]) / 2.0 - (b1[q] + b1[q + g.px]) / 2.0;
     cc = (u2[q] + u2[q + g.plane]) / 2.0 - (b2[q] + b2[q + g.plane]) / 2.0;
+    if (ratio != 1.0) {
+      a = ratio * a + (1.0 - ratio) * ((u0[q] + u0[q + 1]) / 2.0);
+      b = ratio * b + (1.0 - ratio) * ((u1[q] + u1[q + g.px]) / 2.0);
+      cc = ratio * cc + (1.0 - ratio) * ((u2[q] + u2[q + g.plane]) / 2.0);
+    }
   }
   d0[q] = a; d1[q] = b; d2[q] = cc;
 }
@@ -309,7 +317,7 @@ int fb_cell_delta(flipb200_ctx* c) {
   const Grid& g = c->g;
   dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.k1 - g.k0);
   k_cell_delta<<<grd, blk, 0, c->stream>>>(g, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->r, c->pd,
-                                           c->Ap);
+                                           c->Ap, c->P.flip_ratio);
   CK_LAUNCH(); c->launches++;
   // particles of my top base plane read the deltas of plane k1
   double* dc[3] = {c->r, c->pd, c->Ap};

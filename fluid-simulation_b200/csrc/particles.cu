@@ -397,7 +397,7 @@ k_g2p(Grid g, int64_t n, const uint8_t* __restrict__ fl,
       const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
       double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
       const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-      DevScalars* __restrict__ ds) {
+      DevScalars* __restrict__ ds, double ratio) {
   __shared__ double red[32];
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   double speed = 0.0;
@@ -422,7 +422,11 @@ k_g2p(Grid g, int64_t n, const uint8_t* __restrict__ fl,
         wsum += cw;
         dx += dcx[qq] * cw; dy += dcy[qq] * cw; dz += dcz[qq] * cw;
       }
+      if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }            // PIC/FLIP blend (see k_cell_delta)
       if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; }   // fluid.cc:258-262, 981
+      vx[t] = a; vy[t] = b; vz[t] = cc;
+    } else if (ratio != 1.0) {
+      a *= ratio; b *= ratio; cc *= ratio;
       vx[t] = a; vy[t] = b; vz[t] = cc;
     }
     speed = sqrt(a * a + b * b + cc * cc);                  // Vec3::length, fluid.cc:982
@@ -446,7 +450,7 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
            const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
            double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
            const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-           DevScalars* __restrict__ ds) {
+           DevScalars* __restrict__ ds, double ratio) {
   __shared__ double red[4];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -481,7 +485,9 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
         if (inmask & (1u << m)) wsum += cw;
         dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
       }
-      if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; vx[n] = a; vy[n] = b; vz[n] = cc; }   // fluid.cc:258-262, 981
+      if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }          // PIC/FLIP blend (see k_cell_delta)
+      if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; }   // fluid.cc:258-262, 981
+      if (wsum != 0.0 || ratio != 1.0) { vx[n] = a; vy[n] = b; vz[n] = cc; }
       speed = fmax(speed, sqrt(a * a + b * b + cc * cc));      // fluid.cc:982
     }
   }
@@ -503,7 +509,7 @@ k_g2p_row(Grid g, const int32_t* __restrict__ start,
           const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
           double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
           const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-          DevScalars* __restrict__ ds) {
+          DevScalars* __restrict__ ds, double ratio) {
   extern __shared__ double rsm[];
   __shared__ double red[ROW_WARPS];
   const int lane = threadIdx.x;
@@ -558,10 +564,9 @@ k_g2p_row(Grid g, const int32_t* __restrict__ start,
           if (inmask & (1u << m)) wsum += cw;
           dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
         }
-        if (wsum != 0.0) {                                           // fluid.cc:258-262, 981
-          a += dx / wsum; b += dy / wsum; cc += dz / wsum;
-          sm[3 * ROW_STRIDE + u] = a; sm[4 * ROW_STRIDE + u] = b; sm[5 * ROW_STRIDE + u] = cc;
-        }
+        if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }        // PIC/FLIP blend (see k_cell_delta)
+        if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; }   // fluid.cc:258-262, 981
+        if (wsum != 0.0 || ratio != 1.0) { sm[3 * ROW_STRIDE + u] = a; sm[4 * ROW_STRIDE + u] = b; sm[5 * ROW_STRIDE + u] = cc; }
         speed = fmax(speed, sqrt(a * a + b * b + cc * cc));          // fluid.cc:982
       }
       __syncwarp();
@@ -584,12 +589,16 @@ k_g2p_row(Grid g, const int32_t* __restrict__ start,
 }
 
 // particles of the trailing "outside" bucket: no grid contact, but their speed counts (fluid.cc:982)
-__global__ void k_speed_tail(const int32_t* __restrict__ start, int total, int64_t n /* = n_sorted */, const double* __restrict__ vx,
-                             const double* __restrict__ vy, const double* __restrict__ vz, DevScalars* __restrict__ ds) {
+__global__ void k_speed_tail(const int32_t* __restrict__ start, int total, int64_t n /* = n_sorted */, double* __restrict__ vx,
+                             double* __restrict__ vy, double* __restrict__ vz, DevScalars* __restrict__ ds, double ratio) {
   double speed = 0.0;
   for (int64_t t = (int64_t)start[total] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n;
        t += (int64_t)gridDim.x * blockDim.x) {
     double a = vx[t], b = vy[t], cc = vz[t];
+    if (ratio != 1.0) {   // no node in reach: weight sum 0 => the PIC part is 0 (clampedCatmullRom :185)
+      a *= ratio; b *= ratio; cc *= ratio;
+      vx[t] = a; vy[t] = b; vz[t] = cc;
+    }
     speed = fmax(speed, sqrt(a * a + b * b + cc * cc));
   }
   speed = warp_max(speed);
@@ -651,27 +660,27 @@ int fb_g2p_advect(flipb200_ctx* c) {
       dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
       if (!(mode && mode[0] == 'r'))  // default: per-cell kernel; FLIPB200_G2P=row: shared-memory staged variant (measured 3 % slower)
         k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                               c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+                                               c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);   // dc arrays written by fb_cell_delta
       else {
         static bool attr_set = false;
         if (!attr_set) { CK(cudaFuncSetAttribute(k_g2p_row, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROW_SMEM(6))); attr_set = true; }
         k_g2p_row<<<grd, dim3(32, ROW_WARPS, 1), ROW_SMEM(6), c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                                                           pt.a[4], pt.a[5], c->r, c->pd, c->Ap, c->ds);
+                                                                           pt.a[4], pt.a[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
       }
       c->launches++;
       // the trailing bucket (key == total) holds the particles outside the box (usually none)
-      k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, c->n_sorted, pt.a[3], pt.a[4], pt.a[5], c->ds);
+      k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, c->n_sorted, pt.a[3], pt.a[4], pt.a[5], c->ds, c->P.flip_ratio);
       c->launches++;
     }
     if (pt.n > c->n_sorted) {   // migrated-in tail
       const int64_t o = c->n_sorted, m = pt.n - o;
       k_g2p<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(g, m, c->flags, pt.a[0] + o, pt.a[1] + o, pt.a[2] + o,
-                                                               pt.a[3] + o, pt.a[4] + o, pt.a[5] + o, c->r, c->pd, c->Ap, c->ds);
+                                                               pt.a[3] + o, pt.a[4] + o, pt.a[5] + o, c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
       c->launches++;
     }
   } else {
     k_g2p<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                         c->r, c->pd, c->Ap, c->ds);   // dc arrays written by fb_cell_delta
+                                         c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);   // dc arrays written by fb_cell_delta
     c->launches++;
   }
   CK_LAUNCH();

@@ -46,7 +46,8 @@ typedef struct {
   double  dt_max;            /* 0.1 (fluid.cc:1490)                                           */
   double  relax_tol;         /* 0.1 (fluid.cc:1484)                                           */
   double  restitution;       /* e = 0 (fluid.cc:974)                                          */
-  double  flip_ratio;        /* 1.0: pure FLIP (fluid.cc:981); only 1.0 is implemented        */
+  double  flip_ratio;        /* 1.0: pure FLIP, what main() runs (fluid.cc:981); r < 1 blends in
+                                (1-r) x the PIC velocity of advect/clampedCatmullRom (:904-971, :125-207) */
   double  pcg_tol;           /* 2.220446049250313e-16 (Eigen IterativeSolverBase.h:363)       */
   int32_t pcg_max_iter;      /* <0 => 2*n_fluid (IterativeSolverBase.h:283)                   */
   int32_t max_passes;        /* safety cap on the do..while loop (reference: unbounded); 200  */

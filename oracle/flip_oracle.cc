@@ -87,6 +87,7 @@ void oracle_default_params(oracle_params* p) {
   p->max_passes = 200;
   p->threads = 1;
   p->pcg_max_iter = -1;
+  p->flip_ratio = 1.0;
 }
 
 int oracle_has_eigen(void) {
@@ -512,7 +513,11 @@ static inline void get_velocity(const oracle_ctx* c, int gu, int i, int j, int k
   out[2] = (c->dget(gu + 2, i, j, k) + c->dget(gu + 2, i, j, k + 1)) / 2.0;
 }
 
-/* PointList::FLIPadvect fluid.cc:972-1038 with CatmullRomFLIP :210-263 */
+/* PointList::FLIPadvect fluid.cc:972-1038 with CatmullRomFLIP :210-263.
+ * flip_ratio r < 1 (an extension: main() only ever runs r = 1, the PIC call at :1488 is commented
+ * out) blends in the PIC velocity of PointList::advect :904-971, i.e. clampedCatmullRom :125-207
+ * (same window, same weights, velocity = getVelocity(node, vels), 0 when the weight sum is 0 :185):
+ *   v_p = r * (v_p + delta) + (1 - r) * v_pic */
 void oracle_flip_advect(oracle_ctx* c, double* dt_inout) {
   const int64_t np = (int64_t)c->px.size();
   const int ox = c->P.ox, oy = c->P.oy, oz = c->P.oz;
@@ -525,7 +530,7 @@ void oracle_flip_advect(oracle_ctx* c, double* dt_inout) {
     const double x = c->px[n], y = c->py[n], z = c->pz[n];
     int lo[3], hi[3];
     window(c, x, y, z, lo, hi);
-    double weight = 0, dxs = 0, dys = 0, dzs = 0;
+    double weight = 0, dxs = 0, dys = 0, dzs = 0, pu = 0, pv = 0, pw = 0;
     for (int i = lo[0]; i <= hi[0]; ++i)
       for (int j = lo[1]; j <= hi[1]; ++j)
         for (int k = lo[2]; k <= hi[2]; ++k)
@@ -538,9 +543,15 @@ void oracle_flip_advect(oracle_ctx* c, double* dt_inout) {
             dxs += (velc[0] - velp[0]) * cw;                   /* :252 */
             dys += (velc[1] - velp[1]) * cw;
             dzs += (velc[2] - velp[2]) * cw;
+            pu += velc[0] * cw; pv += velc[1] * cw; pw += velc[2] * cw;   /* clampedCatmullRom :171-176 */
           }
     if (weight != 0) {                                         /* :258-262 */
       c->vx[n] += dxs / weight; c->vy[n] += dys / weight; c->vz[n] += dzs / weight;   /* :981 */
+    }
+    if (c->P.flip_ratio != 1.0) {
+      const double r = c->P.flip_ratio;
+      const double qu = weight != 0 ? pu / weight : 0.0, qv = weight != 0 ? pv / weight : 0.0, qw = weight != 0 ? pw / weight : 0.0;   /* :178-186 */
+      c->vx[n] = r * c->vx[n] + (1.0 - r) * qu; c->vy[n] = r * c->vy[n] + (1.0 - r) * qv; c->vz[n] = r * c->vz[n] + (1.0 - r) * qw;
     }
     double len = std::sqrt(c->vx[n] * c->vx[n] + c->vy[n] * c->vy[n] + c->vz[n] * c->vz[n]);
     if (maxSpeed < len) maxSpeed = len;

@@ -49,6 +49,7 @@ typedef struct {
   int32_t max_passes;     /* safety cap on the do..while loop (reference has none)    */
   int32_t threads;        /* 1 = serial particle loops (parity); >1 OpenMP (timing)   */
   int32_t pcg_max_iter;   /* <0 => 2n (IterativeSolverBase.h:283)                     */
+  double  flip_ratio;     /* 1 = pure FLIP (fluid.cc:981, what main() runs); 0 = PIC of advect (:904-971) */
 } oracle_params;
 
 typedef struct {

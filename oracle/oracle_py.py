@@ -24,6 +24,7 @@ class OracleParams(C.Structure):
         ("dt_max", C.c_double), ("relax_tol", C.c_double), ("restitution", C.c_double),
         ("solver", C.c_int32), ("max_passes", C.c_int32), ("threads", C.c_int32),
         ("pcg_max_iter", C.c_int32),
+        ("flip_ratio", C.c_double),
     ]
 
 

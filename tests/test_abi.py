@@ -51,7 +51,7 @@ def test_bad_arguments(fb):
     p = fb.default_params(wall=0)
     h = C.c_void_p()
     assert lib.flipb200_create(C.byref(p), None, C.byref(h)) == fb.ERR_ARG
-    p = fb.default_params(flip_ratio=0.95)
+    p = fb.default_params(flip_ratio=1.5)
     assert lib.flipb200_create(C.byref(p), None, C.byref(h)) == fb.ERR_ARG
     assert lib.flipb200_step(None, None, None) == fb.ERR_ARG
 
