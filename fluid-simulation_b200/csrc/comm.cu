@@ -19,6 +19,7 @@
 #include <mutex>
 #include <condition_variable>
 #include <map>
+#include <vector>
 #include <nccl.h>
 
 #define MAXR 16
@@ -409,7 +410,8 @@ extern "C" int flipb200_halo_mode(flipb200_ctx* c) { return c ? c->halo.mode : F
 // [3] distributed levels [4] kernels per iteration [5] ghost-pushing kernels per iteration [6] rank [7] world
 extern "C" int flipb200_debug_info(flipb200_ctx* c, int32_t* out8) {
   if (!c || !out8) return FLIPB200_ERR_ARG;
-  out8[0] = c->halo.mode; out8[1] = c->it_exec ? 1 : 0; out8[2] = c->mg_levels; out8[3] = c->mg_nd;
+  out8[0] = c->halo.mode + (c->halo.red_on ? 10 : 0);   // +10: all-reduce fused too
+  out8[1] = c->it_exec ? 1 : 0; out8[2] = c->mg_levels; out8[3] = c->mg_nd;
   out8[4] = (int32_t)c->it_kernels; out8[5] = c->it_nprod; out8[6] = c->rank; out8[7] = c->world;
   return FLIPB200_OK;
 }
@@ -461,6 +463,14 @@ PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, siz
       h.dst_up = (char*)hs.peer[1][lout][aout] + ((ptrdiff_t)(SLAB_GHOST - 1) - (g.k1 - 1)) * (ptrdiff_t)pb;
   }
   return h;
+}
+
+RedPub fb_red_make(flipb200_ctx* c) {
+  RedPub r = red_off();
+  if (!c->halo.red_on) return r;
+  r.on = 1; r.rank = c->rank; r.world = c->world;
+  for (int q = 0; q < c->world; ++q) r.peers[q] = c->halo.peer_mail[q];
+  return r;
 }
 
 // where a halo copy used to be: nothing to do with device flags; the in-process transport orders
@@ -550,6 +560,38 @@ int fb_halo_setup(flipb200_ctx* c) {
     cudaFree(flag);
     if (!hflag) return 0;
     hs.mode = 2;
+    // mailboxes of the fused all-reduce: every rank maps every rank's (FLIPB200_FUSED_REDUCE=0: NCCL all-reduce)
+    const char* fr = getenv("FLIPB200_FUSED_REDUCE");
+    if (!(fr && fr[0] == '0') && c->world <= RED_MAXR) {
+      CK(cudaMalloc((void**)&hs.mail, sizeof(RedMail)));
+      CK(cudaMemsetAsync(hs.mail, 0, sizeof(RedMail), c->stream));
+      cudaIpcMemHandle_t mh; memset(&mh, 0, sizeof(mh));
+      int okm = cudaIpcGetMemHandle(&mh, hs.mail) == cudaSuccess ? 1 : 0;
+      cudaIpcMemHandle_t* dh = nullptr;
+      std::vector<cudaIpcMemHandle_t> all(c->world);
+      CK(cudaMalloc((void**)&dh, sizeof(mh) * c->world));
+      CK(cudaMemcpyAsync(dh + c->rank, &mh, sizeof(mh), cudaMemcpyHostToDevice, c->stream));
+      NC(g_nccl.GroupStart());
+      for (int r = 0; r < c->world; ++r) NC(g_nccl.Broadcast(dh + r, dh + r, sizeof(mh), ncclChar, r, c->comm->nc, c->stream));
+      NC(g_nccl.GroupEnd());
+      CK(cudaMemcpyAsync(all.data(), dh, sizeof(mh) * c->world, cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      cudaFree(dh);
+      for (int r = 0; r < c->world && okm; ++r) {
+        if (r == c->rank) { hs.peer_mail[r] = hs.mail; continue; }
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { okm = 0; cudaGetLastError(); }
+        hs.peer_mail[r] = (RedMail*)p;
+      }
+      int* flag2 = nullptr;
+      CK(cudaMalloc((void**)&flag2, sizeof(int)));
+      CK(cudaMemcpyAsync(flag2, &okm, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+      NC(g_nccl.AllReduce(flag2, flag2, 1, ncclInt32, ncclMin, c->comm->nc, c->stream));
+      CK(cudaMemcpyAsync(&okm, flag2, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaStreamSynchronize(c->stream));
+      cudaFree(flag2);
+      hs.red_on = okm;
+    }
   }
   for (int dir = 0; dir < 2; ++dir) {
     int m = 0;

@@ -77,6 +77,8 @@ struct DevScalars {
   double part[4];                    // [0] p.Ap  [1] r.z  [2] r.r
   int halo_base;                     // sequence number base of the fused ghost-plane pushes (halo.cuh)
   int pad2;
+  unsigned blk_cnt[4];               // fused all-reduce (halo.cuh): finished blocks of the current dot-product kernel
+  unsigned red_seq[4];               //   and the sequence number of the last collected sum, per PART_* id
 };
 #define PART_PAP 0
 #define PART_RZ 1
@@ -131,6 +133,10 @@ struct HaloState {
   long long abs_seq;                 // producer kernels enqueued so far
   long long seg_base;                // host mirror of DevScalars::halo_base for the segment being enqueued
   long long last_prod[MG_MAX_LEVELS][3];
+  // all-reduce fused into the dot-product kernels (mode 2 only): every rank's mailbox, peer-mapped
+  struct RedMail* mail;              // own
+  struct RedMail* peer_mail[16];     // [rank] (own included); null when the fused all-reduce is off
+  int red_on;
 };
 
 struct flipb200_ctx {
@@ -285,7 +291,8 @@ int fb_mg_alloc(flipb200_ctx* c);
 void fb_mg_free(flipb200_ctx* c);
 int fb_mg_setup(flipb200_ctx* c, double dt);                    // per step: coarse flags + boxes
 int fb_mg_vcycle(flipb200_ctx* c, int it);
-void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg);     // part[] -> ring slots after an all-reduce                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it&3]
+void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg);
+int fb_pcg_reduce_dot(flipb200_ctx* c, int id, int it_arg);         // all-reduce of ds->part[id] into the ring (fused mailboxes or NCCL)     // part[] -> ring slots after an all-reduce                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it&3]
 int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 int fb_reserve_particles(flipb200_ctx* c, int64_t n);
 int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n, int64_t id0);

@@ -269,7 +269,7 @@ void flipb200_destroy(flipb200_ctx* c) {
   fb_graph_invalidate(c);
   fb_mg_free(c);
   fb_comm_free(c);
-  cudaFree(c->halo_tmp); cudaFree(c->halo.flags);
+  cudaFree(c->halo_tmp); cudaFree(c->halo.flags); cudaFree(c->halo.mail);
   cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static);
   for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }
   cudaFree(c->wacc); cudaFree(c->wf); cudaFree(c->bf[0]); cudaFree(c->bf[1]);

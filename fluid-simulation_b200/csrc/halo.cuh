@@ -109,6 +109,29 @@ __device__ __forceinline__ void halo_signal(const PeerHalo& H, DevScalars* ds, b
   }
 }
 
+// ---- all-reduce of a dot product over peer memory ------------------------------------------------
+// Blocks add their partial sums into ds->part[id] as on one GPU.  One 32-thread kernel
+// (k_pcg_exchange, pcg.cu) then does the whole all-reduce: lane r stores this rank's sum into slot
+// [rank] of rank r's mailbox (peer store over NVLink) and release-stores the sequence number next
+// to it, waits for slot [r] of its own mailbox, and the warp adds the `world` values in rank order
+// (identical bits on every rank) into the ring slot the next kernel reads.  Replaces an 8-byte
+// ncclAllReduce (17-23 us) plus a publish kernel by one launch and one NVLink round trip.  Slots are
+// double-buffered by sequence parity; reuse is safe because a rank reaches exchange n+2 of an id
+// only after every rank has finished n (the other dot products of the iteration depend on it).
+// (Publishing from the last block of the producing kernel was tried first: the per-block
+// fence + returning atomic made k_update_xr / k_spmv 5 % slower, a net loss.)
+#define RED_MAXR 16
+struct RedMail {
+  double val[4][2][RED_MAXR];        // [PART_* id][seq parity][source rank]
+  unsigned seq[4][2][RED_MAXR];
+};
+struct RedPub {
+  int on, rank, world;
+  RedMail* peers[RED_MAXR];          // [rank]; own mailbox included
+};
+static inline RedPub red_off() { RedPub r; memset(&r, 0, sizeof(r)); return r; }
+RedPub fb_red_make(flipb200_ctx* c);   // comm.cu
+
 // host (comm.cu): describe one launch as consumer of (lin, ain) and/or producer of (lout, aout)
 PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, size_t elem_out, int kdn, int kup, int nb);
 

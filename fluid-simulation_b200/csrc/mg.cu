@@ -593,9 +593,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   }
   CK_LAUNCH();
   if (dist) {
-    int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
+    int rc = fb_pcg_reduce_dot(c, PART_RZ, it);
     if (rc) return rc;
-    fb_pcg_publish(c, 1 << PART_RZ, it);
   }
   fb_prof(c, "allreduce rz");
   return 0;

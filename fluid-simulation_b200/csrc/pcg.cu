@@ -169,6 +169,50 @@ __global__ void k_pcg_publish(DevScalars* __restrict__ ds, int mask, int it_arg)
   if (mask & (1 << PART_RZ)) { ds->rz[s] = ds->part[PART_RZ]; ds->part[PART_RZ] = 0.0; }
   if (mask & (1 << PART_RR)) { ds->rr[s] = ds->part[PART_RR]; ds->part[PART_RR] = 0.0; }
 }
+// all-reduce of ds->part[id] over the peer-mapped mailboxes (halo.cuh).  One warp; lane r talks to rank r.
+__global__ void k_pcg_exchange(DevScalars* __restrict__ ds, const __grid_constant__ RedPub R, int id, int it_arg, int noexit) {
+  if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
+  const int lane = threadIdx.x;
+  const unsigned seq = ds->red_seq[id] + 1u;
+  const int par = (int)(seq & 1u);
+  const double mine = ds->part[id];
+  double v = 0.0;
+  bool bad = false;
+  if (lane < R.world) {
+    R.peers[lane]->val[id][par][R.rank] = mine;
+    __threadfence_system();
+    st_release_sys(&R.peers[lane]->seq[id][par][R.rank], seq);
+    RedMail* my = R.peers[R.rank];
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(&my->seq[id][par][lane]) - seq) < 0)
+      if (clock64() - t0 > HALO_SPIN_LIMIT) { bad = true; break; }
+    v = *(volatile double*)&my->val[id][par][lane];
+  }
+  if (__any_sync(0xffffffffu, bad)) { if (lane == 0) { ds->pcg_status = FLIPB200_ERR_COMM; ds->pcg_done = 1; } return; }
+  double sum = 0.0;
+  for (int r = 0; r < R.world; ++r) sum += __shfl_sync(0xffffffffu, v, r);     // rank order: same bits on every rank
+  if (lane == 0) {
+    const int s = it & 3;
+    if (id == PART_PAP) ds->pAp[s] = sum; else if (id == PART_RZ) ds->rz[s] = sum; else ds->rr[s] = sum;
+    ds->part[id] = 0.0;
+    ds->red_seq[id] = seq;
+  }
+}
+// all-reduce + publish of one dot product: fused (mailboxes over NVLink) or NCCL
+static int reduce_dot(flipb200_ctx* c, int id, int it_arg, int noexit) {
+  if (c->halo.red_on) {
+    k_pcg_exchange<<<1, 32, 0, c->stream>>>(c->ds, fb_red_make(c), id, it_arg, noexit);
+    c->launches++;
+    return 0;
+  }
+  int rc = fb_allreduce(c, &c->ds->part[id], 1, FB_F64, FB_SUM);
+  if (rc) return rc;
+  fb_pcg_publish(c, 1 << id, it_arg);
+  return 0;
+}
+int fb_pcg_reduce_dot(flipb200_ctx* c, int id, int it_arg) { return reduce_dot(c, id, it_arg, 0); }
+
 void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg) {
   k_pcg_publish<<<1, 1, 0, c->stream>>>(c->ds, mask, it_arg);
   c->launches++;
@@ -275,18 +319,18 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
                                               fused ? fb_halo_make(c, 0, HA_PD, -1, -1, 0, k0, k1, tg.x * tg.y) : halo_off());
   fb_prof(c, "k_spmv");
   if (dist) {
-    if ((rc = fb_allreduce(c, &c->ds->part[PART_PAP], 1, FB_F64, FB_SUM))) return rc;
-    fb_pcg_publish(c, 1 << PART_PAP, it_arg);
+    if (use_mg) { if ((rc = reduce_dot(c, PART_PAP, it_arg, noexit))) return rc; }
+    else {
+      if ((rc = fb_allreduce(c, &c->ds->part[PART_PAP], 1, FB_F64, FB_SUM))) return rc;
+      fb_pcg_publish(c, 1 << PART_PAP, it_arg);
+    }
   }
   fb_prof(c, "allreduce pAp");
   if (use_mg) {
     k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     fb_prof(c, "k_update_xr");
-    if (dist) {
-      if ((rc = fb_allreduce(c, &c->ds->part[PART_RR], 1, FB_F64, FB_SUM))) return rc;
-      fb_pcg_publish(c, 1 << PART_RR, it_arg);
-    }
+    if (dist && (rc = reduce_dot(c, PART_RR, it_arg, noexit))) return rc;
     if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg); c->launches++; }
     fb_prof(c, "allreduce rr");
     rc = fb_mg_vcycle(c, it_arg);
