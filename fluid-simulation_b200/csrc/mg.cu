@@ -332,109 +332,146 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
 // {1,3,3,1}^3 weights x rn_i, fused with the coarse level's first Jacobi sweep x1 = w D^-1 b_c.
 // One lane per coarse cell: the lane loads its two children of each of the 16 fine rows as one
 // float2 (coalesced across the warp) and gets the two outer taps from its neighbours by shuffle.
+// The block marches RS_ZC coarse planes: the y/x-reduced sum of a fine plane is shared by the two
+// coarse planes it feeds, so a coarse cell costs ~9 fine-row loads instead of 16 (RS_ZC = 8; small
+// levels are latency-bound and keep one plane per block, mg_zchunk).
 __global__ void __launch_bounds__(256)
 k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
               const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
-              DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
+              DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode);
-  halo_wait(H, ds, K == H.kdn, K == H.kup);         // boundary coarse planes read the fine ghost planes
+  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
+  const bool bdn = K0 <= H.kdn && H.kdn < K1, bup = K0 <= H.kup && H.kup < K1;
+  halo_wait(H, ds, bdn, bup);                       // boundary coarse planes read the fine ghost planes
   if (J < cbox.y1) {                                // whole warp
     const bool in = I < cbox.x1;
     // the fine sweeps write pairs over [fx0, fxe): everything in that x-range is fresh (0 off the fluid)
     const int fx0 = fbox.x0 & ~1, fxe = min(gf.px, (fbox.x1 + 1) & ~1);
     const int xf = 2 * I;                             // children xf, xf+1
     const bool cv = in && xf >= fx0 && xf < fxe;
-    const bool eL = in && xf - 1 >= fx0 && xf - 1 < fxe, eR = in && xf + 2 >= fx0 && xf + 2 < fxe;
+    const bool eL = lane == 0 && in && xf - 1 >= fx0 && xf - 1 < fxe, eR = lane == 31 && in && xf + 2 >= fx0 && xf + 2 < fxe;
     const int xc = cv ? xf : fx0;                     // clamped (value discarded when !cv)
-    // issue all 16 row loads first (rows outside the fine box are clamped and get weight 0)
-    float2 v[16]; float ea[16], ed[16], w[16];
+    // rows 2J-1 .. 2J+2 with weights 1 3 3 1 (0 outside the fine box)
+    int jr[4]; float wy[4];
 #pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      const int oz = (t >> 2) - 1, oy = (t & 3) - 1;
-      const int kf = 2 * (K + gc.kg0) + oz - gf.kg0, jf = 2 * J + oy;
-      const bool rin = kf >= fbox.z0 && kf < fbox.z1 && jf >= fbox.y0 && jf < fbox.y1;
-      const int kc = min(max(kf, fbox.z0), fbox.z1 - 1), jc = min(max(jf, fbox.y0), fbox.y1 - 1);
-      const float* row = rn + gidx(gf, 0, jc, kc);
-      w[t] = rin ? (((oz == 0 || oz == 1) ? 3.f : 1.f) * ((oy == 0 || oy == 1) ? 3.f : 1.f)) : 0.f;
-      v[t] = *reinterpret_cast<const float2*>(row + xc);
-      ea[t] = (lane == 0 && eL) ? row[xf - 1] : 0.f;
-      ed[t] = (lane == 31 && eR) ? row[xf + 2] : 0.f;
+    for (int t = 0; t < 4; ++t) {
+      const int jf = 2 * J + t - 1;
+      wy[t] = (jf >= fbox.y0 && jf < fbox.y1) ? ((t == 1 || t == 2) ? 3.f : 1.f) : 0.f;
+      jr[t] = min(max(jf, fbox.y0), fbox.y1 - 1);
     }
-    float sum = 0.f;
+    // y/x-reduced sum of fine plane kf for this coarse column: sum_rows wy * (a + 3 vx + 3 vy + d)
+    auto plane_sum = [&](int kf) -> float {
+      const bool pin = kf >= fbox.z0 && kf < fbox.z1;               // block-uniform
+      const int kc = min(max(kf, fbox.z0), fbox.z1 - 1);
+      float2 v[4]; float ea[4], ed[4];
 #pragma unroll
-    for (int t = 0; t < 16; ++t) {
-      float vx = cv ? v[t].x : 0.f, vy = cv ? v[t].y : 0.f;
-      float a = __shfl_up_sync(0xffffffffu, vy, 1), d = __shfl_down_sync(0xffffffffu, vx, 1);
-      if (lane == 0) a = ea[t];
-      if (lane == 31) d = ed[t];
-      sum += w[t] * ((a + d) + 3.f * (vx + vy));
-    }
-    if (in) {
-      const int qc = gidx(gc, I, J, K);
-      const uint8_t f = fc[qc];
-      const float r = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
-      const float x1 = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * r : 0.f;
-      bc[qc] = r;
-      x1c[qc] = x1;
-      halo_push1<float>(H, qc, K, x1);
+      for (int t = 0; t < 4; ++t) {
+        const float* row = rn + gidx(gf, 0, jr[t], kc);
+        v[t] = *reinterpret_cast<const float2*>(row + xc);
+        ea[t] = eL ? row[xf - 1] : 0.f;
+        ed[t] = eR ? row[xf + 2] : 0.f;
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float vx = cv ? v[t].x : 0.f, vy = cv ? v[t].y : 0.f;
+        float a = __shfl_up_sync(0xffffffffu, vy, 1), d = __shfl_down_sync(0xffffffffu, vx, 1);
+        if (lane == 0) a = ea[t];
+        if (lane == 31) d = ed[t];
+        sum += wy[t] * ((a + d) + 3.f * (vx + vy));
+      }
+      return pin ? sum : 0.f;
+    };
+    const int kb = 2 * (K0 + gc.kg0) - gf.kg0;       // local fine plane of the first child of K0
+    float sm1 = plane_sum(kb - 1), s0 = plane_sum(kb);
+    for (int K = K0; K < K1; ++K) {
+      const int kf = kb + 2 * (K - K0);
+      const float s1 = plane_sum(kf + 1), s2 = plane_sum(kf + 2);
+      const float sum = (sm1 + s2) + 3.f * (s0 + s1);
+      if (in) {
+        const int qc = gidx(gc, I, J, K);
+        const uint8_t f = fc[qc];
+        const float r = (f & FB_FLUID) ? sum * (1.f / 512.f) : 0.f;
+        const float x1 = (f & FB_FLUID) ? mcc.winv[6 - __popc(f & FB_SMASK)] * r : 0.f;
+        bc[qc] = r;
+        x1c[qc] = x1;
+        halo_push1<float>(H, qc, K, x1);
+      }
+      sm1 = s1; s0 = s2;
     }
   }
-  halo_signal(H, ds, K == H.kdn, K == H.kup);
+  halo_signal(H, ds, bdn, bup);
 }
 
 // prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells).
-// One lane per coarse column I = two fine nodes (2I, 2I+1): the four coarse rows that feed this
-// fine row are loaded coalesced and combined, the x-neighbours I-1 / I+1 come by shuffle.
+// One lane per coarse column I = two fine nodes (2I, 2I+1); the x-neighbours I-1 / I+1 come by
+// shuffle.  The block marches PR_ZC fine planes: the y-combined coarse value Y(K) of a coarse plane
+// feeds the four fine planes 2K-1 .. 2K+2, so it stays in a three-plane register window and a fine
+// row costs ~1.5 coarse-row loads instead of 4.
 __global__ void __launch_bounds__(256)
 k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ nrm,
              const float* __restrict__ ec, float* __restrict__ x, DevScalars* __restrict__ ds,
-             const __grid_constant__ PeerHalo H) {
+             int PR_ZC, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode);
-  halo_wait(H, ds, k == H.kdn, k == H.kup);         // boundary fine planes read the coarse ghost planes
+  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
+  const bool bdn = k0c <= H.kdn && H.kdn < k1c, bup = k0c <= H.kup && H.kup < k1c;
+  halo_wait(H, ds, bdn, bup);                       // boundary fine planes read the coarse ghost planes
   if (j < fbox.y1) {                                // whole warp
-    const int kg = k + gf.kg0;                         // global fine plane
-    const int I = i >> 1, J = j >> 1, K = (kg >> 1) - gc.kg0;
-    int J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((kg & 1) ? 1 : -1);
-    const bool yin = J2 >= 0 && J2 < gc.ny, zin = K2 + gc.kg0 >= 0 && K2 + gc.kg0 < gc.gnz;
-    J2 = yin ? J2 : J; K2 = zin ? K2 : K;
-    const float wy = yin ? 1.f : 0.f, wz = zin ? 1.f : 0.f;
-    const float* p00 = ec + gidx(gc, 0, J, K);
-    const float* p10 = ec + gidx(gc, 0, J2, K);
-    const float* p01 = ec + gidx(gc, 0, J, K2);
-    const float* p11 = ec + gidx(gc, 0, J2, K2);
-    auto comb = [&](int ii) -> float {                // y/z-combined coarse value of column ii (weights 3|1)
-      return 3.f * (3.f * p00[ii] + wy * p10[ii]) + wz * (3.f * p01[ii] + wy * p11[ii]);
-    };
+    const int I = i >> 1, J = j >> 1;
+    int J2 = J + ((j & 1) ? 1 : -1);
+    const bool yin = J2 >= 0 && J2 < gc.ny;
+    J2 = yin ? J2 : J;
+    const float wy = yin ? 1.f : 0.f;
     const bool cin = I < gc.nx;
-    const float E = cin ? comb(I) : 0.f;
-    float EL = __shfl_up_sync(0xffffffffu, E, 1), ER = __shfl_down_sync(0xffffffffu, E, 1);
-    if (lane == 0) EL = (I - 1 >= 0 && I - 1 < gc.nx) ? comb(I - 1) : 0.f;
-    if (lane == 31) ER = (I + 1 < gc.nx) ? comb(I + 1) : 0.f;
-    if (I - 1 < 0) EL = 0.f;
-    if (I + 1 >= gc.nx) ER = 0.f;
+    const int Ie = lane == 0 ? I - 1 : I + 1;         // the column the edge lanes cannot get by shuffle
+    const bool ein = (lane == 0 || lane == 31) && Ie >= 0 && Ie < gc.nx;
+    // y-combined coarse value (weights 3|1) of global coarse plane Kg for column I (and Ie on the edge lanes)
+    auto ycomb = [&](int Kg, float& ye) -> float {
+      ye = 0.f;
+      if (Kg < 0 || Kg >= gc.gnz) return 0.f;         // block-uniform
+      const float* r0 = ec + gidx(gc, 0, J, Kg - gc.kg0);
+      const float* r1 = ec + gidx(gc, 0, J2, Kg - gc.kg0);
+      if (ein) ye = 3.f * r0[Ie] + wy * r1[Ie];
+      return cin ? 3.f * r0[I] + wy * r1[I] : 0.f;
+    };
     const int xe = min(gf.px, (fbox.x1 + 1) & ~1);
-    if (i < xe) {
-      const int q = gidx(gf, i, j, k);
-      const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);      // three independent loads in flight
-      const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
-      float2 xv = *reinterpret_cast<const float2*>(x + q);
-      if ((f.x | f.y) & FB_FLUID) {
-        if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
-        if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
-        *reinterpret_cast<float2*>(x + q) = xv;
-        halo_push2<float>(H, q, k, xv.x, xv.y);
+    int Kc = (k0c + gf.kg0) >> 1;
+    float em, e0, ep;
+    float Ym = ycomb(Kc - 1, em), Y0 = ycomb(Kc, e0), Yp = ycomb(Kc + 1, ep);
+    for (int k = k0c; k < k1c; ++k) {
+      const int kg = k + gf.kg0;                       // global fine plane; its donors are kg>>1 (3) and kg>>1 -+ 1 (1)
+      if ((kg >> 1) != Kc) {
+        Kc = kg >> 1;
+        Ym = Y0; em = e0; Y0 = Yp; e0 = ep;
+        Yp = ycomb(Kc + 1, ep);
+      }
+      const bool up = kg & 1;
+      const float E = 3.f * Y0 + (up ? Yp : Ym);
+      const float Ee = 3.f * e0 + (up ? ep : em);
+      float EL = __shfl_up_sync(0xffffffffu, E, 1), ER = __shfl_down_sync(0xffffffffu, E, 1);
+      if (lane == 0) EL = Ee;
+      if (lane == 31) ER = Ee;
+      if (i < xe) {
+        const int q = gidx(gf, i, j, k);
+        const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);      // three independent loads in flight
+        const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
+        float2 xv = *reinterpret_cast<const float2*>(x + q);
+        if ((f.x | f.y) & FB_FLUID) {
+          if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
+          if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
+          *reinterpret_cast<float2*>(x + q) = xv;
+          halo_push2<float>(H, q, k, xv.x, xv.y);
+        }
       }
     }
   }
-  halo_signal(H, ds, k == H.kdn, k == H.kup);
+  halo_signal(H, ds, bdn, bup);
 }
 
 // coarsest level (<= 4096 cells) in ONE block: 40 steps of the Chebyshev semi-iteration on the
@@ -508,6 +545,14 @@ k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* _
 // residual and solved redundantly by every rank; r.z is all-reduced at the end.
 // Ghost planes of `arr` before a sweep reads them: a copy (NCCL / in-process pulls), or -- with the
 // pushes fused into the producing kernels (halo.cuh) -- nothing but the test transport's host barrier.
+// planes a restrict / prolong block marches: the largest chunk that still leaves `min_blocks` blocks
+// (8 on the 256^3 level, 1 on the latency-bound coarse levels); the env variable pins it for experiments.
+static int mg_zchunk(const char* env, int blocks_xy, int nz, int min_blocks) {
+  if (const char* e = getenv(env)) { int v = atoi(e); if (v >= 1 && v <= 64) return v; }
+  for (int zc = 8; zc > 1; zc >>= 1)
+    if ((int64_t)blocks_xy * cdiv(nz, zc) >= min_blocks) return zc;
+  return 1;
+}
 #define HALO(L, arr) do { if ((L).dist) { int rc__ = fused ? fb_halo_point(c) : fb_halo_fill(c, (L).g, (arr), sizeof(float), 1, 1); if (rc__) return rc__; } } while (0)
 int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const int nl = c->mg_levels;
@@ -544,10 +589,12 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     {
       // the sequence number is taken even when this rank has nothing to restrict
-      dim3 cg(max(1, cdiv(cb.x1 - cb.x0, 32)), max(1, cdiv(cb.y1 - cb.y0, 8)), max(1, cb.z1 - cb.z0));
+      dim3 cg(max(1, cdiv(cb.x1 - cb.x0, 32)), max(1, cdiv(cb.y1 - cb.y0, 8)), 1);
+      const int zc = mg_zchunk("FLIPB200_RS_ZC", cg.x * cg.y, cb.z1 - cb.z0, 1024);
+      cg.z = max(1, cdiv(cb.z1 - cb.z0, zc));
       PeerHalo H = fb_halo_make(c, l, HA_XA, C.dist ? l + 1 : -1, C.dist ? HA_XA : -1, F, ck0, ck1, cg.x * cg.y);
       if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0)
-        k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, H);
+        k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H);
     }
     fb_prof(c, l == 0 ? "L0 halo+restrict" : (l == 1 ? "L1 halo+restrict" : "L2+ halo+restrict"));
     if (L.dist && !C.dist) {
@@ -571,11 +618,13 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const Box& fb = L.box;
-    dim3 pg(cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), fb.z1 - fb.z0);
+    dim3 pg(cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), 1);
+    const int pzc = mg_zchunk("FLIPB200_PR_ZC", pg.x * pg.y, fb.z1 - fb.z0, 1024);
+    pg.z = cdiv(fb.z1 - fb.z0, pzc);
     const dim3 tg = stencil_grid(S[l]);
     const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(C, C.xb);
-    k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds,
+    k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds, pzc,
                                              fb_halo_make(c, C.dist ? l + 1 : -1, C.dist ? HA_XB : -1, l, HA_XB, F, k0, k1, pg.x * pg.y));
     fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
