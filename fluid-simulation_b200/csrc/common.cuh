@@ -168,6 +168,7 @@ struct flipb200_ctx {
   MgLevel mg[MG_MAX_LEVELS];
   int mg_levels;           // 0 => hierarchy not allocated (precond != 1)
   int mg_nd;               // levels [0, mg_nd) are slab-distributed, [mg_nd, mg_levels) replicated (0 when world == 1)
+  int mg_tail0;            // levels [mg_tail0, mg_levels) run inside the one-block tail kernel (mg.cu)
   // cell-sort arrays
   int32_t* cell_count;     // total+2 entries (last bucket: invalid particles)
   int32_t* cell_start;

@@ -15,7 +15,8 @@
 //    cells dropped and the rest renormalised (constant extrapolation at Neumann walls) -- the
 //    normaliser of every fine cell is an integer n64/64 kept in a byte array per level;
 //    restriction R = P^T / 8.  => M^-1 is symmetric positive definite, as CG requires.
-//  * coarsest level (<= 4096 cells): 41 Jacobi sweeps inside one thread block, in shared memory.
+//  * levels of <= 4096 cells run inside ONE thread block (k_mg_tail); the coarsest (<= 512 cells) is
+//    solved by 40 Chebyshev steps in shared memory.
 //  * precision: the whole cycle runs in fp32 on a residual scaled to O(1) (the outer CG stays fp64
 //    and converges to the same 2.2e-16; prototype: 23 vs 22 iterations, tools/mg_proto3.py), which
 //    halves the preconditioner's HBM traffic.  r.z is accumulated in fp64 against the fp64 residual.
@@ -26,8 +27,9 @@
 #include "pcg.cuh"
 #include "halo.cuh"
 
-#define MG_COARSE_SWEEPS 40
-#define MG_COARSEST_CELLS 4096
+#define MG_TAIL_CELLS 4096       // levels up to this size run inside the one-block tail kernel
+#define MG_COARSEST_CELLS 512    // coarsening stops here (Chebyshev solve)
+#define MG_TAIL_MAX 4
 
 #define MG_REPLICATED_CELLS (1 << 19)   // z-slab runs: levels with at most this many cells are solved on every rank
 
@@ -58,8 +60,10 @@ static int mg_alloc_level(flipb200_ctx* c, MgLevel& L, bool own_flags) {
   return 0;
 }
 
-__global__ void k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* __restrict__ b,
-                              float* __restrict__ xout, const DevScalars* __restrict__ ds);
+struct MgTail;
+struct DevScalars;
+typedef void (*TailKernel)(const MgTail, const DevScalars*);
+static TailKernel tail_kernel(int n);
 
 int fb_mg_alloc(flipb200_ctx* c) {
   c->mg_levels = 0; c->mg_nd = 0;
@@ -68,9 +72,11 @@ int fb_mg_alloc(flipb200_ctx* c) {
   Grid f = c->g; f.nz = f.gnz;
   int nl = 1;
   Grid dims[MG_MAX_LEVELS]; dims[0] = f;
+  const char* te = getenv("FLIPB200_MG_TAIL");      // =0: stop coarsening at MG_TAIL_CELLS (tail = coarsest level only)
+  const int64_t stop_cells = (te && te[0] == '0') ? MG_TAIL_CELLS : MG_COARSEST_CELLS;
   while (nl < MG_MAX_LEVELS) {
     const Grid& p = dims[nl - 1];
-    if ((int64_t)p.nx * p.ny * p.nz <= MG_COARSEST_CELLS || min(p.nx, min(p.ny, p.nz)) < 4) break;
+    if ((int64_t)p.nx * p.ny * p.nz <= stop_cells || min(p.nx, min(p.ny, p.nz)) < 4) break;
     mg_level_dims(p, &dims[nl]);
     ++nl;
   }
@@ -101,8 +107,14 @@ int fb_mg_alloc(flipb200_ctx* c) {
     } else L.g = dims[l];
     if (mg_alloc_level(c, L, l > 0)) return FLIPB200_ERR_CUDA;
   }
-  CK(cudaFuncSetAttribute(k_mg_coarsest, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+  for (int n = 1; n <= MG_TAIL_MAX; ++n)
+    CK(cudaFuncSetAttribute((const void*)tail_kernel(n), cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
   c->mg_levels = nl; c->mg_nd = nd;
+  // first level of the one-block tail: replicated, not level 0, small enough, at most MG_TAIL_MAX levels
+  int t0 = nl - 1;
+  while (t0 - 1 >= max(1, nd) && nl - (t0 - 1) <= MG_TAIL_MAX &&
+         (int64_t)dims[t0 - 1].nx * dims[t0 - 1].ny * dims[t0 - 1].nz <= MG_TAIL_CELLS) --t0;
+  c->mg_tail0 = t0;
   return 0;
 }
 
@@ -441,10 +453,26 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
       return cin ? 3.f * r0[I] + wy * r1[I] : 0.f;
     };
     const int xe = min(gf.px, (fbox.x1 + 1) & ~1);
+    const bool act = i < xe;
     int Kc = (k0c + gf.kg0) >> 1;
     float em, e0, ep;
     float Ym = ycomb(Kc - 1, em), Y0 = ycomb(Kc, e0), Yp = ycomb(Kc + 1, ep);
-    for (int k = k0c; k < k1c; ++k) {
+    // the fine-plane operands are fetched one plane ahead (the march is latency-bound otherwise)
+    int q = gidx(gf, act ? i : 0, j, k0c);
+    uchar2 f = make_uchar2(0, 0), nn = make_uchar2(1, 1), f1 = f, nn1 = nn;
+    float2 xv = make_float2(0.f, 0.f), xv1 = xv;
+    if (act) {
+      f = *reinterpret_cast<const uchar2*>(ff + q);
+      nn = *reinterpret_cast<const uchar2*>(nrm + q);
+      xv = *reinterpret_cast<const float2*>(x + q);
+    }
+    for (int k = k0c; k < k1c; ++k, q += gf.plane) {
+      if (act && k + 1 < k1c) {
+        const int qn = q + gf.plane;
+        f1 = *reinterpret_cast<const uchar2*>(ff + qn);
+        nn1 = *reinterpret_cast<const uchar2*>(nrm + qn);
+        xv1 = *reinterpret_cast<const float2*>(x + qn);
+      }
       const int kg = k + gf.kg0;                       // global fine plane; its donors are kg>>1 (3) and kg>>1 -+ 1 (1)
       if ((kg >> 1) != Kc) {
         Kc = kg >> 1;
@@ -457,41 +485,162 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
       float EL = __shfl_up_sync(0xffffffffu, E, 1), ER = __shfl_down_sync(0xffffffffu, E, 1);
       if (lane == 0) EL = Ee;
       if (lane == 31) ER = Ee;
-      if (i < xe) {
-        const int q = gidx(gf, i, j, k);
-        const uchar2 f = *reinterpret_cast<const uchar2*>(ff + q);      // three independent loads in flight
-        const uchar2 nn = *reinterpret_cast<const uchar2*>(nrm + q);
-        float2 xv = *reinterpret_cast<const float2*>(x + q);
-        if ((f.x | f.y) & FB_FLUID) {
-          if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
-          if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
-          *reinterpret_cast<float2*>(x + q) = xv;
-          halo_push2<float>(H, q, k, xv.x, xv.y);
-        }
+      if ((f.x | f.y) & FB_FLUID) {                    // never true on inactive lanes (f = 0)
+        if (f.x & FB_FLUID) xv.x += __fdividef(3.f * E + EL, (float)nn.x);     // node 2I   : donors I (3) and I-1 (1)
+        if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
+        *reinterpret_cast<float2*>(x + q) = xv;
+        halo_push2<float>(H, q, k, xv.x, xv.y);
       }
+      f = f1; nn = nn1; xv = xv1;
     }
   }
   halo_signal(H, ds, bdn, bup);
 }
 
-// coarsest level (<= 4096 cells) in ONE block: 40 steps of the Chebyshev semi-iteration on the
+// ---- the tail of the V-cycle in ONE block ---------------------------------------------------------
+// Levels with <= MG_TAIL_CELLS cells (16^3 and below at 256^3) cost more in launch latency than in
+// work, so one 1024-thread block runs that whole part of the cycle: the level loops are plain
+// per-cell restatements of k_mg_smooth / k_mg_resid / k_mg_restrict / k_mg_prolong over the level's
+// (L1-resident) global arrays with a __syncthreads between the sweeps, and the coarsest level
+// (<= MG_COARSEST_CELLS) is solved by MG_CHEB_STEPS steps of the Chebyshev semi-iteration on the
 // Jacobi-scaled operator D^-1 A (spectrum inside [MG_CHEB_LMIN, 2]) -- a fixed polynomial, hence
 // still a symmetric linear preconditioner, and close to an exact coarse solve (22 vs 27 outer
-// iterations against 41 plain Jacobi sweeps, tools/mg_proto4.py).  The search direction d lives
-// in shared memory with a zero halo (ping-pong); x, r of the (<= 4) cells of a thread in registers.
+// iterations against 41 plain Jacobi sweeps, tools/mg_proto4.py).  Its search direction d lives in
+// shared memory with a zero halo (ping-pong); x, r of the (<= 4) cells of a thread in registers.
+// The arrays are rewritten inside the kernel: no __restrict__ / read-only loads here.
 #define MG_CHEB_STEPS 40
 #define MG_CHEB_LMIN 0.005f
-__global__ void __launch_bounds__(1024)
-k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* __restrict__ b,
-              float* __restrict__ xout, const DevScalars* __restrict__ ds) {
-  extern __shared__ float smx[];
-  if (ds->pcg_done) return;
-  const int bx = S.box.x1 - S.box.x0, by = S.box.y1 - S.box.y0, bz = S.box.z1 - S.box.z0;
+struct TailLevel {
+  Grid g; Box box;
+  MgCoef m1, m2;            // weights W1 / W2
+  const uint8_t* fl; const uint8_t* nrm;
+  float *xa, *xb, *b;
+};
+struct MgTail { int n, cheb_steps; float cheb_lmin; TailLevel L[MG_TAIL_MAX]; };   // L[0] finest tail level ... L[n-1] coarsest
+
+// the (<= 4) cells of a thread on one tail level: computed once, reused by every sweep of the level
+struct TailCells {
+  int q[4];                 // array index, -1: no cell
+  int ijk[4];               // i | j << 10 | k << 20
+  uint8_t f[4];             // flag byte (0 when !fluid: the sweeps only need fluid cells)
+  uint8_t in[4];            // bit d set: neighbour d (x-,x+,y-,y+,z-,z+) is inside the grid
+};
+__device__ __forceinline__ void tail_cells(const TailLevel& L, TailCells& c) {
+  const int bx = L.box.x1 - L.box.x0, by = L.box.y1 - L.box.y0, bz = L.box.z1 - L.box.z0;
+  const int n = bx * by * bz;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int e = threadIdx.x + u * 1024;
+    c.q[u] = -1; c.f[u] = 0; c.in[u] = 0; c.ijk[u] = 0;
+    if (e < n) {
+      const int i = L.box.x0 + e % bx, j = L.box.y0 + (e / bx) % by, k = L.box.z0 + e / (bx * by);
+      c.q[u] = gidx(L.g, i, j, k);
+      c.ijk[u] = i | (j << 10) | (k << 20);
+      c.f[u] = L.fl[c.q[u]];
+      c.in[u] = (i > 0 ? 1 : 0) | (i < L.g.nx - 1 ? 2 : 0) | (j > 0 ? 4 : 0) | (j < L.g.ny - 1 ? 8 : 0) |
+                (k > 0 ? 16 : 0) | (k < L.g.nz - 1 ? 32 : 0);
+    }
+  }
+}
+// sum of the six neighbours (0 outside the grid; non-fluid cells hold 0)
+__device__ __forceinline__ float tail_nsum(const Grid& g, int q, uint8_t in, const float* x) {
+  const float xm = (in & 1) ? x[q - 1] : 0.f, xp = (in & 2) ? x[q + 1] : 0.f;
+  const float ym = (in & 4) ? x[q - g.px] : 0.f, yp = (in & 8) ? x[q + g.px] : 0.f;
+  const float zm = (in & 16) ? x[q - g.plane] : 0.f, zp = (in & 32) ? x[q + g.plane] : 0.f;
+  return (zm + zp) + (ym + yp) + (xm + xp);
+}
+__device__ __forceinline__ void tail_smooth(const TailLevel& L, const TailCells& c, const MgCoef& mc, const float* xi, float* xo) {
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    if (c.q[u] < 0) continue;
+    float o = 0.f;
+    if (c.f[u] & FB_FLUID) {
+      const int kk = 6 - __popc(c.f[u] & FB_SMASK);
+      const float xc = xi[c.q[u]];
+      o = xc + mc.winv[kk] * (L.b[c.q[u]] - mc.h2inv * ((float)kk * xc - tail_nsum(L.g, c.q[u], c.in[u], xi)));
+    }
+    xo[c.q[u]] = o;
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void tail_resid(const TailLevel& L, const TailCells& c, const float* x, float* rn) {
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    if (c.q[u] < 0) continue;
+    float o = 0.f;
+    if (c.f[u] & FB_FLUID) {
+      const int kk = 6 - __popc(c.f[u] & FB_SMASK);
+      o = (L.b[c.q[u]] - L.m1.h2inv * ((float)kk * x[c.q[u]] - tail_nsum(L.g, c.q[u], c.in[u], x))) *
+          (64.f / (float)L.nrm[c.q[u]]);
+    }
+    rn[c.q[u]] = o;
+  }
+  __syncthreads();
+}
+// C.b = R rn, C.xa = W1 D^-1 C.b  (k_mg_restrict); cc: the thread's cells on the COARSE level
+__device__ __forceinline__ void tail_restrict(const TailLevel& F, const TailLevel& C, const TailCells& cc, const float* rn) {
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    if (cc.q[u] < 0) continue;
+    float r = 0.f, x1 = 0.f;
+    if (cc.f[u] & FB_FLUID) {
+      const int ci = cc.ijk[u] & 1023, cj = (cc.ijk[u] >> 10) & 1023, ck = cc.ijk[u] >> 20;
+      float sum = 0.f;
+#pragma unroll 1
+      for (int tz = 0; tz < 4; ++tz) {
+        const int kf = 2 * ck + tz - 1;
+        if (kf < F.box.z0 || kf >= F.box.z1) continue;
+        const float wz = (tz == 1 || tz == 2) ? 3.f : 1.f;
+#pragma unroll
+        for (int ty = 0; ty < 4; ++ty) {
+          const int jf = 2 * cj + ty - 1;
+          if (jf < F.box.y0 || jf >= F.box.y1) continue;
+          const float wzy = wz * ((ty == 1 || ty == 2) ? 3.f : 1.f);
+          const float* row = rn + gidx(F.g, 0, jf, kf);
+          float rs = 0.f;
+#pragma unroll
+          for (int tx = 0; tx < 4; ++tx) {
+            const int xf = 2 * ci + tx - 1;
+            if (xf >= F.box.x0 && xf < F.box.x1) rs += ((tx == 1 || tx == 2) ? 3.f : 1.f) * row[xf];
+          }
+          sum += wzy * rs;
+        }
+      }
+      r = sum * (1.f / 512.f);
+      x1 = C.m1.winv[6 - __popc(cc.f[u] & FB_SMASK)] * r;
+    }
+    C.b[cc.q[u]] = r;
+    C.xa[cc.q[u]] = x1;
+  }
+  __syncthreads();
+}
+// F.xb += P C.xb  (k_mg_prolong); c: the thread's cells on the FINE level
+__device__ __forceinline__ void tail_prolong(const TailLevel& F, const TailLevel& C, const TailCells& c) {
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    if (c.q[u] < 0 || !(c.f[u] & FB_FLUID)) continue;
+    const int i = c.ijk[u] & 1023, j = (c.ijk[u] >> 10) & 1023, k = c.ijk[u] >> 20;
+    const int I = i >> 1, J = j >> 1, K = k >> 1;
+    const int I2 = I + ((i & 1) ? 1 : -1), J2 = J + ((j & 1) ? 1 : -1), K2 = K + ((k & 1) ? 1 : -1);
+    float sum = 0.f;
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const int ci = (m & 1) ? I2 : I, cj = (m & 2) ? J2 : J, ck = (m & 4) ? K2 : K;
+      if (ci < 0 || ci >= C.g.nx || cj < 0 || cj >= C.g.ny || ck < 0 || ck >= C.g.nz) continue;
+      sum += (float)(((m & 1) ? 1 : 3) * ((m & 2) ? 1 : 3) * ((m & 4) ? 1 : 3)) * C.xb[gidx(C.g, ci, cj, ck)];
+    }
+    F.xb[c.q[u]] += __fdividef(sum, (float)F.nrm[c.q[u]]);
+  }
+  __syncthreads();
+}
+// coarsest level: b -> xb
+__device__ void tail_cheb(const TailLevel& L, float* smx, int steps, float lmin) {
+  const int bx = L.box.x1 - L.box.x0, by = L.box.y1 - L.box.y0, bz = L.box.z1 - L.box.z0;
   const int n = bx * by * bz;
   const int sx = bx + 2, sxy = sx * (by + 2), stot = sxy * (bz + 2);
   float* A = smx; float* B = smx + stot;
   for (int e = threadIdx.x; e < 2 * stot; e += blockDim.x) smx[e] = 0.f;
-  const float lmax = 2.f, lmin = MG_CHEB_LMIN;
+  const float lmax = 2.f;
   const float theta = 0.5f * (lmax + lmin), delta = 0.5f * (lmax - lmin), sigma = theta / delta;
   float xr[4], rr[4], kinv[4]; int sidx[4], gq[4];
   __syncthreads();
@@ -501,20 +650,20 @@ k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* _
     xr[u] = 0.f; rr[u] = 0.f; kinv[u] = 0.f; sidx[u] = -1; gq[u] = 0;
     if (e < n) {
       int li = e % bx, lj = (e / bx) % by, lk = e / (bx * by);
-      int q = gidx(S.g, S.box.x0 + li, S.box.y0 + lj, S.box.z0 + lk);
-      uint8_t f = fl[q];
+      int q = gidx(L.g, L.box.x0 + li, L.box.y0 + lj, L.box.z0 + lk);
+      uint8_t f = L.fl[q];
       sidx[u] = (lk + 1) * sxy + (lj + 1) * sx + li + 1; gq[u] = q;
       if (f & FB_FLUID) {
         int kk = 6 - __popc(f & FB_SMASK);
         kinv[u] = 1.f / (float)kk;
-        rr[u] = b[q] * kinv[u] / mc.h2inv;          // r0 = D^-1 b
+        rr[u] = L.b[q] * kinv[u] / L.m1.h2inv;      // r0 = D^-1 b
         A[sidx[u]] = rr[u] / theta;                 // d0
       }
     }
   }
   __syncthreads();
   float rho = 1.f / sigma;
-  for (int s = 0; s < MG_CHEB_STEPS; ++s) {
+  for (int s = 0; s < steps; ++s) {
     const float* di = (s & 1) ? B : A;
     float* dn = (s & 1) ? A : B;
     const float rho_new = 1.f / (2.f * sigma - rho);
@@ -534,7 +683,36 @@ k_mg_coarsest(Sweep S, MgCoef mc, const uint8_t* __restrict__ fl, const float* _
   }
 #pragma unroll
   for (int u = 0; u < 4; ++u)
-    if (sidx[u] >= 0) xout[gq[u]] = xr[u];
+    if (sidx[u] >= 0) L.xb[gq[u]] = xr[u];
+  __syncthreads();
+}
+
+template <int N>                                     // N = number of tail levels (T.n)
+__global__ void __launch_bounds__(1024)
+k_mg_tail(const __grid_constant__ MgTail T, const DevScalars* __restrict__ ds) {
+  extern __shared__ float smx[];
+  if (ds->pcg_done) return;
+  TailCells c[N];                                    // every loop below unrolls: registers
+#pragma unroll
+  for (int l = 0; l < N; ++l) tail_cells(T.L[l], c[l]);
+#pragma unroll
+  for (int l = 0; l < N - 1; ++l) {                  // down: b, xa (first pre-sweep) come from the restriction above
+    const TailLevel& L = T.L[l];
+    tail_smooth(L, c[l], L.m2, L.xa, L.xb);
+    tail_resid(L, c[l], L.xb, L.xa);
+    tail_restrict(L, T.L[l + 1], c[l + 1], L.xa);
+  }
+  tail_cheb(T.L[N - 1], smx, T.cheb_steps, T.cheb_lmin);
+#pragma unroll
+  for (int l = N - 2; l >= 0; --l) {                 // up
+    const TailLevel& L = T.L[l];
+    tail_prolong(L, T.L[l + 1], c[l]);
+    tail_smooth(L, c[l], L.m2, L.xb, L.xa);
+    tail_smooth(L, c[l], L.m1, L.xa, L.xb);
+  }
+}
+static TailKernel tail_kernel(int n) {
+  switch (n) { case 1: return k_mg_tail<1>; case 2: return k_mg_tail<2>; case 3: return k_mg_tail<3>; default: return k_mg_tail<4>; }
 }
 
 // ---- host orchestration ----------------------------------------------------------------------
@@ -567,7 +745,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   }
   if (sweep_empty(S[0])) return 0;
   const size_t F = sizeof(float);
-  for (int l = 0; l < nl - 1; ++l) {
+  const int t0 = c->mg_tail0;
+  for (int l = 0; l < t0; ++l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const dim3 tg = stencil_grid(S[l]);
@@ -606,15 +785,31 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     c->launches += 3;
   }
   {
-    MgLevel& L = c->mg[nl - 1];
-    const Box& b = L.box;
+    MgTail T;
+    memset(&T, 0, sizeof(T));
+    T.n = nl - t0;
+    for (int l = t0; l < nl; ++l) {
+      MgLevel& L = c->mg[l];
+      TailLevel& t = T.L[l - t0];
+      t.g = L.g; t.box = L.box; t.m1 = mc[l]; t.m2 = mc2[l];
+      t.fl = L.flags; t.nrm = L.nrm; t.xa = L.xa; t.xb = L.xb; t.b = L.b;
+    }
+    const Box& b = c->mg[nl - 1].box;
+    // 40 steps on [0.005, 2] also on the 8^3 coarsest level: shorter polynomials on a narrower interval
+    // (30 on [0.01, 2], 24 on [0.01, 2] ...) saved 5 us per cycle but cost 1-2 CG iterations per step.
+    T.cheb_steps = MG_CHEB_STEPS;
+    T.cheb_lmin = MG_CHEB_LMIN;
+    if (const char* e = getenv("FLIPB200_CHEB")) {   // "steps,lmin" (experiments)
+      int st = 0; float lm = 0.f;
+      if (sscanf(e, "%d,%f", &st, &lm) == 2 && st > 0 && st <= 200 && lm > 0.f && lm < 1.f) { T.cheb_steps = st; T.cheb_lmin = lm; }
+    }
     size_t smem = 2 * sizeof(float) * (size_t)(b.x1 - b.x0 + 2) * (b.y1 - b.y0 + 2) * (b.z1 - b.z0 + 2);
     if (smem > 160 * 1024 || (int64_t)(b.x1 - b.x0) * (b.y1 - b.y0) * (b.z1 - b.z0) > 4096) return FLIPB200_ERR_ARG;
-    k_mg_coarsest<<<1, 1024, smem, c->stream>>>(S[nl - 1], mc[nl - 1], L.flags, L.b, L.xb, c->ds);
+    tail_kernel(T.n)<<<1, 1024, smem, c->stream>>>(T, c->ds);
     c->launches++;
-    fb_prof(c, "coarsest");
+    fb_prof(c, "tail (small levels + coarsest)");
   }
-  for (int l = nl - 2; l >= 0; --l) {
+  for (int l = t0 - 1; l >= 0; --l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const Box& fb = L.box;
