@@ -34,6 +34,7 @@ struct NcclApi {
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
   ncclResult_t (*GroupStart)();
   ncclResult_t (*GroupEnd)();
   const char* (*GetErrorString)(ncclResult_t);
@@ -56,7 +57,7 @@ static bool nccl_load() {
   *(void**)(&g_nccl.field) = dlsym(h, name);                               \
   if (!g_nccl.field) { fprintf(stderr, "flipb200: %s missing in NCCL\n", name); return false; }
   SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
-  SYM(Send, "ncclSend") SYM(Recv, "ncclRecv") SYM(AllReduce, "ncclAllReduce") SYM(Broadcast, "ncclBroadcast")
+  SYM(Send, "ncclSend") SYM(Recv, "ncclRecv") SYM(AllReduce, "ncclAllReduce") SYM(Broadcast, "ncclBroadcast") SYM(AllGather, "ncclAllGather")
   SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd") SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
   g_nccl.h = h;
@@ -305,32 +306,54 @@ int fb_allreduce(flipb200_ctx* c, void* dev, int count, int type, int op) {
 }
 
 // ---- all-gather of the owned planes of a replicated grid ----------------------------------------
-int fb_allgather_planes(flipb200_ctx* c, const Grid& gg, void* base, size_t elem, const int* zs) {
+// All-gather of the z-planes [zs[r], zs[r+1]) that rank r owns of up to two arrays of one level
+// (one NCCL launch: in-place ncclAllGather when the ranks own equally many planes, grouped
+// broadcasts otherwise).
+int fb_allgather_planes2(flipb200_ctx* c, const Grid& gg, void* base0, void* base1, size_t elem, const int* zs) {
   if (c->world == 1) return 0;
   if (comm_missing(c)) return FLIPB200_ERR_COMM;
   const size_t pb = (size_t)gg.plane * elem;
-  char* b = (char*)base;
+  void* bases[2] = {base0, base1};
   if (c->comm->kind == 1) {
+    bool uniform = zs[0] == 0;
+    for (int r = 1; r < c->world; ++r) uniform = uniform && (zs[r + 1] - zs[r] == zs[1] - zs[0]);
     NC(g_nccl.GroupStart());
-    for (int r = 0; r < c->world; ++r) {
-      const size_t n = (size_t)(zs[r + 1] - zs[r]) * pb;
-      if (n) NC(g_nccl.Broadcast(b + (size_t)zs[r] * pb, b + (size_t)zs[r] * pb, n, ncclChar, r, c->comm->nc, c->stream));
+    for (int a = 0; a < 2; ++a) {
+      char* b = (char*)bases[a];
+      if (!b) continue;
+      if (uniform && g_nccl.AllGather) {
+        const size_t n = (size_t)(zs[1] - zs[0]) * pb;
+        NC(g_nccl.AllGather(b + (size_t)c->rank * n, b, n, ncclChar, c->comm->nc, c->stream));
+        continue;
+      }
+      for (int r = 0; r < c->world; ++r) {
+        const size_t n = (size_t)(zs[r + 1] - zs[r]) * pb;
+        if (n) NC(g_nccl.Broadcast(b + (size_t)zs[r] * pb, b + (size_t)zs[r] * pb, n, ncclChar, r, c->comm->nc, c->stream));
+      }
     }
     NC(g_nccl.GroupEnd());
     return 0;
   }
   LocalGroup* lg = c->comm->lg;
-  lg->ptr[c->rank][0] = base;
+  lg->ptr[c->rank][0] = base0;
+  lg->ptr[c->rank][1] = base1;
   CK(cudaStreamSynchronize(c->stream));
   lg->barrier();
-  for (int r = 0; r < c->world; ++r) {
-    const size_t n = (size_t)(zs[r + 1] - zs[r]) * pb;
-    if (r == c->rank || !n) continue;
-    CK(cudaMemcpyAsync(b + (size_t)zs[r] * pb, (char*)lg->ptr[r][0] + (size_t)zs[r] * pb, n, cudaMemcpyDefault, c->stream));
+  for (int a = 0; a < 2; ++a) {
+    char* b = (char*)bases[a];
+    if (!b) continue;
+    for (int r = 0; r < c->world; ++r) {
+      const size_t n = (size_t)(zs[r + 1] - zs[r]) * pb;
+      if (r == c->rank || !n) continue;
+      CK(cudaMemcpyAsync(b + (size_t)zs[r] * pb, (char*)lg->ptr[r][a] + (size_t)zs[r] * pb, n, cudaMemcpyDefault, c->stream));
+    }
   }
   CK(cudaStreamSynchronize(c->stream));
   lg->barrier();
   return 0;
+}
+int fb_allgather_planes(flipb200_ctx* c, const Grid& gg, void* base, size_t elem, const int* zs) {
+  return fb_allgather_planes2(c, gg, base, nullptr, elem, zs);
 }
 
 // ---- particle migration --------------------------------------------------------------------------

@@ -1,6 +1,7 @@
 // common.cuh -- shared definitions of the B200-native FLIP substep library (libflipb200.so).
 // Product code: never includes or links anything under oracle/.
 #pragma once
+#include <stdlib.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -311,6 +312,7 @@ int fb_halo_sum_up(flipb200_ctx* c, double* const arr[4]);
 int fb_allreduce(flipb200_ctx* c, void* dev, int count, int type, int op);
 // every rank ends with all owned planes of a REPLICATED (global) grid; zs[r] = first plane of rank r
 int fb_allgather_planes(flipb200_ctx* c, const Grid& gglobal, void* base, size_t elem, const int* zs);
+int fb_allgather_planes2(flipb200_ctx* c, const Grid& g, void* base0, void* base1, size_t elem, const int* zs);
 // exchange the particles of the trailing down / up buckets with the neighbours (particles.cu)
 int fb_comm_exchange_counts(flipb200_ctx* c, const int64_t send[2], int64_t recv[2]);
 int fb_comm_exchange_particles(flipb200_ctx* c, int narr, void* const src[], void* const dst[], const size_t elem[],

@@ -777,8 +777,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     fb_prof(c, l == 0 ? "L0 halo+restrict" : (l == 1 ? "L1 halo+restrict" : "L2+ halo+restrict"));
     if (L.dist && !C.dist) {
-      int rc = fb_allgather_planes(c, C.g, C.b, sizeof(float), C.zs);
-      if (!rc) rc = fb_allgather_planes(c, C.g, C.xa, sizeof(float), C.zs);
+      int rc = fb_allgather_planes2(c, C.g, C.b, C.xa, sizeof(float), C.zs);
       if (rc) return rc;
       fb_prof(c, "allgather b, xa");
     }

@@ -2,6 +2,7 @@
 // two patterns the pressure solver is made of: (S) pure streaming axpy-type updates and (T) 7-point
 // stencil sweeps, on 256^3 fp64 arrays with a 1-byte flag array.
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/kbench tools/kbench.cu
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdint.h>
@@ -120,6 +121,132 @@ __global__ void t4_vec2(int n, const uint8_t* __restrict__ fl, const double* __r
   if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
 }
 
+// T5: T4 with the centre column fetched PD = 2 planes ahead and the flags one plane ahead
+template <int BY, int ZP>
+__global__ void t5_pref(int n, const uint8_t* __restrict__ fl, const double* __restrict__ p, double* __restrict__ Ap, double* out) {
+  const int lane = threadIdx.x;
+  int i = blockIdx.x * 64 + 2 * lane, j = blockIdx.y * BY + threadIdx.y, k0 = blockIdx.z * ZP;
+  int plane = n * n;
+  int q = k0 * plane + j * n + i;
+  const bool jlo = j > 0, jhi = j < n - 1;
+  double acc = 0;
+  const double2 z2 = make_double2(0, 0);
+  double2 pm = k0 > 0 ? *(const double2*)(p + q - plane) : z2;
+  double2 pc = *(const double2*)(p + q);
+  double2 pn = k0 < n - 1 ? *(const double2*)(p + q + plane) : z2;
+  uchar2 f = *(const uchar2*)(fl + q);
+#pragma unroll
+  for (int z = 0; z < ZP; ++z, q += plane) {
+    int k = k0 + z;
+    double2 pnn = (z + 1 < ZP && k + 2 < n) ? *(const double2*)(p + q + 2 * plane) : z2;
+    uchar2 fn = (z + 1 < ZP) ? *(const uchar2*)(fl + q + plane) : make_uchar2(0, 0);
+    double2 ym = jlo ? *(const double2*)(p + q - n) : z2;
+    double2 yp = jhi ? *(const double2*)(p + q + n) : z2;
+    double left = __shfl_up_sync(~0u, pc.y, 1), right = __shfl_down_sync(~0u, pc.x, 1);
+    if (lane == 0) left = i > 0 ? p[q - 1] : 0.0;
+    if (lane == 31) right = i + 2 < n ? p[q + 2] : 0.0;
+    double2 ap = z2;
+    if (f.x & 64) { int kk = 6 - __popc(f.x & 63); ap.x = kk * 0.1 * pc.x - 0.1 * ((pm.x + pn.x) + (ym.x + yp.x) + (left + pc.y)); acc += pc.x * ap.x; }
+    if (f.y & 64) { int kk = 6 - __popc(f.y & 63); ap.y = kk * 0.1 * pc.y - 0.1 * ((pm.y + pn.y) + (ym.y + yp.y) + (pc.x + right)); acc += pc.y * ap.y; }
+    if ((f.x | f.y) & 64) *(double2*)(Ap + q) = ap;
+    pm = pc; pc = pn; pn = pnn; f = fn;
+  }
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
+  __shared__ double sm[32];
+  if (lane == 0) sm[threadIdx.y] = acc;
+  __syncthreads();
+  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+}
+
+// T6: planes staged in shared memory by TMA (box 68 x (BY+2) x 1 doubles, out-of-range -> 0), NST-deep
+// ring with one mbarrier per slot; the block marches ZP planes.  Centre column rotates in registers.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int cnt) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(cnt)); }
+__device__ __forceinline__ void mbar_expect(uint64_t* b, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+  asm volatile("{\n.reg .pred p;\nWAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, int c0, int c1, int c2, uint64_t* b) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+               ::"r"(smem_u32(dst)), "l"(m), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(b)) : "memory");
+}
+template <int BY, int ZP, int NST>
+__global__ void __launch_bounds__(32 * BY)
+t6_tma(const __grid_constant__ CUtensorMap mp, int n, const uint8_t* __restrict__ fl, double* __restrict__ Ap, double* out) {
+  constexpr int TX = 68, TY = BY + 2;
+  constexpr int STAGE = ((TX * TY * 8 + 127) / 128) * 128;
+  extern __shared__ __align__(128) unsigned char smraw[];
+  __shared__ __align__(8) uint64_t bar[NST];
+  __shared__ double sm[32];
+  const int lane = threadIdx.x, ty = threadIdx.y, tid = ty * 32 + lane;
+  const int i0 = blockIdx.x * 64, j0 = blockIdx.y * BY, k0 = blockIdx.z * ZP;
+  if (tid == 0) {
+    for (int s = 0; s < NST; ++s) mbar_init(&bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  // plane t (0 .. ZP+1) is z = k0 - 1 + t, slot t % NST, parity (t / NST) & 1
+  auto issue = [&](int t) {
+    const int s = t % NST;
+    mbar_expect(&bar[s], TX * TY * 8);
+    tma_load_3d(smraw + s * STAGE, &mp, i0 - 2, j0 - 1, k0 - 1 + t, &bar[s]);
+  };
+  if (tid == 0)
+    for (int t = 0; t < NST && t < ZP + 2; ++t) issue(t);
+  const int i = i0 + 2 * lane, j = j0 + ty;
+  const int plane = n * n;
+  int q = k0 * plane + j * n + i;
+  const int off = (ty + 1) * TX + 2 * lane + 2;             // this lane's pair inside a stage
+  auto tile = [&](int t) -> const double* { return (const double*)(smraw + (t % NST) * STAGE); };
+  mbar_wait(&bar[0], 0);
+  double2 pm = *(const double2*)(tile(0) + off);
+  mbar_wait(&bar[1 % NST], (1 / NST) & 1);
+  double2 pc = *(const double2*)(tile(1) + off);
+  uchar2 f = *(const uchar2*)(fl + q);
+  double acc = 0;
+#pragma unroll 1
+  for (int z = 0; z < ZP; ++z, q += plane) {
+    const int t = z + 1;                                     // plane of the centre
+    uchar2 fn = (z + 1 < ZP) ? *(const uchar2*)(fl + q + plane) : make_uchar2(0, 0);
+    mbar_wait(&bar[(t + 1) % NST], ((t + 1) / NST) & 1);
+    const double* tc = tile(t);
+    double2 pn = *(const double2*)(tile(t + 1) + off);
+    double2 ym = *(const double2*)(tc + off - TX);
+    double2 yp = *(const double2*)(tc + off + TX);
+    double left = __shfl_up_sync(~0u, pc.y, 1), right = __shfl_down_sync(~0u, pc.x, 1);
+    if (lane == 0) left = tc[off - 1];
+    if (lane == 31) right = tc[off + 2];
+    double2 ap = make_double2(0, 0);
+    if (f.x & 64) { int kk = 6 - __popc(f.x & 63); ap.x = kk * 0.1 * pc.x - 0.1 * ((pm.x + pn.x) + (ym.x + yp.x) + (left + pc.y)); acc += pc.x * ap.x; }
+    if (f.y & 64) { int kk = 6 - __popc(f.y & 63); ap.y = kk * 0.1 * pc.y - 0.1 * ((pm.y + pn.y) + (ym.y + yp.y) + (pc.x + right)); acc += pc.y * ap.y; }
+    if ((f.x | f.y) & 64) *(double2*)(Ap + q) = ap;
+    pm = pc; pc = pn; f = fn;
+    __syncthreads();                                         // everyone is done with plane t-1 (slot (t-1) % NST)
+    if (tid == 0 && t - 1 + NST < ZP + 2) issue(t - 1 + NST);
+  }
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
+  if (lane == 0) sm[ty] = acc;
+  __syncthreads();
+  if (tid == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+}
+
+typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static CUtensorMap make_map(void* base, int n, int by) {
+  void* fn = nullptr; cudaDriverEntryPointQueryResult qr;
+  CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+  CUtensorMap m;
+  cuuint64_t dims[3] = {(cuuint64_t)n, (cuuint64_t)n, (cuuint64_t)n};
+  cuuint64_t strides[2] = {(cuuint64_t)n * 8, (cuuint64_t)n * n * 8};
+  cuuint32_t box[3] = {68, (cuuint32_t)by + 2, 1};
+  cuuint32_t es[3] = {1, 1, 1};
+  CUresult r = ((EncodeTiled)fn)(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { printf("cuTensorMapEncodeTiled failed %d\n", (int)r); exit(1); }
+  return m;
+}
+
 int main(int argc, char** argv) {
   if (argc > 1) N = atoi(argv[1]);
   T = (size_t)N * N * N;
@@ -172,6 +299,23 @@ int main(int argc, char** argv) {
 #define RUN_T4(BY, ZP)                                                                                       \
   us = timeit([&] { t4_vec2<BY, ZP><<<dim3(N / 64, N / BY, N / ZP), dim3(32, BY)>>>(N, fl, p, Ap, out); }); \
   printf("T4 vec2 BY=%d ZP=%d          %8.1f us  %7.1f GB/s\n", BY, ZP, us, gb17 / us * 1e6);
+#define RUN_T5(BY, ZP)                                                                                       \
+  us = timeit([&] { t5_pref<BY, ZP><<<dim3(N / 64, N / BY, N / ZP), dim3(32, BY)>>>(N, fl, p, Ap, out); }); \
+  printf("T5 pref BY=%d ZP=%d          %8.1f us  %7.1f GB/s\n", BY, ZP, us, gb17 / us * 1e6);
+#define RUN_T6(BY, ZP, NST)                                                                                  \
+  {                                                                                                          \
+    CUtensorMap mp = make_map(p, N, BY);                                                                     \
+    size_t smem = (size_t)NST * (((68 * (BY + 2) * 8 + 127) / 128) * 128);                                   \
+    CK(cudaFuncSetAttribute(t6_tma<BY, ZP, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
+    us = timeit([&] { t6_tma<BY, ZP, NST><<<dim3(N / 64, N / BY, N / ZP), dim3(32, BY), smem>>>(mp, N, fl, Ap, out); }); \
+    printf("T6 tma  BY=%d ZP=%d NST=%d   %8.1f us  %7.1f GB/s\n", BY, ZP, NST, us, gb17 / us * 1e6);       \
+  }
+  if (argc > 2) {   // stencil variants only
+    RUN_T4(4, 4) RUN_T4(8, 4) RUN_T4(4, 8)
+    RUN_T5(4, 4) RUN_T5(8, 4) RUN_T5(4, 8) RUN_T5(8, 8) RUN_T5(4, 16) RUN_T5(8, 16)
+    RUN_T6(8, 16, 4) RUN_T6(8, 32, 4) RUN_T6(8, 64, 4) RUN_T6(16, 32, 4) RUN_T6(16, 64, 4) RUN_T6(8, 32, 6) RUN_T6(4, 32, 4) RUN_T6(4, 64, 6) RUN_T6(8, 256, 4)
+    return 0;
+  }
   RUN_T4(4, 1) RUN_T4(8, 1) RUN_T4(4, 2) RUN_T4(8, 2) RUN_T4(4, 4) RUN_T4(8, 4) RUN_T4(4, 8) RUN_T4(8, 8) RUN_T4(16, 4) RUN_T4(4, 16)
   return 0;
 }
