@@ -462,6 +462,7 @@ PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, siz
   HaloState& hs = c->halo;
   if (hs.mode == 0) return h;
   h.mode = hs.mode; h.kdn = kdn; h.kup = kup; h.nb = nb;
+  if (hs.dbg) { h.dbg = hs.dbg + 8 * (hs.dbg_n % HALO_DBG_MAX); hs.dbg_n++; }
   h.my_flags = hs.flags; h.cnt = hs.flags + 2;
   h.sig_dn = hs.peer_flags[0] ? hs.peer_flags[0] + 1 : nullptr;
   h.sig_up = hs.peer_flags[1] ? hs.peer_flags[1] + 0 : nullptr;
@@ -531,6 +532,13 @@ int fb_halo_setup(flipb200_ctx* c) {
   const char* e = getenv("FLIPB200_FUSED_HALO");
   if (e && e[0] == '0') return 0;
   CK(cudaMalloc((void**)&hs.flags, 4 * sizeof(unsigned)));
+  {
+    const char* de = getenv("FLIPB200_HALO_DEBUG");
+    if (de && de[0] == '1' && !hs.dbg) {
+      CK(cudaMalloc((void**)&hs.dbg, 8 * HALO_DBG_MAX * sizeof(unsigned long long)));
+      CK(cudaMemset(hs.dbg, 0, 8 * HALO_DBG_MAX * sizeof(unsigned long long)));
+    }
+  }
   CK(cudaMemsetAsync(hs.flags, 0, 4 * sizeof(unsigned), c->stream));
   CK(cudaStreamSynchronize(c->stream));
   const int nd = c->mg_nd;

@@ -126,7 +126,10 @@ struct Comm;   // comm.cu: NCCL (one process per GPU) or in-process threaded ran
 
 // host state of the ghost-plane pushes fused into the PCG kernels (halo.cuh, comm.cu)
 enum { HA_XA = 0, HA_XB = 1, HA_PD = 2 };
+#define HALO_DBG_MAX 64
 struct HaloState {
+  unsigned long long* dbg;   // FLIPB200_HALO_DEBUG=1: 8 timestamps per fb_halo_make call of an iteration
+  int dbg_n;
   int mode;                          // 0 off (halo copies), 1 push + host barrier (in-process ranks), 2 push + device flags
   unsigned* flags;                   // device: [0..1] flags written by the lower / upper neighbour, [2..3] block counters
   unsigned* peer_flags[2];           // the neighbours' flag blocks (peer mappings): [0] lower, [1] upper

@@ -8,7 +8,7 @@
 // only its boundary blocks wait on a flag -- interior blocks run while the planes are in flight.
 //
 //   producer block that owns boundary plane kdn / kup:   st.global to the peer pointer, then
-//       __threadfence_system, block counter; the LAST boundary block release-stores the sequence
+//       one system fence per block, block counter; the LAST boundary block release-stores the sequence
 //       number of this producer kernel into the neighbour's flag word.
 //   consumer block that reads ghost plane kdn-1 / kup+1: thread 0 acquire-spins until the flag
 //       reaches the sequence number of the latest producer of that array (bounded: a time-out sets
@@ -42,12 +42,33 @@ struct PeerHalo {
   unsigned* sig_dn;          // lower neighbour's my_flags[1]
   unsigned* sig_up;          // upper neighbour's my_flags[0]
   unsigned* cnt;             // [2] block counters (own memory)
+  unsigned long long* dbg;   // FLIPB200_HALO_DEBUG=1: timestamps of this launch's boundary blocks (8 per launch)
 };
+__device__ __forceinline__ unsigned long long halo_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ unsigned ld_relaxed_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -63,18 +84,27 @@ __device__ __forceinline__ void halo_wait(const PeerHalo& H, DevScalars* ds, boo
   if (!(w0 || w1)) return;
   const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
   if (tid == 0) {
+    // relaxed polls, ONE acquire fence after the flags have arrived (an acquire load per poll is a
+    // system-scope round trip each time)
+    if (H.dbg && blockIdx.x == 0 && blockIdx.y == 0) H.dbg[w0 ? 0 : 1] = halo_now();
     const unsigned base = (unsigned)ds->halo_base;
     const long long t0 = clock64();
     if (w0) {
       const unsigned need = base + (unsigned)H.wrel_dn;
-      while ((int)(ld_acquire_sys(&H.my_flags[0]) - need) < 0)
+      while ((int)(ld_relaxed_sys(&H.my_flags[0]) - need) < 0)
         if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
     }
     if (w1) {
       const unsigned need = base + (unsigned)H.wrel_up;
-      while ((int)(ld_acquire_sys(&H.my_flags[1]) - need) < 0)
+      while ((int)(ld_relaxed_sys(&H.my_flags[1]) - need) < 0)
         if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
     }
+    // The ghost planes and the flag live in THIS GPU's memory; the neighbour ordered them with a
+    // system-scope release.  What is left to do here is to keep this SM's later loads behind the flag
+    // load and away from stale L1 lines: a gpu-scope fence (0.7 us; the system-scope one costs 3.5 us
+    // of round trip that orders nothing more on the reading side).
+    fence_acq_rel_gpu();
+    if (H.dbg && blockIdx.x == 0 && blockIdx.y == 0) H.dbg[w0 ? 2 : 3] = halo_now();
   }
   __syncthreads();
 }
@@ -99,31 +129,44 @@ __device__ __forceinline__ void halo_signal(const PeerHalo& H, DevScalars* ds, b
   if (H.mode != 2) return;
   const bool s0 = bdn && H.push_dn, s1 = bup && H.push_up;
   if (!(s0 || s1)) return;
-  __threadfence_system();            // my peer stores are visible system-wide before the flag
+  // bar.sync orders the block's peer stores before thread 0's fence (cumulativity), so one thread
+  // fences for the block -- at gpu scope: it only has to order the stores before the block counter
+  // (a gpu-scope atomic).  The last block observes every other block through that counter (atomic,
+  // then the fence inside its release = acquire side) and its system-scope release-store of the
+  // sequence number is cumulative over all of them.  Measured (FLIPB200_HALO_DEBUG): a system-scope
+  // fence is a 3.5 us round trip; with one per block plus one in front of the release the signalling
+  // path of a boundary block (17 us) was longer than a whole level-1 sweep (12 us).
   __syncthreads();
   const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
   if (tid == 0) {
+    const bool dbg = H.dbg && blockIdx.x == 0 && blockIdx.y == 0;
+    if (dbg) H.dbg[4] = halo_now();                  // block done computing + pushing
+    fence_acq_rel_gpu();
+    if (dbg) H.dbg[5] = halo_now();
     const unsigned seq = (unsigned)ds->halo_base + (unsigned)H.srel;
-    if (s0 && atomicAdd(&H.cnt[0], 1u) == (unsigned)H.nb - 1u) { H.cnt[0] = 0u; __threadfence_system(); st_release_sys(H.sig_dn, seq); }
-    if (s1 && atomicAdd(&H.cnt[1], 1u) == (unsigned)H.nb - 1u) { H.cnt[1] = 0u; __threadfence_system(); st_release_sys(H.sig_up, seq); }
+    if (s0 && atomicAdd(&H.cnt[0], 1u) == (unsigned)H.nb - 1u) { H.cnt[0] = 0u; st_release_sys(H.sig_dn, seq); if (H.dbg) H.dbg[6] = halo_now(); }
+    if (s1 && atomicAdd(&H.cnt[1], 1u) == (unsigned)H.nb - 1u) { H.cnt[1] = 0u; st_release_sys(H.sig_up, seq); if (H.dbg) H.dbg[7] = halo_now(); }
   }
 }
 
 // ---- all-reduce of a dot product over peer memory ------------------------------------------------
 // Blocks add their partial sums into ds->part[id] as on one GPU.  One 32-thread kernel
 // (k_pcg_exchange, pcg.cu) then does the whole all-reduce: lane r stores this rank's sum into slot
-// [rank] of rank r's mailbox (peer store over NVLink) and release-stores the sequence number next
-// to it, waits for slot [r] of its own mailbox, and the warp adds the `world` values in rank order
-// (identical bits on every rank) into the ring slot the next kernel reads.  Replaces an 8-byte
-// ncclAllReduce (17-23 us) plus a publish kernel by one launch and one NVLink round trip.  Slots are
-// double-buffered by sequence parity; reuse is safe because a rank reaches exchange n+2 of an id
-// only after every rank has finished n (the other dot products of the iteration depend on it).
+// [rank] of rank r's mailbox (peer store over NVLink), waits for slot [r] of its own mailbox, and the
+// warp adds the `world` values in rank order (identical bits on every rank) into the ring slot the
+// next kernel reads.  The mailbox words are self-validating (the NCCL "LL" idea): the double travels
+// as two 8-byte words {32 value bits, 32-bit sequence number}; an aligned 8-byte store is single-copy
+// atomic, so the reader just polls both words until they carry this exchange's sequence number --
+// no fence on either side (a system-scope fence costs ~3.5 us on B200, measured with
+// FLIPB200_HALO_DEBUG).  Replaces an 8-byte ncclAllReduce (17-23 us) plus a publish kernel by one
+// launch and one NVLink one-way trip.  Slots are double-buffered by sequence parity; reuse is safe
+// because a rank reaches exchange n+2 of an id only after every rank has finished n (the other dot
+// products of the iteration depend on it).
 // (Publishing from the last block of the producing kernel was tried first: the per-block
 // fence + returning atomic made k_update_xr / k_spmv 5 % slower, a net loss.)
 #define RED_MAXR 16
 struct RedMail {
-  double val[4][2][RED_MAXR];        // [PART_* id][seq parity][source rank]
-  unsigned seq[4][2][RED_MAXR];
+  unsigned long long w[4][2][RED_MAXR][2];   // [PART_* id][seq parity][source rank][lo, hi]: value half | seq << 32
 };
 struct RedPub {
   int on, rank, world;

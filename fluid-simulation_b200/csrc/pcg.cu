@@ -180,14 +180,20 @@ __global__ void k_pcg_exchange(DevScalars* __restrict__ ds, const __grid_constan
   double v = 0.0;
   bool bad = false;
   if (lane < R.world) {
-    R.peers[lane]->val[id][par][R.rank] = mine;
-    __threadfence_system();
-    st_release_sys(&R.peers[lane]->seq[id][par][R.rank], seq);
-    RedMail* my = R.peers[R.rank];
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(mine);
+    const unsigned long long tag = (unsigned long long)seq << 32;
+    unsigned long long* dst = R.peers[lane]->w[id][par][R.rank];
+    st_relaxed_sys_u64(dst, (bits & 0xffffffffull) | tag);
+    st_relaxed_sys_u64(dst + 1, (bits >> 32) | tag);
+    const unsigned long long* src = R.peers[R.rank]->w[id][par][lane];
     const long long t0 = clock64();
-    while ((int)(ld_acquire_sys(&my->seq[id][par][lane]) - seq) < 0)
+    unsigned long long lo, hi;
+    for (;;) {
+      lo = ld_relaxed_sys_u64(src); hi = ld_relaxed_sys_u64(src + 1);
+      if ((unsigned)(lo >> 32) == seq && (unsigned)(hi >> 32) == seq) break;
       if (clock64() - t0 > HALO_SPIN_LIMIT) { bad = true; break; }
-    v = *(volatile double*)&my->val[id][par][lane];
+    }
+    v = __longlong_as_double((long long)((lo & 0xffffffffull) | (hi << 32)));
   }
   if (__any_sync(0xffffffffu, bad)) { if (lane == 0) { ds->pcg_status = FLIPB200_ERR_COMM; ds->pcg_done = 1; } return; }
   double sum = 0.0;
@@ -510,7 +516,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   if (prof && !c->prof) c->prof = (IterProf*)calloc(1, sizeof(IterProf));
   if (which == FLIPB200_KERNEL_PCG_ITER && !prof) graph = get_iteration_graph(c, S, cf, use_mg, dt, 1);
   for (int it = 0; it < 3 + iters; ++it) {
-    if (prof && it >= 3) { c->prof->on = true; c->prof->n = 0; }
+    if (prof && it >= 3) { c->prof->on = true; c->prof->n = 0; c->halo.dbg_n = 0; }
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
       k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1, 0, halo_off());
@@ -539,6 +545,19 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     for (int m = 1; m < p->n; ++m) fprintf(stderr, "  r%d %-28s %8.1f us\n", c->rank, p->name[m], p->acc[m] / p->iters * 1e3);
     for (int m = 0; m < PROF_MAX; ++m) p->acc[m] = 0.0;
     p->iters = 0;
+    if (c->halo.dbg) {   // boundary-block timestamps of the last profiled iteration (ns, relative to the first)
+      unsigned long long h[8 * HALO_DBG_MAX];
+      CK(cudaMemcpy(h, c->halo.dbg, sizeof(h), cudaMemcpyDeviceToHost));
+      unsigned long long t0 = ~0ull;
+      const int n = c->halo.dbg_n < HALO_DBG_MAX ? c->halo.dbg_n : HALO_DBG_MAX;
+      for (int m = 0; m < 8 * n; ++m) if (h[m] && h[m] < t0) t0 = h[m];
+      fprintf(stderr, "flipb200 rank %d: halo timestamps (us): launch | wait_dn start,end | wait_up start,end | computed | fenced | flag_dn | flag_up\n", c->rank);
+      for (int m = 0; m < n; ++m) {
+        double v[8];
+        for (int q = 0; q < 8; ++q) v[q] = h[8 * m + q] ? (double)(h[8 * m + q] - t0) * 1e-3 : -1.0;
+        fprintf(stderr, "  h%d %2d | %7.1f %7.1f | %7.1f %7.1f | %7.1f | %7.1f | %7.1f | %7.1f\n", c->rank, m, v[0], v[2], v[1], v[3], v[4], v[5], v[6], v[7]);
+      }
+    }
   }
   CK(cudaEventRecord(c->ev[7], c->stream));
   CK(cudaStreamSynchronize(c->stream));
