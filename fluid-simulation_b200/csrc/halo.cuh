@@ -116,6 +116,11 @@ __device__ __forceinline__ void halo_push2(const PeerHalo& H, int q, int k, T v0
   if (H.push_dn && k == H.kdn) st2<T>(reinterpret_cast<T*>(H.dst_dn) + q, v0, v1);
   if (H.push_up && k == H.kup) st2<T>(reinterpret_cast<T*>(H.dst_up) + q, v0, v1);
 }
+__device__ __forceinline__ void halo_push4(const PeerHalo& H, int q, int k, float4 v) {
+  if (H.mode == 0) return;
+  if (H.push_dn && k == H.kdn) *reinterpret_cast<float4*>(reinterpret_cast<float*>(H.dst_dn) + q) = v;
+  if (H.push_up && k == H.kup) *reinterpret_cast<float4*>(reinterpret_cast<float*>(H.dst_up) + q) = v;
+}
 template <typename T>
 __device__ __forceinline__ void halo_push1(const PeerHalo& H, int q, int k, T v) {
   if (H.mode == 0) return;

@@ -340,6 +340,98 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
   halo_signal(H, ds, bdn, bup);
 }
 
+// ---- STENCIL4 variants of the two sweeps (levels whose rows are >= 128 nodes wide) ----------------
+__device__ __forceinline__ float smooth_node(const MgCoef& mc, uint32_t f, float c, float b, float sum) {
+  if (!(f & FB_FLUID)) return 0.f;
+  const int kk = 6 - __popc(f & FB_SMASK);
+  return c + mc.winv[kk] * (b - mc.h2inv * ((float)kk * c - sum));
+}
+__device__ __forceinline__ float resid_node(const MgCoef& mc, uint32_t f, uint32_t nn, float c, float b, float sum) {
+  if (!(f & FB_FLUID)) return 0.f;
+  const int kk = 6 - __popc(f & FB_SMASK);
+  return (b - mc.h2inv * ((float)kk * c - sum)) * (64.f / (float)nn);
+}
+template <bool DOT>
+__global__ void __launch_bounds__(32 * ST_BY)
+k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
+             const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
+             const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg, int dist,
+             const __grid_constant__ PeerHalo H) {
+  __shared__ double sm[32];
+  if (ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
+  halo_wait(H, ds, bdn, bup);
+  double acc[1] = {0.0};
+  StencilMarch4 m;
+  if (m.begin(S, xi)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, xi);
+      uint32_t f = 0;
+      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      double2 ra = make_double2(0.0, 0.0), rb = ra;
+      if (m.act) {
+        f = *reinterpret_cast<const uint32_t*>(fl + m.q);
+        bv = *reinterpret_cast<const float4*>(b + m.q);
+        if (DOT) { ra = ld2<double>(r64 + m.q); rb = ld2<double>(r64 + m.q + 2); }
+      }
+      float4 o;
+      o.x = smooth_node(mc, f & 0xffu, m.pc.x, bv.x, m.sum0());
+      o.y = smooth_node(mc, (f >> 8) & 0xffu, m.pc.y, bv.y, m.sum1());
+      o.z = smooth_node(mc, (f >> 16) & 0xffu, m.pc.z, bv.z, m.sum2());
+      o.w = smooth_node(mc, f >> 24, m.pc.w, bv.w, m.sum3());
+      if (m.act) { *reinterpret_cast<float4*>(xo + m.q) = o; halo_push4(H, m.q, m.k, o); }
+      if (DOT) acc[0] += (ra.x * (double)o.x + ra.y * (double)o.y) + (rb.x * (double)o.z + rb.y * (double)o.w);
+      m.advance(S);
+    }
+  }
+  halo_signal(H, ds, bdn, bup);
+  if (DOT) {
+    block_sum<1>(acc, sm);
+    if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
+      const double rrp = ds->rr[(it + 3) & 3];
+      atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[0] * (rrp > 0.0 ? sqrt(rrp) : 1.0));
+    }
+  }
+}
+__global__ void __launch_bounds__(32 * ST_BY)
+k_mg_resid4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
+            const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
+            float* __restrict__ rn, DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
+  if (ds->pcg_done) return;
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
+  halo_wait(H, ds, bdn, bup);
+  StencilMarch4 m;
+  if (m.begin(S, x)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, x);
+      uint32_t f = 0, nn = 0x40404040u;
+      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m.act) {
+        f = *reinterpret_cast<const uint32_t*>(fl + m.q);
+        nn = *reinterpret_cast<const uint32_t*>(nrm + m.q);
+        bv = *reinterpret_cast<const float4*>(b + m.q);
+      }
+      float4 o;
+      o.x = resid_node(mc, f & 0xffu, nn & 0xffu, m.pc.x, bv.x, m.sum0());
+      o.y = resid_node(mc, (f >> 8) & 0xffu, (nn >> 8) & 0xffu, m.pc.y, bv.y, m.sum1());
+      o.z = resid_node(mc, (f >> 16) & 0xffu, (nn >> 16) & 0xffu, m.pc.z, bv.z, m.sum2());
+      o.w = resid_node(mc, f >> 24, nn >> 24, m.pc.w, bv.w, m.sum3());
+      if (m.act) { *reinterpret_cast<float4*>(rn + m.q) = o; halo_push4(H, m.q, m.k, o); }
+      m.advance(S);
+    }
+  }
+  halo_signal(H, ds, bdn, bup);
+}
+
 // restriction b_c[I] = (1/8) sum_i P[i,I] res_i = (1/512) sum over the 4x4x4 fine cells of
 // {1,3,3,1}^3 weights x rn_i, fused with the coarse level's first Jacobi sweep x1 = w D^-1 b_c.
 // One lane per coarse cell: the lane loads its two children of each of the 16 fine rows as one
@@ -490,6 +582,85 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
         if (f.y & FB_FLUID) xv.y += __fdividef(3.f * E + ER, (float)nn.y);     // node 2I+1 : donors I (3) and I+1 (1)
         *reinterpret_cast<float2*>(x + q) = xv;
         halo_push2<float>(H, q, k, xv.x, xv.y);
+      }
+      f = f1; nn = nn1; xv = xv1;
+    }
+  }
+  halo_signal(H, ds, bdn, bup);
+}
+
+// Four fine nodes (two coarse columns) per lane: the issue-bound 2-node shape spends most of its
+// instructions on per-lane overhead.  Used on the levels whose rows fill a 128-node warp.
+__global__ void __launch_bounds__(256)
+k_mg_prolong4(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ nrm,
+              const float* __restrict__ ec, float* __restrict__ x, DevScalars* __restrict__ ds,
+              int PR_ZC, const __grid_constant__ PeerHalo H) {
+  if (ds->pcg_done) return;
+  const int lane = threadIdx.x;
+  const int i = (fbox.x0 & ~3) + blockIdx.x * 128 + 4 * lane;
+  const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
+  const bool bdn = k0c <= H.kdn && H.kdn < k1c, bup = k0c <= H.kup && H.kup < k1c;
+  halo_wait(H, ds, bdn, bup);
+  if (j < fbox.y1) {                                // whole warp
+    const int I = i >> 1, J = j >> 1;               // coarse columns I, I + 1 (I even)
+    int J2 = J + ((j & 1) ? 1 : -1);
+    const bool yin = J2 >= 0 && J2 < gc.ny;
+    J2 = yin ? J2 : J;
+    const float wy = yin ? 1.f : 0.f;
+    const bool c0in = I < gc.nx, c1in = I + 1 < gc.nx;
+    const int Ie = lane == 0 ? I - 1 : I + 2;         // the column the edge lanes cannot get by shuffle
+    const bool ein = (lane == 0 || lane == 31) && Ie >= 0 && Ie < gc.nx;
+    auto ycomb = [&](int Kg, float& ye) -> float2 {
+      ye = 0.f;
+      if (Kg < 0 || Kg >= gc.gnz) return make_float2(0.f, 0.f);     // block-uniform
+      const float* r0 = ec + gidx(gc, 0, J, Kg - gc.kg0);
+      const float* r1 = ec + gidx(gc, 0, J2, Kg - gc.kg0);
+      if (ein) ye = 3.f * r0[Ie] + wy * r1[Ie];
+      float2 a = make_float2(0.f, 0.f), b = a;
+      if (c0in) { a = *reinterpret_cast<const float2*>(r0 + I); b = *reinterpret_cast<const float2*>(r1 + I); }   // px is even: I + 1 is addressable
+      return make_float2(3.f * a.x + wy * b.x, c1in ? 3.f * a.y + wy * b.y : 0.f);
+    };
+    const int xe = min(gf.px, (fbox.x1 + 3) & ~3);
+    const bool act = i < xe;
+    int Kc = (k0c + gf.kg0) >> 1;
+    float em, e0, ep;
+    float2 Ym = ycomb(Kc - 1, em), Y0 = ycomb(Kc, e0), Yp = ycomb(Kc + 1, ep);
+    int q = gidx(gf, act ? i : 0, j, k0c);
+    uint32_t f = 0, nn = 0x01010101u, f1 = 0, nn1 = 0x01010101u;
+    float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), xv1 = xv;
+    if (act) {
+      f = *reinterpret_cast<const uint32_t*>(ff + q);
+      nn = *reinterpret_cast<const uint32_t*>(nrm + q);
+      xv = *reinterpret_cast<const float4*>(x + q);
+    }
+    for (int k = k0c; k < k1c; ++k, q += gf.plane) {
+      if (act && k + 1 < k1c) {
+        const int qn = q + gf.plane;
+        f1 = *reinterpret_cast<const uint32_t*>(ff + qn);
+        nn1 = *reinterpret_cast<const uint32_t*>(nrm + qn);
+        xv1 = *reinterpret_cast<const float4*>(x + qn);
+      }
+      const int kg = k + gf.kg0;
+      if ((kg >> 1) != Kc) {
+        Kc = kg >> 1;
+        Ym = Y0; em = e0; Y0 = Yp; e0 = ep;
+        Yp = ycomb(Kc + 1, ep);
+      }
+      const bool up = kg & 1;
+      const float E0 = 3.f * Y0.x + (up ? Yp.x : Ym.x);          // column I
+      const float E1 = 3.f * Y0.y + (up ? Yp.y : Ym.y);          // column I + 1
+      const float Ee = 3.f * e0 + (up ? ep : em);
+      float EL = __shfl_up_sync(0xffffffffu, E1, 1), ER = __shfl_down_sync(0xffffffffu, E0, 1);
+      if (lane == 0) EL = Ee;
+      if (lane == 31) ER = Ee;
+      if (f & ((uint32_t)FB_FLUID * 0x01010101u)) {               // any of the four fluid (inactive lanes: f = 0)
+        if (f & FB_FLUID) xv.x += __fdividef(3.f * E0 + EL, (float)(nn & 0xffu));                    // node 2I     : I (3), I-1 (1)
+        if ((f >> 8) & FB_FLUID) xv.y += __fdividef(3.f * E0 + E1, (float)((nn >> 8) & 0xffu));      // node 2I + 1 : I (3), I+1 (1)
+        if ((f >> 16) & FB_FLUID) xv.z += __fdividef(3.f * E1 + E0, (float)((nn >> 16) & 0xffu));    // node 2I + 2 : I+1 (3), I (1)
+        if ((f >> 24) & FB_FLUID) xv.w += __fdividef(3.f * E1 + ER, (float)(nn >> 24));              // node 2I + 3 : I+1 (3), I+2 (1)
+        *reinterpret_cast<float4*>(x + q) = xv;
+        halo_push4(H, q, k, xv);
       }
       f = f1; nn = nn1; xv = xv1;
     }
@@ -739,8 +910,14 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const dim3 pblk(32, 8, 1);
   Sweep S[MG_MAX_LEVELS];
   MgCoef mc[MG_MAX_LEVELS], mc2[MG_MAX_LEVELS];   // mc: weight W1 (first pre-sweep, last post-sweep), mc2: W2
+  // STENCIL4 (four nodes per lane) on the levels whose rows fill a 128-node warp; FLIPB200_ST4=0: never
+  Sweep S4[MG_MAX_LEVELS];
+  bool w4[MG_MAX_LEVELS];
+  static const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();
   for (int l = 0; l < nl; ++l) {
     S[l] = make_sweep(c->mg[l].g, c->mg[l].box);
+    S4[l] = make_sweep(c->mg[l].g, c->mg[l].box, 4);
+    w4[l] = st4_on && (S4[l].xe - S4[l].box.x0) >= 128;
     mc[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA1); mc2[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA2);
   }
   if (sweep_empty(S[0])) return 0;
@@ -749,15 +926,19 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   for (int l = 0; l < t0; ++l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
-    const dim3 tg = stencil_grid(S[l]);
+    const dim3 tg = w4[l] ? stencil_grid(S4[l], 4) : stencil_grid(S[l]);
     const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(L, L.xa);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
-                                                            fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
+    if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+                                                                        fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
+    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+                                                                 fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
-    k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
-                                                    fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    if (w4[l]) k_mg_resid4<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
+                                                                fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
+                                                         fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+resid" : (l == 1 ? "L1 halo+resid" : "L2+ halo+resid"));
     HALO(L, L.xa);
     Box cb = C.box;
@@ -812,23 +993,32 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const Box& fb = L.box;
-    dim3 pg(cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), 1);
-    const int pzc = mg_zchunk("FLIPB200_PR_ZC", pg.x * pg.y, fb.z1 - fb.z0, 1024);
+    dim3 pg(w4[l] ? cdiv(((fb.x1 + 3) & ~3) - (fb.x0 & ~3), 128) : cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), 1);
+    const int pzc = mg_zchunk("FLIPB200_PR_ZC", pg.x * pg.y, fb.z1 - fb.z0, w4[l] ? 512 : 1024);
     pg.z = cdiv(fb.z1 - fb.z0, pzc);
-    const dim3 tg = stencil_grid(S[l]);
+    const dim3 tg = w4[l] ? stencil_grid(S4[l], 4) : stencil_grid(S[l]);
     const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(C, C.xb);
-    k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds, pzc,
-                                             fb_halo_make(c, C.dist ? l + 1 : -1, C.dist ? HA_XB : -1, l, HA_XB, F, k0, k1, pg.x * pg.y));
+    {
+      PeerHalo PH = fb_halo_make(c, C.dist ? l + 1 : -1, C.dist ? HA_XB : -1, l, HA_XB, F, k0, k1, pg.x * pg.y);
+      if (w4[l]) k_mg_prolong4<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds, pzc, PH);
+      else k_mg_prolong<<<pg, pblk, 0, c->stream>>>(L.g, fb, C.g, L.flags, L.nrm, C.xb, L.xb, c->ds, pzc, PH);
+    }
     fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
-    k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
-                                                            fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+                                                                        fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+                                                                 fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
     HALO(L, L.xa);
     // the last sweep's output is read through ghosts only as the coarse correction of the level above
-    if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
-                                                                       fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
+    if (l == 0 && w4[l]) k_mg_smooth4<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
+                                                                                 fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
+    else if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
+                                                                            fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
+    else if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+                                                                             fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
                                                                  fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 2)" : (l == 1 ? "L1 halo+smooth (post 2)" : "L2+ halo+smooth (post 2)"));

@@ -39,10 +39,11 @@ struct Sweep {
   int xe;        // exclusive x limit for lanes (even, <= px)
   int zp;        // boundary-first block order (zperm): set for z-slab runs
 };
-static inline Sweep make_sweep(const Grid& g, const Box& b) {
+// W = x-nodes per lane (2, or 4 for the fp32 STENCIL4 shape): the lane range is aligned to W
+static inline Sweep make_sweep(const Grid& g, const Box& b, int W = 2) {
   Sweep s; s.g = g; s.box = b; s.zp = (g.k0 > 0) ? 1 : 0;   // slabs have ghost planes below k0
-  s.box.x0 = b.x0 & ~1;
-  int xe = (b.x1 + 1) & ~1;
+  s.box.x0 = b.x0 & ~(W - 1);
+  int xe = (b.x1 + W - 1) & ~(W - 1);
   s.xe = xe < g.px ? xe : g.px;
   return s;
 }
@@ -52,8 +53,8 @@ static inline bool sweep_empty(const Sweep& s) {
 static inline dim3 stream_grid(const Sweep& s) {
   return dim3(cdiv(s.xe - s.box.x0, 64), cdiv(s.box.y1 - s.box.y0, SW_BY), s.box.z1 - s.box.z0);
 }
-static inline dim3 stencil_grid(const Sweep& s) {
-  return dim3(cdiv(s.xe - s.box.x0, 64), cdiv(s.box.y1 - s.box.y0, ST_BY), cdiv(s.box.z1 - s.box.z0, ST_ZP));
+static inline dim3 stencil_grid(const Sweep& s, int W = 2) {
+  return dim3(cdiv(s.xe - s.box.x0, 32 * W), cdiv(s.box.y1 - s.box.y0, ST_BY), cdiv(s.box.z1 - s.box.z0, ST_ZP));
 }
 #define STREAM_BLOCK dim3(32, SW_BY, 1)
 #define STENCIL_BLOCK dim3(32, ST_BY, 1)
@@ -110,6 +111,47 @@ struct StencilMarch {
   __device__ __forceinline__ T c1() const { return pc.y; }
   __device__ __forceinline__ T sum0() const { return (pm.x + pn.x) + (ym.x + yp.x) + (left + pc.y); }
   __device__ __forceinline__ T sum1() const { return (pm.y + pn.y) + (ym.y + yp.y) + (pc.x + right); }
+  __device__ __forceinline__ void advance(const Sweep& S) { pm = pc; pc = pn; q += S.g.plane; ++k; }
+};
+
+// STENCIL4: the same march with FOUR fp32 x-nodes per lane (float4 loads, a warp covers 128 nodes).
+// The fp32 multigrid sweeps of the big levels are issue-bound in the 2-node shape (80 % of the issue
+// slots at 49 % DRAM, profiles/r1c_summary.txt); four nodes per lane halve the per-node overhead of
+// the index math, shuffles and predicates.  Same association of the sums as StencilMarch: identical bits.
+struct StencilMarch4 {
+  float4 pm, pc, pn, ym, yp;
+  float left, right;
+  int i, j, k, q, lane;
+  bool act, jlo, jhi;
+  static __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+  static __device__ __forceinline__ float4 zero4() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+
+  __device__ __forceinline__ bool begin(const Sweep& S, const float* __restrict__ src) {
+    lane = threadIdx.x;
+    i = S.box.x0 + blockIdx.x * 128 + 4 * lane;
+    j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
+    k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP;
+    if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
+    act = i < S.xe;
+    jlo = j > 0; jhi = j < S.g.ny - 1;
+    q = gidx(S.g, i, j, k);
+    pm = (act && k > 0) ? ld4(src + q - S.g.plane) : zero4();
+    pc = act ? ld4(src + q) : zero4();
+    return true;
+  }
+  __device__ __forceinline__ void load(const Sweep& S, const float* __restrict__ src) {
+    pn = (act && k < S.g.nz - 1) ? ld4(src + q + S.g.plane) : zero4();
+    ym = (act && jlo) ? ld4(src + q - S.g.px) : zero4();
+    yp = (act && jhi) ? ld4(src + q + S.g.px) : zero4();
+    left = __shfl_up_sync(0xffffffffu, pc.w, 1);
+    right = __shfl_down_sync(0xffffffffu, pc.x, 1);
+    if (lane == 0) left = (act && i > 0) ? src[q - 1] : 0.f;
+    if (lane == 31) right = (act && i + 4 < S.g.px) ? src[q + 4] : 0.f;
+  }
+  __device__ __forceinline__ float sum0() const { return (pm.x + pn.x) + (ym.x + yp.x) + (left + pc.y); }
+  __device__ __forceinline__ float sum1() const { return (pm.y + pn.y) + (ym.y + yp.y) + (pc.x + pc.z); }
+  __device__ __forceinline__ float sum2() const { return (pm.z + pn.z) + (ym.z + yp.z) + (pc.y + pc.w); }
+  __device__ __forceinline__ float sum3() const { return (pm.w + pn.w) + (ym.w + yp.w) + (pc.z + right); }
   __device__ __forceinline__ void advance(const Sweep& S) { pm = pc; pc = pn; q += S.g.plane; ++k; }
 };
 
