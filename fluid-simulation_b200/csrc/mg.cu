@@ -510,6 +510,78 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
   halo_signal(H, ds, bdn, bup);
 }
 
+// Two coarse cells (four fine children per row, one float4) per lane; used when the coarse rows are
+// at least 64 cells wide.  Same association of the sums as k_mg_restrict.
+__global__ void __launch_bounds__(256)
+k_mg_restrict4(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
+               const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
+               DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H) {
+  if (ds->pcg_done) return;
+  const int lane = threadIdx.x;
+  const int I = (cbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;         // cells I, I + 1
+  const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
+  const bool bdn = K0 <= H.kdn && H.kdn < K1, bup = K0 <= H.kup && H.kup < K1;
+  halo_wait(H, ds, bdn, bup);
+  if (J < cbox.y1) {                                // whole warp
+    const bool in = I < cbox.x1;
+    const int fx0 = fbox.x0 & ~1, fxe = min(gf.px, (fbox.x1 + 1) & ~1);   // fresh x-range of the fine sweeps (pairs)
+    const int xf = 2 * I;                             // children xf .. xf+3
+    const bool cv0 = in && xf >= fx0 && xf < fxe, cv1 = in && xf + 2 >= fx0 && xf + 2 < fxe;
+    const bool eL = lane == 0 && in && xf - 1 >= fx0 && xf - 1 < fxe, eR = lane == 31 && in && xf + 4 >= fx0 && xf + 4 < fxe;
+    const int xc = in ? xf : 0;                       // in-bounds address (values masked by cv0 / cv1)
+    int jr[4]; float wy[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int jf = 2 * J + t - 1;
+      wy[t] = (jf >= fbox.y0 && jf < fbox.y1) ? ((t == 1 || t == 2) ? 3.f : 1.f) : 0.f;
+      jr[t] = min(max(jf, fbox.y0), fbox.y1 - 1);
+    }
+    auto plane_sum = [&](int kf) -> float2 {
+      const bool pin = kf >= fbox.z0 && kf < fbox.z1;               // block-uniform
+      const int kc = min(max(kf, fbox.z0), fbox.z1 - 1);
+      float4 v[4]; float ea[4], ed[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float* row = rn + gidx(gf, 0, jr[t], kc);
+        v[t] = *reinterpret_cast<const float4*>(row + xc);
+        ea[t] = eL ? row[xf - 1] : 0.f;
+        ed[t] = eR ? row[xf + 4] : 0.f;
+      }
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float vx = cv0 ? v[t].x : 0.f, vy = cv0 ? v[t].y : 0.f, vz = cv1 ? v[t].z : 0.f, vw = cv1 ? v[t].w : 0.f;
+        float a = __shfl_up_sync(0xffffffffu, vw, 1), d = __shfl_down_sync(0xffffffffu, vx, 1);
+        if (lane == 0) a = ea[t];
+        if (lane == 31) d = ed[t];
+        s0 += wy[t] * ((a + vz) + 3.f * (vx + vy));
+        s1 += wy[t] * ((vy + d) + 3.f * (vz + vw));
+      }
+      return pin ? make_float2(s0, s1) : make_float2(0.f, 0.f);
+    };
+    const int kb = 2 * (K0 + gc.kg0) - gf.kg0;       // local fine plane of the first child of K0
+    float2 sm1 = plane_sum(kb - 1), s0 = plane_sum(kb);
+    for (int K = K0; K < K1; ++K) {
+      const int kf = kb + 2 * (K - K0);
+      const float2 s1 = plane_sum(kf + 1), s2 = plane_sum(kf + 2);
+      if (in) {
+        const int qc = gidx(gc, I, J, K);
+        const uchar2 f = *reinterpret_cast<const uchar2*>(fc + qc);
+        const bool in1 = I + 1 < cbox.x1;
+        float r0 = 0.f, r1 = 0.f, y0 = 0.f, y1 = 0.f;
+        if (f.x & FB_FLUID) { r0 = ((sm1.x + s2.x) + 3.f * (s0.x + s1.x)) * (1.f / 512.f); y0 = mcc.winv[6 - __popc(f.x & FB_SMASK)] * r0; }
+        if (in1 && (f.y & FB_FLUID)) { r1 = ((sm1.y + s2.y) + 3.f * (s0.y + s1.y)) * (1.f / 512.f); y1 = mcc.winv[6 - __popc(f.y & FB_SMASK)] * r1; }
+        st2<float>(bc + qc, r0, r1);
+        st2<float>(x1c + qc, y0, y1);
+        halo_push2<float>(H, qc, K, y0, y1);
+      }
+      sm1 = s1; s0 = s2;
+    }
+  }
+  halo_signal(H, ds, bdn, bup);
+}
+
 // prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells).
 // One lane per coarse column I = two fine nodes (2I, 2I+1); the x-neighbours I-1 / I+1 come by
 // shuffle.  The block marches PR_ZC fine planes: the y-combined coarse value Y(K) of a coarse plane
@@ -949,12 +1021,15 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     {
       // the sequence number is taken even when this rank has nothing to restrict
-      dim3 cg(max(1, cdiv(cb.x1 - cb.x0, 32)), max(1, cdiv(cb.y1 - cb.y0, 8)), 1);
-      const int zc = mg_zchunk("FLIPB200_RS_ZC", cg.x * cg.y, cb.z1 - cb.z0, 1024);
+      const bool r4 = w4[l] && cb.x1 - (cb.x0 & ~1) >= 64;
+      dim3 cg(max(1, r4 ? cdiv(cb.x1 - (cb.x0 & ~1), 64) : cdiv(cb.x1 - cb.x0, 32)), max(1, cdiv(cb.y1 - cb.y0, 8)), 1);
+      const int zc = mg_zchunk("FLIPB200_RS_ZC", cg.x * cg.y, cb.z1 - cb.z0, r4 ? 512 : 1024);
       cg.z = max(1, cdiv(cb.z1 - cb.z0, zc));
       PeerHalo H = fb_halo_make(c, l, HA_XA, C.dist ? l + 1 : -1, C.dist ? HA_XA : -1, F, ck0, ck1, cg.x * cg.y);
-      if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0)
-        k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H);
+      if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0) {
+        if (r4) k_mg_restrict4<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H);
+        else k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H);
+      }
     }
     fb_prof(c, l == 0 ? "L0 halo+restrict" : (l == 1 ? "L1 halo+restrict" : "L2+ halo+restrict"));
     if (L.dist && !C.dist) {
