@@ -100,6 +100,54 @@ k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, cons
   if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_PAP] : &ds->pAp[it & 3], acc[0]);
 }
 
+// K1 in the STENCIL4 shape (four doubles per lane); used when the sweep's rows are >= 128 nodes wide
+__global__ void __launch_bounds__(32 * ST_BY)
+k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+        const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit,
+        int dist, const __grid_constant__ PeerHalo H) {
+  __shared__ double sm[32];
+  if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
+  {
+    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+    halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
+  }
+  double acc[1] = {0.0};
+  StencilMarch4D m;
+  if (m.begin(S, p)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, p);
+      const uint32_t f = m.act ? *reinterpret_cast<const uint32_t*>(fl + m.q) : 0u;
+      const uint32_t f0 = f & 0xffu, f1 = (f >> 8) & 0xffu, f2 = (f >> 16) & 0xffu, f3 = f >> 24;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+      if (f0 & FB_FLUID) { a0 = cf.diag[6 - __popc(f0 & FB_SMASK)] * m.pca.x + cf.off * m.sum0(); acc[0] += m.pca.x * a0; }
+      if (f1 & FB_FLUID) { a1 = cf.diag[6 - __popc(f1 & FB_SMASK)] * m.pca.y + cf.off * m.sum1(); acc[0] += m.pca.y * a1; }
+      if (f2 & FB_FLUID) { a2 = cf.diag[6 - __popc(f2 & FB_SMASK)] * m.pcb.x + cf.off * m.sum2(); acc[0] += m.pcb.x * a2; }
+      if (f3 & FB_FLUID) { a3 = cf.diag[6 - __popc(f3 & FB_SMASK)] * m.pcb.y + cf.off * m.sum3(); acc[0] += m.pcb.y * a3; }
+      if ((f0 | f1) & FB_FLUID) st2<double>(Ap + m.q, a0, a1);
+      if ((f2 | f3) & FB_FLUID) st2<double>(Ap + m.q + 2, a2, a3);
+      m.advance(S);
+    }
+  }
+  block_sum<1>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_PAP] : &ds->pAp[it & 3], acc[0]);
+}
+
+// launch K1 in the shape that fits the sweep (FLIPB200_ST4=0: always two nodes per lane)
+static void launch_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit, int dist, const PeerHalo& H) {
+  static const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();
+  const Sweep S4 = make_sweep(c->g, c->box, 4);
+  if (st4_on && S4.xe - S4.box.x0 >= 128) {
+    k_spmv4<<<stencil_grid(S4, 4), STENCIL_BLOCK, 0, c->stream>>>(S4, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);
+  } else {
+    const Sweep S = make_sweep(c->g, c->box);
+    k_spmv<<<stencil_grid(S), STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);
+  }
+}
+
 // K2: alpha = rz_old / pAp;  x += alpha p;  r -= alpha Ap;  rr = |r|^2
 //     MODE 0 (Jacobi): rz = r.M^-1 r.   MODE 1 (MG): b0 = float(r*sc), x1 = w D^-1 b0 with
 //     sc = 1/|r_prev| so that the fp32 V-cycle works on O(1) numbers whatever |r| has become.
@@ -321,8 +369,7 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   if (fused) rc = fb_halo_point(c); else rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1);
   if (rc) return rc;
   fb_prof(c, "halo pd");
-  k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist,
-                                              fused ? fb_halo_make(c, 0, HA_PD, -1, -1, 0, k0, k1, tg.x * tg.y) : halo_off());
+  launch_spmv(c, cf, it_arg, noexit, dist, fused ? fb_halo_make(c, 0, HA_PD, -1, -1, 0, k0, k1, tg.x * tg.y) : halo_off());
   fb_prof(c, "k_spmv");
   if (dist) {
     if (use_mg) { if ((rc = reduce_dot(c, PART_PAP, it_arg, noexit))) return rc; }
@@ -519,7 +566,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     if (prof && it >= 3) { c->prof->on = true; c->prof->n = 0; c->halo.dbg_n = 0; }
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
-      k_spmv<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it, 1, 0, halo_off());
+      launch_spmv(c, cf, it, 1, 0, halo_off());
       c->launches++;
     } else if (graph) {
       if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }

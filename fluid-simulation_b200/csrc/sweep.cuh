@@ -155,6 +155,55 @@ struct StencilMarch4 {
   __device__ __forceinline__ void advance(const Sweep& S) { pm = pc; pc = pn; q += S.g.plane; ++k; }
 };
 
+// fp64 STENCIL4: four doubles per lane as two double2 halves (a, b).  k_spmv in this shape sweeps
+// 256^3 in 55.9 us against 65.6 us for two doubles per lane (tools/kbench.cu T7 vs T4).
+struct StencilMarch4D {
+  double2 pma, pmb, pca, pcb, pna, pnb, yma, ymb, ypa, ypb;
+  double left, right;
+  const double* ptr;          // &src[q]: advanced by one plane per step (keeps the address math out of the loop)
+  int i, j, k, q, lane;
+  bool act, jlo, jhi, xlo, xhi;
+
+  __device__ __forceinline__ bool begin(const Sweep& S, const double* __restrict__ src) {
+    lane = threadIdx.x;
+    i = S.box.x0 + blockIdx.x * 128 + 4 * lane;
+    j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
+    k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP;
+    if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
+    act = i < S.xe;
+    jlo = act && j > 0; jhi = act && j < S.g.ny - 1;
+    xlo = lane == 0 && act && i > 0; xhi = lane == 31 && act && i + 4 < S.g.px;
+    q = gidx(S.g, i, j, k);
+    ptr = src + q;
+    const bool lo = act && k > 0;
+    const ptrdiff_t P = S.g.plane;
+    pma = lo ? ld2<double>(ptr - P) : zero2<double>();
+    pmb = lo ? ld2<double>(ptr - P + 2) : zero2<double>();
+    pca = act ? ld2<double>(ptr) : zero2<double>();
+    pcb = act ? ld2<double>(ptr + 2) : zero2<double>();
+    return true;
+  }
+  __device__ __forceinline__ void load(const Sweep& S, const double* __restrict__) {
+    const bool hi = act && k < S.g.nz - 1;
+    const ptrdiff_t P = S.g.plane, X = S.g.px;
+    pna = hi ? ld2<double>(ptr + P) : zero2<double>();
+    pnb = hi ? ld2<double>(ptr + P + 2) : zero2<double>();
+    yma = jlo ? ld2<double>(ptr - X) : zero2<double>();
+    ymb = jlo ? ld2<double>(ptr - X + 2) : zero2<double>();
+    ypa = jhi ? ld2<double>(ptr + X) : zero2<double>();
+    ypb = jhi ? ld2<double>(ptr + X + 2) : zero2<double>();
+    left = __shfl_up_sync(0xffffffffu, pcb.y, 1);
+    right = __shfl_down_sync(0xffffffffu, pca.x, 1);
+    if (lane == 0) left = xlo ? ptr[-1] : 0.0;
+    if (lane == 31) right = xhi ? ptr[4] : 0.0;
+  }
+  __device__ __forceinline__ double sum0() const { return (pma.x + pna.x) + (yma.x + ypa.x) + (left + pca.y); }
+  __device__ __forceinline__ double sum1() const { return (pma.y + pna.y) + (yma.y + ypa.y) + (pca.x + pcb.x); }
+  __device__ __forceinline__ double sum2() const { return (pmb.x + pnb.x) + (ymb.x + ypb.x) + (pca.y + pcb.y); }
+  __device__ __forceinline__ double sum3() const { return (pmb.y + pnb.y) + (ymb.y + ypb.y) + (pcb.x + right); }
+  __device__ __forceinline__ void advance(const Sweep& S) { pma = pca; pmb = pcb; pca = pna; pcb = pnb; q += S.g.plane; ptr += S.g.plane; ++k; }
+};
+
 // block reduction for the (32, BY) shapes: thread (0,0) ends with the sum
 template <int NV>
 __device__ __forceinline__ void block_sum_xy(double (&v)[NV], double* smem /* >= 32*NV */) {
