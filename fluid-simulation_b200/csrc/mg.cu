@@ -22,7 +22,9 @@
 //    halves the preconditioner's HBM traffic.  r.z is accumulated in fp64 against the fp64 residual.
 // Kernel shapes: sweep.cuh.  Finest-level bytes per node and V-cycle: smooth 13, residual 14,
 // restrict 4.5, prolong 9.5, smooth 13, smooth+dot 21  = 75 B (fp32) vs 91 B for ONE Jacobi-PCG
-// iteration in fp64.
+// iteration in fp64.  Levels whose rows are >= 128 nodes wide use the four-nodes-per-lane variants
+// (k_mg_smooth4 / k_mg_resid4 / k_mg_restrict4 / k_mg_prolong4): the two-node kernels are
+// issue-bound there (73-80 % of the issue slots at <= 50 % DRAM, profiles/r1c_summary.txt).
 #include "sweep.cuh"
 #include "pcg.cuh"
 #include "halo.cuh"
@@ -985,7 +987,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   // STENCIL4 (four nodes per lane) on the levels whose rows fill a 128-node warp; FLIPB200_ST4=0: never
   Sweep S4[MG_MAX_LEVELS];
   bool w4[MG_MAX_LEVELS];
-  static const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();
+  const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
   for (int l = 0; l < nl; ++l) {
     S[l] = make_sweep(c->mg[l].g, c->mg[l].box);
     S4[l] = make_sweep(c->mg[l].g, c->mg[l].box, 4);

@@ -138,7 +138,7 @@ k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, con
 
 // launch K1 in the shape that fits the sweep (FLIPB200_ST4=0: always two nodes per lane)
 static void launch_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit, int dist, const PeerHalo& H) {
-  static const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();
+  const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
   const Sweep S4 = make_sweep(c->g, c->box, 4);
   if (st4_on && S4.xe - S4.box.x0 >= 128) {
     k_spmv4<<<stencil_grid(S4, 4), STENCIL_BLOCK, 0, c->stream>>>(S4, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);

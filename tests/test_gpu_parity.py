@@ -365,3 +365,25 @@ def test_pic_flip_blend(fb, oracle_mod, scenes, ratio):
     # the PIC part reads u = sum(cw v)/float(w) itself (FLIP only reads differences of it), so the documented
     # fp32 summation-order deviation of w (<= 5e-7) shows: measured 9e-8 at r = 0
     assert rel_l2(vg, vo) < 2e-6 and rel_l2(pg, po) < 1e-6
+
+
+def test_stencil4_matches_stencil2(fb, monkeypatch):
+    """The four-nodes-per-lane sweep kernels (rows >= 128 nodes: k_spmv4, k_mg_smooth4, k_mg_resid4,
+    k_mg_restrict4, k_mg_prolong4) against the two-nodes-per-lane ones on a wide, flat tank with an
+    odd box (x range not a multiple of 4): same iteration count (+-1) and the same pressure."""
+    res = {}
+    for st4 in ("1", "0"):
+        monkeypatch.setenv("FLIPB200_ST4", st4)
+        f = fb.Flip(nx=150, ny=20, nz=24, ox=75, oy=10, oz=12, precond=1)
+        f.seed_box((3, 2, 2), (141, 14, 21), seed=99)
+        f.p2g(); f.classify()
+        f.rhs_div(0.125)
+        it, rel = f.pcg_solve(0.125)
+        assert rel < 2.220446049250313e-16
+        res[st4] = (it, f.get_grid(fb.GRID_P))
+        f.close()
+    assert abs(res["1"][0] - res["0"][0]) <= 1, (res["1"][0], res["0"][0])
+    assert rel_l2(res["1"][1], res["0"][1]) < 1e-9
+    # hydrostatic answer (open top at y = 14): p = rho*|g|*dx*depth
+    p = res["1"][1]
+    assert np.allclose(p[70, 2:14, 12], 10.0 * (14 - np.arange(2, 14)), rtol=1e-8)

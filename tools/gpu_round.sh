@@ -14,7 +14,7 @@ $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 12000 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launch.log 2>&1
 echo "launch list rc=$?"
 # level-0 launches: the first launch of the V-cycle kernels is level 0, the 4th prolong of a cycle is level 1 -> 0
-for KS in k_spmv:2 k_update_xr:2 k_update_p:2 k_mg_smooth:0 k_mg_resid:0 k_mg_restrict:0 k_mg_prolong:3 k_p2g_cell:1 k_g2p_cell:0 k_advect:0 k_reorder:1 k_key_count:1 k_classify:1 k_rhs_div:1 k_vel_update:1 k_cell_delta:0; do
+for KS in k_spmv:2 k_update_xr:2 k_update_p:2 k_mg_smooth:0 k_mg_resid:0 k_mg_restrict:0 k_mg_prolong:3 k_mg_tail:0 k_p2g_cell:1 k_g2p_cell:0 k_advect:0 k_reorder:1 k_key_count:1 k_classify:1 k_rhs_div:1 k_vel_update:1 k_cell_delta:0; do
   K=${KS%%:*}; SK=${KS##*:}
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:"^${K}" -s $SK -c 1 -f -o gpurun_out/${TAG}_${K} $CMD > gpurun_out/${TAG}_ncu_${K}.log 2>&1
   echo "ncu $K rc=$?"

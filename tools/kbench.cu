@@ -195,6 +195,49 @@ __global__ void __launch_bounds__(32 * BY) t7_vec4(int n, const uint8_t* __restr
   if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
 }
 
+// T8: T7 + prefetch.global.L2 of every plane of the march at block start (PF = 1) or two planes ahead (PF = 2)
+template <int BY, int ZP, int PF>
+__global__ void __launch_bounds__(32 * BY) t8_pf(int n, const uint8_t* __restrict__ fl, const double* __restrict__ p, double* __restrict__ Ap, double* out) {
+  const int lane = threadIdx.x;
+  int i = blockIdx.x * 128 + 4 * lane, j = blockIdx.y * BY + threadIdx.y, k0 = blockIdx.z * ZP;
+  int plane = n * n;
+  int q = k0 * plane + j * n + i;
+  const bool jlo = j > 0, jhi = j < n - 1;
+  double acc = 0;
+  const double2 z2 = make_double2(0, 0);
+  double2 pma = k0 > 0 ? *(const double2*)(p + q - plane) : z2, pmb = k0 > 0 ? *(const double2*)(p + q - plane + 2) : z2;
+  double2 pca = *(const double2*)(p + q), pcb = *(const double2*)(p + q + 2);
+  if (PF == 1) {
+#pragma unroll
+    for (int z = 1; z <= ZP; ++z)
+      if (k0 + z < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + q + (size_t)z * plane));
+  }
+#pragma unroll
+  for (int z = 0; z < ZP; ++z, q += plane) {
+    int k = k0 + z;
+    if (PF == 2 && z + 2 <= ZP && k + 2 < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + q + 2 * (size_t)plane));
+    double2 pna = k < n - 1 ? *(const double2*)(p + q + plane) : z2, pnb = k < n - 1 ? *(const double2*)(p + q + plane + 2) : z2;
+    double2 yma = jlo ? *(const double2*)(p + q - n) : z2, ymb = jlo ? *(const double2*)(p + q - n + 2) : z2;
+    double2 ypa = jhi ? *(const double2*)(p + q + n) : z2, ypb = jhi ? *(const double2*)(p + q + n + 2) : z2;
+    uint32_t f = *(const uint32_t*)(fl + q);
+    double left = __shfl_up_sync(~0u, pcb.y, 1), right = __shfl_down_sync(~0u, pca.x, 1);
+    if (lane == 0) left = i > 0 ? p[q - 1] : 0.0;
+    if (lane == 31) right = i + 4 < n ? p[q + 4] : 0.0;
+    double2 a0 = z2, a1 = z2;
+    if (f & 64) { int kk = 6 - __popc(f & 63); a0.x = kk * 0.1 * pca.x - 0.1 * ((pma.x + pna.x) + (yma.x + ypa.x) + (left + pca.y)); acc += pca.x * a0.x; }
+    if ((f >> 8) & 64) { int kk = 6 - __popc((f >> 8) & 63); a0.y = kk * 0.1 * pca.y - 0.1 * ((pma.y + pna.y) + (yma.y + ypa.y) + (pca.x + pcb.x)); acc += pca.y * a0.y; }
+    if ((f >> 16) & 64) { int kk = 6 - __popc((f >> 16) & 63); a1.x = kk * 0.1 * pcb.x - 0.1 * ((pmb.x + pnb.x) + (ymb.x + ypb.x) + (pca.y + pcb.y)); acc += pcb.x * a1.x; }
+    if ((f >> 24) & 64) { int kk = 6 - __popc((f >> 24) & 63); a1.y = kk * 0.1 * pcb.y - 0.1 * ((pmb.y + pnb.y) + (ymb.y + ypb.y) + (pcb.x + right)); acc += pcb.y * a1.y; }
+    if (f & 0x40404040u) { *(double2*)(Ap + q) = a0; *(double2*)(Ap + q + 2) = a1; }
+    pma = pca; pmb = pcb; pca = pna; pcb = pnb;
+  }
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
+  __shared__ double sm[32];
+  if (lane == 0) sm[threadIdx.y] = acc;
+  __syncthreads();
+  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+}
+
 // T6: planes staged in shared memory by TMA (box 68 x (BY+2) x 1 doubles, out-of-range -> 0), NST-deep
 // ring with one mbarrier per slot; the block marches ZP planes.  Centre column rotates in registers.
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -284,6 +327,12 @@ static CUtensorMap make_map(void* base, int n, int by) {
   return m;
 }
 
+__global__ void fill_rand(size_t n, double* p) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    unsigned long long h = i * 0x9E3779B97F4A7C15ull; h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+    p[i] = (double)(h & 0xffffff) * (1.0 / 16777216.0) - 0.5;
+  }
+}
 int main(int argc, char** argv) {
   if (argc > 1) N = atoi(argv[1]);
   T = (size_t)N * N * N;
@@ -301,6 +350,7 @@ int main(int argc, char** argv) {
     }
     CK(cudaMemcpy(fl, h.data(), T, cudaMemcpyHostToDevice));
   }
+  if (argc > 4) { fill_rand<<<148 * 8, 256>>>(T, p); CK(cudaDeviceSynchronize()); printf("p = random\n"); }
   int sms = 148;
   double gb49 = 49.0 * T / 1e9, gb17 = 17.0 * T / 1e9, gb16 = 16.0 * T / 1e9;
   float us;
@@ -353,6 +403,10 @@ int main(int argc, char** argv) {
   us = timeit([&] { t7_vec4<BY, ZP><<<dim3(N / 128, N / BY, N / ZP), dim3(32, BY)>>>(N, fl, p, Ap, out); }); \
   printf("T7 vec4 BY=%d ZP=%d          %8.1f us  %7.1f GB/s\n", BY, ZP, us, gb17 / us * 1e6);
     RUN_T7(4, 4) RUN_T7(8, 4) RUN_T7(4, 8) RUN_T7(2, 4) RUN_T7(4, 2) RUN_T7(8, 2)
+#define RUN_T8(BY, ZP, PF)                                                                                   \
+  us = timeit([&] { t8_pf<BY, ZP, PF><<<dim3(N / 128, N / BY, N / ZP), dim3(32, BY)>>>(N, fl, p, Ap, out); }); \
+  printf("T8 pf%d  BY=%d ZP=%d          %8.1f us  %7.1f GB/s\n", PF, BY, ZP, us, gb17 / us * 1e6);
+    RUN_T8(4, 4, 1) RUN_T8(4, 8, 1) RUN_T8(4, 4, 2) RUN_T8(4, 8, 2) RUN_T8(4, 16, 2) RUN_T8(2, 8, 1)
     if (argc > 3) return 0;
     RUN_T5(4, 4) RUN_T5(8, 4) RUN_T5(4, 8) RUN_T5(8, 8) RUN_T5(4, 16) RUN_T5(8, 16)
     RUN_T6(8, 16, 4) RUN_T6(8, 32, 4) RUN_T6(8, 64, 4) RUN_T6(16, 32, 4) RUN_T6(16, 64, 4) RUN_T6(8, 32, 6) RUN_T6(4, 32, 4) RUN_T6(4, 64, 6) RUN_T6(8, 256, 4)
