@@ -132,11 +132,8 @@ int fb_classify(flipb200_ctx* c) {
 //   MODE 1: bout = b2 (new);    ds->err_num = |bold - b2|^2, ds->err_den = |bold|^2 (fluid.cc:1483)
 //           and ds->bnorm2 = |b2|^2 (b2 is the next pass's b: same velocities, same dt)
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float rhs_div_cell(const Grid& g, int q, uint8_t f, const double* __restrict__ u0,
-                                              const double* __restrict__ u1, const double* __restrict__ u2,
+__device__ __forceinline__ float rhs_div_cell(uint8_t f, double vx, double vy, double vz, double vix, double vjy, double vkz,
                                               double scale, double dx, double gx, double gy, double gz) {
-  double vx = u0[q], vy = u1[q], vz = u2[q];
-  double vix = u0[q + 1], vjy = u1[q + g.px], vkz = u2[q + g.plane];   // fluid cells are inside the shell
   float R = 0.0f;
   if (f & FB_SXM) R = __double2float_rn(__dsub_rn((double)R, __dmul_rn(scale, __dadd_rn(vx, gx))));    // :449
   if (f & FB_SXP) R = __double2float_rn(__dadd_rn((double)R, __dmul_rn(scale, __dadd_rn(vix, gx))));   // :453
@@ -145,9 +142,10 @@ __device__ __forceinline__ float rhs_div_cell(const Grid& g, int q, uint8_t f, c
   if (f & FB_SZM) R = __double2float_rn(__dsub_rn((double)R, __dmul_rn(scale, __dadd_rn(vz, gz))));    // :467
   if (f & FB_SZP) R = __double2float_rn(__dadd_rn((double)R, __dmul_rn(scale, __dadd_rn(vkz, gz))));   // :471
   double du = 0.0, dv = 0.0, dw = 0.0;
-  if (!(f & FB_SXP)) du = __ddiv_rn(__dsub_rn(vix, vx), dx);   // :592-595
-  if (!(f & FB_SYP)) dv = __ddiv_rn(__dsub_rn(vjy, vy), dx);
-  if (!(f & FB_SZP)) dw = __ddiv_rn(__dsub_rn(vkz, vz), dx);
+  // :592-595.  x / 1.0 == x exactly: the reference's dx = 1 skips the three fp64 divisions
+  if (!(f & FB_SXP)) { du = __dsub_rn(vix, vx); if (dx != 1.0) du = __ddiv_rn(du, dx); }
+  if (!(f & FB_SYP)) { dv = __dsub_rn(vjy, vy); if (dx != 1.0) dv = __ddiv_rn(dv, dx); }
+  if (!(f & FB_SZP)) { dw = __dsub_rn(vkz, vz); if (dx != 1.0) dw = __ddiv_rn(dw, dx); }
   return __double2float_rn(__dsub_rn(__dsub_rn(__dsub_rn((double)R, du), dv), dw));   // :605
 }
 
@@ -165,9 +163,13 @@ k_rhs_div(Grid g, Box box, int tiles_x, int tiles_y, int nitems, const uint8_t* 
     int i = box.x0 + tx * 32 + threadIdx.x, j = box.y0 + ty * 8 + threadIdx.y, k = box.z0 + tz;
     if (i < box.x1 && j < box.y1) {
       int q = gidx(g, i, j, k);
-      uint8_t f = fl[q];
+      // every load is issued before the flag is looked at (one round trip instead of two); the +1
+      // neighbours of a node on the last row / plane of the array are clamped (such a node is never fluid)
+      const int qx = i + 1 < g.px ? q + 1 : q, qy = j + 1 < g.ny ? q + g.px : q, qz = k + 1 < g.nz ? q + g.plane : q;
+      const uint8_t f = fl[q];
+      const double vx = u0[q], vy = u1[q], vz = u2[q], vix = u0[qx], vjy = u1[qy], vkz = u2[qz];
       float D = 0.0f;
-      if (f & FB_FLUID) D = rhs_div_cell(g, q, f, u0, u1, u2, scale, dx, gx, gy, gz);
+      if (f & FB_FLUID) D = rhs_div_cell(f, vx, vy, vz, vix, vjy, vkz, scale, dx, gx, gy, gz);
       if (MODE == 1) {
         double bo = (double)bold[q];
         double d = bo - (double)D;

@@ -490,8 +490,9 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     c->launches += 2;
   }
   const bool graph = !done && get_iteration_graph(c, S, cf, use_mg, dt, 0);
-  // first batch: about as many iterations as the previous solve needed, then small batches
-  int batch = c->last_iters > 4 ? c->last_iters - 1 : (use_mg ? 8 : 32);
+  // first batch: as many iterations as the previous solve needed (consecutive solves of a scene need
+  // the same number +-1: usually one batch, one host round trip), then small batches
+  int batch = c->last_iters > 4 ? c->last_iters : (use_mg ? 8 : 32);
   int it = 0;
   while (!done) {
     int stop = min(it + batch, max_iter);

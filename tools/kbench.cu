@@ -10,6 +10,7 @@
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1); } } while (0)
 
 static int N = 256;
+__device__ int g_spread = 32;   // partial sums go to out[(bx+by+bz) % g_spread]
 static size_t T;
 static cudaEvent_t e0, e1;
 
@@ -84,7 +85,7 @@ __global__ void t3_node(int n, const uint8_t* __restrict__ fl, const double* __r
   int tid = threadIdx.y * BX + threadIdx.x;
   if ((tid & 31) == 0) sm[tid >> 5] = acc;
   __syncthreads();
-  if (tid == 0) { double t = 0; for (int w = 0; w < BX * BY / 32; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+  if (tid == 0) { double t = 0; for (int w = 0; w < BX * BY / 32; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
 }
 // T4: 2 nodes per thread (double2), x neighbours by shuffle, ZP planes per block marched with
 // registers; unconditional loads
@@ -118,7 +119,7 @@ __global__ void t4_vec2(int n, const uint8_t* __restrict__ fl, const double* __r
   __shared__ double sm[32];
   if (lane == 0) sm[threadIdx.y] = acc;
   __syncthreads();
-  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
 }
 
 // T5: T4 with the centre column fetched PD = 2 planes ahead and the flags one plane ahead
@@ -155,7 +156,7 @@ __global__ void t5_pref(int n, const uint8_t* __restrict__ fl, const double* __r
   __shared__ double sm[32];
   if (lane == 0) sm[threadIdx.y] = acc;
   __syncthreads();
-  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
 }
 
 // T7: T4 with FOUR doubles per lane (a warp covers 128 nodes)
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(32 * BY) t7_vec4(int n, const uint8_t* __restr
   __shared__ double sm[32];
   if (lane == 0) sm[threadIdx.y] = acc;
   __syncthreads();
-  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
 }
 
 // T8: T7 + prefetch.global.L2 of every plane of the march at block start (PF = 1) or two planes ahead (PF = 2)
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(32 * BY) t8_pf(int n, const uint8_t* __restric
   __shared__ double sm[32];
   if (lane == 0) sm[threadIdx.y] = acc;
   __syncthreads();
-  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+  if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
 }
 
 // T6: planes staged in shared memory by TMA (box 68 x (BY+2) x 1 doubles, out-of-range -> 0), NST-deep
@@ -307,7 +308,7 @@ t6_tma(const __grid_constant__ CUtensorMap mp, int n, const uint8_t* __restrict_
   for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(~0u, acc, o);
   if (lane == 0) sm[ty] = acc;
   __syncthreads();
-  if (tid == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % 32, t); }
+  if (tid == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
 }
 
 typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -407,6 +408,9 @@ int main(int argc, char** argv) {
   us = timeit([&] { t8_pf<BY, ZP, PF><<<dim3(N / 128, N / BY, N / ZP), dim3(32, BY)>>>(N, fl, p, Ap, out); }); \
   printf("T8 pf%d  BY=%d ZP=%d          %8.1f us  %7.1f GB/s\n", PF, BY, ZP, us, gb17 / us * 1e6);
     RUN_T8(4, 4, 1) RUN_T8(4, 8, 1) RUN_T8(4, 4, 2) RUN_T8(4, 8, 2) RUN_T8(4, 16, 2) RUN_T8(2, 8, 1)
+    { int one = 1; CK(cudaMemcpyToSymbol(g_spread, &one, sizeof(int))); printf("single-address atomics:\n"); }
+    RUN_T7(4, 4) RUN_T4(4, 4)
+    { int v = 32; CK(cudaMemcpyToSymbol(g_spread, &v, sizeof(int))); }
     if (argc > 3) return 0;
     RUN_T5(4, 4) RUN_T5(8, 4) RUN_T5(4, 8) RUN_T5(8, 8) RUN_T5(4, 16) RUN_T5(8, 16)
     RUN_T6(8, 16, 4) RUN_T6(8, 32, 4) RUN_T6(8, 64, 4) RUN_T6(16, 32, 4) RUN_T6(16, 64, 4) RUN_T6(8, 32, 6) RUN_T6(4, 32, 4) RUN_T6(4, 64, 6) RUN_T6(8, 256, 4)
