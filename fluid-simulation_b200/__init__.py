@@ -58,7 +58,7 @@ class Stats(C.Structure):
 EXPORTS = [
     "flipb200_default_params", "flipb200_strerror", "flipb200_version", "flipb200_create",
     "flipb200_destroy", "flipb200_set_particles", "flipb200_get_particles", "flipb200_num_particles",
-    "flipb200_seed_box", "flipb200_step", "flipb200_step_host", "flipb200_p2g", "flipb200_classify",
+    "flipb200_seed_box", "flipb200_emit_box", "flipb200_step", "flipb200_step_host", "flipb200_p2g", "flipb200_classify",
     "flipb200_rhs_div", "flipb200_pcg_solve", "flipb200_vel_update", "flipb200_relax_error",
     "flipb200_g2p_advect", "flipb200_get_grid", "flipb200_set_grid", "flipb200_time_kernel",
     "flipb200_host_alloc", "flipb200_host_free",
@@ -98,6 +98,7 @@ def load():
     lib.flipb200_get_particles.argtypes = [vp] + [vp] * 6 + [C.c_int64, C.POINTER(C.c_int64)]
     lib.flipb200_num_particles.argtypes = [vp, C.POINTER(C.c_int64)]
     lib.flipb200_seed_box.argtypes = [vp, ip, ip, C.c_uint64]
+    lib.flipb200_emit_box.argtypes = [vp, ip, ip, C.c_uint64]
     lib.flipb200_step.argtypes = [vp, dp, C.POINTER(Stats)]
     lib.flipb200_step_host.argtypes = [vp] + [vp] * 6 + [C.c_int64, dp, vp, C.POINTER(Stats)]
     lib.flipb200_p2g.argtypes = [vp]
@@ -223,6 +224,8 @@ class Flip:
     def from_scene(cls, scene, **kw):
         nx, ny, nz = scene.n
         ox, oy, oz = scene.origin
+        if getattr(scene, "solid", None) is not None and "solid" not in kw:
+            kw["solid"] = scene.solid
         f = cls(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=scene.wall, **kw)
         f.set_particles(scene.pos, scene.vel)
         return f
@@ -261,6 +264,12 @@ class Flip:
         lo = (C.c_int32 * 3)(*lo)
         hi = (C.c_int32 * 3)(*hi)
         _check(self.lib.flipb200_seed_box(self.h, lo, hi, seed), "seed_box")
+
+    def emit_box(self, lo, hi, seed=1234):
+        """Re-seeding hook (fluid.cc:1374-1382, 1495-1497): seed_box + interpFromGrid (:883-895)."""
+        lo = (C.c_int32 * 3)(*lo)
+        hi = (C.c_int32 * 3)(*hi)
+        _check(self.lib.flipb200_emit_box(self.h, lo, hi, seed), "emit_box")
 
     # ---- the step (fluid.cc:1378-1490) ----
     def step(self, dt):

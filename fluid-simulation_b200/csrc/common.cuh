@@ -288,6 +288,8 @@ int fb_rhs_div(flipb200_ctx* c, double dt, int mode);
 int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters, double* rel);
 int fb_vel_update(flipb200_ctx* c, double dt_sub);
 int fb_cell_delta(flipb200_ctx* c);
+int fb_cell_delta_r(flipb200_ctx* c, double ratio);
+int fb_emit_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 int fb_g2p_advect(flipb200_ctx* c);
 int fb_fetch_scalars(flipb200_ctx* c);
 int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units);

@@ -315,11 +315,14 @@ k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u
   d0[q] = a; d1[q] = b; d2[q] = cc;
 }
 
-int fb_cell_delta(flipb200_ctx* c) {
+int fb_cell_delta(flipb200_ctx* c) { return fb_cell_delta_r(c, c->P.flip_ratio); }
+
+// ratio = 0 leaves the plain cell-centred velocity getVelocity(c, vels) in the arrays (PIC gather input)
+int fb_cell_delta_r(flipb200_ctx* c, double ratio) {
   const Grid& g = c->g;
   dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.k1 - g.k0);
   k_cell_delta<<<grd, blk, 0, c->stream>>>(g, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->r, c->pd,
-                                           c->Ap, c->P.flip_ratio);
+                                           c->Ap, ratio);
   CK_LAUNCH(); c->launches++;
   // particles of my top base plane read the deltas of plane k1
   double* dc[3] = {c->r, c->pd, c->Ap};

@@ -752,3 +752,26 @@ int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint6
   c->sorted = false;
   return 0;
 }
+
+// Re-seeding hook of the reference driver (commented out at fluid.cc:1374-1382 and :1495-1497):
+// scatter new particles into a source box, then PointList::interpFromGrid (:883-895) gives every new
+// particle the PIC velocity clampedCatmullRom(p, vels) (:125-207): sum(cw * getVelocity(node)) / sum(cw)
+// over the in-shell nodes of its window, 0 when the weight sum is 0.  Here: fb_seed_box appends the
+// particles, k_cell_delta with ratio 0 leaves getVelocity(c, vels) in the idle PCG vectors and the
+// per-particle gather kernel with ratio 0 turns it into the particle velocity (v = 0*v + interp).
+// Collective on z-slab runs (ghost fill of the cell-centred velocities).
+int fb_emit_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed) {
+  const int64_t base = c->pt.n;
+  int rc = fb_seed_box(c, lo, hi, seed);
+  if (rc) return rc;
+  const int64_t add = c->pt.n - base;
+  if ((rc = fb_cell_delta_r(c, 0.0))) return rc;
+  if (add > 0) {
+    Particles& pt = c->pt;
+    k_g2p<<<(unsigned)((add + 255) / 256), 256, 0, c->stream>>>(c->g, add, c->flags, pt.a[0] + base, pt.a[1] + base, pt.a[2] + base,
+                                                                pt.a[3] + base, pt.a[4] + base, pt.a[5] + base, c->r, c->pd, c->Ap, c->ds, 0.0);
+    CK_LAUNCH(); c->launches++;
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}

@@ -133,6 +133,12 @@ int flipb200_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3],
   return fb_seed_box(c, lo, hi, seed);
 }
 
+int flipb200_emit_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed) {
+  if (!c || !lo || !hi) return FLIPB200_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  return fb_emit_box(c, lo, hi, seed);
+}
+
 int flipb200_p2g(flipb200_ctx* c) {
   if (!c) return FLIPB200_ERR_ARG;
   CK(cudaSetDevice(c->device));

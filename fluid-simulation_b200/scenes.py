@@ -14,6 +14,7 @@ drop, exactly `ppc` particles per fluid voxel with stratified jitter in 2x2x2 su
 All positions are in reference coordinates (index i = c + origin).
 """
 from dataclasses import dataclass
+from typing import Optional
 
 import numpy as np
 
@@ -26,6 +27,7 @@ class Scene:
     wall: int
     pos: np.ndarray   # (P, 3) float64, reference coordinates
     vel: np.ndarray   # (P, 3) float64
+    solid: Optional[np.ndarray] = None   # (nz, ny, nx) uint8 interior obstacles (the shell is implied by `wall`)
 
     @property
     def num_particles(self):
@@ -117,3 +119,40 @@ def small_cube_drop(n=25, half=4, ppv=10, seed=0):
     origin = n // 2
     pos = uniform_point_scatter([-half] * 3, [half] * 3, ppv, seed)
     return Scene(f"small_cube_drop_{n}", (n, n, n), (origin,) * 3, 2, pos, np.zeros_like(pos))
+
+
+# ---- the reference driver's alternative scenes (commented out in fluid.cc) -------------------------
+# fluid shapes: fluid.cc:1176 ("normal"), :1178-1190 ("pea"), :1192-1203 ("side"), :1205-1216 ("stable");
+# obstacles inside the solid-shell loop: :1303-1315 ("two_blocks"), :1317-1329 ("three_blocks"),
+# and after it :1334-1345 ("big_wall").  All in reference coordinates on the 121^3 box.
+_REF_FLUIDS = {
+    "normal": [((-20, -20, -20), (20, 20, 20))],
+    "pea": [((-1, -1, -1), (1, 1, 1)), ((-1, 6, -1), (1, 9, 1))],
+    "side": [((-57, -57, -57), (57, -40, -40))],
+    "stable": [((-57, -57, -57), (57, -55, 57))],
+}
+_REF_OBSTACLES = {
+    "two_blocks": [((-11, -58, -3), (-6, -8, 3)), ((6, -58, -3), (11, -8, 3))],
+    "three_blocks": [((-11, -58, -3), (-7, -8, 3)), ((-2, -58, -3), (2, -8, 3)), ((7, -58, -3), (11, -8, 3))],
+    "big_wall": [((-58, -58, -30), (58, -50, -25))],
+}
+
+
+def reference_scene(fluid="normal", obstacle=None, seed=0, ppv=10, n=121, origin=60, wall=2):
+    """One of the reference driver's scenes: `fluid` in normal | pea | side | stable, `obstacle` in
+    None | two_blocks | three_blocks | big_wall.  Particles: UniformPointScatter (10 per voxel volume)
+    over every fluid box with mt19937(seed), as fluid.cc:1348-1350 does over fluidGrid."""
+    boxes = _REF_FLUIDS[fluid]
+    parts = [uniform_point_scatter(lo, hi, ppv, seed + 7919 * b) for b, (lo, hi) in enumerate(boxes)]
+    pos = np.concatenate(parts, axis=0)
+    pos = np.ascontiguousarray(pos[np.all(np.abs(pos) < origin - 2, axis=1)])       # PointList::add, fluid.cc:841
+    solid = None
+    if obstacle is not None:
+        solid = np.zeros((n, n, n), dtype=np.uint8)                                  # (z, y, x)
+        for lo, hi in _REF_OBSTACLES[obstacle]:
+            solid[lo[2] + origin:hi[2] + origin + 1, lo[1] + origin:hi[1] + origin + 1, lo[0] + origin:hi[0] + origin + 1] = 1
+        # particles are not seeded inside an obstacle
+        c = np.rint(pos).astype(np.int64) + origin
+        pos = np.ascontiguousarray(pos[solid[c[:, 2], c[:, 1], c[:, 0]] == 0])
+    name = f"reference_{fluid}" + (f"_{obstacle}" if obstacle else "")
+    return Scene(name, (n, n, n), (origin,) * 3, wall, pos, np.zeros_like(pos), solid)

@@ -128,6 +128,11 @@ int  flipb200_num_particles(flipb200_ctx*, int64_t* n);
 /* Device-side seeding (the role of UniformPointScatter at fluid.cc:1348-1350, stratified):
  * exactly 8 particles per voxel of the index box [lo,hi] (inclusive), zero velocity. */
 int  flipb200_seed_box(flipb200_ctx*, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
+/* Re-seeding hook (commented out in the reference driver, fluid.cc:1374-1382 and :1495-1497): appends
+ * 8 particles per voxel of the box like flipb200_seed_box and gives each new particle the PIC
+ * velocity of PointList::interpFromGrid (fluid.cc:883-895, clampedCatmullRom :125-207) gathered from
+ * the current grid velocities (those of the last step / p2g + classify).  Collective on z-slab runs. */
+int  flipb200_emit_box(flipb200_ctx*, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 
 /* One time step == the loop body fluid.cc:1378-1490 with device-resident particles.
  * dt_inout: in = dt used by the solve (fluid.cc:1469-1475), out = FLIPadvect's dt (:1490). */

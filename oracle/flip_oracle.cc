@@ -583,6 +583,34 @@ void oracle_flip_advect(oracle_ctx* c, double* dt_inout) {
   }
 }
 
+/* PointList::interpFromGrid fluid.cc:883-895 for the particles [first, first + count) (the ones whose
+ * initializedVelocities flag would be false): v = clampedCatmullRom(p, vels) :125-207 -- the window of
+ * :127-136, nodes within 58 (:162), velocity getVelocity(node, vels) (:164), weights spline^3 (:178),
+ * u /= weight, (0,0,0) when the weight sum is 0 (:185-197).  The min/max of :150-176 are computed by
+ * the reference but never applied. */
+void oracle_interp_from_grid(oracle_ctx* c, int64_t first, int64_t count) {
+  const int ox = c->P.ox, oy = c->P.oy, oz = c->P.oz;
+  const int64_t np = (int64_t)c->px.size();
+  for (int64_t n = first; n < first + count && n < np; ++n) {
+    const double x = c->px[n], y = c->py[n], z = c->pz[n];
+    int lo[3], hi[3];
+    window(c, x, y, z, lo, hi);
+    double weight = 0, u = 0, v = 0, w = 0;
+    for (int i = lo[0]; i <= hi[0]; ++i)
+      for (int j = lo[1]; j <= hi[1]; ++j)
+        for (int k = lo[2]; k <= hi[2]; ++k)
+          if (c->inside(i, j, k)) {
+            double velc[3];
+            get_velocity(c, ORACLE_U, i, j, k, velc);
+            double cw = oracle_spline(x - (i - ox)) * oracle_spline(y - (j - oy)) * oracle_spline(z - (k - oz));
+            weight += cw;
+            u += velc[0] * cw; v += velc[1] * cw; w += velc[2] * cw;
+          }
+    if (weight != 0) { c->vx[n] = u / weight; c->vy[n] = v / weight; c->vz[n] = w / weight; }
+    else { c->vx[n] = 0; c->vy[n] = 0; c->vz[n] = 0; }
+  }
+}
+
 /* the step body, fluid.cc:1378-1490 */
 int oracle_step(oracle_ctx* c, double* dt_inout, oracle_stats* st) {
   oracle_stats s; memset(&s, 0, sizeof(s));

@@ -84,6 +84,7 @@ int  oracle_solve(oracle_ctx*, double* rel_err);                  /* :1473-1474 
 void oracle_vel_update(oracle_ctx*, double dt_sub);               /* :1475 -> :612-703 */
 double oracle_relax_error(oracle_ctx*, double dt);                /* :1477-1483 */
 void oracle_flip_advect(oracle_ctx*, double* dt_inout);           /* :1490 -> :972-1038 */
+void oracle_interp_from_grid(oracle_ctx*, int64_t first, int64_t count);   /* :883-895 (re-seeding hook :1495-1497) */
 int  oracle_step(oracle_ctx*, double* dt_inout, oracle_stats*);   /* whole body :1378-1490 */
 
 /* per-pass history of the last oracle_step (errors, iterations); returns #passes */

@@ -84,6 +84,8 @@ def load(prefer_ref=True):
     lib.oracle_relax_error.argtypes = [C.c_void_p, C.c_double]
     lib.oracle_relax_error.restype = C.c_double
     lib.oracle_flip_advect.argtypes = [C.c_void_p, dp]
+    lib.oracle_interp_from_grid.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+    lib.oracle_interp_from_grid.restype = None
     lib.oracle_step.argtypes = [C.c_void_p, dp, C.POINTER(OracleStats)]
     lib.oracle_step.restype = C.c_int
     lib.oracle_pass_history.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]
@@ -211,6 +213,10 @@ class Oracle:
 
     def vel_update(self, dt_sub): self.lib.oracle_vel_update(self.h, dt_sub)
     def relax_error(self, dt): return self.lib.oracle_relax_error(self.h, dt)
+
+    def interp_from_grid(self, first, count):
+        """PointList::interpFromGrid (fluid.cc:883-895) for particles [first, first + count)."""
+        self.lib.oracle_interp_from_grid(self.h, int(first), int(count))
 
     def flip_advect(self, dt):
         d = C.c_double(dt)

@@ -26,6 +26,8 @@ def match_particles(pos0, pos_a, vel_a, pos0_b):
 def oracle_for_scene(oracle_mod, sc, **kw):
     nx, ny, nz = sc.n
     ox, oy, oz = sc.origin
+    if getattr(sc, "solid", None) is not None and "solid" not in kw:
+        kw["solid"] = sc.solid
     o = oracle_mod.Oracle(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=sc.wall, **kw)
     o.set_particles(sc.pos, sc.vel)
     return o

@@ -375,7 +375,7 @@ def test_stencil4_matches_stencil2(fb, monkeypatch):
     for st4 in ("1", "0"):
         monkeypatch.setenv("FLIPB200_ST4", st4)
         f = fb.Flip(nx=150, ny=20, nz=24, ox=75, oy=10, oz=12, precond=1)
-        f.seed_box((2, 2, 2), (148, 14, 22), seed=99)       # the whole interior below y = 14: walls on every side
+        f.seed_box((2, 2, 2), (147, 14, 21), seed=99)       # the whole interior up to y = 14 (inclusive box): walls on every side
         f.p2g(); f.classify()
         f.rhs_div(0.125)
         it, rel = f.pcg_solve(0.125)
@@ -384,7 +384,50 @@ def test_stencil4_matches_stencil2(fb, monkeypatch):
         f.close()
     assert abs(res["1"][0] - res["0"][0]) <= 1, (res["1"][0], res["0"][0])
     assert rel_l2(res["1"][1], res["0"][1]) < 1e-9
-    # hydrostatic answer: particles below y = 14 mark the nodes up to y = 15 fluid (the splat reaches
+    # hydrostatic answer: particles in the voxels up to y = 14 mark the nodes up to y = 15 fluid (the splat reaches
     # one node up, as in test_mgpcg_obstacle_and_tank_128), p = rho*|g|*dx*depth
     p = res["1"][1]
     assert np.allclose(p[12, 2:14, 70], 10.0 * (16 - np.arange(2, 14)), rtol=1e-9)     # (z, y, x)
+
+
+def test_emit_box_interp_from_grid(fb, oracle_mod, scenes):
+    """Re-seeding hook (fluid.cc:1374-1382, 1495-1497): particles appended on the device get the PIC
+    velocity of PointList::interpFromGrid (:883-895, clampedCatmullRom :125-207) from the grid
+    velocities of the step that just ran; the old particles are untouched."""
+    sc = random_velocity_scene(scenes, n=25, half=5, vscale=1.0)
+    f, o = _pair(fb, oracle_mod, sc)
+    f.step(0.1); o.step(0.1)
+    n0 = sc.num_particles
+    p_before, v_before = f.get_particles()
+    for a in range(3):                                    # same grid velocities on both sides: isolates the gather
+        f.set_grid(fb.GRID_U + a, o.dgrid(a))
+    f.emit_box((9, 14, 9), (15, 20, 15), seed=5)          # index box straddling the top of the fluid cube, up to the shell
+    pg, vg = f.get_particles()
+    add = pg.shape[0] - n0
+    assert add == 8 * 7 * 7 * 7
+    assert np.array_equal(pg[:n0], p_before) and np.array_equal(vg[:n0], v_before)
+    po, vo = o.get_particles()
+    o.set_particles(np.concatenate([po, pg[n0:]]), np.concatenate([vo, np.zeros((add, 3))]))
+    o.interp_from_grid(n0, add)
+    _, vo2 = o.get_particles()
+    assert np.count_nonzero(np.abs(vo2[n0:]).sum(axis=1) > 0) > add // 4      # the box does overlap moving fluid
+    assert np.max(np.abs(vg[n0:] - vo2[n0:])) < 1e-13 * max(1.0, np.abs(vo2[n0:]).max())
+    # and the enlarged particle set steps on in step with the oracle
+    dg, st = f.step(0.1); do, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
+    pg2, _ = f.get_particles(); po2, _ = o.get_particles()
+    assert rel_l2(pg2, po2) < 1e-7
+
+
+def test_reference_obstacle_scene(fb, oracle_mod, scenes):
+    """One of the reference driver's commented-out scenes at full size (121^3): the "side" fluid slab
+    (fluid.cc:1192-1203) against the "big wall" obstacle (:1334-1345), one step against the oracle."""
+    sc = scenes.reference_scene("side", obstacle="big_wall")
+    f, o = _pair(fb, oracle_mod, sc)
+    dg, st = f.step(0.1); do, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
+    assert dg == pytest.approx(do, rel=1e-9)
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+    assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
+    pg, _ = f.get_particles(); po, _ = o.get_particles()
+    assert rel_l2(pg, po) < 1e-7

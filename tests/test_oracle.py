@@ -121,3 +121,39 @@ def test_jacobi_port_matches_eigen(oracle_mod):
         o.solve()
         res.append(o.p.copy())
     assert np.linalg.norm(res[0] - res[1]) / np.linalg.norm(res[0]) < 1e-10
+
+
+def test_reference_alternative_scenes():
+    """The reference driver's commented-out scenes (fluid.cc:1176-1216 fluid shapes, :1303-1345
+    obstacles): voxel boxes and scatter counts as the driver would produce them."""
+    from fluid_simulation_b200 import scenes
+    sc = scenes.reference_scene("normal")
+    assert sc.num_particles == 689210                      # 10 * 41^3, all inside |p| < 58 (fluid.cc:841)
+    assert sc.solid is None and sc.n == (121, 121, 121)
+    pea = scenes.reference_scene("pea")
+    assert pea.num_particles == 10 * 27 + 10 * 36          # cube [-1,1]^3 and the drop above it (j = 6..9)
+    assert pea.pos[:, 1].max() < 9.5 and pea.pos[:, 1].min() >= -1.5
+    side = scenes.reference_scene("side", obstacle="three_blocks")
+    # boxes reach coordinate 57: voxel 57 spans [56.5, 57.5), PointList::add keeps |p| < 58
+    assert np.all(np.abs(side.pos) < 58)
+    assert int(side.solid.sum()) == 3 * 5 * 51 * 7         # x 5 wide, y -58..-8, z -3..3
+    assert side.solid[60, 10, 60] == 1 and side.solid[60, 10, 64] == 0     # (z, y, x): centre block spans x in [-2, 2]
+    c = np.rint(side.pos).astype(int) + 60
+    assert not np.any(side.solid[c[:, 2], c[:, 1], c[:, 0]])
+    wall = scenes.reference_scene("stable", obstacle="big_wall")
+    assert int(wall.solid.sum()) == 117 * 9 * 6
+
+
+def test_interp_from_grid_uniform_field(oracle_mod):
+    """interpFromGrid / clampedCatmullRom (fluid.cc:883-895, 125-207) reproduces a uniform velocity
+    field exactly wherever the weight sum is non-zero, and returns 0 where no node is in bounds."""
+    n = 13
+    o = oracle_mod.Oracle(nx=n, ny=n, nz=n, ox=6, oy=6, oz=6)
+    for a, val in enumerate((1.5, -2.0, 0.25)):
+        o.dgrid(a)[...] = val
+    pos = np.array([[0.2, -0.3, 0.4], [3.9, 3.9, -3.9], [0.0, 0.0, 0.0]])
+    o.set_particles(pos, np.full_like(pos, 7.0))
+    o.interp_from_grid(0, 2)
+    _, v = o.get_particles()
+    assert np.allclose(v[:2], [[1.5, -2.0, 0.25]] * 2, rtol=1e-14)
+    assert np.all(v[2] == 7.0)                             # outside [first, first + count): untouched

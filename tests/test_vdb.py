@@ -78,3 +78,21 @@ def test_run_sh_fluid_drop_in(tmp_path):
         assert d.shape == (121, 121, 121) and np.isfinite(d).all() and d.min() >= 0.0
         assert d[0].max() == 0.0 and d[:, 0].max() == 0.0          # solid shell stays 0 (fluid.cc:1442-1445)
         assert 0.4 * 689210 < d.sum(dtype=np.float64) < 689210      # sum of spline weights per particle in (0.125, 1]
+
+
+@pytest.mark.gpu
+def test_run_sh_alternative_scene_with_reseeding(tmp_path):
+    """The driver's commented-out scenes (FLUID_SCENE / FLUID_OBSTACLE, fluid.cc:1178-1216, 1303-1345)
+    and the re-seeding hook (FLUID_RESEED, :1374-1382 / :1495-1497): the particle mass in the output
+    grids grows when new particles are emitted."""
+    import subprocess
+    from vdb_reader import read_vdb
+    env = dict(os.environ, FLUID_STEPS="4", FLUID_SCENE="pea", FLUID_OBSTACLE="three_blocks", FLUID_RESEED="2")
+    r = subprocess.run([os.path.join(ROOT, "run.sh"), "fluid"], cwd=tmp_path, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "Iteration:\t4" in r.stdout
+    grids = read_vdb(str(tmp_path / "mygrids.vdb"))
+    assert len(grids) == 4
+    mass = [float(g["dense"].sum(dtype=np.float64)) for g in grids]
+    assert 0.4 * 630 < mass[0] < 630 and abs(mass[1] - mass[0]) < 0.2 * mass[0]      # 10 * (27 + 36) particles
+    assert mass[2] > mass[1] + 0.4 * 8 * 63                                         # step 2 emitted 8 per voxel into both boxes
