@@ -35,7 +35,7 @@ class Params(C.Structure):
         ("flip_ratio", C.c_double), ("pcg_tol", C.c_double),
         ("pcg_max_iter", C.c_int32), ("max_passes", C.c_int32),
         ("precond", C.c_int32), ("device", C.c_int32),
-        ("track_ids", C.c_int32), ("reserved0", C.c_int32),
+        ("track_ids", C.c_int32), ("extrapolate", C.c_int32),
         ("max_particles", C.c_int64),
     ]
 

@@ -162,6 +162,7 @@ struct flipb200_ctx {
   uint8_t* solid;          // input solid mask incl. shell (1 byte)
   uint8_t* flags;          // FB_* (static solid part + per-step fluid bit)
   uint8_t* flags_static;   // solid part only
+  int32_t* ext_layer;      // params.extrapolate: wave that defined each node (+ a counter behind it), lazily allocated
   double *u[3];            // vels; during P2G: momentum accumulators
   double *ub[3];           // velBeforeUpdate; after the relaxation loop: cell-centred FLIP delta
   double *wacc;            // weight accumulator (fp64), rounded once to fp32 into wf

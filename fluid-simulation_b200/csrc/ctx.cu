@@ -24,6 +24,7 @@ void flipb200_default_params(flipb200_params* p) {
   p->precond = 1;                // multigrid V-cycle (IC-free); 0 = Jacobi
   p->device = -1;
   p->track_ids = 0;
+  p->extrapolate = 0;            // fluid.cc:1147: the call is commented out
   p->max_particles = 0;
 }
 
@@ -164,6 +165,7 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
   if (p->nx < 2 * p->wall + 2 || p->ny < 2 * p->wall + 2 || p->nz < 2 * p->wall + 2) return FLIPB200_ERR_ARG;
   if (p->wall < 1 || p->relax_div < 1 || !(p->dx > 0) || !(p->rho > 0)) return FLIPB200_ERR_ARG;
   if (!(p->flip_ratio >= 0.0 && p->flip_ratio <= 1.0)) return FLIPB200_ERR_ARG;   // 1 = the reference's pure FLIP (fluid.cc:981)
+  if (p->extrapolate != 0 && (p->extrapolate != 1 || world > 1)) return FLIPB200_ERR_ARG;   // single GPU only (grid.cu fb_extrapolate)
   flipb200_ctx* c = (flipb200_ctx*)calloc(1, sizeof(flipb200_ctx));
   if (!c) return FLIPB200_ERR_ARG;
   c->P = *p;
@@ -270,7 +272,7 @@ void flipb200_destroy(flipb200_ctx* c) {
   fb_mg_free(c);
   fb_comm_free(c);
   cudaFree(c->halo_tmp); cudaFree(c->halo.flags); cudaFree(c->halo.mail);
-  cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static);
+  cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static); cudaFree(c->ext_layer);
   for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }
   cudaFree(c->wacc); cudaFree(c->wf); cudaFree(c->bf[0]); cudaFree(c->bf[1]);
   cudaFree(c->x); cudaFree(c->r); cudaFree(c->pd); cudaFree(c->Ap);

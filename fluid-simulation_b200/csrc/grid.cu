@@ -75,6 +75,73 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// extrapolate (fluid.cc:705-802; the call at :1147 is commented out, params.extrapolate = 1 runs it).
+// `defined` of P2Gtransfer (:1109-1125, :1141) = outside 58 | solid | w > 0, so the targets are the
+// non-solid in-shell air nodes.  Wave 1 averages, for every such node, the velocities of the
+// w > 0 nodes of its 3x3x3 neighbourhood (clamped to the box); wave n + 1 those of the nodes wave n
+// defined -- the reference's frontier BFS as a gather: layer[q] = wave that defined q (0: w > 0,
+// -1: not yet, -2: never a target), sources of wave n are the nodes of layer n - 1.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_extrap_init(Grid g, const float* __restrict__ wf, const uint8_t* __restrict__ fs, int32_t* __restrict__ layer) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nx || j >= g.ny) return;
+  const int q = gidx(g, i, j, k);
+  const bool blocked = !inside_shell(g, i, j, k) || (fs[q] & FB_SOLID);
+  layer[q] = blocked ? -2 : (wf[q] > 0.0f ? 0 : -1);
+}
+__global__ void __launch_bounds__(256)
+k_extrap_wave(Grid g, int wave, int32_t* __restrict__ layer, double* __restrict__ u0, double* __restrict__ u1,
+              double* __restrict__ u2, int* __restrict__ n_new) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= g.nx || j >= g.ny) return;
+  const int q = gidx(g, i, j, k);
+  if (layer[q] != -1) return;
+  double a = u0[q], b = u1[q], c = u2[q];                    // the sums start from the node's own value (:739)
+  int cnt = 0;
+  for (int dk = -1; dk <= 1; ++dk)
+    for (int dj = -1; dj <= 1; ++dj)
+      for (int di = -1; di <= 1; ++di) {
+        const int ii = i + di, jj = j + dj, kk = k + dk;
+        if (ii < 0 || jj < 0 || kk < 0 || ii >= g.nx || jj >= g.ny || kk >= g.nz) continue;
+        const int n = gidx(g, ii, jj, kk);
+        if (layer[n] != wave - 1) continue;                   // wave-(n-1) nodes are read-only during wave n
+        a += u0[n]; b += u1[n]; c += u2[n]; ++cnt;
+      }
+  if (cnt) {
+    u0[q] = a / cnt; u1[q] = b / cnt; u2[q] = c / cnt;       // :751, :796
+    layer[q] = wave;
+    atomicAdd(n_new, 1);
+  }
+}
+
+int fb_extrapolate(flipb200_ctx* c) {
+  const Grid& g = c->g;
+  if (c->world > 1) return FLIPB200_ERR_ARG;                  // the waves would need a ghost exchange each: single GPU only
+  if (!c->ext_layer) CK(cudaMalloc((void**)&c->ext_layer, (size_t)g.total * sizeof(int32_t) + 256));
+  int* n_new = reinterpret_cast<int*>(c->ext_layer + g.total);
+  dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.nz);
+  k_extrap_init<<<grd, blk, 0, c->stream>>>(g, c->wf, c->flags_static, c->ext_layer);
+  c->launches++;
+  const int max_waves = g.nx + g.ny + g.nz;
+  for (int wave = 1; wave <= max_waves; wave += 4) {           // one host round trip per four waves
+    CK(cudaMemsetAsync(n_new, 0, sizeof(int), c->stream));
+    for (int w = wave; w < wave + 4; ++w)
+      k_extrap_wave<<<grd, blk, 0, c->stream>>>(g, w, c->ext_layer, c->u[0], c->u[1], c->u[2], n_new);
+    c->launches += 4;
+    int h = 0;
+    CK(cudaMemcpyAsync(&h, n_new, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (h == 0) break;
+  }
+  // velBeforeUpdate = vels->deepCopy() (fluid.cc:1455) comes after P2Gtransfer: take the extrapolated field
+  for (int a = 0; a < 3; ++a)
+    CK(cudaMemcpyAsync(c->ub[a], c->u[a], (size_t)g.total * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  CK_LAUNCH();
+  return 0;
+}
+
 __global__ void k_reset_classify(DevScalars* ds) {
   ds->n_fluid = 0;
   ds->bbox[0] = ds->bbox[1] = ds->bbox[2] = 1 << 30;
@@ -89,6 +156,7 @@ int fb_classify(flipb200_ctx* c) {
                                          c->ub[2], c->x, c->flags_static, c->flags, c->ds);
   CK_LAUNCH(); c->launches += 2;
   int rc;
+  if (c->P.extrapolate && (rc = fb_extrapolate(c))) return rc;
   if (c->world > 1) {
     // global cell count and bounding box; ghost planes of what the neighbours' stencils read
     if ((rc = fb_allreduce(c, &c->ds->n_fluid, 1, FB_I32, FB_SUM))) return rc;
@@ -112,6 +180,9 @@ int fb_classify(flipb200_ctx* c) {
     gb.x0 = max(0, bb[0] - 2) & ~31;            // rows stay sector/line aligned
     gb.y0 = max(0, bb[1] - 2); gb.z0 = max(0, bb[2] - 2);
     gb.x1 = min(g.nx, bb[3] + 3); gb.y1 = min(g.ny, bb[4] + 3); gb.z1 = min(g.gnz, bb[5] + 3);
+    // with extrapolated (non-zero) air velocities velUpdate's solid loop (fluid.cc:668-700) matters on
+    // every solid cell of the domain, not only next to the fluid: sweep the whole grid
+    if (c->P.extrapolate) { gb.x0 = gb.y0 = gb.z0 = 0; gb.x1 = g.nx; gb.y1 = g.ny; gb.z1 = g.gnz; }
     b = gb;
     // this rank sweeps the part of the global box that lies in its owned planes (local indices);
     // a rank the box does not reach sweeps one inert plane so that every rank launches the same kernels

@@ -56,7 +56,9 @@ typedef struct {
   int32_t track_ids;         /* 1: carry particle ids through the cell sort so that get_particles /
                                 step_host return the caller's original order (the reference never
                                 reorders its PointList); 0: arrays come back cell-sorted          */
-  int32_t reserved0;
+  int32_t extrapolate;       /* 0: what main() runs (the call at fluid.cc:1147 is commented out); 1: run
+                                extrapolate (fluid.cc:705-802) on the P2G velocities -- layer by layer every
+                                air node gets the average of the nodes defined one layer earlier (single GPU) */
   int64_t max_particles;     /* capacity to reserve; 0 => grow on set_particles               */
 } flipb200_params;
 

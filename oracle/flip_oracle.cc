@@ -88,6 +88,7 @@ void oracle_default_params(oracle_params* p) {
   p->threads = 1;
   p->pcg_max_iter = -1;
   p->flip_ratio = 1.0;
+  p->extrapolate = 0;
 }
 
 int oracle_has_eigen(void) {
@@ -220,6 +221,62 @@ void oracle_p2g(oracle_ctx* c) {
   for (int64_t q = 0; q < c->N; ++q) {
     double w = W[q];
     if (w > 0) { U[q] /= w; V[q] /= w; Wv[q] /= w; }
+  }
+  if (c->P.extrapolate) oracle_extrapolate(c);               /* :1147 (commented out in the reference) */
+}
+
+/* extrapolate fluid.cc:705-802 with the `defined` grid P2Gtransfer builds (:1109-1125, :1141): defined =
+ * outside 58 | solid | w > 0.  Wave 0 (:714-748): every defined, non-solid, in-bounds node (= w > 0) adds
+ * its velocity to each undefined node of its 3x3x3 neighbourhood (clamped to the box, :720-725) and
+ * counts it; the touched nodes are divided by their count and become defined (:749-753).  Then the
+ * frontier repeats the same from the nodes defined by the previous wave only (:754-800) until nothing
+ * new is reached.  The sums start from the node's own value (:739), 0 for an air node. */
+void oracle_extrapolate(oracle_ctx* c) {
+  const int nx = c->P.nx, ny = c->P.ny, nz = c->P.nz;
+  std::vector<float>& W = c->fg[ORACLE_W];
+  std::vector<double>& U = c->dg[ORACLE_U];
+  std::vector<double>& V = c->dg[ORACLE_V];
+  std::vector<double>& Wv = c->dg[ORACLE_WV];
+  std::vector<uint8_t> defined(c->N, 0);
+  std::vector<int32_t> count(c->N, 0);
+  std::vector<int64_t> frontier, next;
+  for (int i = 0; i < nx; ++i) for (int j = 0; j < ny; ++j) for (int k = 0; k < nz; ++k) {
+    const int64_t q = c->id(i, j, k);
+    defined[q] = (!c->inside(i, j, k) || c->isSolid(i, j, k) || W[q] > 0) ? 1 : 0;
+  }
+  auto spread = [&](int i, int j, int k, std::vector<int64_t>& out) {
+    const int64_t q = c->id(i, j, k);
+    for (int a = (i == 0 ? i : i - 1); a <= (i == nx - 1 ? i : i + 1); ++a)
+      for (int b = (j == 0 ? j : j - 1); b <= (j == ny - 1 ? j : j + 1); ++b)
+        for (int d = (k == 0 ? k : k - 1); d <= (k == nz - 1 ? k : k + 1); ++d) {
+          const int64_t n = c->id(a, b, d);
+          if (defined[n]) continue;
+          if (count[n] == 0) out.push_back(n);
+          count[n] += 1;
+          U[n] = U[q] + U[n]; V[n] = V[q] + V[n]; Wv[n] = Wv[q] + Wv[n];
+        }
+  };
+  auto settle = [&](const std::vector<int64_t>& v) {
+    for (size_t t = 0; t < v.size(); ++t) {
+      const int64_t n = v[t];
+      U[n] = U[n] / count[n]; V[n] = V[n] / count[n]; Wv[n] = Wv[n] / count[n];
+      defined[n] = 1;
+    }
+  };
+  for (int i = 0; i < nx; ++i) for (int j = 0; j < ny; ++j) for (int k = 0; k < nz; ++k) {   /* :714-748, x outer */
+    const int64_t q = c->id(i, j, k);
+    if (defined[q] && !c->isSolid(i, j, k) && c->inside(i, j, k)) spread(i, j, k, frontier);
+  }
+  settle(frontier);
+  while (!frontier.empty()) {                                  /* :754-800 */
+    next.clear();
+    for (size_t t = 0; t < frontier.size(); ++t) {
+      const int64_t q = frontier[t];
+      const int i = (int)(q % nx), j = (int)((q / nx) % ny), k = (int)(q / ((int64_t)nx * ny));
+      spread(i, j, k, next);
+    }
+    settle(next);
+    frontier.swap(next);
   }
 }
 

@@ -50,6 +50,8 @@ typedef struct {
   int32_t threads;        /* 1 = serial particle loops (parity); >1 OpenMP (timing)   */
   int32_t pcg_max_iter;   /* <0 => 2n (IterativeSolverBase.h:283)                     */
   double  flip_ratio;     /* 1 = pure FLIP (fluid.cc:981, what main() runs); 0 = PIC of advect (:904-971) */
+  int32_t extrapolate;    /* 0 = what main() runs (the call at fluid.cc:1147 is commented out); 1 = run extrapolate :705-802 at the end of P2Gtransfer */
+  int32_t reserved0;
 } oracle_params;
 
 typedef struct {
@@ -76,6 +78,7 @@ double oracle_spline(double x);                                   /* fluid.cc:22
 /* stages (mirror the step-loop call sequence, fluid.cc:1378-1490) */
 void oracle_clear_vel(oracle_ctx*);                               /* :1378 */
 void oracle_p2g(oracle_ctx*);                                     /* :1384 -> :1106-1148 */
+void oracle_extrapolate(oracle_ctx*);                             /* :1147 (commented out) -> :705-802 */
 int  oracle_classify(oracle_ctx*);                                /* :1388-1448 (container, indices, output) -> numActive */
 void oracle_save_vel_before(oracle_ctx*);                         /* :1455 */
 void oracle_rhs_div(oracle_ctx*, double dt);                      /* :1465-1470 */

@@ -25,6 +25,7 @@ class OracleParams(C.Structure):
         ("solver", C.c_int32), ("max_passes", C.c_int32), ("threads", C.c_int32),
         ("pcg_max_iter", C.c_int32),
         ("flip_ratio", C.c_double),
+        ("extrapolate", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 
@@ -86,6 +87,8 @@ def load(prefer_ref=True):
     lib.oracle_flip_advect.argtypes = [C.c_void_p, dp]
     lib.oracle_interp_from_grid.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
     lib.oracle_interp_from_grid.restype = None
+    lib.oracle_extrapolate.argtypes = [C.c_void_p]
+    lib.oracle_extrapolate.restype = None
     lib.oracle_step.argtypes = [C.c_void_p, dp, C.POINTER(OracleStats)]
     lib.oracle_step.restype = C.c_int
     lib.oracle_pass_history.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32]

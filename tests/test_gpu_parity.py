@@ -431,3 +431,34 @@ def test_reference_obstacle_scene(fb, oracle_mod, scenes):
     assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
     pg, _ = f.get_particles(); po, _ = o.get_particles()
     assert rel_l2(pg, po) < 1e-7
+
+
+def test_extrapolate(fb, oracle_mod, scenes):
+    """params.extrapolate = 1 runs the reference's extrapolate (fluid.cc:705-802, call commented out at
+    :1147) on the P2G velocities: wave by wave every air node gets the average of the nodes defined one
+    wave earlier.  Grid after P2G and one full step against the oracle, with an interior obstacle."""
+    sc = random_velocity_scene(scenes, n=25, half=5, vscale=1.0)
+    solid = np.zeros((25, 25, 25), dtype=np.uint8)
+    solid[10:15, 4:8, 10:15] = 1
+    f = fb.Flip(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, track_ids=1, solid=solid, extrapolate=1)
+    f.set_particles(sc.pos, sc.vel)
+    o = oracle_mod.Oracle(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, solid=solid, extrapolate=1)
+    o.set_particles(sc.pos, sc.vel)
+    f.p2g(); f.classify()
+    o.clear_vel(); o.p2g(); o.classify(); o.save_vel_before()
+    ug, uo = _grids(fb, f), _ogrids(o)
+    air = (o.fgrid(oracle_mod.F_W) == 0) & (solid == 0)
+    assert np.count_nonzero(uo[0][air]) > 5000                 # the air really was filled
+    # same bound as test_p2g_classify (u = sum(cw v) / float(w) carries the fp32 weight rounding), now
+    # over the whole box, and in the air alone
+    assert rel_l2(ug, uo) < 1e-6 and rel_l2(ug[:, air], uo[:, air]) < 1e-6
+    assert np.max(np.abs(ug - uo)) < 1e-6 * np.abs(uo).max()
+    assert rel_l2(_grids(fb, f, fb.GRID_UB), _ogrids(o, 3)) < 1e-6              # velBeforeUpdate is the extrapolated field too
+    f.set_particles(sc.pos, sc.vel); o.set_particles(sc.pos, sc.vel)
+    dg, st = f.step(0.1); do, so = o.step(0.1)
+    assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid)
+    assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+    pg, _ = f.get_particles(); po, _ = o.get_particles()
+    assert rel_l2(pg, po) < 1e-7
+    with pytest.raises(fb.FlipError):                          # z-slab contexts do not support it
+        fb.Flip(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, extrapolate=1, rank=0, world=2)

@@ -157,3 +157,26 @@ def test_interp_from_grid_uniform_field(oracle_mod):
     _, v = o.get_particles()
     assert np.allclose(v[:2], [[1.5, -2.0, 0.25]] * 2, rtol=1e-14)
     assert np.all(v[2] == 7.0)                             # outside [first, first + count): untouched
+
+
+def test_extrapolate_uniform_velocity(oracle_mod):
+    """extrapolate (fluid.cc:705-802, run at the end of P2Gtransfer when params.extrapolate = 1): a fluid
+    blob moving with one velocity fills every non-solid in-bounds air node with that velocity; solid
+    and out-of-bounds nodes stay 0; without the flag the air stays 0 (what main() runs)."""
+    from fluid_simulation_b200 import scenes
+    sc = scenes.small_cube_drop(n=17, half=3)
+    sc.vel = np.tile(np.array([0.5, -1.25, 2.0]), (sc.num_particles, 1))
+    solid = np.zeros((17, 17, 17), dtype=np.uint8)
+    solid[3:6, 3:6, 3:6] = 1
+    for ext in (0, 1):
+        o = oracle_for_scene(oracle_mod, sc, solid=solid, extrapolate=ext)
+        o.clear_vel(); o.p2g()
+        u = np.stack([o.dgrid(a) for a in range(3)], -1)
+        inside = np.zeros((17, 17, 17), dtype=bool); inside[2:15, 2:15, 2:15] = True
+        air = inside & (solid == 0) & (o.fgrid(oracle_mod.F_W) == 0)
+        assert air.sum() > 1000
+        if ext:
+            assert np.allclose(u[air], [0.5, -1.25, 2.0], rtol=1e-6)      # node velocities carry the fp32 weight-sum rounding (1e-8)
+        else:
+            assert np.all(u[air] == 0.0)
+        assert np.all(u[~inside] == 0.0) and np.all(u[solid == 1] == 0.0)
