@@ -19,14 +19,17 @@ from fluid_simulation_b200 import scenes    # noqa: E402
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def run(name, sc, nsteps):
+def run(name, sc, nsteps, **kw):
+    """kw: optional oracle parameters stored with the vectors (solid, extrapolate, flip_ratio)."""
     nx, ny, nz = sc.n
     ox, oy, oz = sc.origin
-    o = O.Oracle(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=sc.wall)
+    o = O.Oracle(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=sc.wall, **kw)
     assert o.has_eigen, "goldens must come from oracle/_ref (reference Eigen), not the port"
     o.set_particles(sc.pos, sc.vel)
     out = dict(n=np.array(sc.n), origin=np.array(sc.origin), wall=np.array(sc.wall),
                pos0=sc.pos.astype(np.float64), vel0=sc.vel.astype(np.float64))
+    for k, v in kw.items():
+        out["opt_" + k] = np.asarray(v)
     dt = 0.1
     passes, nfluid, dts, errs = [], [], [], []
     for s in range(nsteps):
@@ -51,3 +54,10 @@ if __name__ == "__main__":
     rng = np.random.default_rng(11)
     sc.vel = rng.normal(0.0, 0.5, size=sc.pos.shape)
     run("dam_break_column_24", sc, 10)
+    # the optional paths in one scene: interior obstacle (fluid.cc:1303-1345), extrapolate (:705-802),
+    # PIC/FLIP blend 0.9 (:904-971, :125-207)
+    sc = scenes.small_cube_drop(n=25, half=5, seed=3)
+    sc.vel = np.random.default_rng(103).normal(0.0, 1.0, size=sc.pos.shape)
+    solid = np.zeros((25, 25, 25), dtype=np.uint8)
+    solid[10:15, 4:8, 10:15] = 1
+    run("obstacle_extrapolate_pic_25", sc, 5, solid=solid, extrapolate=1, flip_ratio=0.9)

@@ -20,14 +20,24 @@ TOL_POS10 = 1e-4     # north_star: positions after 10 steps rel-L2
 
 
 def test_golden_files_present():
-    assert len(GOLDEN) >= 2
+    assert len(GOLDEN) >= 3
+
+
+def _opts(g):
+    """Optional parameters stored with a golden file (solid, extrapolate, flip_ratio)."""
+    kw = {}
+    for k in g.files:
+        if k.startswith("opt_"):
+            v = g[k]
+            kw[k[4:]] = v if v.ndim else v.item()
+    return kw
 
 
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p) for p in GOLDEN])
 def test_oracle_reproduces_golden(oracle_mod, path):
     g = np.load(path)
     nx, ny, nz = (int(v) for v in g["n"]); ox, oy, oz = (int(v) for v in g["origin"])
-    o = oracle_mod.Oracle(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=int(g["wall"]))
+    o = oracle_mod.Oracle(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=int(g["wall"]), **_opts(g))
     o.set_particles(g["pos0"], g["vel0"])
     exact = bool(o.has_eigen)
     dt = 0.1
@@ -49,7 +59,7 @@ def test_oracle_reproduces_golden(oracle_mod, path):
 def test_cuda_path_matches_golden(fb, path):
     g = np.load(path)
     nx, ny, nz = (int(v) for v in g["n"]); ox, oy, oz = (int(v) for v in g["origin"])
-    f = fb.Flip(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=int(g["wall"]), track_ids=1)
+    f = fb.Flip(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=int(g["wall"]), track_ids=1, **_opts(g))
     f.set_particles(g["pos0"], g["vel0"])
     dt = 0.1
     for s in range(len(g["passes"])):
