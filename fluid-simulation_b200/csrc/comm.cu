@@ -433,7 +433,7 @@ extern "C" int flipb200_halo_mode(flipb200_ctx* c) { return c ? c->halo.mode : F
 // [3] distributed levels [4] kernels per iteration [5] ghost-pushing kernels per iteration [6] rank [7] world
 extern "C" int flipb200_debug_info(flipb200_ctx* c, int32_t* out8) {
   if (!c || !out8) return FLIPB200_ERR_ARG;
-  out8[0] = c->halo.mode + (c->halo.red_on ? 10 : 0);   // +10: all-reduce fused too
+  out8[0] = c->halo.mode + (c->halo.red_on ? 10 : 0) + (c->halo.gather_on ? 20 : 0);   // +10: all-reduce fused too, +20: all-gather by peer stores
   out8[1] = c->it_exec ? 1 : 0; out8[2] = c->mg_levels; out8[3] = c->mg_nd;
   out8[4] = (int32_t)c->it_kernels; out8[5] = c->it_nprod; out8[6] = c->rank; out8[7] = c->world;
   return FLIPB200_OK;
@@ -497,6 +497,41 @@ RedPub fb_red_make(flipb200_ctx* c) {
   return r;
 }
 
+// All-gather of the first replicated level by peer stores (halo.cuh GatherPush): wanted when the level
+// is fed by a distributed one and has its own kernels (not inside the one-block tail);
+// FLIPB200_FUSED_GATHER=0 keeps the NCCL all-gather.
+static bool gather_wanted(const flipb200_ctx* c) {
+  const char* e = getenv("FLIPB200_FUSED_GATHER");
+  if (e && e[0] == '0') return false;
+  const int nd = c->mg_nd;
+  return c->world > 1 && c->world <= RED_MAXR && nd >= 1 && nd < c->mg_levels && nd < c->mg_tail0 && !c->mg[nd].dist;
+}
+
+GatherPush fb_gather_make(flipb200_ctx* c, int nblocks) {
+  GatherPush g = gather_off();
+  HaloState& hs = c->halo;
+  if (!hs.gather_on || hs.mode == 0) return g;
+  g.on = 1; g.mode = hs.mode; g.rank = c->rank; g.world = c->world; g.nblocks = nblocks;
+  g.srel = (int)(hs.abs_seq - hs.seg_base);
+  hs.gather_seq = hs.abs_seq;
+  hs.abs_seq++;
+  for (int r = 0; r < c->world; ++r) {
+    g.b[r] = hs.gather_b[r]; g.xa[r] = hs.gather_xa[r];
+    g.flag[r] = hs.mode == 2 && hs.peer_mail[r] ? hs.peer_mail[r]->gflag_ptr() : nullptr;
+  }
+  g.cnt = hs.flags + 4;
+  return g;
+}
+
+void fb_gather_wait(flipb200_ctx* c, PeerHalo* h) {
+  HaloState& hs = c->halo;
+  if (!hs.gather_on || hs.mode != 2) return;
+  h->mode = 2;
+  h->gat_flags = hs.mail->gflag_ptr();
+  h->gat_n = c->world; h->gat_self = c->rank;
+  h->gat_rel = (int)(hs.gather_seq - hs.seg_base);
+}
+
 // where a halo copy used to be: nothing to do with device flags; the in-process transport orders
 // producers and consumers with its host barrier
 int fb_halo_point(flipb200_ctx* c) {
@@ -531,7 +566,7 @@ int fb_halo_setup(flipb200_ctx* c) {
   if (c->world == 1 || !c->comm || c->mg_levels < 2 || c->mg_nd < 1) return 0;
   const char* e = getenv("FLIPB200_FUSED_HALO");
   if (e && e[0] == '0') return 0;
-  CK(cudaMalloc((void**)&hs.flags, 4 * sizeof(unsigned)));
+  CK(cudaMalloc((void**)&hs.flags, 8 * sizeof(unsigned)));   // [0,1] flags, [2,3] push counters, [4] gather counter
   {
     const char* de = getenv("FLIPB200_HALO_DEBUG");
     if (de && de[0] == '1' && !hs.dbg) {
@@ -539,7 +574,7 @@ int fb_halo_setup(flipb200_ctx* c) {
       CK(cudaMemset(hs.dbg, 0, 8 * HALO_DBG_MAX * sizeof(unsigned long long)));
     }
   }
-  CK(cudaMemsetAsync(hs.flags, 0, 4 * sizeof(unsigned), c->stream));
+  CK(cudaMemsetAsync(hs.flags, 0, 8 * sizeof(unsigned), c->stream));
   CK(cudaStreamSynchronize(c->stream));
   const int nd = c->mg_nd;
   // my exported pointers: flags, pd, then (xa, xb) of every distributed level
@@ -561,6 +596,15 @@ int fb_halo_setup(flipb200_ctx* c) {
       for (int l = 0; l < nd; ++l) { theirs[dir][m++] = o->mg[l].xa; theirs[dir][m++] = o->mg[l].xb; }
     }
     hs.mode = 1;                                     // flags unused: host barriers order the kernels
+    if (gather_wanted(c)) {
+      bool okg = true;
+      for (int r = 0; r < c->world; ++r) {
+        flipb200_ctx* o = lg->member[r];
+        if (!o || o->mg_nd != nd || o->mg_levels != c->mg_levels) { okg = false; break; }
+        hs.gather_b[r] = o->mg[nd].b; hs.gather_xa[r] = o->mg[nd].xa;
+      }
+      hs.gather_on = okg ? 1 : 0;
+    }
   } else {
     cudaIpcMemHandle_t hm[2 + 2 * MG_MAX_LEVELS], hd[2 + 2 * MG_MAX_LEVELS], hu[2 + 2 * MG_MAX_LEVELS];
     memset(hm, 0, sizeof(hm));
@@ -596,31 +640,51 @@ int fb_halo_setup(flipb200_ctx* c) {
     if (!(fr && fr[0] == '0') && c->world <= RED_MAXR) {
       CK(cudaMalloc((void**)&hs.mail, sizeof(RedMail)));
       CK(cudaMemsetAsync(hs.mail, 0, sizeof(RedMail), c->stream));
-      cudaIpcMemHandle_t mh; memset(&mh, 0, sizeof(mh));
-      int okm = cudaIpcGetMemHandle(&mh, hs.mail) == cudaSuccess ? 1 : 0;
-      cudaIpcMemHandle_t* dh = nullptr;
-      std::vector<cudaIpcMemHandle_t> all(c->world);
-      CK(cudaMalloc((void**)&dh, sizeof(mh) * c->world));
-      CK(cudaMemcpyAsync(dh + c->rank, &mh, sizeof(mh), cudaMemcpyHostToDevice, c->stream));
+      // every rank maps every rank's mailbox and -- for the all-gather by peer stores -- its (b, xa) of
+      // the first replicated level: three handles per rank travel in one grouped broadcast
+      const bool wantg = gather_wanted(c);
+      struct H3 { cudaIpcMemHandle_t h[3]; int ok[3]; };
+      H3 mh; memset(&mh, 0, sizeof(mh));
+      mh.ok[0] = cudaIpcGetMemHandle(&mh.h[0], hs.mail) == cudaSuccess ? 1 : 0;
+      if (wantg) {
+        mh.ok[1] = cudaIpcGetMemHandle(&mh.h[1], c->mg[nd].b) == cudaSuccess ? 1 : 0;
+        mh.ok[2] = cudaIpcGetMemHandle(&mh.h[2], c->mg[nd].xa) == cudaSuccess ? 1 : 0;
+      }
+      cudaGetLastError();
+      int okm = mh.ok[0], okg = wantg && mh.ok[1] && mh.ok[2] ? 1 : 0;
+      H3* dh = nullptr;
+      std::vector<H3> all(c->world);
+      CK(cudaMalloc((void**)&dh, sizeof(H3) * c->world));
+      CK(cudaMemcpyAsync(dh + c->rank, &mh, sizeof(H3), cudaMemcpyHostToDevice, c->stream));
       NC(g_nccl.GroupStart());
-      for (int r = 0; r < c->world; ++r) NC(g_nccl.Broadcast(dh + r, dh + r, sizeof(mh), ncclChar, r, c->comm->nc, c->stream));
+      for (int r = 0; r < c->world; ++r) NC(g_nccl.Broadcast(dh + r, dh + r, sizeof(H3), ncclChar, r, c->comm->nc, c->stream));
       NC(g_nccl.GroupEnd());
-      CK(cudaMemcpyAsync(all.data(), dh, sizeof(mh) * c->world, cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaMemcpyAsync(all.data(), dh, sizeof(H3) * c->world, cudaMemcpyDeviceToHost, c->stream));
       CK(cudaStreamSynchronize(c->stream));
       cudaFree(dh);
-      for (int r = 0; r < c->world && okm; ++r) {
-        if (r == c->rank) { hs.peer_mail[r] = hs.mail; continue; }
+      for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank) { hs.peer_mail[r] = hs.mail; hs.gather_b[r] = c->mg[nd].b; hs.gather_xa[r] = c->mg[nd].xa; continue; }
         void* p = nullptr;
-        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { okm = 0; cudaGetLastError(); }
-        hs.peer_mail[r] = (RedMail*)p;
+        if (okm) {
+          if (!all[r].ok[0] || cudaIpcOpenMemHandle(&p, all[r].h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { okm = 0; cudaGetLastError(); }
+          hs.peer_mail[r] = (RedMail*)p;
+        }
+        for (int a = 1; a <= 2 && okg; ++a) {
+          p = nullptr;
+          if (!all[r].ok[a] || cudaIpcOpenMemHandle(&p, all[r].h[a], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { okg = 0; cudaGetLastError(); }
+          if (a == 1) hs.gather_b[r] = (float*)p; else hs.gather_xa[r] = (float*)p;
+        }
       }
       int* flag2 = nullptr;
-      CK(cudaMalloc((void**)&flag2, sizeof(int)));
-      CK(cudaMemcpyAsync(flag2, &okm, sizeof(int), cudaMemcpyHostToDevice, c->stream));
-      NC(g_nccl.AllReduce(flag2, flag2, 1, ncclInt32, ncclMin, c->comm->nc, c->stream));
-      CK(cudaMemcpyAsync(&okm, flag2, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+      int both[2] = {okm, okm && okg ? 1 : 0};
+      CK(cudaMalloc((void**)&flag2, 2 * sizeof(int)));
+      CK(cudaMemcpyAsync(flag2, both, 2 * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+      NC(g_nccl.AllReduce(flag2, flag2, 2, ncclInt32, ncclMin, c->comm->nc, c->stream));
+      CK(cudaMemcpyAsync(both, flag2, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
       CK(cudaStreamSynchronize(c->stream));
       cudaFree(flag2);
+      okm = both[0];
+      hs.gather_on = both[1];
       hs.red_on = okm;
     }
   }

@@ -141,6 +141,11 @@ struct HaloState {
   struct RedMail* mail;              // own
   struct RedMail* peer_mail[16];     // [rank] (own included); null when the fused all-reduce is off
   int red_on;
+  // all-gather of the first replicated level by peer stores (halo.cuh GatherPush)
+  int gather_on;
+  float* gather_b[16];               // [rank] that rank's b / xa array of level mg_nd
+  float* gather_xa[16];
+  long long gather_seq;              // sequence number of the latest gather
 };
 
 struct flipb200_ctx {

@@ -28,6 +28,8 @@
 #include "sweep.cuh"
 #include <string.h>
 
+#define RED_MAXR 16   // ranks the peer-mapped mailboxes / gather tables are sized for
+
 struct PeerHalo {
   int mode;
   int kdn, kup;              // planes (sweep index space) whose blocks are the boundary blocks: first / last owned
@@ -43,6 +45,10 @@ struct PeerHalo {
   unsigned* sig_up;          // upper neighbour's my_flags[0]
   unsigned* cnt;             // [2] block counters (own memory)
   unsigned long long* dbg;   // FLIPB200_HALO_DEBUG=1: timestamps of this launch's boundary blocks (8 per launch)
+  // consumer of the first replicated level: EVERY block waits until every rank's restriction has
+  // pushed its planes (GatherPush below): gat_flags[r] >= halo_base + gat_rel for r != gat_self
+  const unsigned* gat_flags;
+  int gat_n, gat_self, gat_rel;
 };
 __device__ __forceinline__ unsigned long long halo_now() {
   unsigned long long t;
@@ -80,6 +86,17 @@ __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
 // bdn / bup: this block reads the ghost plane below kdn / above kup.
 __device__ __forceinline__ void halo_wait(const PeerHalo& H, DevScalars* ds, bool bdn, bool bup) {
   if (H.mode != 2) return;
+  if (H.gat_n) {                                     // block-uniform
+    const int t = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+    if (t < H.gat_n && t != H.gat_self) {
+      const unsigned need = (unsigned)ds->halo_base + (unsigned)H.gat_rel;
+      const long long t0 = clock64();
+      while ((int)(ld_relaxed_sys(&H.gat_flags[t]) - need) < 0)
+        if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
+      fence_acq_rel_gpu();
+    }
+    __syncthreads();
+  }
   const bool w0 = bdn && H.wait_dn, w1 = bup && H.wait_up;
   if (!(w0 || w1)) return;
   const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
@@ -154,6 +171,51 @@ __device__ __forceinline__ void halo_signal(const PeerHalo& H, DevScalars* ds, b
   }
 }
 
+// ---- all-gather of the first replicated multigrid level by peer stores ----------------------------
+// The restriction that feeds the first replicated level writes its planes of (b, xa) into EVERY
+// rank's copy of the level (same layout everywhere), so no collective launch is needed: an NCCL
+// all-gather of those two small arrays costs 26 us (2 GPUs) to 41 us (8 GPUs) of launch latency per
+// V-cycle.  Every block pushes; the last block to finish fences once at system scope and stores the
+// sequence number into slot [rank] of every rank's gflag array (in the mailbox allocation, which
+// every rank has mapped).  Write-after-read: a rank reaches the next restriction only after the
+// r.z exchange of this iteration, which every rank enters after its last reader of the level.
+struct GatherPush {
+  int on, mode, rank, world;
+  int srel;                          // sequence number = ds->halo_base + srel
+  int nblocks;                       // blocks of the launch (all of them push)
+  float* b[RED_MAXR];                // [rank] level arrays (own entries unused)
+  float* xa[RED_MAXR];
+  unsigned* flag[RED_MAXR];          // [rank] -> that rank's gflag array
+  unsigned* cnt;                     // block counter (own memory)
+};
+static inline GatherPush gather_off() { GatherPush g; memset(&g, 0, sizeof(g)); return g; }
+__device__ __forceinline__ void gather_push1(const GatherPush& G, int q, float r, float x1) {
+  if (!G.on) return;
+  for (int p = 0; p < G.world; ++p)
+    if (p != G.rank) { G.b[p][q] = r; G.xa[p][q] = x1; }
+}
+__device__ __forceinline__ void gather_push2(const GatherPush& G, int q, float r0, float r1, float x0, float x1) {
+  if (!G.on) return;
+  for (int p = 0; p < G.world; ++p)
+    if (p != G.rank) { st2<float>(G.b[p] + q, r0, r1); st2<float>(G.xa[p] + q, x0, x1); }
+}
+// by ALL threads of EVERY block, at the end of the kernel
+__device__ __forceinline__ void gather_signal(const GatherPush& G, DevScalars* ds) {
+  if (!G.on || G.mode != 2) return;
+  __syncthreads();
+  const int tid = threadIdx.x + blockDim.x * (threadIdx.y + blockDim.y * threadIdx.z);
+  if (tid == 0) {
+    fence_acq_rel_gpu();
+    if (atomicAdd(G.cnt, 1u) == (unsigned)G.nblocks - 1u) {
+      *G.cnt = 0u;
+      fence_acq_rel_sys();                                     // cumulative over the block counter: every block's stores
+      const unsigned seq = (unsigned)ds->halo_base + (unsigned)G.srel;
+      for (int p = 0; p < G.world; ++p)
+        if (p != G.rank) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(G.flag[p] + G.rank), "r"(seq) : "memory");
+    }
+  }
+}
+
 // ---- all-reduce of a dot product over peer memory ------------------------------------------------
 // Blocks add their partial sums into ds->part[id] as on one GPU.  One 32-thread kernel
 // (k_pcg_exchange, pcg.cu) then does the whole all-reduce: lane r stores this rank's sum into slot
@@ -169,9 +231,11 @@ __device__ __forceinline__ void halo_signal(const PeerHalo& H, DevScalars* ds, b
 // products of the iteration depend on it).
 // (Publishing from the last block of the producing kernel was tried first: the per-block
 // fence + returning atomic made k_update_xr / k_spmv 5 % slower, a net loss.)
-#define RED_MAXR 16
 struct RedMail {
   unsigned long long w[4][2][RED_MAXR][2];   // [PART_* id][seq parity][source rank][lo, hi]: value half | seq << 32
+  unsigned gflag[RED_MAXR];                  // all-gather by peer stores (GatherPush): [source rank] = sequence number
+  // address of gflag through a (possibly peer-mapped) mailbox pointer, computed on the host
+  unsigned* gflag_ptr() { return reinterpret_cast<unsigned*>(reinterpret_cast<char*>(this) + sizeof(w)); }
 };
 struct RedPub {
   int on, rank, world;
@@ -182,5 +246,7 @@ RedPub fb_red_make(flipb200_ctx* c);   // comm.cu
 
 // host (comm.cu): describe one launch as consumer of (lin, ain) and/or producer of (lout, aout)
 PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, size_t elem_out, int kdn, int kup, int nb);
+GatherPush fb_gather_make(flipb200_ctx* c, int nblocks);   // takes a sequence number
+void fb_gather_wait(flipb200_ctx* c, PeerHalo* h);         // consumer of the latest gather
 
 static inline PeerHalo halo_off() { PeerHalo h; memset(&h, 0, sizeof(h)); return h; }

@@ -444,7 +444,8 @@ k_mg_resid4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
 __global__ void __launch_bounds__(256)
 k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
               const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
-              DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H) {
+              DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H,
+              const __grid_constant__ GatherPush G) {
   if (ds->pcg_done) return;
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
@@ -505,11 +506,13 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
         bc[qc] = r;
         x1c[qc] = x1;
         halo_push1<float>(H, qc, K, x1);
+        gather_push1(G, qc, r, x1);
       }
       sm1 = s1; s0 = s2;
     }
   }
   halo_signal(H, ds, bdn, bup);
+  gather_signal(G, ds);
 }
 
 // Two coarse cells (four fine children per row, one float4) per lane; used when the coarse rows are
@@ -517,7 +520,8 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
 __global__ void __launch_bounds__(256)
 k_mg_restrict4(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
                const float* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
-               DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H) {
+               DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H,
+               const __grid_constant__ GatherPush G) {
   if (ds->pcg_done) return;
   const int lane = threadIdx.x;
   const int I = (cbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;         // cells I, I + 1
@@ -577,11 +581,19 @@ k_mg_restrict4(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* 
         st2<float>(bc + qc, r0, r1);
         st2<float>(x1c + qc, y0, y1);
         halo_push2<float>(H, qc, K, y0, y1);
+        gather_push2(G, qc, r0, r1, y0, y1);
       }
       sm1 = s1; s0 = s2;
     }
   }
   halo_signal(H, ds, bdn, bup);
+  gather_signal(G, ds);
+}
+
+// a rank with nothing to restrict into the first replicated level still has to announce that
+__global__ void k_mg_gather_signal(DevScalars* __restrict__ ds, const __grid_constant__ GatherPush G) {
+  if (ds->pcg_done) return;
+  gather_signal(G, ds);
 }
 
 // prolongation + correction  x_f[i] += (sum_I w64(i,I) e_c[I]) / n64_i   (e_c is 0 off the fluid cells).
@@ -997,16 +1009,19 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   if (sweep_empty(S[0])) return 0;
   const size_t F = sizeof(float);
   const int t0 = c->mg_tail0;
+  bool gathered = false;                            // the level below was assembled by peer stores: its first reader waits for them
   for (int l = 0; l < t0; ++l) {
     MgLevel& L = c->mg[l];
     MgLevel& C = c->mg[l + 1];
     const dim3 tg = w4[l] ? stencil_grid(S4[l], 4) : stencil_grid(S[l]);
     const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;
     HALO(L, L.xa);
-    if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
-                                                                        fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
-    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
-                                                                 fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
+    {
+      PeerHalo Hs = fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs);
+      if (gathered) { fb_gather_wait(c, &Hs); gathered = false; }
+      if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
+      else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
+    }
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
     if (w4[l]) k_mg_resid4<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
@@ -1028,16 +1043,20 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
       const int zc = mg_zchunk("FLIPB200_RS_ZC", cg.x * cg.y, cb.z1 - cb.z0, r4 ? 512 : 1024);
       cg.z = max(1, cdiv(cb.z1 - cb.z0, zc));
       PeerHalo H = fb_halo_make(c, l, HA_XA, C.dist ? l + 1 : -1, C.dist ? HA_XA : -1, F, ck0, ck1, cg.x * cg.y);
-      if (cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0) {
-        if (r4) k_mg_restrict4<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H);
-        else k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H);
-      }
+      const bool some = cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0;
+      // the restriction into the first replicated level pushes its planes to every rank (halo.cuh GatherPush)
+      gathered = L.dist && !C.dist && c->halo.gather_on;
+      const GatherPush G = gathered ? fb_gather_make(c, some ? cg.x * cg.y * cg.z : 1) : gather_off();
+      if (some) {
+        if (r4) k_mg_restrict4<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
+        else k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
+      } else if (gathered && G.mode == 2) k_mg_gather_signal<<<1, 32, 0, c->stream>>>(c->ds, G);
     }
     fb_prof(c, l == 0 ? "L0 halo+restrict" : (l == 1 ? "L1 halo+restrict" : "L2+ halo+restrict"));
     if (L.dist && !C.dist) {
-      int rc = fb_allgather_planes2(c, C.g, C.b, C.xa, sizeof(float), C.zs);
+      int rc = gathered ? fb_halo_point(c) : fb_allgather_planes2(c, C.g, C.b, C.xa, sizeof(float), C.zs);
       if (rc) return rc;
-      fb_prof(c, "allgather b, xa");
+      fb_prof(c, gathered ? "gather b, xa (peer stores)" : "allgather b, xa");
     }
     c->launches += 3;
   }

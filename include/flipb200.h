@@ -111,7 +111,8 @@ int  flipb200_get_particle_ids(flipb200_ctx*, uint32_t* ids, int64_t cap);   /* 
  * 1 = pushed by the producing kernels + host barrier (in-process ranks), 2 = pushed over NVLink peer
  * mappings with device-side flags (one process per GPU; csrc/halo.cuh) */
 int  flipb200_halo_mode(flipb200_ctx*);
-/* diagnostics: out8 = { halo mode, iteration graph active, multigrid levels, distributed levels,
+/* diagnostics: out8 = { halo mode (+10: dot products exchanged over peer mailboxes, +20: first replicated
+ * multigrid level gathered by peer stores), iteration graph active, multigrid levels, distributed levels,
  * kernels per PCG iteration, ghost-pushing kernels per iteration, rank, world } */
 int  flipb200_debug_info(flipb200_ctx*, int32_t* out8);
 /* flipb200_step_host for a slab (collective): the rank uploads ITS n particles (every base plane

@@ -146,6 +146,11 @@ def test_slab_multigrid_levels(fb, scenes, nd):
         assert st.passes == st1.passes and st.n_fluid == st1.n_fluid
         assert abs(st.pcg_iters_total - st1.pcg_iters_total) <= st1.passes, (st.pcg_iters_total, st1.pcg_iters_total)
     assert rel_l2(gather_grid(fs, fb.GRID_P), f1.get_grid(fb.GRID_P)) < 1e-8
+    # nd = 1: level 1 (24^3) is the first replicated level and has its own kernels, so the restriction
+    # into it pushes its planes to every rank (+20); nd = 2: level 2 sits in the one-block tail, the
+    # all-gather stays a collective copy
+    for f in fs:
+        assert (f.debug_info()["halo_mode"] >= 20) == (nd == 1), f.debug_info()
     for f in fs + [f1]:
         f.close()
 
