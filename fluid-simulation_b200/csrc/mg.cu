@@ -450,7 +450,7 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
+  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
   const bool bdn = K0 <= H.kdn && H.kdn < K1, bup = K0 <= H.kup && H.kup < K1;
   halo_wait(H, ds, bdn, bup);                       // boundary coarse planes read the fine ghost planes
   if (J < cbox.y1) {                                // whole warp
@@ -526,7 +526,7 @@ k_mg_restrict4(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* 
   const int lane = threadIdx.x;
   const int I = (cbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;         // cells I, I + 1
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
+  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
   const bool bdn = K0 <= H.kdn && H.kdn < K1, bup = K0 <= H.kup && H.kup < K1;
   halo_wait(H, ds, bdn, bup);
   if (J < cbox.y1) {                                // whole warp
@@ -609,7 +609,7 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
+  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
   const bool bdn = k0c <= H.kdn && H.kdn < k1c, bup = k0c <= H.kup && H.kup < k1c;
   halo_wait(H, ds, bdn, bup);                       // boundary fine planes read the coarse ghost planes
   if (j < fbox.y1) {                                // whole warp
@@ -685,7 +685,7 @@ k_mg_prolong4(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const 
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~3) + blockIdx.x * 128 + 4 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
+  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
   const bool bdn = k0c <= H.kdn && H.kdn < k1c, bup = k0c <= H.kup && H.kup < k1c;
   halo_wait(H, ds, bdn, bup);
   if (j < fbox.y1) {                                // whole warp
@@ -1007,6 +1007,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     mc[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA1); mc2[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA2);
   }
   if (sweep_empty(S[0])) return 0;
+  // Sweep directions on a single GPU (sweep.cuh ZP_DOWN): k_spmv up, k_update_xr down, pre-smooth up,
+  // residual down, restrict up | prolong up, post-smooth 1 down, post-smooth 2 up, k_update_p down.
   const size_t F = sizeof(float);
   const int t0 = c->mg_tail0;
   bool gathered = false;                            // the level below was assembled by peer stores: its first reader waits for them
@@ -1024,9 +1026,9 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
-    if (w4[l]) k_mg_resid4<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
+    if (w4[l]) k_mg_resid4<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
                                                                 fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
-    else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
+    else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
                                                          fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+resid" : (l == 1 ? "L1 halo+resid" : "L2+ halo+resid"));
     HALO(L, L.xa);
@@ -1102,9 +1104,9 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
-    if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+    if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
                                                                         fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
-    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
                                                                  fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
     HALO(L, L.xa);

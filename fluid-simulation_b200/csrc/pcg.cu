@@ -380,7 +380,7 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   }
   fb_prof(c, "allreduce pAp");
   if (use_mg) {
-    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
+    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     fb_prof(c, "k_update_xr");
     if (dist && (rc = reduce_dot(c, PART_RR, it_arg, noexit))) return rc;
@@ -388,10 +388,10 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     fb_prof(c, "allreduce rr");
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit,
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
   } else {
-    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit, dist, halo_off());
+    k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit, dist, halo_off());
     if (dist) {
       if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 2, FB_F64, FB_SUM))) return rc;   // r.z and r.r are adjacent
       fb_pcg_publish(c, (1 << PART_RZ) | (1 << PART_RR), it_arg);

@@ -37,8 +37,11 @@ struct Sweep {
   Grid g;
   Box box;
   int xe;        // exclusive x limit for lanes (even, <= px)
-  int zp;        // boundary-first block order (zperm): set for z-slab runs
+  int zp;        // block order in z (zperm): 0 ascending, 1 boundary chunks first (z-slab runs), 2 descending
 };
+#define ZP_UP 0
+#define ZP_EDGE 1
+#define ZP_DOWN 2
 // W = x-nodes per lane (2, or 4 for the fp32 STENCIL4 shape): the lane range is aligned to W
 static inline Sweep make_sweep(const Grid& g, const Box& b, int W = 2) {
   Sweep s; s.g = g; s.box = b; s.zp = (g.k0 > 0) ? 1 : 0;   // slabs have ghost planes below k0
@@ -62,9 +65,19 @@ static inline dim3 stencil_grid(const Sweep& s, int W = 2) {
 // Block z index -> plane (chunk) index: the first and the last chunk of the sweep are issued FIRST.
 // z-slab runs push those boundary planes to the neighbours (halo.cuh); doing them at the start of
 // the kernel hides the NVLink signalling latency behind the interior of the sweep.
-// Only z-slab runs use it (Sweep::zp / the PeerHalo mode): on a single GPU the permuted order measured
-// 13 % slower for k_update_xr (176 vs 156 us at 256^3), the plain order is kept there.
-__device__ __forceinline__ int zperm(int bz, int nz, int on) { return !on ? bz : (bz == 0 ? 0 : (bz == 1 ? nz - 1 : bz - 1)); }
+// Only z-slab runs use it (Sweep::zp / the PeerHalo mode).
+// ZP_DOWN issues the chunks from the top: on a single GPU consecutive sweeps of the PCG iteration
+// alternate their direction (sweep_down() below), so each one starts on the planes the previous
+// sweep left in the 126 MB L2 (a 256^3 level-0 sweep streams 150-950 MB).
+__device__ __forceinline__ int zperm(int bz, int nz, int on) {
+  return on == ZP_UP ? bz : (on == ZP_DOWN ? nz - 1 - bz : (bz == 0 ? 0 : (bz == 1 ? nz - 1 : bz - 1)));
+}
+// the same sweep issued from the top (no-op for z-slab sweeps and with FLIPB200_ZIGZAG=0)
+static inline Sweep sweep_down(Sweep s) {
+  static const bool on = [] { const char* e = getenv("FLIPB200_ZIGZAG"); return !(e && e[0] == '0'); }();
+  if (on && s.zp == ZP_UP) s.zp = ZP_DOWN;
+  return s;
+}
 
 // STREAM prologue: i (even x of this lane), j, k, q and `act`
 #define STREAM_PROLOGUE(S)                                                      \
