@@ -72,7 +72,7 @@ struct DevScalars {
   int pcg_max_iter;                  // iteration limit of the current solve
   int pcg_it;                        // current iteration (kernels launched from a CUDA graph read it here)
   int n_invalid;                     // particles whose support lies outside the box
-  int pad;
+  int x_pending;                     // the stop test fired before k_update_p<1> applied x += alpha p (k_pcg_finish_x)
   // z-slab runs: kernels accumulate this rank's share of the current dot products here; after the
   // all-reduce k_pcg_publish moves the sum into the ring slot (single GPU: straight into the ring)
   double part[4];                    // [0] p.Ap  [1] r.z  [2] r.r

@@ -32,7 +32,6 @@
 
 struct PeerHalo {
   int mode;
-  int down;                  // single GPU (mode 0): the restrict / prolong kernels issue their chunks from the top (sweep.cuh ZP_DOWN)
   int kdn, kup;              // planes (sweep index space) whose blocks are the boundary blocks: first / last owned
   int wait_dn, wait_up;      // consumer side: wait for the lower / upper neighbour's producer
   int push_dn, push_up;      // producer side: push + signal to the lower / upper neighbour

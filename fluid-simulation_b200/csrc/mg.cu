@@ -262,8 +262,12 @@ int fb_mg_setup(flipb200_ctx* c, double dt) {
 
 // ---- V-cycle kernels (fp32) --------------------------------------------------------------------
 // damped-Jacobi sweep  xo = xi + w D^-1 (b - A xi)   (STENCIL shape).
-// DOT (last sweep of level 0): also rz[it&3] += sum r64 * xo / sc  -- the CG's r.z in fp64.
-template <bool DOT>
+// DOT (last sweep of level 0): also the CG's r.z, accumulated in fp64:
+//   DOT 2 (default): rz[it&3] += sum b * xo / sc^2 -- r taken as b / sc, the fp32 right-hand side this
+//          sweep reads anyway (z = M b exactly, so b.z is the inner product M defines; the 6e-8
+//          rounding of r only perturbs alpha and beta, x and r stay consistent: same iteration counts);
+//   DOT 1 (FLIPB200_RZ64=1): rz[it&3] += sum r64 * xo / sc, 8 more bytes per node.
+template <int DOT>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
             const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
@@ -289,13 +293,14 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
       if (m.act) {
         f = *reinterpret_cast<const uchar2*>(fl + m.q);
         bv = ld2<float>(b + m.q);
-        if (DOT) rv = ld2<double>(r64 + m.q);
+        if (DOT == 1) rv = ld2<double>(r64 + m.q);
       }
       float o0 = 0.f, o1 = 0.f;
       if (f.x & FB_FLUID) { int kk = 6 - __popc(f.x & FB_SMASK); o0 = m.c0() + mc.winv[kk] * (bv.x - mc.h2inv * ((float)kk * m.c0() - m.sum0())); }
       if (f.y & FB_FLUID) { int kk = 6 - __popc(f.y & FB_SMASK); o1 = m.c1() + mc.winv[kk] * (bv.y - mc.h2inv * ((float)kk * m.c1() - m.sum1())); }
       if (m.act) { st2<float>(xo + m.q, o0, o1); halo_push2<float>(H, m.q, m.k, o0, o1); }
-      if (DOT) acc[0] += rv.x * (double)o0 + rv.y * (double)o1;
+      if (DOT == 1) acc[0] += rv.x * (double)o0 + rv.y * (double)o1;
+      if (DOT == 2) acc[0] += (double)bv.x * (double)o0 + (double)bv.y * (double)o1;
       m.advance(S);
     }
   }
@@ -304,7 +309,7 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
       const double rrp = ds->rr[(it + 3) & 3];
-      atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[0] * (rrp > 0.0 ? sqrt(rrp) : 1.0));
+      atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[0] * (rrp > 0.0 ? (DOT == 2 ? rrp : sqrt(rrp)) : 1.0));
     }
   }
 }
@@ -353,7 +358,7 @@ __device__ __forceinline__ float resid_node(const MgCoef& mc, uint32_t f, uint32
   const int kk = 6 - __popc(f & FB_SMASK);
   return (b - mc.h2inv * ((float)kk * c - sum)) * (64.f / (float)nn);
 }
-template <bool DOT>
+template <int DOT>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
              const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
@@ -379,7 +384,7 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
       if (m.act) {
         f = *reinterpret_cast<const uint32_t*>(fl + m.q);
         bv = *reinterpret_cast<const float4*>(b + m.q);
-        if (DOT) { ra = ld2<double>(r64 + m.q); rb = ld2<double>(r64 + m.q + 2); }
+        if (DOT == 1) { ra = ld2<double>(r64 + m.q); rb = ld2<double>(r64 + m.q + 2); }
       }
       float4 o;
       o.x = smooth_node(mc, f & 0xffu, m.pc.x, bv.x, m.sum0());
@@ -387,7 +392,8 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
       o.z = smooth_node(mc, (f >> 16) & 0xffu, m.pc.z, bv.z, m.sum2());
       o.w = smooth_node(mc, f >> 24, m.pc.w, bv.w, m.sum3());
       if (m.act) { *reinterpret_cast<float4*>(xo + m.q) = o; halo_push4(H, m.q, m.k, o); }
-      if (DOT) acc[0] += (ra.x * (double)o.x + ra.y * (double)o.y) + (rb.x * (double)o.z + rb.y * (double)o.w);
+      if (DOT == 1) acc[0] += (ra.x * (double)o.x + ra.y * (double)o.y) + (rb.x * (double)o.z + rb.y * (double)o.w);
+      if (DOT == 2) acc[0] += ((double)bv.x * (double)o.x + (double)bv.y * (double)o.y) + ((double)bv.z * (double)o.z + (double)bv.w * (double)o.w);
       m.advance(S);
     }
   }
@@ -396,7 +402,7 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
       const double rrp = ds->rr[(it + 3) & 3];
-      atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[0] * (rrp > 0.0 ? sqrt(rrp) : 1.0));
+      atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[it & 3], acc[0] * (rrp > 0.0 ? (DOT == 2 ? rrp : sqrt(rrp)) : 1.0));
     }
   }
 }
@@ -450,7 +456,7 @@ k_mg_restrict(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* _
   const int lane = threadIdx.x;
   const int I = cbox.x0 + blockIdx.x * 32 + lane;
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
+  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : ZP_UP) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
   const bool bdn = K0 <= H.kdn && H.kdn < K1, bup = K0 <= H.kup && H.kup < K1;
   halo_wait(H, ds, bdn, bup);                       // boundary coarse planes read the fine ghost planes
   if (J < cbox.y1) {                                // whole warp
@@ -526,7 +532,7 @@ k_mg_restrict4(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* 
   const int lane = threadIdx.x;
   const int I = (cbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;         // cells I, I + 1
   const int J = cbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
+  const int K0 = cbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : ZP_UP) * RS_ZC, K1 = min(K0 + RS_ZC, cbox.z1);
   const bool bdn = K0 <= H.kdn && H.kdn < K1, bup = K0 <= H.kup && H.kup < K1;
   halo_wait(H, ds, bdn, bup);
   if (J < cbox.y1) {                                // whole warp
@@ -609,7 +615,7 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~1) + blockIdx.x * 64 + 2 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
+  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : ZP_UP) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
   const bool bdn = k0c <= H.kdn && H.kdn < k1c, bup = k0c <= H.kup && H.kup < k1c;
   halo_wait(H, ds, bdn, bup);                       // boundary fine planes read the coarse ghost planes
   if (j < fbox.y1) {                                // whole warp
@@ -685,7 +691,7 @@ k_mg_prolong4(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const 
   const int lane = threadIdx.x;
   const int i = (fbox.x0 & ~3) + blockIdx.x * 128 + 4 * lane;
   const int j = fbox.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : H.down) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
+  const int k0c = fbox.z0 + zperm(blockIdx.z, gridDim.z, H.mode ? ZP_EDGE : ZP_UP) * PR_ZC, k1c = min(k0c + PR_ZC, fbox.z1);
   const bool bdn = k0c <= H.kdn && H.kdn < k1c, bup = k0c <= H.kup && H.kup < k1c;
   halo_wait(H, ds, bdn, bup);
   if (j < fbox.y1) {                                // whole warp
@@ -1000,6 +1006,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   Sweep S4[MG_MAX_LEVELS];
   bool w4[MG_MAX_LEVELS];
   const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
+  const bool rz64 = [] { const char* e = getenv("FLIPB200_RZ64"); return e && e[0] == '1'; }();
   for (int l = 0; l < nl; ++l) {
     S[l] = make_sweep(c->mg[l].g, c->mg[l].box);
     S4[l] = make_sweep(c->mg[l].g, c->mg[l].box, 4);
@@ -1021,8 +1028,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     {
       PeerHalo Hs = fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs);
       if (gathered) { fb_gather_wait(c, &Hs); gathered = false; }
-      if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
-      else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
+      if (w4[l]) k_mg_smooth4<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
+      else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
     }
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
@@ -1104,20 +1111,23 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
-    if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+    if (w4[l]) k_mg_smooth4<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
                                                                         fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
-    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
+    else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
                                                                  fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
     HALO(L, L.xa);
     // the last sweep's output is read through ghosts only as the coarse correction of the level above
-    if (l == 0 && w4[l]) k_mg_smooth4<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
-                                                                                 fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
-    else if (l == 0) k_mg_smooth<true><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist,
-                                                                            fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs));
-    else if (w4[l]) k_mg_smooth4<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+    if (l == 0) {
+      const PeerHalo Hd = fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs);
+      if (w4[l] && rz64) k_mg_smooth4<1><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
+      else if (w4[l]) k_mg_smooth4<2><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
+      else if (rz64) k_mg_smooth<1><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
+      else k_mg_smooth<2><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
+    }
+    else if (w4[l]) k_mg_smooth4<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
                                                                              fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
-    else k_mg_smooth<false><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
+    else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
                                                                  fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 2)" : (l == 1 ? "L1 halo+smooth (post 2)" : "L2+ halo+smooth (post 2)"));
     c->launches += 3;

@@ -27,7 +27,7 @@ __global__ void k_pcg_reset(DevScalars* ds, double bnorm2, double threshold, int
   for (int s = 0; s < 4; ++s) { ds->pAp[s] = 0.0; ds->rz[s] = 0.0; ds->rr[s] = 0.0; }
   // |r|^2 of "iteration -1" (= |b|^2): scale of the first preconditioner applications
   ds->rr[2] = bnorm2; ds->rr[3] = bnorm2;
-  ds->pcg_done = 0; ds->pcg_iters = 0; ds->pcg_status = 0; ds->rr_final = 0.0; ds->pcg_it = 0;
+  ds->pcg_done = 0; ds->pcg_iters = 0; ds->pcg_status = 0; ds->rr_final = 0.0; ds->pcg_it = 0; ds->x_pending = 0;
   for (int s = 0; s < 4; ++s) ds->part[s] = 0.0;
 }
 
@@ -150,7 +150,9 @@ static void launch_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noex
 
 // K2: alpha = rz_old / pAp;  x += alpha p;  r -= alpha Ap;  rr = |r|^2
 //     MODE 0 (Jacobi): rz = r.M^-1 r.   MODE 1 (MG): b0 = float(r*sc), x1 = w D^-1 b0 with
-//     sc = 1/|r_prev| so that the fp32 V-cycle works on O(1) numbers whatever |r| has become.
+//     sc = 1/|r_prev| so that the fp32 V-cycle works on O(1) numbers whatever |r| has become;
+//     x += alpha p is left to k_update_p<1> of the same iteration, which reads p anyway (8 B/node
+//     less); when the stop test ends the solve in between, k_pcg_finish_x applies it.
 template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
@@ -176,13 +178,15 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
   double acc[2] = {0.0, 0.0};
   if (act) {
     uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
-    double2 xv = ld2<double>(x + q), rv = ld2<double>(r + q), pv = ld2<double>(p + q), av = ld2<double>(Ap + q);
+    double2 rv = ld2<double>(r + q), av = ld2<double>(Ap + q);
+    double2 xv = zero2<double>(), pv = zero2<double>();
+    if (MODE == 0) { xv = ld2<double>(x + q); pv = ld2<double>(p + q); }
     const bool f0 = f.x & FB_FLUID, f1 = f.y & FB_FLUID;
     int k0 = 6 - __popc(f.x & FB_SMASK), k1 = 6 - __popc(f.y & FB_SMASK);
     double r0 = 0.0, r1 = 0.0;
     if (f0) { xv.x += alpha * pv.x; r0 = rv.x - alpha * av.x; }      // :73-74
     if (f1) { xv.y += alpha * pv.y; r1 = rv.y - alpha * av.y; }
-    if (f0 | f1) { st2<double>(x + q, xv.x, xv.y); st2<double>(r + q, r0, r1); }
+    if (f0 | f1) { if (MODE == 0) st2<double>(x + q, xv.x, xv.y); st2<double>(r + q, r0, r1); }
     acc[0] = r0 * r0 + r1 * r1;                                        // :76
     if (MODE == 0) acc[1] = r0 * (r0 * cf.inv[k0]) + r1 * (r1 * cf.inv[k1]);   // :80,83
     else {
@@ -200,12 +204,65 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
   if (MODE == 1) halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
+// k_update_xr<1> with FOUR nodes per lane (block = 8 rows x 128 nodes).  Once x += alpha p had moved
+// to k_update_p the two-node shape had too few bytes in flight: 120 us = 0.70 of the copy rate for
+// 33 B/node at 256^3.  Same arithmetic per node: identical bits.
+__global__ void __launch_bounds__(32 * SW_BY)
+k_update_xr4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+             double* __restrict__ r, const double* __restrict__ Ap, float* __restrict__ b0, float* __restrict__ x1,
+             DevScalars* __restrict__ ds, int it_arg, int noexit, int dist, const __grid_constant__ PeerHalo H) {
+  __shared__ double sm[32];
+  if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
+  const double pAp = ds->pAp[it & 3];
+  const double rz_old = ds->rz[(it + 3) & 3];
+  if (!noexit && !(pAp > 0.0)) {   // breakdown (also catches NaN)
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0) {
+      ds->pcg_status = FLIPB200_ERR_BREAKDOWN; ds->pcg_done = 1; ds->pcg_iters = it;
+      ds->rr_final = ds->rr[(it + 3) & 3];
+    }
+    return;
+  }
+  const double alpha = rz_old / pAp;                   // ConjugateGradient.h:72
+  const double rrp = ds->rr[(it + 3) & 3];
+  const double sc = rrp > 0.0 ? rsqrt(rrp) : 1.0;
+  const int i = S.box.x0 + blockIdx.x * 128 + 4 * threadIdx.x;
+  const int j = S.box.y0 + blockIdx.y * SW_BY + threadIdx.y;
+  const int k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp);
+  const bool act = i < S.xe && j < S.box.y1;
+  const int q = gidx(S.g, i, j, k);
+  double acc[1] = {0.0};
+  if (act) {
+    const uint32_t f = *reinterpret_cast<const uint32_t*>(fl + q);
+    const double2 ra = ld2<double>(r + q), rb = ld2<double>(r + q + 2);
+    const double2 aa = ld2<double>(Ap + q), ab = ld2<double>(Ap + q + 2);
+    const uint32_t fa = f & 0xffu, fb = (f >> 8) & 0xffu, fc = (f >> 16) & 0xffu, fd = f >> 24;
+    const double r0 = (fa & FB_FLUID) ? ra.x - alpha * aa.x : 0.0;      // :74
+    const double r1 = (fb & FB_FLUID) ? ra.y - alpha * aa.y : 0.0;
+    const double r2 = (fc & FB_FLUID) ? rb.x - alpha * ab.x : 0.0;
+    const double r3 = (fd & FB_FLUID) ? rb.y - alpha * ab.y : 0.0;
+    if ((fa | fb) & FB_FLUID) st2<double>(r + q, r0, r1);
+    if ((fc | fd) & FB_FLUID) st2<double>(r + q + 2, r2, r3);
+    acc[0] = (r0 * r0 + r1 * r1) + (r2 * r2 + r3 * r3);                 // :76
+    float4 s, y;
+    s.x = (float)(r0 * sc); s.y = (float)(r1 * sc); s.z = (float)(r2 * sc); s.w = (float)(r3 * sc);
+    y.x = cf.winv[6 - __popc(fa & FB_SMASK)] * s.x; y.y = cf.winv[6 - __popc(fb & FB_SMASK)] * s.y;
+    y.z = cf.winv[6 - __popc(fc & FB_SMASK)] * s.z; y.w = cf.winv[6 - __popc(fd & FB_SMASK)] * s.w;
+    *reinterpret_cast<float4*>(b0 + q) = s;
+    *reinterpret_cast<float4*>(x1 + q) = y;
+    halo_push4(H, q, k, y);
+  }
+  block_sum<1>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RR] : &ds->rr[it & 3], acc[0]);
+  halo_signal(H, ds, k == H.kdn, k == H.kup);
+}
+
 // stop test of ConjugateGradient.h:77-78 (MG path: evaluated before the preconditioner is applied)
 __global__ void k_pcg_check(DevScalars* __restrict__ ds, int it_arg) {
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   const double rr = ds->rr[it & 3];
-  if (rr < ds->threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; }
+  if (rr < ds->threshold) { ds->pcg_done = 1; ds->pcg_iters = it; ds->rr_final = rr; ds->x_pending = 1; }
 }
 
 // z-slab runs: after the all-reduce of ds->part[], move the global sums into the ring slot of this
@@ -278,7 +335,7 @@ void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg) {
 template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
-           const double* __restrict__ r, const float* __restrict__ zf, double* __restrict__ p,
+           const double* __restrict__ r, const float* __restrict__ zf, double* __restrict__ p, double* __restrict__ x,
            DevScalars* __restrict__ ds, int it_arg, int noexit, const __grid_constant__ PeerHalo H) {
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
@@ -292,10 +349,17 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   const double beta = first ? 0.0 : ds->rz[it & 3] / ds->rz[(it + 3) & 3];
   const double rrp = ds->rr[(it + 3) & 3];
   const double invsc = MODE == 1 ? (rrp > 0.0 ? sqrt(rrp) : 1.0) : 0.0;
+  const double alpha = (MODE == 1 && !first) ? ds->rz[(it + 3) & 3] / ds->pAp[it & 3] : 0.0;   // as in k_update_xr of this iteration
   STREAM_PROLOGUE(S)
   if (act) {
     uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
     double2 pv = ld2<double>(p + q);
+    if (MODE == 1 && !first) {                       // x += alpha p with the old direction (ConjugateGradient.h:73)
+      double2 xv = ld2<double>(x + q);
+      if (f.x & FB_FLUID) xv.x += alpha * pv.x;
+      if (f.y & FB_FLUID) xv.y += alpha * pv.y;
+      if ((f.x | f.y) & FB_FLUID) st2<double>(x + q, xv.x, xv.y);
+    }
     double z0, z1;
     if (MODE == 0) {
       double2 rv = ld2<double>(r + q);
@@ -310,6 +374,24 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
     halo_push2<double>(H, q, k, p0, p1);          // the neighbours' ghost planes see 0 off the fluid cells
   }
   halo_signal(H, ds, k == H.kdn, k == H.kup);
+}
+
+// The stop test ended the solve between k_update_xr and k_update_p of iteration pcg_iters: apply that
+// iteration's x += alpha p (the ring slots are intact, k_pcg_advance did not run).
+__global__ void __launch_bounds__(32 * SW_BY)
+k_pcg_finish_x(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, double* __restrict__ x,
+               const double* __restrict__ p, const DevScalars* __restrict__ ds) {
+  if (!ds->x_pending) return;
+  const int it = ds->pcg_iters;
+  const double alpha = ds->rz[(it + 3) & 3] / ds->pAp[it & 3];
+  STREAM_PROLOGUE(S)
+  if (act) {
+    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    double2 xv = ld2<double>(x + q), pv = ld2<double>(p + q);
+    if (f.x & FB_FLUID) xv.x += alpha * pv.x;
+    if (f.y & FB_FLUID) xv.y += alpha * pv.y;
+    if ((f.x | f.y) & FB_FLUID) st2<double>(x + q, xv.x, xv.y);
+  }
 }
 
 // end of an iteration: clear the ring slot the next iteration accumulates into, enforce the
@@ -380,15 +462,22 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   }
   fb_prof(c, "allreduce pAp");
   if (use_mg) {
-    k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
-                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
+    const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();
+    const Sweep S4 = make_sweep(c->g, c->box, 4);
+    if (st4_on && S4.xe - S4.box.x0 >= 128) {
+      const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
+      k_update_xr4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), cf, c->flags, c->r, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
+                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off());
+    } else
+      k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
+                                                         fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     fb_prof(c, "k_update_xr");
     if (dist && (rc = reduce_dot(c, PART_RR, it_arg, noexit))) return rc;
     if (!noexit) { k_pcg_check<<<1, 1, 0, c->stream>>>(c->ds, it_arg); c->launches++; }
     fb_prof(c, "allreduce rr");
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->r, L0.xb, c->pd, c->ds, it_arg, noexit,
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, it_arg, noexit,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
   } else {
     k_update_xr<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->x, c->r, c->pd, c->Ap, nullptr, nullptr, c->ds, it_arg, noexit, dist, halo_off());
@@ -396,7 +485,7 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
       if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 2, FB_F64, FB_SUM))) return rc;   // r.z and r.r are adjacent
       fb_pcg_publish(c, (1 << PART_RZ) | (1 << PART_RR), it_arg);
     }
-    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, c->ds, it_arg, noexit, halo_off());
+    k_update_p<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, nullptr, c->pd, nullptr, c->ds, it_arg, noexit, halo_off());
   }
   fb_prof(c, "k_update_p");
   k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, it_arg, noexit, halo_seg_close(c));
@@ -484,7 +573,7 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (use_mg && !done) {
     int rc = fb_mg_vcycle(c, -1);                  // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 0,
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, -1, 0,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 0, halo_seg_close(c));
     c->launches += 2;
@@ -511,6 +600,10 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     if (rc) return rc;
     done = c->hs->pcg_done != 0 || it >= max_iter;
     batch = use_mg ? 2 : 8;
+  }
+  if (c->hs->x_pending) {
+    k_pcg_finish_x<<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->pd, c->ds);
+    CK_LAUNCH(); c->launches++;
   }
   c->last_iters = c->hs->pcg_iters;
   if (iters_out) *iters_out = c->hs->pcg_iters;
@@ -547,7 +640,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds, dist,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     int rc = fb_mg_vcycle(c, -1); if (rc) return rc;
-    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->ds, -1, 1,
+    k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, -1, 1,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1, halo_seg_close(c));
   } else {
