@@ -358,7 +358,9 @@ __device__ __forceinline__ float resid_node(const MgCoef& mc, uint32_t f, uint32
   const int kk = 6 - __popc(f & FB_SMASK);
   return (b - mc.h2inv * ((float)kk * c - sum)) * (64.f / (float)nn);
 }
-template <int DOT>
+// PEER = false (single GPU): the ghost-plane wait / push / signal code is not compiled in (its
+// presence alone costs ~5 us per level-0 sweep, tools/kbench.cu T9).
+template <int DOT, bool PEER>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
              const float* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
@@ -369,7 +371,7 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
   const int it = pcg_iter(ds, it_arg);
   const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
-  halo_wait(H, ds, bdn, bup);
+  if (PEER) halo_wait(H, ds, bdn, bup);
   double acc[1] = {0.0};
   StencilMarch4 m;
   if (m.begin(S, xi)) {
@@ -391,13 +393,13 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
       o.y = smooth_node(mc, (f >> 8) & 0xffu, m.pc.y, bv.y, m.sum1());
       o.z = smooth_node(mc, (f >> 16) & 0xffu, m.pc.z, bv.z, m.sum2());
       o.w = smooth_node(mc, f >> 24, m.pc.w, bv.w, m.sum3());
-      if (m.act) { *reinterpret_cast<float4*>(xo + m.q) = o; halo_push4(H, m.q, m.k, o); }
+      if (m.act) { *reinterpret_cast<float4*>(xo + m.q) = o; if (PEER) halo_push4(H, m.q, m.k, o); }
       if (DOT == 1) acc[0] += (ra.x * (double)o.x + ra.y * (double)o.y) + (rb.x * (double)o.z + rb.y * (double)o.w);
       if (DOT == 2) acc[0] += ((double)bv.x * (double)o.x + (double)bv.y * (double)o.y) + ((double)bv.z * (double)o.z + (double)bv.w * (double)o.w);
       m.advance(S);
     }
   }
-  halo_signal(H, ds, bdn, bup);
+  if (PEER) halo_signal(H, ds, bdn, bup);
   if (DOT) {
     block_sum<1>(acc, sm);
     if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) {
@@ -406,6 +408,7 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
     }
   }
 }
+template <bool PEER>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_mg_resid4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
             const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
@@ -413,7 +416,7 @@ k_mg_resid4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
   if (ds->pcg_done) return;
   const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
-  halo_wait(H, ds, bdn, bup);
+  if (PEER) halo_wait(H, ds, bdn, bup);
   StencilMarch4 m;
   if (m.begin(S, x)) {
     const int kend = min(m.k + ST_ZP, S.box.z1);
@@ -433,11 +436,11 @@ k_mg_resid4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
       o.y = resid_node(mc, (f >> 8) & 0xffu, (nn >> 8) & 0xffu, m.pc.y, bv.y, m.sum1());
       o.z = resid_node(mc, (f >> 16) & 0xffu, (nn >> 16) & 0xffu, m.pc.z, bv.z, m.sum2());
       o.w = resid_node(mc, f >> 24, nn >> 24, m.pc.w, bv.w, m.sum3());
-      if (m.act) { *reinterpret_cast<float4*>(rn + m.q) = o; halo_push4(H, m.q, m.k, o); }
+      if (m.act) { *reinterpret_cast<float4*>(rn + m.q) = o; if (PEER) halo_push4(H, m.q, m.k, o); }
       m.advance(S);
     }
   }
-  halo_signal(H, ds, bdn, bup);
+  if (PEER) halo_signal(H, ds, bdn, bup);
 }
 
 // restriction b_c[I] = (1/8) sum_i P[i,I] res_i = (1/512) sum over the 4x4x4 fine cells of
@@ -994,6 +997,17 @@ static int mg_zchunk(const char* env, int blocks_xy, int nz, int min_blocks) {
     if ((int64_t)blocks_xy * cdiv(nz, zc) >= min_blocks) return zc;
   return 1;
 }
+// the four-node sweeps without the peer code when the run has no z neighbours
+template <int DOT, typename... A>
+static void launch_smooth4(dim3 g, cudaStream_t st, const PeerHalo& H, A... a) {
+  if (H.mode) k_mg_smooth4<DOT, true><<<g, STENCIL_BLOCK, 0, st>>>(a..., H);
+  else k_mg_smooth4<DOT, false><<<g, STENCIL_BLOCK, 0, st>>>(a..., H);
+}
+template <typename... A>
+static void launch_resid4(dim3 g, cudaStream_t st, const PeerHalo& H, A... a) {
+  if (H.mode) k_mg_resid4<true><<<g, STENCIL_BLOCK, 0, st>>>(a..., H);
+  else k_mg_resid4<false><<<g, STENCIL_BLOCK, 0, st>>>(a..., H);
+}
 #define HALO(L, arr) do { if ((L).dist) { int rc__ = fused ? fb_halo_point(c) : fb_halo_fill(c, (L).g, (arr), sizeof(float), 1, 1); if (rc__) return rc__; } } while (0)
 int fb_mg_vcycle(flipb200_ctx* c, int it) {
   const int nl = c->mg_levels;
@@ -1028,15 +1042,16 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     {
       PeerHalo Hs = fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs);
       if (gathered) { fb_gather_wait(c, &Hs); gathered = false; }
-      if (w4[l]) k_mg_smooth4<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
+      if (w4[l]) launch_smooth4<0>(tg, c->stream, Hs, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, (const double*)nullptr, c->ds, it, dist);
       else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
     }
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
-    if (w4[l]) k_mg_resid4<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
-                                                                fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
-    else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds,
-                                                         fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    {
+      const PeerHalo Hr = fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs);
+      if (w4[l]) launch_resid4(tg, c->stream, Hr, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
+      else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds, Hr);
+    }
     fb_prof(c, l == 0 ? "L0 halo+resid" : (l == 1 ? "L1 halo+resid" : "L2+ halo+resid"));
     HALO(L, L.xa);
     Box cb = C.box;
@@ -1111,24 +1126,26 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     }
     fb_prof(c, l == 0 ? "L0 halo+prolong" : (l == 1 ? "L1 halo+prolong" : "L2+ halo+prolong"));
     HALO(L, L.xb);
-    if (w4[l]) k_mg_smooth4<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
-                                                                        fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
-    else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist,
-                                                                 fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs));
+    {
+      const PeerHalo H1 = fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs);
+      if (w4[l]) launch_smooth4<0>(tg, c->stream, H1, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, (const double*)nullptr, c->ds, it, dist);
+      else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist, H1);
+    }
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
     HALO(L, L.xa);
     // the last sweep's output is read through ghosts only as the coarse correction of the level above
     if (l == 0) {
       const PeerHalo Hd = fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs);
-      if (w4[l] && rz64) k_mg_smooth4<1><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
-      else if (w4[l]) k_mg_smooth4<2><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
+      if (w4[l] && rz64) launch_smooth4<1>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
+      else if (w4[l]) launch_smooth4<2>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
       else if (rz64) k_mg_smooth<1><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
       else k_mg_smooth<2><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
     }
-    else if (w4[l]) k_mg_smooth4<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S4[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
-                                                                             fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
-    else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist,
-                                                                 fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs));
+    else {
+      const PeerHalo H2 = fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs);
+      if (w4[l]) launch_smooth4<0>(tg, c->stream, H2, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)nullptr, c->ds, it, dist);
+      else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, H2);
+    }
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 2)" : (l == 1 ? "L1 halo+smooth (post 2)" : "L2+ halo+smooth (post 2)"));
     c->launches += 3;
   }

@@ -101,6 +101,9 @@ k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, cons
 }
 
 // K1 in the STENCIL4 shape (four doubles per lane); used when the sweep's rows are >= 128 nodes wide
+// PEER = false (single GPU): the ghost-plane wait of z-slab runs is not compiled in -- its mere
+// presence costs 5 us of 65 at 256^3 (tools/kbench.cu T9, FL bit 3).
+template <bool PEER>
 __global__ void __launch_bounds__(32 * ST_BY)
 k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
         const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit,
@@ -108,7 +111,7 @@ k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, con
   __shared__ double sm[32];
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
-  {
+  if (PEER) {
     const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
     halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
   }
@@ -118,7 +121,7 @@ k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, con
     const int kend = min(m.k + ST_ZP, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
-      if (m.k >= kend) break;
+      if (m.k >= kend) break;      // predicating the planes of a partial chunk instead measured slower (kbench T9, FL bit 0)
       m.load(S, p);
       const uint32_t f = m.act ? *reinterpret_cast<const uint32_t*>(fl + m.q) : 0u;
       const uint32_t f0 = f & 0xffu, f1 = (f >> 8) & 0xffu, f2 = (f >> 16) & 0xffu, f3 = f >> 24;
@@ -141,7 +144,8 @@ static void launch_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noex
   const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
   const Sweep S4 = make_sweep(c->g, c->box, 4);
   if (st4_on && S4.xe - S4.box.x0 >= 128) {
-    k_spmv4<<<stencil_grid(S4, 4), STENCIL_BLOCK, 0, c->stream>>>(S4, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);
+    if (H.mode) k_spmv4<true><<<stencil_grid(S4, 4), STENCIL_BLOCK, 0, c->stream>>>(S4, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);
+    else k_spmv4<false><<<stencil_grid(S4, 4), STENCIL_BLOCK, 0, c->stream>>>(S4, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);
   } else {
     const Sweep S = make_sweep(c->g, c->box);
     k_spmv<<<stencil_grid(S), STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);

@@ -152,14 +152,18 @@ struct StencilMarch4 {
     pc = act ? ld4(src + q) : zero4();
     return true;
   }
-  __device__ __forceinline__ void load(const Sweep& S, const float* __restrict__ src) {
-    pn = (act && k < S.g.nz - 1) ? ld4(src + q + S.g.plane) : zero4();
-    ym = (act && jlo) ? ld4(src + q - S.g.px) : zero4();
-    yp = (act && jhi) ? ld4(src + q + S.g.px) : zero4();
+  // live = false (block-uniform: plane k lies beyond the block's chunk) turns every load off: a
+  // march can predicate the planes of a partial last chunk this way instead of leaving the unrolled
+  // loop with a break.  Measured slower (tools/kbench.cu T9: 64.7 vs 61.4 us); the kernels break.
+  __device__ __forceinline__ void load(const Sweep& S, const float* __restrict__ src, bool live = true) {
+    const bool a = act && live;
+    pn = (a && k < S.g.nz - 1) ? ld4(src + q + S.g.plane) : zero4();
+    ym = (a && jlo) ? ld4(src + q - S.g.px) : zero4();
+    yp = (a && jhi) ? ld4(src + q + S.g.px) : zero4();
     left = __shfl_up_sync(0xffffffffu, pc.w, 1);
     right = __shfl_down_sync(0xffffffffu, pc.x, 1);
-    if (lane == 0) left = (act && i > 0) ? src[q - 1] : 0.f;
-    if (lane == 31) right = (act && i + 4 < S.g.px) ? src[q + 4] : 0.f;
+    if (lane == 0) left = (a && i > 0) ? src[q - 1] : 0.f;
+    if (lane == 31) right = (a && i + 4 < S.g.px) ? src[q + 4] : 0.f;
   }
   __device__ __forceinline__ float sum0() const { return (pm.x + pn.x) + (ym.x + yp.x) + (left + pc.y); }
   __device__ __forceinline__ float sum1() const { return (pm.y + pn.y) + (ym.y + yp.y) + (pc.x + pc.z); }
@@ -170,7 +174,9 @@ struct StencilMarch4 {
 
 // fp64 STENCIL4: four doubles per lane as two double2 halves (a, b).  k_spmv in this shape sweeps
 // 256^3 in 55.9 us against 65.6 us for two doubles per lane (tools/kbench.cu T7 vs T4).
-struct StencilMarch4D {
+// FULL = true: the caller guarantees that every lane of the block lies inside the sweep's x range
+template <bool FULL>
+struct StencilMarch4DT {
   double2 pma, pmb, pca, pcb, pna, pnb, yma, ymb, ypa, ypb;
   double left, right;
   const double* ptr;          // &src[q]: advanced by one plane per step (keeps the address math out of the loop)
@@ -183,7 +189,7 @@ struct StencilMarch4D {
     j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
     k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP;
     if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
-    act = i < S.xe;
+    act = FULL || i < S.xe;
     jlo = act && j > 0; jhi = act && j < S.g.ny - 1;
     xlo = lane == 0 && act && i > 0; xhi = lane == 31 && act && i + 4 < S.g.px;
     q = gidx(S.g, i, j, k);
@@ -196,19 +202,19 @@ struct StencilMarch4D {
     pcb = act ? ld2<double>(ptr + 2) : zero2<double>();
     return true;
   }
-  __device__ __forceinline__ void load(const Sweep& S, const double* __restrict__) {
-    const bool hi = act && k < S.g.nz - 1;
+  __device__ __forceinline__ void load(const Sweep& S, const double* __restrict__, bool live = true) {
+    const bool hi = live && act && k < S.g.nz - 1, lo_y = live && jlo, hi_y = live && jhi;
     const ptrdiff_t P = S.g.plane, X = S.g.px;
     pna = hi ? ld2<double>(ptr + P) : zero2<double>();
     pnb = hi ? ld2<double>(ptr + P + 2) : zero2<double>();
-    yma = jlo ? ld2<double>(ptr - X) : zero2<double>();
-    ymb = jlo ? ld2<double>(ptr - X + 2) : zero2<double>();
-    ypa = jhi ? ld2<double>(ptr + X) : zero2<double>();
-    ypb = jhi ? ld2<double>(ptr + X + 2) : zero2<double>();
+    yma = lo_y ? ld2<double>(ptr - X) : zero2<double>();
+    ymb = lo_y ? ld2<double>(ptr - X + 2) : zero2<double>();
+    ypa = hi_y ? ld2<double>(ptr + X) : zero2<double>();
+    ypb = hi_y ? ld2<double>(ptr + X + 2) : zero2<double>();
     left = __shfl_up_sync(0xffffffffu, pcb.y, 1);
     right = __shfl_down_sync(0xffffffffu, pca.x, 1);
-    if (lane == 0) left = xlo ? ptr[-1] : 0.0;
-    if (lane == 31) right = xhi ? ptr[4] : 0.0;
+    if (lane == 0) left = (live && xlo) ? ptr[-1] : 0.0;
+    if (lane == 31) right = (live && xhi) ? ptr[4] : 0.0;
   }
   __device__ __forceinline__ double sum0() const { return (pma.x + pna.x) + (yma.x + ypa.x) + (left + pca.y); }
   __device__ __forceinline__ double sum1() const { return (pma.y + pna.y) + (yma.y + ypa.y) + (pca.x + pcb.x); }
@@ -216,6 +222,7 @@ struct StencilMarch4D {
   __device__ __forceinline__ double sum3() const { return (pmb.y + pnb.y) + (ymb.y + ypb.y) + (pcb.x + right); }
   __device__ __forceinline__ void advance(const Sweep& S) { pma = pca; pmb = pcb; pca = pna; pcb = pnb; q += S.g.plane; ptr += S.g.plane; ++k; }
 };
+typedef StencilMarch4DT<false> StencilMarch4D;
 
 // block reduction for the (32, BY) shapes: thread (0,0) ends with the sum
 template <int NV>

@@ -7,6 +7,10 @@
 #include <stdio.h>
 #include <stdint.h>
 #include <vector>
+// T9 replays the product's k_spmv4 on this notebook's data: the product headers give the same march
+#include "../fluid-simulation_b200/csrc/halo.cuh"
+#include "../fluid-simulation_b200/csrc/pcg.cuh"
+#undef CK
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1); } } while (0)
 
 static int N = 256;
@@ -194,6 +198,59 @@ __global__ void __launch_bounds__(32 * BY) t7_vec4(int n, const uint8_t* __restr
   if (lane == 0) sm[threadIdx.y] = acc;
   __syncthreads();
   if (lane == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < BY; ++w) t += sm[w]; if (t != 0) atomicAdd(out + (blockIdx.x + blockIdx.y + blockIdx.z) % g_spread, t); }
+}
+
+// T9: the product kernel k_spmv4 (csrc/pcg.cu) with its features switchable, to find what separates it
+// from T7.  FL bit 0: leave a partial chunk with a break; bit 1: diagonal from the coefficient table
+// (else kk * 0.1); bit 2: two predicated half stores (else one test for the four nodes); bit 3: the
+// ghost-plane wait of z-slab runs compiled in; bit 4: done flag / iteration read from DevScalars;
+// bit 5: no x-range predicate (every lane inside the sweep); bit 6: T7's plain block reduction.
+template <int FL>
+__global__ void __launch_bounds__(32 * ST_BY)
+t9_prod(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+        const double* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit,
+        int dist, const __grid_constant__ PeerHalo H) {
+  __shared__ double sm[32];
+  if (FL & 16) { if (!noexit && ds->pcg_done) return; }
+  const int it = (FL & 16) ? pcg_iter(ds, it_arg) : it_arg;
+  if (FL & 8) {
+    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+    halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
+  }
+  double acc[1] = {0.0};
+  StencilMarch4DT<(FL & 32) != 0> m;
+  if (m.begin(S, p)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (FL & 1) { if (m.k >= kend) break; }
+      const bool live = (FL & 1) || m.k < kend;
+      m.load(S, p, live);
+      const uint32_t f = (m.act && live) ? *reinterpret_cast<const uint32_t*>(fl + m.q) : 0u;
+      const uint32_t f0 = f & 0xffu, f1 = (f >> 8) & 0xffu, f2 = (f >> 16) & 0xffu, f3 = f >> 24;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#define T9_DIAG(fx) ((FL & 2) ? cf.diag[6 - __popc((fx) & FB_SMASK)] : (6 - __popc((fx) & FB_SMASK)) * 0.1)
+      if (f0 & FB_FLUID) { a0 = T9_DIAG(f0) * m.pca.x + cf.off * m.sum0(); acc[0] += m.pca.x * a0; }
+      if (f1 & FB_FLUID) { a1 = T9_DIAG(f1) * m.pca.y + cf.off * m.sum1(); acc[0] += m.pca.y * a1; }
+      if (f2 & FB_FLUID) { a2 = T9_DIAG(f2) * m.pcb.x + cf.off * m.sum2(); acc[0] += m.pcb.x * a2; }
+      if (f3 & FB_FLUID) { a3 = T9_DIAG(f3) * m.pcb.y + cf.off * m.sum3(); acc[0] += m.pcb.y * a3; }
+      if (FL & 4) {
+        if ((f0 | f1) & FB_FLUID) st2<double>(Ap + m.q, a0, a1);
+        if ((f2 | f3) & FB_FLUID) st2<double>(Ap + m.q + 2, a2, a3);
+      } else if ((f0 | f1 | f2 | f3) & FB_FLUID) { st2<double>(Ap + m.q, a0, a1); st2<double>(Ap + m.q + 2, a2, a3); }
+      m.advance(S);
+    }
+  }
+  if (FL & 64) {
+    double a = acc[0];
+    for (int o = 16; o; o >>= 1) a += __shfl_xor_sync(~0u, a, o);
+    if (threadIdx.x == 0) sm[threadIdx.y] = a;
+    __syncthreads();
+    if (threadIdx.x == 0 && threadIdx.y == 0) { double t = 0; for (int w = 0; w < ST_BY; ++w) t += sm[w]; if (t != 0) atomicAdd(&ds->pAp[it & 3], t); }
+    return;
+  }
+  block_sum<1>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_PAP] : &ds->pAp[it & 3], acc[0]);
 }
 
 // T8: T7 + prefetch.global.L2 of every plane of the march at block start (PF = 1) or two planes ahead (PF = 2)
@@ -408,6 +465,24 @@ int main(int argc, char** argv) {
   us = timeit([&] { t8_pf<BY, ZP, PF><<<dim3(N / 128, N / BY, N / ZP), dim3(32, BY)>>>(N, fl, p, Ap, out); }); \
   printf("T8 pf%d  BY=%d ZP=%d          %8.1f us  %7.1f GB/s\n", PF, BY, ZP, us, gb17 / us * 1e6);
     RUN_T8(4, 4, 1) RUN_T8(4, 8, 1) RUN_T8(4, 4, 2) RUN_T8(4, 8, 2) RUN_T8(4, 16, 2) RUN_T8(2, 8, 1)
+    {   // T9: product kernel, product flag encoding (FB_FLUID = bit 6 here too), whole box or the product's 255-row box
+      static_assert(FB_FLUID == 64, "flag encoding");
+      DevScalars* ds; CK(cudaMalloc(&ds, sizeof(DevScalars))); CK(cudaMemset(ds, 0, sizeof(DevScalars)));
+      PcgCoef cf; memset(&cf, 0, sizeof(cf));
+      for (int k = 1; k <= 6; ++k) { cf.diag[k] = 0.1 * k; cf.inv[k] = 1.0 / cf.diag[k]; }
+      cf.off = -0.1;
+      Grid g; memset(&g, 0, sizeof(g));
+      g.nx = N; g.ny = N; g.nz = N; g.px = N; g.plane = N * N; g.total = N * N * N; g.gnz = N; g.k1 = N;
+      for (int yb = 0; yb < 1; ++yb) {
+        Box b = {0, yb, 0, N, N, N};      // yb = 1: rows 1..N-1 as in the bench scene
+        Sweep S4 = make_sweep(g, b, 4);
+#define RUN_T9(FL) \
+        us = timeit([&] { t9_prod<FL><<<stencil_grid(S4, 4), STENCIL_BLOCK>>>(S4, cf, fl, p, Ap, ds, 5, 1, 0, halo_off()); }); \
+        printf("T9 prod FL=%2d y0=%d          %8.1f us  %7.1f GB/s\n", FL, yb, us, gb17 / us * 1e6);
+        RUN_T9(1) RUN_T9(33) RUN_T9(65) RUN_T9(97) RUN_T9(23) RUN_T9(55) RUN_T9(119) RUN_T9(31)
+      }
+      RUN_T7(4, 4)
+    }
     { int one = 1; CK(cudaMemcpyToSymbol(g_spread, &one, sizeof(int))); printf("single-address atomics:\n"); }
     RUN_T7(4, 4) RUN_T4(4, 4)
     { int v = 32; CK(cudaMemcpyToSymbol(g_spread, &v, sizeof(int))); }
