@@ -309,6 +309,73 @@ k_p2g_row(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __r
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// 256-bit variants of the per-cell kernels (FLIPB200_P2G=v4 / FLIPB200_G2P=v4; NOT the default and not
+// yet measured -- written after the GPU budget of round 1 was spent, first A/B of round 2).
+// Why: k_p2g_cell / k_g2p_cell keep 16 warps per SM (122 / 117 registers) with six 8-byte loads in
+// flight per lane = 24 KB per SM, about half of what 6.5 TB/s x ~1 us of latency needs per SM (44 KB);
+// ncu shows 37 % DRAM utilisation and the LSU busy with 16 cache lines per warp request (lanes are 64 B
+// apart).  Here a lane fetches the aligned groups of four particles that cover its cell's range
+// [s, e) with LDG.256 (ld.global.v4.f64): a quarter of the requests, four times the bytes in flight;
+// slots outside [s, e) belong to the neighbouring cells and are skipped.  Accumulation order is the
+// particle order, as in k_p2g_cell: identical bits.  Needs 32-byte aligned arrays (cudaMalloc) and a
+// capacity that is a multiple of 4 (fb_reserve_particles rounds to 64).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ld4_nc(const double* p, double (&v)[4]) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld4(const double* p, double (&v)[4]) {
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st4(double* p, const double (&v)[4]) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
+}
+
+__global__ void __launch_bounds__(128)
+k_p2g_cell4(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
+            const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+            const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+            double* __restrict__ wacc, double* __restrict__ ux, double* __restrict__ uy, double* __restrict__ uz) {
+  int i = box.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int j = box.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int k = box.z0 + blockIdx.z;
+  if (i >= box.x1 || j >= box.y1 || i > g.nx - 2 || j > g.ny - 2 || k + g.kg0 > g.gnz - 2) return;
+  int q = gidx(g, i, j, k);
+  int s = start[q], e = start[q + 1];
+  if (s == e) return;
+  double aw[8], ax[8], ay[8], az[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { aw[m] = 0; ax[m] = 0; ay[m] = 0; az[m] = 0; }
+  const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+  for (int g0 = s & ~3; g0 < e; g0 += 4) {
+    double X[4], Y[4], Z[4], A[4], B[4], C[4];
+    ld4_nc(px + g0, X); ld4_nc(py + g0, Y); ld4_nc(pz + g0, Z);
+    ld4_nc(vx + g0, A); ld4_nc(vy + g0, B); ld4_nc(vz + g0, C);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int n = g0 + t;
+      if (n < s || n >= e) continue;              // a neighbouring cell's particle (or past the end)
+      double wx0 = spline_ref(X[t] - nx0), wx1 = spline_ref(X[t] - (nx0 + 1.0));
+      double wy0 = spline_ref(Y[t] - ny0), wy1 = spline_ref(Y[t] - (ny0 + 1.0));
+      double wz0 = spline_ref(Z[t] - nz0), wz1 = spline_ref(Z[t] - (nz0 + 1.0));
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);   // (sx*sy)*sz, fluid.cc:291
+        aw[m] += cw; ax[m] += cw * A[t]; ay[m] += cw * B[t]; az[m] += cw * C[t];
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+    if (fl[qq] & FB_SOLID) continue;            // fluid.cc:288
+    atomicAdd(&wacc[qq], aw[m]);
+    atomicAdd(&ux[qq], ax[m]);
+    atomicAdd(&uy[qq], ay[m]);
+    atomicAdd(&uz[qq], az[m]);
+  }
+}
+
 // Reference-shaped variant: one thread per particle, 32 atomics each.  Kept as the cross-check of
 // the cell kernel (FLIPB200_P2G=particle) and as the path for unsorted input.
 __global__ void k_p2g_particle(Grid g, int64_t n, const uint8_t* __restrict__ fl,
@@ -361,7 +428,10 @@ int fb_p2g(flipb200_ctx* c) {
   if (c->n_sorted > 0) {
     Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
     dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
-    if (!(mode && mode[0] == 'r'))   // default: per-cell kernel; FLIPB200_P2G=row: shared-memory staged variant (measured 9 % slower at 8 ppc)
+    if (mode && mode[0] == 'v')      // FLIPB200_P2G=v4: 256-bit loads (unmeasured, see k_p2g_cell4)
+      k_p2g_cell4<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                              pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    else if (!(mode && mode[0] == 'r'))   // default: per-cell kernel; FLIPB200_P2G=row: shared-memory staged variant (measured 9 % slower at 8 ppc)
       k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
                                              pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
     else {
@@ -491,6 +561,78 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
       if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }
       if (wsum != 0.0 || ratio != 1.0) { vx[n] = a; vy[n] = b; vz[n] = cc; }
       speed = fmax(speed, a * a + b * b + cc * cc);            // squared: sqrt is monotone, taken once below
+    }
+  }
+  speed = sqrt(warp_max(speed));                               // fluid.cc:982 (Vec3::length)
+  int tid = threadIdx.x + blockDim.x * threadIdx.y, lane = tid & 31, w = tid >> 5;
+  if (lane == 0) red[w] = speed;
+  __syncthreads();
+  if (tid == 0) {
+    double m = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
+    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
+  }
+}
+
+// k_g2p_cell with 256-bit particle accesses (see k_p2g_cell4).  A group of four that lies wholly inside
+// the cell's range is written back with one 256-bit store, the partial groups at either end
+// element by element (their other slots belong to the neighbouring cells' threads).
+__global__ void __launch_bounds__(128)
+k_g2p_cell4(Grid g, const int32_t* __restrict__ start,
+            const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+            double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
+            const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
+            DevScalars* __restrict__ ds, double ratio) {
+  __shared__ double red[4];
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  int k = g.k0 + blockIdx.z;
+  double speed = 0.0;
+  int s = 0, e = 0, q = 0;
+  if (i <= g.nx - 2 && j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
+  if (s < e) {
+    double ddx[8], ddy[8], ddz[8];
+    unsigned inmask = 0;
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
+      int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+      bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
+      ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
+      if (in) inmask |= 1u << m;
+    }
+    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+    for (int g0 = s & ~3; g0 < e; g0 += 4) {
+      double X[4], Y[4], Z[4], A[4], B[4], C[4];
+      ld4_nc(px + g0, X); ld4_nc(py + g0, Y); ld4_nc(pz + g0, Z);
+      ld4(vx + g0, A); ld4(vy + g0, B); ld4(vz + g0, C);          // written by this kernel: no .nc
+      unsigned wr = 0;                                            // slots whose velocity changed
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int n = g0 + t;
+        if (n < s || n >= e) continue;
+        double wx0 = spline_ref(X[t] - nx0), wx1 = spline_ref(X[t] - (nx0 + 1.0));
+        double wy0 = spline_ref(Y[t] - ny0), wy1 = spline_ref(Y[t] - (ny0 + 1.0));
+        double wz0 = spline_ref(Z[t] - nz0), wz1 = spline_ref(Z[t] - (nz0 + 1.0));
+        double wsum = 0, dx = 0, dy = 0, dz = 0;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+          if (inmask & (1u << m)) wsum += cw;
+          dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
+        }
+        double a = A[t], b = B[t], cc = C[t];
+        if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }          // PIC/FLIP blend (see k_cell_delta)
+        if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }   // as k_g2p_cell
+        if (wsum != 0.0 || ratio != 1.0) { A[t] = a; B[t] = b; C[t] = cc; wr |= 1u << t; }
+        speed = fmax(speed, a * a + b * b + cc * cc);
+      }
+      if (g0 >= s && g0 + 4 <= e) {               // all four slots are this cell's
+        if (wr) { st4(vx + g0, A); st4(vy + g0, B); st4(vz + g0, C); }
+      } else {
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          if (wr & (1u << t)) { vx[g0 + t] = A[t]; vy[g0 + t] = B[t]; vz[g0 + t] = C[t]; }
+      }
     }
   }
   speed = sqrt(warp_max(speed));                               // fluid.cc:982 (Vec3::length)
@@ -660,7 +802,10 @@ int fb_g2p_advect(flipb200_ctx* c) {
   if (c->sorted && !(mode && mode[0] == 'p' && c->world == 1)) {
     if (c->n_sorted > 0) {
       dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
-      if (!(mode && mode[0] == 'r'))  // default: per-cell kernel; FLIPB200_G2P=row: shared-memory staged variant (measured 3 % slower)
+      if (mode && mode[0] == 'v')     // FLIPB200_G2P=v4: 256-bit accesses (unmeasured, see k_g2p_cell4)
+        k_g2p_cell4<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                                c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
+      else if (!(mode && mode[0] == 'r'))  // default: per-cell kernel; FLIPB200_G2P=row: shared-memory staged variant (measured 3 % slower)
         k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
                                                c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);   // dc arrays written by fb_cell_delta
       else {
