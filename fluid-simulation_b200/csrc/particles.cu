@@ -791,6 +791,186 @@ k_advect(Grid g, int64_t n, const uint8_t* __restrict__ fl, double dt_max, doubl
 
 __global__ void k_reset_max(DevScalars* ds) { ds->max_speed_bits = 0ull; }
 
+// ---------------------------------------------------------------------------------------------
+// G2P and advection in ONE pass (FLIPB200_G2P=f1 / f4; NOT the default and not yet measured -- written
+// after the GPU budget of round 1 was spent, first A/B of round 2).  The two-kernel path moves
+// 48 + 24 B (k_g2p_cell) and 48 + 24 B (k_advect) per particle because FLIPadvect's dt is a function
+// of the global max speed (fluid.cc:992-999).  But dt = min(dt_max, dx / maxSpeed) IS dt_max whenever
+// maxSpeed <= dx / dt_max, which the host can bet on when the previous step ended that way: the
+// fused kernel advects with dt_max and writes positions AND velocities into the alternate (sort)
+// buffers -- 48 B read + 48 B written, the algorithmic 96 B -- while accumulating the max speed.
+// If the bet holds (checked on the host with the same expression) the buffers are swapped; if not,
+// the inputs are untouched and the two-kernel path runs as if nothing had happened.  Same operation
+// sequence per particle as k_g2p_cell followed by k_advect: identical bits.  W = particles per load
+// (1: 8-byte accesses, 4: 256-bit, see k_p2g_cell4).  Single GPU, cell-sorted particles only.
+// ---------------------------------------------------------------------------------------------
+// one particle of FLIPadvect phase 2 (fluid.cc:1000-1036), exactly as k_advect does it
+__device__ __forceinline__ void advect_one(const Grid& g, const uint8_t* __restrict__ fl, double timestep, double e,
+                                           double x, double y, double z, double& a, double& b, double& cc,
+                                           double& ox, double& oy, double& oz) {
+  const double nxp = __dadd_rn(x, __dmul_rn(timestep, a));
+  const double nyp = __dadd_rn(y, __dmul_rn(timestep, b));
+  const double nzp = __dadd_rn(z, __dmul_rn(timestep, cc));
+  const bool bad = !(fabs(nxp) < 1.0e9) || !(fabs(nyp) < 1.0e9) || !(fabs(nzp) < 1.0e9);
+  const int rx = bad ? 0 : (int)round(nxp), ry = bad ? 0 : (int)round(nyp), rz = bad ? 0 : (int)round(nzp);
+  if (!bad && solid_at(g, fl, rx + g.ox, ry + g.oy, rz + g.oz)) {   // fluid.cc:1011
+    const double sx = __dmul_rn(a, timestep), sy = __dmul_rn(b, timestep), sz = __dmul_rn(cc, timestep);
+    const int tx = (int)x, ty = (int)y, tz = (int)z;               // Coord(double...) truncates (openvdb/math/Coord.h:61)
+    if (solid_at(g, fl, (int)round(__dadd_rn(x, sx)) + g.ox, ty + g.oy, tz + g.oz)) a *= -1.0 * e;    // :1017-1020
+    if (solid_at(g, fl, tx + g.ox, (int)round(__dadd_rn(y, sy)) + g.oy, tz + g.oz)) b *= -1.0 * e;    // :1021-1024
+    if (solid_at(g, fl, tx + g.ox, ty + g.oy, (int)round(__dadd_rn(z, sz)) + g.oz)) cc *= -1.0 * e;   // :1025-1028
+    ox = __dadd_rn(x, __dmul_rn(a, timestep));                     // :1029
+    oy = __dadd_rn(y, __dmul_rn(b, timestep));
+    oz = __dadd_rn(z, __dmul_rn(cc, timestep));
+  } else {
+    ox = nxp; oy = nyp; oz = nzp;                                  // :1033
+  }
+}
+
+template <int W> __device__ __forceinline__ void ldw_nc(const double* p, double (&v)[W]);
+template <> __device__ __forceinline__ void ldw_nc<1>(const double* p, double (&v)[1]) { v[0] = __ldg(p); }
+template <> __device__ __forceinline__ void ldw_nc<4>(const double* p, double (&v)[4]) { ld4_nc(p, v); }
+
+template <int W>
+__global__ void __launch_bounds__(128)
+k_g2p_advect_cell(Grid g, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
+                  const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+                  const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+                  double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
+                  double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
+                  const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
+                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest) {
+  __shared__ double red[4];
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int j = blockIdx.y * blockDim.y + threadIdx.y;
+  int k = g.k0 + blockIdx.z;
+  double speed = 0.0;
+  int s = 0, e = 0, q = 0;
+  if (i <= g.nx - 2 && j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
+  if (s < e) {
+    double ddx[8], ddy[8], ddz[8];
+    unsigned inmask = 0;
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
+      int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+      bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
+      ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
+      if (in) inmask |= 1u << m;
+    }
+    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+    for (int g0 = s & ~(W - 1); g0 < e; g0 += W) {
+      double X[W], Y[W], Z[W], A[W], B[W], C[W];
+      ldw_nc<W>(px + g0, X); ldw_nc<W>(py + g0, Y); ldw_nc<W>(pz + g0, Z);
+      ldw_nc<W>(vx + g0, A); ldw_nc<W>(vy + g0, B); ldw_nc<W>(vz + g0, C);
+#pragma unroll
+      for (int t = 0; t < W; ++t) {
+        const int n = g0 + t;
+        if (n < s || n >= e) continue;
+        double wx0 = spline_ref(X[t] - nx0), wx1 = spline_ref(X[t] - (nx0 + 1.0));
+        double wy0 = spline_ref(Y[t] - ny0), wy1 = spline_ref(Y[t] - (ny0 + 1.0));
+        double wz0 = spline_ref(Z[t] - nz0), wz1 = spline_ref(Z[t] - (nz0 + 1.0));
+        double wsum = 0, dx = 0, dy = 0, dz = 0;
+#pragma unroll
+        for (int m = 0; m < 8; ++m) {
+          double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+          if (inmask & (1u << m)) wsum += cw;
+          dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
+        }
+        double a = A[t], b = B[t], cc = C[t];
+        if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }          // PIC/FLIP blend (see k_cell_delta)
+        if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }   // as k_g2p_cell
+        speed = fmax(speed, a * a + b * b + cc * cc);                       // before the collision, fluid.cc:982
+        advect_one(g, fl, timestep, e_rest, X[t], Y[t], Z[t], a, b, cc, X[t], Y[t], Z[t]);
+        A[t] = a; B[t] = b; C[t] = cc;
+      }
+      bool stored = false;
+      if constexpr (W == 4) {
+        if (g0 >= s && g0 + 4 <= e) {             // all four slots are this cell's
+          st4(opx + g0, X); st4(opy + g0, Y); st4(opz + g0, Z); st4(ovx + g0, A); st4(ovy + g0, B); st4(ovz + g0, C);
+          stored = true;
+        }
+      }
+      if (!stored) {
+#pragma unroll
+        for (int t = 0; t < W; ++t) {
+          const int n = g0 + t;
+          if (n < s || n >= e) continue;
+          opx[n] = X[t]; opy[n] = Y[t]; opz[n] = Z[t]; ovx[n] = A[t]; ovy[n] = B[t]; ovz[n] = C[t];
+        }
+      }
+    }
+  }
+  speed = sqrt(warp_max(speed));                               // fluid.cc:982 (Vec3::length)
+  int tid = threadIdx.x + blockDim.x * threadIdx.y, lane = tid & 31, w = tid >> 5;
+  if (lane == 0) red[w] = speed;
+  __syncthreads();
+  if (tid == 0) {
+    double m = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
+    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
+  }
+}
+
+// the trailing "outside the box" bucket of the fused path: no grid contact (k_speed_tail), then advection
+__global__ void k_g2p_advect_tail(Grid g, const int32_t* __restrict__ start, int64_t n /* = n_sorted */, const uint8_t* __restrict__ fl,
+                                  const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+                                  const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+                                  double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
+                                  double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
+                                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest) {
+  double speed = 0.0;
+  for (int64_t t = (int64_t)start[g.total] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n;
+       t += (int64_t)gridDim.x * blockDim.x) {
+    double x = px[t], y = py[t], z = pz[t];
+    double a = vx[t], b = vy[t], cc = vz[t];
+    if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }
+    speed = fmax(speed, sqrt(a * a + b * b + cc * cc));
+    advect_one(g, fl, timestep, e_rest, x, y, z, a, b, cc, x, y, z);
+    opx[t] = x; opy[t] = y; opz[t] = z; ovx[t] = a; ovy[t] = b; ovz[t] = cc;
+  }
+  speed = warp_max(speed);
+  if ((threadIdx.x & 31) == 0 && speed > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(speed));
+}
+
+// dt of fluid.cc:992-999 from the collected max speed (the two-kernel path does this inside k_advect)
+__global__ void k_set_dt(DevScalars* ds, double dt_max, double dxc) {
+  const double maxSpeed = __longlong_as_double((long long)ds->max_speed_bits);
+  double timestep = dt_max;
+  if (maxSpeed != 0.0) timestep = dt_max < dxc / maxSpeed ? dt_max : dxc / maxSpeed;
+  ds->dt_out = timestep;
+}
+
+// returns 0 and *done = true when the bet on dt == dt_max held (buffers swapped, step finished);
+// *done = false: nothing was changed, the caller runs the two-kernel path
+static int g2p_advect_fused(flipb200_ctx* c, int W, bool* done) {
+  const Grid& g = c->g;
+  Particles& pt = c->pt;
+  *done = false;
+  const double dt_spec = c->P.dt_max;
+  dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
+  if (W == 4)
+    k_g2p_advect_cell<4><<<grd, blk, 0, c->stream>>>(g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                                     pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds,
+                                                     c->P.flip_ratio, dt_spec, c->P.restitution);
+  else
+    k_g2p_advect_cell<1><<<grd, blk, 0, c->stream>>>(g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                                     pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds,
+                                                     c->P.flip_ratio, dt_spec, c->P.restitution);
+  k_g2p_advect_tail<<<64, 256, 0, c->stream>>>(g, c->cell_start, c->n_sorted, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                               pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->ds, c->P.flip_ratio, dt_spec,
+                                               c->P.restitution);
+  k_set_dt<<<1, 1, 0, c->stream>>>(c->ds, c->P.dt_max, c->P.dx);
+  CK_LAUNCH(); c->launches += 3;
+  int rc = fb_fetch_scalars(c);
+  if (rc) return rc;
+  if (c->hs->dt_out != dt_spec) return 0;          // bet lost: pt.a is untouched
+  for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
+  c->sorted = false;   // positions moved: cell order is stale
+  *done = true;
+  return 0;
+}
+
+
 int fb_g2p_advect(flipb200_ctx* c) {
   const Grid& g = c->g;
   Particles& pt = c->pt;
@@ -799,6 +979,15 @@ int fb_g2p_advect(flipb200_ctx* c) {
   int blocks = (int)((pt.n + 255) / 256);
   if (blocks == 0) blocks = 1;
   const char* mode = getenv("FLIPB200_G2P");
+  // FLIPB200_G2P=f1 / f4: one-pass G2P + advection, betting on dt == dt_max when the previous step ended that way
+  if (mode && mode[0] == 'f' && c->world == 1 && c->sorted && pt.n == c->n_sorted && pt.n > 0 &&
+      (c->hs->dt_out == c->P.dt_max || c->hs->dt_out == 0.0)) {
+    bool done = false;
+    int rc = g2p_advect_fused(c, mode[1] == '4' ? 4 : 1, &done);
+    if (rc || done) return rc;
+    k_reset_max<<<1, 1, 0, c->stream>>>(c->ds);
+    c->launches++;
+  }
   if (c->sorted && !(mode && mode[0] == 'p' && c->world == 1)) {
     if (c->n_sorted > 0) {
       dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);

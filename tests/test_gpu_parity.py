@@ -15,7 +15,9 @@ TOL_GRID = 1e-5      # north_star: single-step grid velocity / pressure rel-L2
 TOL_POS10 = 1e-4     # north_star: positions after 10 steps rel-L2
 # kernel variants that have not run on a GPU yet join the parametrised tests only on request
 # (FLIPB200_TEST_EXPERIMENTAL=1), so that an unmeasured variant can never turn the suite red
-PARTICLE_MODES = ["row", "cell", "particle"] + (["v4"] if os.environ.get("FLIPB200_TEST_EXPERIMENTAL") == "1" else [])
+_EXP = os.environ.get("FLIPB200_TEST_EXPERIMENTAL") == "1"
+PARTICLE_MODES = ["row", "cell", "particle"] + (["v4"] if _EXP else [])
+G2P_MODES = PARTICLE_MODES + (["f1", "f4"] if _EXP else [])      # one-pass G2P + advection (bet on dt == dt_max)
 
 
 @pytest.fixture(scope="module")
@@ -96,7 +98,7 @@ def test_rhs_div_pcg_velupdate_relax(fb, oracle_mod, scenes):
     assert e == pytest.approx(eo, rel=1e-12)
 
 
-@pytest.mark.parametrize("mode", PARTICLE_MODES)
+@pytest.mark.parametrize("mode", G2P_MODES)
 def test_g2p_advect(fb, oracle_mod, scenes, mode, monkeypatch):
     """a17/a18 from identical grids; includes particles that hit the solid shell (both G2P kernels)."""
     monkeypatch.setenv("FLIPB200_G2P", mode)
