@@ -14,6 +14,13 @@ Prints ONE JSON line (rank 0).  `value` = particles x K / device time with input
 `roofline` = the PCG stencil kernel (17 algorithmic bytes per swept node) against the measured HBM
 peak; `cpu_baseline` = the CPU oracle on a bounded sample.
 
+Other workloads (BASELINE configs[3] and [4]; parity-test configurations, not the headline line):
+  --workload cube-drop --grid-n 512   cube of side n/3 (8 ppc) dropped in an n^3 box cut into N z-slabs
+                                      of n/N planes -- STRONG scaling ("scaling": "strong")
+  --workload pcg                      pressure projection only: the 7-point MG-PCG on the full-tank system
+                                      (b = divergence after one gravity kick), a "step" = 200 iterations
+                                      without convergence exit; metric pcg_iterations_per_s, weak scaling
+
 N > 1 (torchrun, one rank per GPU): ONE tank of n x n x (n*N) nodes cut into N z-slabs (SURVEY.md
 8e) -- weak scaling, every GPU owns an n^3 block and ~the same particles; ghost planes, PCG dot
 products and particle migration go over the library's own NCCL communicator.  `value` counts the
@@ -127,6 +134,67 @@ def run_cpu_sample(steps, warmup, threads):
     return sc.num_particles * steps / el, el / steps * 1e3, kind, desc, o.has_eigen
 
 
+PCG_BLOCK = 200      # iterations per "step" of the pcg workload
+
+
+def bench_pcg(args, f, fb, config, rank, world, local_rank, barrier, max_over_ranks, n, nzg):
+    """BASELINE configs[4]: pressure-projection-only weak scaling.  The system is the one the first
+    relaxation pass of the full-tank scene solves (b = divergence after one gravity kick, non-zero in
+    the layer next to the floor); a step = PCG_BLOCK iterations of the product's CUDA-graph iteration
+    without convergence exit (flipb200_time_kernel, CUDA events on the library's stream, max over
+    ranks); the run-to-tolerance iteration count of the same system is reported next to it."""
+    import torch.distributed as dist
+    dt = 0.1
+    f.p2g()
+    n_fluid = f.classify()
+    f.rhs_div(dt)
+    iters_tol, rel = f.pcg_solve(dt)                       # run to 2.2e-16 (also the warm-up of the iteration graph)
+    for _ in range(args.warmup):
+        f.time_kernel(fb.KERNEL_PCG_ITER, 20)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0 and not os.environ.get("FLIPB200_BENCH_NOSMI"):
+        sampler.start()
+    ms_block = 0.0
+    launches = 0
+    nodes = 0
+    for _ in range(args.steps):
+        ms_iter, nodes = f.time_kernel(fb.KERNEL_PCG_ITER, PCG_BLOCK)
+        ms_block += ms_iter * PCG_BLOCK
+    barrier()
+    clocks = sampler.stop()
+    info = f.debug_info()
+    launches = info["kernels_per_iteration"] * PCG_BLOCK * args.steps
+    ms_block = max_over_ranks(ms_block)
+    it_s = PCG_BLOCK * args.steps / (ms_block * 1e-3)
+    peak, peak_src = measured_peak_gbs()
+    ms_spmv, _ = f.time_kernel(fb.KERNEL_SPMV, args.kernel_iters)
+    ach = 17.0 * nodes / (ms_spmv * 1e-3) / 1e9
+    config = dict(config)
+    config["workload"] = (f"pressure projection only: 7-point {'MG-' if args.precond == 1 else 'Jacobi-'}PCG (fp64) on the full-tank system, "
+                          f"{n}x{n}x{nzg} grid = {n}^3 per GPU, {n_fluid} unknowns, b = divergence after one gravity kick; "
+                          f"step = {PCG_BLOCK} iterations without convergence exit (BASELINE configs[4])")
+    config["engine"] = info
+    config["l2"] = "vectors larger than L2 (8 B x n^3 each)" if n >= 256 else "working set may fit L2 at this n"
+    if rank == 0:
+        line = {"metric": "pcg_iterations_per_s", "value": it_s, "unit": "iterations/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_block / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "clocks": clocks,
+                "e2e": None, "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "kernel": "k_spmv (7-pt matrix-free A.p + p.Ap)", "achieved": ach, "peak": peak, "unit": "GB/s",
+                             "frac": ach / peak, "traffic": None, "algorithmic_bytes": 17 * nodes, "peak_source": peak_src,
+                             "swept_nodes_per_gpu": nodes, "us_per_launch": ms_spmv * 1e3},
+                "cpu_baseline": None,
+                "pcg": {"us_per_iteration": ms_block / (PCG_BLOCK * args.steps) * 1e3, "iterations_to_tolerance": iters_tol,
+                        "rel_residual": rel, "unknowns": n_fluid, "swept_nodes_per_gpu": nodes,
+                        "node_updates_per_s": it_s * nodes * world,
+                        "jacobi_equivalent_frac": 91.0 * nodes * it_s / 1e9 / peak}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -134,6 +202,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="flipb200", choices=["flipb200", "reference"])
     ap.add_argument("--grid-n", dest="n", type=int, default=int(os.environ.get("FLIPB200_BENCH_N", "256")))
+    ap.add_argument("--workload", default="flip", choices=["flip", "cube-drop", "pcg"],
+                    help="flip: dam-break full tank, weak scaling (headline); cube-drop: n^3 box, strong scaling; pcg: pressure solve only")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--kernel-iters", type=int, default=50)
@@ -144,17 +214,38 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     n = args.n
-    nzg = n * world                                    # weak scaling: an n^3 block per GPU, stacked along z
-    lo, hi = scene_box(n, nz=nzg)
-    total_particles = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8
-    particles = total_particles // world
-    config = {"workload": f"dam-break FLIP full-tank fill, {n}x{n}x{nzg} grid, 8 particles/cell ({total_particles} particles, "
-                          f"~{particles}/GPU), fp64, {'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 "
-                          f"(BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}]" + (" per GPU" if world > 1 else "") + ")",
-              "grid": [n, n, nzg], "particles_per_gpu": particles, "particles_total": total_particles,
-              "parallelism": "single GPU" if world == 1 else f"{world} z-slabs of {n} planes, NCCL halo exchange + PCG all-reduces + particle migration",
-              "l2": "inputs larger than L2 (particle arrays 48 B x particles, grid vectors 8 B x n^3)" if n >= 256
-                    else "working set may fit L2 at this n; no flush between steps"}
+    if args.workload == "cube-drop":
+        # BASELINE configs[3]: the reference's cube drop (41/121 of the box, fluid.cc:1176-1216) at n^3, cut into z-slabs
+        nzg = n
+        side = n // 3
+        lo = tuple((n - side) // 2 for _ in range(3))
+        hi = tuple(l + side - 1 for l in lo)
+        total_particles = side ** 3 * 8
+        from importlib import import_module
+        zs, _a = import_module("fluid_simulation_b200.dist").slab_split(nzg, world)
+        own = max(0, min(hi[2] + 1, zs[rank + 1]) - max(lo[2], zs[rank]))
+        particles = side * side * own * 8              # this rank's seeds
+        cap = int((particles + side * side * 8 * 2) * 1.25) + 4096
+        config = {"workload": f"cube-drop FLIP, {n}^3 grid, cube of side {side} voxels, 8 particles/cell ({total_particles} particles), "
+                              f"fp64, {'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 (BASELINE configs[3])",
+                  "grid": [n, n, nzg], "particles_total": total_particles,
+                  "parallelism": "single GPU" if world == 1 else f"{world} z-slabs of ~{n // world} planes, NCCL halo exchange + PCG all-reduces + particle migration",
+                  "l2": "grid vectors (8 B x n^3) larger than L2; no flush between steps"}
+        scaling = "strong"
+    else:
+        nzg = n * world                                    # weak scaling: an n^3 block per GPU, stacked along z
+        lo, hi = scene_box(n, nz=nzg)
+        total_particles = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8
+        particles = total_particles // world
+        cap = int(particles * 1.06) + 4096
+        config = {"workload": f"dam-break FLIP full-tank fill, {n}x{n}x{nzg} grid, 8 particles/cell ({total_particles} particles, "
+                              f"~{particles}/GPU), fp64, {'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 "
+                              f"(BASELINE configs[{2 if n == 256 else 1 if n == 128 else '-'}]" + (" per GPU" if world > 1 else "") + ")",
+                  "grid": [n, n, nzg], "particles_per_gpu": particles, "particles_total": total_particles,
+                  "parallelism": "single GPU" if world == 1 else f"{world} z-slabs of {n} planes, NCCL halo exchange + PCG all-reduces + particle migration",
+                  "l2": "inputs larger than L2 (particle arrays 48 B x particles, grid vectors 8 B x n^3)" if n >= 256
+                        else "working set may fit L2 at this n; no flush between steps"}
+        scaling = "weak"
 
     if args.impl == "reference":
         # Reference arm: the reference's CPU implementation of the path, host cores only.
@@ -163,7 +254,7 @@ def main():
         threads = os.cpu_count() or 1
         v, ms, kind, desc, has_eigen = run_cpu_sample(args.steps, max(args.warmup, 0), threads)
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": scaling,
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": desc,
                                  "eigen_from_reference": bool(has_eigen)},
@@ -195,10 +286,12 @@ def main():
         return float(t.item())
 
     f = fdist.create_slab_flip(fb, rank, world, device=local_rank, nx=n, ny=n, nz=nzg, ox=n // 2, oy=n // 2, oz=nzg // 2,
-                               max_particles=int(particles * 1.06) + 4096, precond=args.precond)
+                               max_particles=cap, precond=args.precond)
     f.seed_box(lo, hi, seed=1234)
     if world == 1:
         assert f.num_particles == particles
+    if args.workload == "pcg":
+        return bench_pcg(args, f, fb, config, rank, world, local_rank, barrier, max_over_ranks, n, nzg)
     dt = 0.1
     stats = []
     for _ in range(args.warmup):
@@ -257,12 +350,12 @@ def main():
     ms_part_step = float(np.mean([s["ms_sort"] + s["ms_p2g"] + s["ms_g2p"] for s in stats]))
     if ms_g2p_step > 0.0 and ms_part_step > 0.0:
         kernels["g2p_advect"] = {"bytes_per_particle": 99.1, "ms": ms_g2p_step,
-                                 "gbs": 99.1 * particles / (ms_g2p_step * 1e-3) / 1e9,
-                                 "frac": 99.1 * particles / (ms_g2p_step * 1e-3) / 1e9 / peak,
+                                 "gbs": 99.1 * npart / (ms_g2p_step * 1e-3) / 1e9,
+                                 "frac": 99.1 * npart / (ms_g2p_step * 1e-3) / 1e9 / peak,
                                  "source": "flipb200_stats.ms_g2p (k_cell_delta + k_g2p_cell + k_advect), mean of the timed steps"}
         kernels["particle_phase"] = {"bytes_per_particle": 151.1, "ms": ms_part_step,
-                                     "gbs": 151.1 * particles / (ms_part_step * 1e-3) / 1e9,
-                                     "frac": 151.1 * particles / (ms_part_step * 1e-3) / 1e9 / peak,
+                                     "gbs": 151.1 * npart / (ms_part_step * 1e-3) / 1e9,
+                                     "frac": 151.1 * npart / (ms_part_step * 1e-3) / 1e9 / peak,
                                      "source": "(52 + 99.1) B x particles / (ms_sort + ms_p2g + ms_g2p): sort traffic is overhead, not algorithmic"}
 
     # ---- e2e: the same step through the host-buffer entry point ----
@@ -314,7 +407,7 @@ def main():
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "cpu_baseline": cpu, "kernels": kernels, "wall_ms_per_step": wall / args.steps * 1e3,
                 "per_step": [{k: s[k] for k in ("passes", "pcg_iters_total", "ms_sort", "ms_p2g", "ms_grid", "ms_pcg",
