@@ -268,27 +268,30 @@ def test_seed_box_and_sort_invariants(fb):
         assert np.all(u[w == 0] == 0)
 
 
-def test_full_size_properties_128(fb):
-    """BASELINE config 2 size (128^3, 8 ppc full tank, 15.0 M particles) through size-independent
-    properties: particle count conservation under the cell sort, hydrostatic pressure at rest
-    (p = rho*|g|*depth within the reference's own fp32-coefficient rounding), and a fluid that
-    stays at rest (max speed after one step bounded by the under-relaxation residual)."""
-    n = 128
-    f = fb.Flip(nx=n, ny=n, nz=n, ox=64, oy=64, oz=64)
-    f.seed_box((2, 2, 2), (125, 123, 125), seed=1234)
-    assert f.num_particles == 124 * 122 * 124 * 8
+@pytest.mark.parametrize("n", [128, 256])
+def test_full_size_properties(fb, n):
+    """BASELINE configs[1] and [2] sizes (128^3: 15.0 M particles; 256^3: 127 M particles, the headline
+    configuration; 8 ppc full tank) through size-independent properties: particle count conservation
+    under the cell sort, exact cell classification, hydrostatic pressure at rest (p = rho*|g|*depth
+    within the reference's own fp32-coefficient rounding; dt = 0.125 is exact in fp32)."""
+    h = n // 2
+    f = fb.Flip(nx=n, ny=n, nz=n, ox=h, oy=h, oz=h)
+    f.seed_box((2, 2, 2), (n - 3, n - 5, n - 3), seed=1234)
+    assert f.num_particles == (n - 4) * (n - 6) * (n - 4) * 8
     f.p2g(); nf = f.classify()
-    assert nf == 124 * 123 * 124          # every interior node below the free surface (+1 layer reached by the splat)
+    assert f.num_particles == (n - 4) * (n - 6) * (n - 4) * 8
+    assert nf == (n - 4) * (n - 5) * (n - 4)   # every interior node below the free surface (+1 layer reached by the splat)
     w = f.get_grid(fb.GRID_WEIGHT)
     assert w.sum(dtype=np.float64) > 0
     dt = 0.125
     f.rhs_div(dt); it, rel = f.pcg_solve(dt)
     assert rel < 2.220446049250313e-16
     p = f.get_grid(fb.GRID_P)
-    top = 2 + 123                          # first air node index in y
-    col = p[64, 2:top, 64]
+    top = 2 + (n - 5)                      # first air node index in y
+    col = p[h, 2:top, h]
     expect = 10.0 * (top - np.arange(2, top))
     assert np.allclose(col, expect, rtol=1e-9)
+    f.close()
 
 
 # ---- multigrid-preconditioned CG (params.precond = 1) ---------------------------------------------
