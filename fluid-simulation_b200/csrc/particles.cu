@@ -331,7 +331,10 @@ __device__ __forceinline__ void st4(double* p, const double (&v)[4]) {
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
 }
 
-__global__ void __launch_bounds__(128)
+// MINB = 4 (FLIPB200_P2G=v4c) caps the kernel at 128 registers (16 warps per SM; ptxas spills 48 bytes),
+// MINB = 1 lets it take ~150 (12 warps per SM)
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB)
 k_p2g_cell4(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
             const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
             const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
@@ -428,9 +431,12 @@ int fb_p2g(flipb200_ctx* c) {
   if (c->n_sorted > 0) {
     Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
     dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
-    if (mode && mode[0] == 'v')      // FLIPB200_P2G=v4: 256-bit loads (unmeasured, see k_p2g_cell4)
-      k_p2g_cell4<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                              pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    if (mode && mode[0] == 'v' && mode[1] && mode[2] == 'c')   // FLIPB200_P2G=v4c: 256-bit loads, capped at 128 registers
+      k_p2g_cell4<4><<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                                 pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
+    else if (mode && mode[0] == 'v')   // FLIPB200_P2G=v4: 256-bit loads (unmeasured, see k_p2g_cell4)
+      k_p2g_cell4<1><<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
+                                                 pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
     else if (!(mode && mode[0] == 'r'))   // default: per-cell kernel; FLIPB200_P2G=row: shared-memory staged variant (measured 9 % slower at 8 ppc)
       k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
                                              pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
@@ -576,7 +582,8 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
 // k_g2p_cell with 256-bit particle accesses (see k_p2g_cell4).  A group of four that lies wholly inside
 // the cell's range is written back with one 256-bit store, the partial groups at either end
 // element by element (their other slots belong to the neighbouring cells' threads).
-__global__ void __launch_bounds__(128)
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB)
 k_g2p_cell4(Grid g, const int32_t* __restrict__ start,
             const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
             double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
@@ -831,8 +838,8 @@ template <int W> __device__ __forceinline__ void ldw_nc(const double* p, double 
 template <> __device__ __forceinline__ void ldw_nc<1>(const double* p, double (&v)[1]) { v[0] = __ldg(p); }
 template <> __device__ __forceinline__ void ldw_nc<4>(const double* p, double (&v)[4]) { ld4_nc(p, v); }
 
-template <int W>
-__global__ void __launch_bounds__(128)
+template <int W, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 k_g2p_advect_cell(Grid g, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
                   const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
                   const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
@@ -942,20 +949,18 @@ __global__ void k_set_dt(DevScalars* ds, double dt_max, double dxc) {
 
 // returns 0 and *done = true when the bet on dt == dt_max held (buffers swapped, step finished);
 // *done = false: nothing was changed, the caller runs the two-kernel path
-static int g2p_advect_fused(flipb200_ctx* c, int W, bool* done) {
+static int g2p_advect_fused(flipb200_ctx* c, int W, bool capped, bool* done) {
   const Grid& g = c->g;
   Particles& pt = c->pt;
   *done = false;
   const double dt_spec = c->P.dt_max;
   dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
-  if (W == 4)
-    k_g2p_advect_cell<4><<<grd, blk, 0, c->stream>>>(g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                                     pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds,
-                                                     c->P.flip_ratio, dt_spec, c->P.restitution);
-  else
-    k_g2p_advect_cell<1><<<grd, blk, 0, c->stream>>>(g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                                     pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds,
-                                                     c->P.flip_ratio, dt_spec, c->P.restitution);
+#define FUSED_ARGS g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2], \
+                   pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec, c->P.restitution
+  if (W == 4 && capped) k_g2p_advect_cell<4, 4><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
+  else if (W == 4) k_g2p_advect_cell<4, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
+  else k_g2p_advect_cell<1, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
+#undef FUSED_ARGS
   k_g2p_advect_tail<<<64, 256, 0, c->stream>>>(g, c->cell_start, c->n_sorted, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
                                                pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->ds, c->P.flip_ratio, dt_spec,
                                                c->P.restitution);
@@ -979,11 +984,11 @@ int fb_g2p_advect(flipb200_ctx* c) {
   int blocks = (int)((pt.n + 255) / 256);
   if (blocks == 0) blocks = 1;
   const char* mode = getenv("FLIPB200_G2P");
-  // FLIPB200_G2P=f1 / f4: one-pass G2P + advection, betting on dt == dt_max when the previous step ended that way
+  // FLIPB200_G2P=f1 / f4 / f4c: one-pass G2P + advection, betting on dt == dt_max when the previous step ended that way
   if (mode && mode[0] == 'f' && c->world == 1 && c->sorted && pt.n == c->n_sorted && pt.n > 0 &&
       (c->hs->dt_out == c->P.dt_max || c->hs->dt_out == 0.0)) {
     bool done = false;
-    int rc = g2p_advect_fused(c, mode[1] == '4' ? 4 : 1, &done);
+    int rc = g2p_advect_fused(c, mode[1] == '4' ? 4 : 1, mode[1] == '4' && mode[2] == 'c', &done);
     if (rc || done) return rc;
     k_reset_max<<<1, 1, 0, c->stream>>>(c->ds);
     c->launches++;
@@ -991,9 +996,12 @@ int fb_g2p_advect(flipb200_ctx* c) {
   if (c->sorted && !(mode && mode[0] == 'p' && c->world == 1)) {
     if (c->n_sorted > 0) {
       dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
-      if (mode && mode[0] == 'v')     // FLIPB200_G2P=v4: 256-bit accesses (unmeasured, see k_g2p_cell4)
-        k_g2p_cell4<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                                c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
+      if (mode && mode[0] == 'v' && mode[1] && mode[2] == 'c')   // FLIPB200_G2P=v4c: capped at 128 registers
+        k_g2p_cell4<4><<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                                   c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
+      else if (mode && mode[0] == 'v')     // FLIPB200_G2P=v4: 256-bit accesses (unmeasured, see k_g2p_cell4)
+        k_g2p_cell4<1><<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                                   c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
       else if (!(mode && mode[0] == 'r'))  // default: per-cell kernel; FLIPB200_G2P=row: shared-memory staged variant (measured 3 % slower)
         k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
                                                c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);   // dc arrays written by fb_cell_delta

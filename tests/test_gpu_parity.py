@@ -16,8 +16,8 @@ TOL_POS10 = 1e-4     # north_star: positions after 10 steps rel-L2
 # kernel variants that have not run on a GPU yet join the parametrised tests only on request
 # (FLIPB200_TEST_EXPERIMENTAL=1), so that an unmeasured variant can never turn the suite red
 _EXP = os.environ.get("FLIPB200_TEST_EXPERIMENTAL") == "1"
-PARTICLE_MODES = ["row", "cell", "particle"] + (["v4"] if _EXP else [])
-G2P_MODES = PARTICLE_MODES + (["f1", "f4"] if _EXP else [])      # one-pass G2P + advection (bet on dt == dt_max)
+PARTICLE_MODES = ["row", "cell", "particle"] + (["v4", "v4c"] if _EXP else [])
+G2P_MODES = PARTICLE_MODES + (["f1", "f4", "f4c"] if _EXP else [])      # one-pass G2P + advection (bet on dt == dt_max)
 
 
 @pytest.fixture(scope="module")
