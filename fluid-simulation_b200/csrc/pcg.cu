@@ -380,6 +380,53 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
+// k_update_p<1> with FOUR nodes per lane (block = 8 rows x 128 nodes), like k_update_xr4: since it also
+// carries x += alpha p the kernel moves 37 B/node and the two-node shape keeps ~42 B per lane in flight.
+// FLIPB200_UP4=1; NOT the default and not yet measured (written after the GPU budget of round 1 was
+// spent).  Same expressions per node as k_update_p<1>: identical bits.
+__global__ void __launch_bounds__(32 * SW_BY)
+k_update_p4(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, const float* __restrict__ zf,
+            double* __restrict__ p, double* __restrict__ x, DevScalars* __restrict__ ds, int it_arg, int noexit,
+            const __grid_constant__ PeerHalo H) {
+  if (!noexit && ds->pcg_done) return;
+  const int it = pcg_iter(ds, it_arg);
+  const bool first = it < 0;
+  const double beta = first ? 0.0 : ds->rz[it & 3] / ds->rz[(it + 3) & 3];
+  const double rrp = ds->rr[(it + 3) & 3];
+  const double invsc = rrp > 0.0 ? sqrt(rrp) : 1.0;
+  const double alpha = !first ? ds->rz[(it + 3) & 3] / ds->pAp[it & 3] : 0.0;   // as in k_update_xr4 of this iteration
+  const int i = S.box.x0 + blockIdx.x * 128 + 4 * threadIdx.x;
+  const int j = S.box.y0 + blockIdx.y * SW_BY + threadIdx.y;
+  const int k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp);
+  const bool act = i < S.xe && j < S.box.y1;
+  const int q = gidx(S.g, i, j, k);
+  if (act) {
+    const uint32_t f = *reinterpret_cast<const uint32_t*>(fl + q);
+    const double2 pa = ld2<double>(p + q), pb = ld2<double>(p + q + 2);
+    const float4 zv = *reinterpret_cast<const float4*>(zf + q);
+    const bool f0 = f & FB_FLUID, f1 = (f >> 8) & FB_FLUID, f2 = (f >> 16) & FB_FLUID, f3 = (f >> 24) & FB_FLUID;
+    if (!first) {                                    // x += alpha p with the old direction (ConjugateGradient.h:73)
+      double2 xa = ld2<double>(x + q), xb = ld2<double>(x + q + 2);
+      if (f0) xa.x += alpha * pa.x;
+      if (f1) xa.y += alpha * pa.y;
+      if (f2) xb.x += alpha * pb.x;
+      if (f3) xb.y += alpha * pb.y;
+      if (f0 | f1) st2<double>(x + q, xa.x, xa.y);
+      if (f2 | f3) st2<double>(x + q + 2, xb.x, xb.y);
+    }
+    const double z0 = (double)zv.x * invsc, z1 = (double)zv.y * invsc, z2 = (double)zv.z * invsc, z3 = (double)zv.w * invsc;
+    const double p0 = f0 ? z0 + beta * pa.x : 0.0;
+    const double p1 = f1 ? z1 + beta * pa.y : 0.0;
+    const double p2 = f2 ? z2 + beta * pb.x : 0.0;
+    const double p3 = f3 ? z3 + beta * pb.y : 0.0;
+    if (f0 | f1) st2<double>(p + q, p0, p1);
+    if (f2 | f3) st2<double>(p + q + 2, p2, p3);
+    halo_push2<double>(H, q, k, p0, p1);             // the neighbours' ghost planes see 0 off the fluid cells
+    halo_push2<double>(H, q + 2, k, p2, p3);
+  }
+  halo_signal(H, ds, k == H.kdn, k == H.kup);
+}
+
 // The stop test ended the solve between k_update_xr and k_update_p of iteration pcg_iters: apply that
 // iteration's x += alpha p (the ring slots are intact, k_pcg_advance did not run).
 __global__ void __launch_bounds__(32 * SW_BY)
@@ -481,6 +528,12 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     fb_prof(c, "allreduce rr");
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
+    const bool up4_on = [] { const char* e = getenv("FLIPB200_UP4"); return e && e[0] == '1'; }();   // experimental, see k_update_p4
+    if (up4_on && st4_on && S4.xe - S4.box.x0 >= 128) {
+      const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
+      k_update_p4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), c->flags, L0.xb, c->pd, c->x, c->ds, it_arg, noexit,
+                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg4.x * sg4.y) : halo_off());
+    } else
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, it_arg, noexit,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
   } else {
