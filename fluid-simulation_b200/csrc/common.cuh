@@ -186,6 +186,7 @@ struct flipb200_ctx {
   Particles pt;
   int64_t n_sorted;        // particles [0, n_sorted) are in cell order; [n_sorted, n) arrived by migration this step
   bool sorted;             // particle arrays are in cell order and cell_start is valid
+  bool keys_ready;         // FLIPB200_SORT=k: pt.key / pt.rank / cell_count describe the CURRENT positions (written by the last advection)
   DevScalars* ds;          // device
   DevScalars* hs;          // pinned host mirror
   Box box;                 // sweep box of this step (local planes, clipped to the owned range)

@@ -99,6 +99,7 @@ int fb_reserve_particles(flipb200_ctx* c, int64_t n) {
   for (int q = 0; q < 6; ++q) { cudaFree(pt.a[q]); cudaFree(pt.b[q]); pt.a[q] = na[q]; pt.b[q] = nb[q]; }
   cudaFree(pt.key); cudaFree(pt.rank); cudaFree(pt.id); cudaFree(pt.id_b);
   pt.key = nk; pt.rank = nr; pt.id = ni; pt.id_b = nib; pt.cap = ncap;
+  c->keys_ready = false;   // key / rank arrays were reallocated
   return 0;
 }
 
@@ -300,6 +301,7 @@ int flipb200_set_particles(flipb200_ctx* c, const double* px, const double* py, 
   if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->sorted = false;
+  c->keys_ready = false;
   if (c->world > 1) {
     // every rank is handed the whole scene and keeps the particles whose base plane it owns
     int rc = fb_sort_particles_ex(c, 1);

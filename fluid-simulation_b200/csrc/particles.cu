@@ -119,8 +119,11 @@ int fb_sort_particles_ex(flipb200_ctx* c, int filter) {
   const Grid& g = c->g;
   Particles& pt = c->pt;
   const int nb = g.total + 3;                 // cells + "outside the box" + "to lower rank" + "to upper rank"
-  CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(nb + 1) * sizeof(int32_t), c->stream));
-  if (pt.n > 0) {
+  // FLIPB200_SORT=k: the last advection already wrote key / rank / histogram of these very positions
+  const bool have_keys = c->keys_ready && c->world == 1 && !filter && pt.n > 0;
+  c->keys_ready = false;
+  if (!have_keys) CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(nb + 1) * sizeof(int32_t), c->stream));
+  if (pt.n > 0 && !have_keys) {
     int blocks = (int)((pt.n + 255) / 256);
     k_key_count<<<blocks, 256, 0, c->stream>>>(g, pt.n, pt.a[0], pt.a[1], pt.a[2], pt.key, pt.rank, c->cell_count,
                                                (filter && c->rank != 0) ? 1 : 0);
@@ -846,7 +849,8 @@ k_g2p_advect_cell(Grid g, const int32_t* __restrict__ start, const uint8_t* __re
                   double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
                   double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
                   const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest) {
+                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest,
+                  uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
   __shared__ double red[4];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -890,6 +894,10 @@ k_g2p_advect_cell(Grid g, const int32_t* __restrict__ start, const uint8_t* __re
         speed = fmax(speed, a * a + b * b + cc * cc);                       // before the collision, fluid.cc:982
         advect_one(g, fl, timestep, e_rest, X[t], Y[t], Z[t], a, b, cc, X[t], Y[t], Z[t]);
         A[t] = a; B[t] = b; C[t] = cc;
+        if (key) {                                  // FLIPB200_SORT=k: the next step's cell key and in-cell rank (k_key_count)
+          const uint32_t kx = particle_key(g, X[t], Y[t], Z[t]);
+          key[n] = kx; rank[n] = (uint32_t)atomicAdd(&count[kx], 1);
+        }
       }
       bool stored = false;
       if constexpr (W == 4) {
@@ -924,7 +932,8 @@ __global__ void k_g2p_advect_tail(Grid g, const int32_t* __restrict__ start, int
                                   const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
                                   double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
                                   double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
-                                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest) {
+                                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest,
+                                  uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
   double speed = 0.0;
   for (int64_t t = (int64_t)start[g.total] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n;
        t += (int64_t)gridDim.x * blockDim.x) {
@@ -934,9 +943,44 @@ __global__ void k_g2p_advect_tail(Grid g, const int32_t* __restrict__ start, int
     speed = fmax(speed, sqrt(a * a + b * b + cc * cc));
     advect_one(g, fl, timestep, e_rest, x, y, z, a, b, cc, x, y, z);
     opx[t] = x; opy[t] = y; opz[t] = z; ovx[t] = a; ovy[t] = b; ovz[t] = cc;
+    if (key) { const uint32_t kx = particle_key(g, x, y, z); key[t] = kx; rank[t] = (uint32_t)atomicAdd(&count[kx], 1); }
   }
   speed = warp_max(speed);
   if ((threadIdx.x & 31) == 0 && speed > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(speed));
+}
+
+// FLIPB200_SORT=k (NOT the default, unmeasured): the advection kernel also emits what k_key_count would
+// compute at the start of the next step -- the cell key of the NEW position and the particle's rank
+// in its cell (histogram atomic) -- so the next sort skips k_key_count and its 24 B/particle re-read
+// of the positions.  Single GPU.  k_advect_key = k_advect + that emission (same arithmetic: advect_one).
+__global__ void __launch_bounds__(256)
+k_advect_key(Grid g, int64_t n, const uint8_t* __restrict__ fl, double dt_max, double dxc, double e,
+             double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
+             double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
+             DevScalars* __restrict__ ds, uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double maxSpeed = __longlong_as_double((long long)ds->max_speed_bits);
+  double timestep = dt_max;                                   // fluid.cc:992-999
+  if (maxSpeed != 0.0) timestep = dt_max < dxc / maxSpeed ? dt_max : dxc / maxSpeed;
+  if (t == 0) ds->dt_out = timestep;
+  if (t >= n) return;
+  double x = px[t], y = py[t], z = pz[t];
+  double a = vx[t], b = vy[t], cc = vz[t];
+  const double a0 = a, b0 = b, c0 = cc;
+  advect_one(g, fl, timestep, e, x, y, z, a, b, cc, x, y, z);
+  px[t] = x; py[t] = y; pz[t] = z;
+  if (__double_as_longlong(a) != __double_as_longlong(a0) || __double_as_longlong(b) != __double_as_longlong(b0) ||
+      __double_as_longlong(cc) != __double_as_longlong(c0)) { vx[t] = a; vy[t] = b; vz[t] = cc; }
+  const uint32_t kx = particle_key(g, x, y, z);
+  key[t] = kx; rank[t] = (uint32_t)atomicAdd(&count[kx], 1);
+}
+static bool sort_emit_keys(const flipb200_ctx* c) {
+  const char* m = getenv("FLIPB200_SORT");
+  return m && m[0] == 'k' && c->world == 1;
+}
+static int clear_cell_count(flipb200_ctx* c) {
+  CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(c->g.total + 3 + 1) * sizeof(int32_t), c->stream));   // as fb_sort_particles_ex
+  return 0;
 }
 
 // dt of fluid.cc:992-999 from the collected max speed (the two-kernel path does this inside k_advect)
@@ -955,15 +999,18 @@ static int g2p_advect_fused(flipb200_ctx* c, int W, bool capped, bool* done) {
   *done = false;
   const double dt_spec = c->P.dt_max;
   dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
+  const bool emit = sort_emit_keys(c);
+  uint32_t* ekey = emit ? pt.key : nullptr; uint32_t* erank = emit ? pt.rank : nullptr; int32_t* ecount = emit ? c->cell_count : nullptr;
+  if (emit) { int rc = clear_cell_count(c); if (rc) return rc; }
 #define FUSED_ARGS g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2], \
-                   pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec, c->P.restitution
+                   pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec, c->P.restitution, ekey, erank, ecount
   if (W == 4 && capped) k_g2p_advect_cell<4, 4><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
   else if (W == 4) k_g2p_advect_cell<4, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
   else k_g2p_advect_cell<1, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
 #undef FUSED_ARGS
   k_g2p_advect_tail<<<64, 256, 0, c->stream>>>(g, c->cell_start, c->n_sorted, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
                                                pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->ds, c->P.flip_ratio, dt_spec,
-                                               c->P.restitution);
+                                               c->P.restitution, ekey, erank, ecount);
   k_set_dt<<<1, 1, 0, c->stream>>>(c->ds, c->P.dt_max, c->P.dx);
   CK_LAUNCH(); c->launches += 3;
   int rc = fb_fetch_scalars(c);
@@ -971,6 +1018,7 @@ static int g2p_advect_fused(flipb200_ctx* c, int W, bool capped, bool* done) {
   if (c->hs->dt_out != dt_spec) return 0;          // bet lost: pt.a is untouched
   for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
   c->sorted = false;   // positions moved: cell order is stale
+  c->keys_ready = emit;
   *done = true;
   return 0;
 }
@@ -1031,6 +1079,15 @@ int fb_g2p_advect(flipb200_ctx* c) {
   // maxSpeed is a global max (fluid.cc:976-991): every rank advects with the same dt
   int rc = fb_allreduce(c, &c->ds->max_speed_bits, 1, FB_U64, FB_MAX);
   if (rc) return rc;
+  if (sort_emit_keys(c) && pt.n > 0) {   // FLIPB200_SORT=k: advection also emits the next step's keys (k_advect_key)
+    if ((rc = clear_cell_count(c))) return rc;
+    k_advect_key<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
+                                                pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds, pt.key, pt.rank, c->cell_count);
+    CK_LAUNCH(); c->launches++;
+    c->sorted = false;
+    c->keys_ready = true;
+    return 0;
+  }
   k_advect<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
                                           pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds);
   CK_LAUNCH(); c->launches++;
@@ -1092,6 +1149,7 @@ int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint6
   CK(cudaStreamSynchronize(c->stream));
   c->pt.n = base + add;
   c->sorted = false;
+  c->keys_ready = false;
   return 0;
 }
 

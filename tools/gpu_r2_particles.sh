@@ -8,12 +8,12 @@ TAG=${1:-r2a}
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest default rc=$?"; tail -2 gpurun_out/${TAG}_pytest.log
 FLIPB200_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q -k "p2g_classify or g2p_advect" > gpurun_out/${TAG}_pytest_exp.log 2>&1; echo "pytest experimental params rc=$?"; tail -5 gpurun_out/${TAG}_pytest_exp.log
-for V in "FLIPB200_P2G=v4 FLIPB200_G2P=v4" "FLIPB200_P2G=v4 FLIPB200_G2P=f4" "FLIPB200_G2P=f1"; do
+for V in "FLIPB200_P2G=v4 FLIPB200_G2P=v4" "FLIPB200_P2G=v4 FLIPB200_G2P=f4" "FLIPB200_G2P=f1" "FLIPB200_SORT=k" "FLIPB200_SORT=k FLIPB200_G2P=f4"; do
   T=$(echo "$V" | tr ' =' '__')
   env $V timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_golden.py -m gpu -q > gpurun_out/${TAG}_pytest_${T}.log 2>&1; echo "pytest [$V] rc=$?"; tail -3 gpurun_out/${TAG}_pytest_${T}.log
 done
 n=0
-for V in "A=0" "FLIPB200_P2G=v4" "FLIPB200_P2G=v4c" "FLIPB200_G2P=v4" "FLIPB200_G2P=v4c" "FLIPB200_G2P=f1" "FLIPB200_G2P=f4" "FLIPB200_G2P=f4c" "FLIPB200_P2G=v4 FLIPB200_G2P=f4"; do
+for V in "A=0" "FLIPB200_P2G=v4" "FLIPB200_P2G=v4c" "FLIPB200_G2P=v4" "FLIPB200_G2P=v4c" "FLIPB200_G2P=f1" "FLIPB200_G2P=f4" "FLIPB200_G2P=f4c" "FLIPB200_SORT=k" "FLIPB200_P2G=v4 FLIPB200_G2P=f4" "FLIPB200_P2G=v4 FLIPB200_G2P=f4 FLIPB200_SORT=k"; do
   n=$((n+1))
   echo "== variant $n: $V"
   env $V timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e > gpurun_out/${TAG}_v${n}_bench.json 2> gpurun_out/${TAG}_v${n}_bench.err; echo "bench rc=$?"
