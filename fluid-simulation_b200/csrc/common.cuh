@@ -304,9 +304,9 @@ void fb_graph_invalidate(flipb200_ctx* c);
 int fb_mg_alloc(flipb200_ctx* c);
 void fb_mg_free(flipb200_ctx* c);
 int fb_mg_setup(flipb200_ctx* c, double dt);                    // per step: coarse flags + boxes
-int fb_mg_vcycle(flipb200_ctx* c, int it);
-void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg);
-int fb_pcg_reduce_dot(flipb200_ctx* c, int id, int it_arg);         // all-reduce of ds->part[id] into the ring (fused mailboxes or NCCL)     // part[] -> ring slots after an all-reduce                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it&3]
+int fb_mg_vcycle(flipb200_ctx* c, int it);                      // z (= mg[0].xb, fp32, scaled) = M^-1 r; r.z -> ds->rz[it & 3]
+void fb_pcg_publish(flipb200_ctx* c, int mask, int it_arg);     // ds->part[] -> ring slots after an all-reduce
+int fb_pcg_reduce_dot(flipb200_ctx* c, int id, int it_arg);     // all-reduce of ds->part[id] into the ring (fused mailboxes or NCCL)
 int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint64_t seed);
 int fb_reserve_particles(flipb200_ctx* c, int64_t n);
 int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n, int64_t id0);
