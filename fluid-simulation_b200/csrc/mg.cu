@@ -1021,6 +1021,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   bool w4[MG_MAX_LEVELS];
   const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
   const bool rz64 = [] { const char* e = getenv("FLIPB200_RZ64"); return e && e[0] == '1'; }();
+  const bool h16 = mg_h16_active(c);                // level 0: b0 and the residual stored as fp16 (experimental, pcg.cuh, mg_h16.cu)
+  const float rzs = h16 ? (float)(1.0 / (mg_h16_bscale(c) * mg_h16_bscale(c))) : 1.f;
   for (int l = 0; l < nl; ++l) {
     S[l] = make_sweep(c->mg[l].g, c->mg[l].box);
     S4[l] = make_sweep(c->mg[l].g, c->mg[l].box, 4);
@@ -1042,14 +1044,16 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     {
       PeerHalo Hs = fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs);
       if (gathered) { fb_gather_wait(c, &Hs); gathered = false; }
-      if (w4[l]) launch_smooth4<0>(tg, c->stream, Hs, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, (const double*)nullptr, c->ds, it, dist);
+      if (l == 0 && h16) fb_h16_smooth4(c, 0, tg, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, it, rzs);
+      else if (w4[l]) launch_smooth4<0>(tg, c->stream, Hs, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, (const double*)nullptr, c->ds, it, dist);
       else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
     }
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
     {
       const PeerHalo Hr = fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs);
-      if (w4[l]) launch_resid4(tg, c->stream, Hr, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
+      if (l == 0 && h16) fb_h16_resid4(c, tg, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa);
+      else if (w4[l]) launch_resid4(tg, c->stream, Hr, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
       else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds, Hr);
     }
     fb_prof(c, l == 0 ? "L0 halo+resid" : (l == 1 ? "L1 halo+resid" : "L2+ halo+resid"));
@@ -1072,7 +1076,9 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
       gathered = L.dist && !C.dist && c->halo.gather_on;
       const GatherPush G = gathered ? fb_gather_make(c, some ? cg.x * cg.y * cg.z : 1) : gather_off();
       if (some) {
-        if (r4) k_mg_restrict4<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
+        if (l == 0 && h16 && !r4) return FLIPB200_ERR_STATE;       // the fp16 residual has no two-node reader
+        if (l == 0 && h16) fb_h16_restrict4(c, cg, pblk, L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, zc);
+        else if (r4) k_mg_restrict4<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
         else k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
       } else if (gathered && G.mode == 2) k_mg_gather_signal<<<1, 32, 0, c->stream>>>(c->ds, G);
     }
@@ -1128,7 +1134,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     HALO(L, L.xb);
     {
       const PeerHalo H1 = fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs);
-      if (w4[l]) launch_smooth4<0>(tg, c->stream, H1, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, (const double*)nullptr, c->ds, it, dist);
+      if (l == 0 && h16) fb_h16_smooth4(c, 0, tg, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, it, rzs);
+      else if (w4[l]) launch_smooth4<0>(tg, c->stream, H1, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, (const double*)nullptr, c->ds, it, dist);
       else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist, H1);
     }
     fb_prof(c, l == 0 ? "L0 halo+smooth (post 1)" : (l == 1 ? "L1 halo+smooth (post 1)" : "L2+ halo+smooth (post 1)"));
@@ -1136,7 +1143,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     // the last sweep's output is read through ghosts only as the coarse correction of the level above
     if (l == 0) {
       const PeerHalo Hd = fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs);
-      if (w4[l] && rz64) launch_smooth4<1>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
+      if (h16) fb_h16_smooth4(c, 2, tg, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, it, rzs);
+      else if (w4[l] && rz64) launch_smooth4<1>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
       else if (w4[l]) launch_smooth4<2>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
       else if (rz64) k_mg_smooth<1><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);
       else k_mg_smooth<2><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);

@@ -33,11 +33,11 @@ __global__ void k_pcg_reset(DevScalars* ds, double bnorm2, double threshold, int
 
 // x = 0, r = b;  Jacobi: p = M^-1 r, rz[3] = r.p   (Eigen ConjugateGradient.h:43,63,66 with x0 = 0)
 //               MG:     b0 = float(r * sc), x1 = w D^-1 b0  (input of the first V-cycle)
-template <int MODE>
+template <int MODE, typename TB = float>   // TB: storage type of the V-cycle's right-hand side b0 (fp16: FLIPB200_MG_H16, pcg.cuh)
 __global__ void __launch_bounds__(32 * SW_BY)
 k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
            const float* __restrict__ b, double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
-           float* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds, int dist,
+           TB* __restrict__ b0, float* __restrict__ x1, double sc, DevScalars* __restrict__ ds, int dist,
            const __grid_constant__ PeerHalo H) {
   __shared__ double sm[32];
   STREAM_PROLOGUE(S)
@@ -55,7 +55,7 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
       acc[0] = r0 * p0 + r1 * p1;
     } else {
       float s0 = (float)(r0 * sc), s1 = (float)(r1 * sc);
-      st2<float>(b0 + q, s0, s1);
+      stq2<TB>(b0 + q, s0, s1);
       st2<float>(x1 + q, cf.winv[k0] * s0, cf.winv[k1] * s1);
       halo_push2<float>(H, q, k, cf.winv[k0] * s0, cf.winv[k1] * s1);
       st2<double>(p + q, 0.0, 0.0);
@@ -211,10 +211,12 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
 // k_update_xr<1> with FOUR nodes per lane (block = 8 rows x 128 nodes).  Once x += alpha p had moved
 // to k_update_p the two-node shape had too few bytes in flight: 120 us = 0.70 of the copy rate for
 // 33 B/node at 256^3.  Same arithmetic per node: identical bits.
+// TB = __half (FLIPB200_MG_H16): b0 is stored as fp16 and scaled by bscale (pcg.cuh); TB = float ignores bscale.
+template <typename TB = float>
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_xr4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
-             double* __restrict__ r, const double* __restrict__ Ap, float* __restrict__ b0, float* __restrict__ x1,
-             DevScalars* __restrict__ ds, int it_arg, int noexit, int dist, const __grid_constant__ PeerHalo H) {
+             double* __restrict__ r, const double* __restrict__ Ap, TB* __restrict__ b0, float* __restrict__ x1,
+             DevScalars* __restrict__ ds, int it_arg, int noexit, int dist, const __grid_constant__ PeerHalo H, double bscale) {
   __shared__ double sm[32];
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
@@ -229,7 +231,8 @@ k_update_xr4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf
   }
   const double alpha = rz_old / pAp;                   // ConjugateGradient.h:72
   const double rrp = ds->rr[(it + 3) & 3];
-  const double sc = rrp > 0.0 ? rsqrt(rrp) : 1.0;
+  double sc = rrp > 0.0 ? rsqrt(rrp) : 1.0;
+  if (!std::is_same<TB, float>::value) sc *= bscale;
   const int i = S.box.x0 + blockIdx.x * 128 + 4 * threadIdx.x;
   const int j = S.box.y0 + blockIdx.y * SW_BY + threadIdx.y;
   const int k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp);
@@ -252,7 +255,7 @@ k_update_xr4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf
     s.x = (float)(r0 * sc); s.y = (float)(r1 * sc); s.z = (float)(r2 * sc); s.w = (float)(r3 * sc);
     y.x = cf.winv[6 - __popc(fa & FB_SMASK)] * s.x; y.y = cf.winv[6 - __popc(fb & FB_SMASK)] * s.y;
     y.z = cf.winv[6 - __popc(fc & FB_SMASK)] * s.z; y.w = cf.winv[6 - __popc(fd & FB_SMASK)] * s.w;
-    *reinterpret_cast<float4*>(b0 + q) = s;
+    stq4<TB>(b0 + q, s);
     *reinterpret_cast<float4*>(x1 + q) = y;
     halo_push4(H, q, k, y);
   }
@@ -387,13 +390,13 @@ k_update_p(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
 __global__ void __launch_bounds__(32 * SW_BY)
 k_update_p4(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, const float* __restrict__ zf,
             double* __restrict__ p, double* __restrict__ x, DevScalars* __restrict__ ds, int it_arg, int noexit,
-            const __grid_constant__ PeerHalo H) {
+            const __grid_constant__ PeerHalo H, double inv_bscale /* 1, or 1 / bscale with FLIPB200_MG_H16 (pcg.cuh) */) {
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   const bool first = it < 0;
   const double beta = first ? 0.0 : ds->rz[it & 3] / ds->rz[(it + 3) & 3];
   const double rrp = ds->rr[(it + 3) & 3];
-  const double invsc = rrp > 0.0 ? sqrt(rrp) : 1.0;
+  const double invsc = (rrp > 0.0 ? sqrt(rrp) : 1.0) * inv_bscale;
   const double alpha = !first ? ds->rz[(it + 3) & 3] / ds->pAp[it & 3] : 0.0;   // as in k_update_xr4 of this iteration
   const int i = S.box.x0 + blockIdx.x * 128 + 4 * threadIdx.x;
   const int j = S.box.y0 + blockIdx.y * SW_BY + threadIdx.y;
@@ -497,6 +500,8 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   const int dist = c->world > 1 ? 1 : 0;
   const bool fused = use_mg && c->halo.mode != 0;
   const int k0 = c->g.k0, k1 = c->g.k1 - 1;
+  const bool h16 = use_mg && mg_h16_active(c);              // experimental fp16 storage of b0 / the level-0 residual (pcg.cuh)
+  const double bscale = h16 ? mg_h16_bscale(c) : 1.0;
   int rc;
   fb_prof(c, "start");
   if (fused) rc = fb_halo_point(c); else rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1);
@@ -517,8 +522,11 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     const Sweep S4 = make_sweep(c->g, c->box, 4);
     if (st4_on && S4.xe - S4.box.x0 >= 128) {
       const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
+      if (h16) k_update_xr4<__half><<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), cf, c->flags, c->r, c->Ap, reinterpret_cast<__half*>(L0.b), L0.xa, c->ds,
+                                                                         it_arg, noexit, dist, halo_off(), bscale);
+      else
       k_update_xr4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), cf, c->flags, c->r, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
-                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off());
+                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off(), 1.0);
     } else
       k_update_xr<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
                                                          fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
@@ -529,10 +537,11 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
     const bool up4_on = [] { const char* e = getenv("FLIPB200_UP4"); return e && e[0] == '1'; }();   // experimental, see k_update_p4
-    if (up4_on && st4_on && S4.xe - S4.box.x0 >= 128) {
+    if ((up4_on || h16) && st4_on && S4.xe - S4.box.x0 >= 128) {
       const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
       k_update_p4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), c->flags, L0.xb, c->pd, c->x, c->ds, it_arg, noexit,
-                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg4.x * sg4.y) : halo_off());
+                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg4.x * sg4.y) : halo_off(),
+                                                       h16 ? 1.0 / bscale : 1.0);
     } else
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S), cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, it_arg, noexit,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
@@ -611,12 +620,17 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   }
   c->halo.seg_base = c->halo.abs_seq;
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2, threshold, max_iter, (int)c->halo.seg_base);
-  if (use_mg)
+  const bool h16 = use_mg && mg_h16_active(c);              // experimental fp16 storage of b0 / the level-0 residual (pcg.cuh)
+  const double bscale = h16 ? mg_h16_bscale(c) : 1.0;
+  if (h16)
+    k_pcg_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, reinterpret_cast<__half*>(L0.b), L0.xa,
+                                                              (bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0) * bscale, c->ds, dist, halo_off());
+  else if (use_mg)
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, L0.b, L0.xa,
                                                       bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds, dist,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
   else {
-    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist, halo_off());
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, (float*)nullptr, nullptr, 0.0, c->ds, dist, halo_off());
     if (dist) {
       int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
       if (rc) return rc;
@@ -630,6 +644,10 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (use_mg && !done) {
     int rc = fb_mg_vcycle(c, -1);                  // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
+    if (h16) {
+      const Sweep S4 = make_sweep(c->g, c->box, 4);
+      k_update_p4<<<dim3(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z), STREAM_BLOCK, 0, c->stream>>>(S4, c->flags, L0.xb, c->pd, c->x, c->ds, -1, 0, halo_off(), 1.0 / bscale);
+    } else
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, -1, 0,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 0, halo_seg_close(c));
@@ -693,7 +711,16 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   if (use_mg) { int rc = fb_mg_setup(c, dt); if (rc) return rc; }
   c->halo.seg_base = c->halo.abs_seq;
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bn, 0.0, 1 << 30, (int)c->halo.seg_base);
-  if (use_mg) {
+  const bool h16 = use_mg && mg_h16_active(c);
+  const double bscale = h16 ? mg_h16_bscale(c) : 1.0;
+  if (h16) {
+    k_pcg_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, reinterpret_cast<__half*>(L0.b), L0.xa,
+                                                              bscale / sqrt(bn), c->ds, dist, halo_off());
+    int rc = fb_mg_vcycle(c, -1); if (rc) return rc;
+    const Sweep S4 = make_sweep(c->g, c->box, 4);
+    k_update_p4<<<dim3(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z), STREAM_BLOCK, 0, c->stream>>>(S4, c->flags, L0.xb, c->pd, c->x, c->ds, -1, 1, halo_off(), 1.0 / bscale);
+    k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1, halo_seg_close(c));
+  } else if (use_mg) {
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds, dist,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     int rc = fb_mg_vcycle(c, -1); if (rc) return rc;
@@ -701,7 +728,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1, halo_seg_close(c));
   } else {
-    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, nullptr, nullptr, 0.0, c->ds, dist, halo_off());
+    k_pcg_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, (float*)nullptr, nullptr, 0.0, c->ds, dist, halo_off());
     if (dist) {
       int rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM);
       if (rc) return rc;

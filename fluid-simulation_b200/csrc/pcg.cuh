@@ -29,3 +29,36 @@ static inline MgCoef make_mg_coef(double h2inv, double omega) {
 // kernels take the iteration number as an argument, or IT_DEV to read it from ds->pcg_it (graph replay)
 #define IT_DEV (-1000)
 __device__ __forceinline__ int pcg_iter(const DevScalars* ds, int it_arg) { return it_arg == IT_DEV ? ds->pcg_it : it_arg; }
+
+// FLIPB200_MG_H16=1 (experimental, OFF by default, unmeasured on the GPU): the level-0 right-hand side b0 and the
+// level-0 residual handed to the restriction are STORED as fp16 (arithmetic stays fp32).  Prototype
+// (tools/mg_proto7.py, full tank 128^3): 21 CG iterations either way, with r.z taken from the stored b0
+// as the fused dot does; fp16 storage of the iterates x costs 2 iterations, bf16 of anything more.
+// Saves 14 of the ~88 B/node the level-0 part of an iteration moves.  fp16 needs O(1) entries: the
+// scaled residual (|b0| = 1, entries ~ 1/sqrt(N)) is multiplied by bscale = 2^floor(log2 sqrt(N)) / 4; the
+// V-cycle is linear, k_update_p4 divides z by it again and the fused r.z by its square.
+// Single GPU, four-node sweeps only (rows >= 128 nodes); the direction update runs as k_update_p4.
+static inline bool mg_h16_active(const flipb200_ctx* c) {
+  const char* e = getenv("FLIPB200_MG_H16");
+  if (!(e && e[0] == '1') || c->world != 1 || c->mg_levels < 2) return false;
+  const char* s4 = getenv("FLIPB200_ST4");
+  if (s4 && s4[0] == '0') return false;
+  const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
+  return xe - x0 >= 128;
+}
+static inline double mg_h16_bscale(const flipb200_ctx* c) {
+  const double n = (double)(c->box.x1 - c->box.x0) * (c->box.y1 - c->box.y0) * (c->box.z1 - c->box.z0);
+  int e = 0;
+  while ((double)(1ll << (2 * (e + 1))) <= n && e < 14) ++e;     // 2^e <= sqrt(n)
+  // a quarter of that: typical entries ~0.25, and |r| may grow by an order of magnitude against the
+  // |r_prev| it is scaled with (CG residuals are not monotone) before a lone entry nears fp16's 65504
+  return (double)(1 << (e > 2 ? e - 2 : 0));
+}
+// mg_h16.cu: host wrappers of the fp16-storage copies of the level-0 sweeps
+struct Sweep;
+void fb_h16_smooth4(flipb200_ctx* c, int dot, dim3 g, const Sweep& S, const MgCoef& m, const uint8_t* fl, const float* b0,
+                    const float* xi, float* xo, int it, float rzs);
+void fb_h16_resid4(flipb200_ctx* c, dim3 g, const Sweep& S, const MgCoef& m, const uint8_t* fl, const uint8_t* nrm, const float* b0,
+                   const float* x, float* rn);
+void fb_h16_restrict4(flipb200_ctx* c, dim3 g, dim3 blk, const Grid& gf, const Box& fbox, const Grid& gc, const Box& cbox, const MgCoef& mcc,
+                      const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc);

@@ -12,6 +12,8 @@
 //                at 4.3 TB/s (65.7 us at 256^3) against 2.7 TB/s for one-thread-per-node.
 #pragma once
 #include "common.cuh"
+#include <cuda_fp16.h>
+#include <type_traits>
 
 #define ST_BY 4
 #define ST_ZP 4
@@ -31,6 +33,28 @@ template <typename T> __device__ __forceinline__ void st2(T* p, T a, T b) {
 template <typename T> __device__ __forceinline__ typename Vec2T<T>::type zero2() {
   typename Vec2T<T>::type v; v.x = T(0); v.y = T(0); return v;
 }
+
+// Storage-type helpers: a vector of fp32 values kept in memory as fp32 or fp16 (FLIPB200_MG_H16, mg.cu).
+template <typename T> __device__ __forceinline__ float4 ldq4(const T* p);
+template <> __device__ __forceinline__ float4 ldq4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <> __device__ __forceinline__ float4 ldq4<__half>(const __half* p) {
+  const uint2 raw = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&raw.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+template <typename T> __device__ __forceinline__ void stq4(T* p, float4 v);
+template <> __device__ __forceinline__ void stq4<float>(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+template <> __device__ __forceinline__ void stq4<__half>(__half* p, float4 v) {
+  const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+  uint2 raw; raw.x = *reinterpret_cast<const unsigned*>(&a); raw.y = *reinterpret_cast<const unsigned*>(&b);
+  *reinterpret_cast<uint2*>(p) = raw;
+}
+template <typename T> __device__ __forceinline__ void stq2(T* p, float a, float b);
+template <> __device__ __forceinline__ void stq2<float>(float* p, float a, float b) { st2<float>(p, a, b); }
+template <> __device__ __forceinline__ void stq2<__half>(__half* p, float a, float b) { *reinterpret_cast<__half2*>(p) = __floats2half2_rn(a, b); }
+template <typename T> __device__ __forceinline__ float ldq1(const T* p);
+template <> __device__ __forceinline__ float ldq1<float>(const float* p) { return *p; }
+template <> __device__ __forceinline__ float ldq1<__half>(const __half* p) { return __half2float(*p); }
 
 // geometry of one sweep over a box of a level
 struct Sweep {
