@@ -62,3 +62,18 @@ void fb_h16_resid4(flipb200_ctx* c, dim3 g, const Sweep& S, const MgCoef& m, con
                    const float* x, float* rn);
 void fb_h16_restrict4(flipb200_ctx* c, dim3 g, dim3 blk, const Grid& gf, const Box& fbox, const Grid& gc, const Box& cbox, const MgCoef& mcc,
                       const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc);
+
+// FLIPB200_P32=1 (experimental, OFF by default, unmeasured; pcg_p32.cu): the CG search direction stored as fp32.
+// Same conditions as the fp16 variant: single GPU, multigrid on, four-node sweeps.
+static inline bool pcg_p32_active(const flipb200_ctx* c) {
+  const char* e = getenv("FLIPB200_P32");
+  if (!(e && e[0] == '1') || c->world != 1 || c->mg_levels < 2) return false;
+  const char* s4 = getenv("FLIPB200_ST4");
+  if (s4 && s4[0] == '0') return false;
+  const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
+  return xe - x0 >= 128;
+}
+struct PcgCoef;
+void fb_p32_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit);
+void fb_p32_update_p(flipb200_ctx* c, const float* zf, int it_arg, int noexit, double inv_bscale, bool down);
+void fb_p32_finish_x(flipb200_ctx* c);

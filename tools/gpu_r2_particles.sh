@@ -27,8 +27,8 @@ print('  value %.4g  ms/step %.2f  p2g %.2f ms (%.2f)  g2p+advect %.2f ms (%.2f)
 print('  per_step', {a: round(v, 2) for a, v in d['per_step'][-1].items() if a.startswith('ms_')})
 PY
 done
-# PCG-side experiments: four-node direction update, fp16 storage of b0 / the level-0 residual
-for V in "FLIPB200_UP4=1" "FLIPB200_MG_H16=1"; do
+# PCG-side experiments: four-node direction update, fp16 storage of b0 / the level-0 residual, fp32 search direction
+for V in "FLIPB200_UP4=1" "FLIPB200_MG_H16=1" "FLIPB200_P32=1" "FLIPB200_MG_H16=1 FLIPB200_P32=1"; do
   T=$(echo "$V" | tr ' =' '__')
   env $V timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_golden.py -m gpu -q > gpurun_out/${TAG}_pytest_${T}.log 2>&1; echo "pytest [$V] rc=$?"; tail -3 gpurun_out/${TAG}_pytest_${T}.log
   env $V timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu --no-e2e > gpurun_out/${TAG}_${T}_bench.json 2> gpurun_out/${TAG}_${T}_bench.err; echo "bench [$V] rc=$?"

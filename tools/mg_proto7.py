@@ -44,8 +44,8 @@ class MGq(MGc):
         if l == 0:
             self.last_b = b                 # what the product's last sweep reads: r.z is taken as b.z (DOT = 2 in mg.cu)
         x = np.zeros_like(b)
-        for w in self.weights:
-            x = self.q(l, x + w * L.invd * (b - L.A(x)))
+        for i, w in enumerate(self.weights):      # kinds 1, 2: outputs of the pre-sweeps
+            x = self.q(l, x + w * L.invd * (b - L.A(x)), "x" if "x" in self.qkinds else str(i + 1))
         r = self.q(l, b - L.A(x), "r")
         P, fi = self.P[l]
         Lc = self.levels[l + 1]
@@ -53,9 +53,9 @@ class MGq(MGc):
         rc = np.where(Lc.active, rc, 0.0)
         ec = self.vcycle(l + 1, rc)
         e = np.zeros_like(b); e[fi[:, 0], fi[:, 1], fi[:, 2]] = P @ ec.ravel()
-        x = self.q(l, x + np.where(L.active, e, 0.0))
-        for w in self.weights[::-1]:
-            x = self.q(l, x + w * L.invd * (b - L.A(x)))
+        x = self.q(l, x + np.where(L.active, e, 0.0), "x" if "x" in self.qkinds else "3")       # kind 3: after the correction
+        for i, w in enumerate(self.weights[::-1]):                                             # kinds 4, 5: post-sweeps (5 = z)
+            x = self.q(l, x + w * L.invd * (b - L.A(x)), "x" if "x" in self.qkinds else str(4 + i))
         return x
 
 
@@ -94,7 +94,10 @@ if __name__ == "__main__":
             ("f16", 2, False, "bxr"), ("f16", 9, False, "bxr")]
     kinds = [("f32", 0, False, "bxr"), ("f16", 1, "rzb", "br"), ("f16", 1, False, "br"), ("f32", 1, "rzb", "br"), ("f16", 1, False, "xr"), ("f16", 1, False, "b"), ("f16", 1, False, "r"), ("f16", 1, False, "x"),
              ("bf16", 1, False, "r"), ("bf16", 1, True, "xr")]
-    for qtype, ql, flex, qk in (kinds if len(sys.argv) > 2 and sys.argv[2] == "kinds" else full):
+    parts = [("f32", 0, False, "bxr"), ("f16", 1, "rzb", "br1"), ("f16", 1, "rzb", "br2"), ("f16", 1, "rzb", "br3"), ("f16", 1, "rzb", "br4"),
+             ("f16", 1, "rzb", "br5"), ("f16", 1, "rzb", "br1234"), ("f16", 1, "rzb", "br234"), ("f16", 1, "rzb", "br12")]
+    sel = sys.argv[2] if len(sys.argv) > 2 else "full"
+    for qtype, ql, flex, qk in {"kinds": kinds, "parts": parts}.get(sel, full):
         mg = MGq(typ, qtype=qtype, qlevels=ql, qkinds=qk, normalize=True, nu=2, smoother="jacobi", omega=0.8, min_n=8, coarse="cheb", lmin=0.005)
         t = time.time()
         if flex == "rzb":                 # r.z := b_stored . z, as the product's fused dot does
@@ -103,5 +106,5 @@ if __name__ == "__main__":
             x, it = pcg_flex(L, b, lambda r: mg.vcycle(0, r), flexible=flex)
         if xref is None:
             xref = x
-        print(f"storage {qtype:5s} of {qk:3s} on levels < {ql}  flexible beta {flex!s:5s}  iters {it:3d}  |x - x_f32| / |x| = "
+        print(f"storage {qtype:5s} of {qk:6s} on levels < {ql}  flexible beta {flex!s:5s}  iters {it:3d}  |x - x_f32| / |x| = "
               f"{np.linalg.norm(x - xref) / np.linalg.norm(xref):.1e}  {time.time() - t:.1f}s", flush=True)
