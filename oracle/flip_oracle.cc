@@ -727,6 +727,11 @@ const uint8_t* oracle_solid(oracle_ctx* c) { return c->solid.data(); }
 int oracle_num_active(oracle_ctx* c) { return c->numActive; }
 const double* oracle_b(oracle_ctx* c) { return c->b.data(); }
 const double* oracle_p(oracle_ctx* c) { return c->p.data(); }
+const double* oracle_b2(oracle_ctx* c) { return c->b2.data(); }
+int64_t oracle_triplets(oracle_ctx* c, const int32_t** rows, const int32_t** cols, const double** vals) {
+  *rows = c->trow.data(); *cols = c->tcol.data(); *vals = c->tval.data();
+  return (int64_t)c->trow.size();
+}
 
 int oracle_kat_solve_dense(int n, const double* A, const double* b, double* x) {
 #ifdef ORACLE_WITH_EIGEN

@@ -15,13 +15,19 @@
  * ConjugateGradient<SparseMatrix<double>, Lower|Upper, IncompleteCholesky<double>>
  * exactly as fluid.cc:1352,1473-1474 does (see eigen_solver.cc).
  *
- * Parity pinning: the reference has NO tests or golden vectors for fluid.cc ("parity
- * unpinned" by the reference for P2G/classify/RHS/divergence/velUpdate/relaxation/G2P/
- * advection).  What pins this oracle: (1) the pressure arithmetic is the reference's own
- * Eigen code; (2) analytic known-answer tests taken from the reference tree's adjacent
- * unit tests (openvdb/unittest/TestConjGradient.cc:57-101 5x5 system,
- * openvdb/unittest/TestPoissonSolver.cc:215-290 hydrostatic P=-y); (3) hand-derived
- * facts in SURVEY.md 3.2 (step-0 pass count 8, error sequence 0.9 .. 0.092).
+ * Parity pinning: PINNED BY THE REFERENCE'S OWN CODE.  The reference has no tests or golden vectors
+ * for fluid.cc, so the pin is the reference itself: /root/reference/fluid.cc compiles UNMODIFIED (main
+ * renamed) over the dense-array OpenVDB/TBB stand-in of oracle/shim/ with the reference's vendored Eigen
+ * (oracle/ref_bridge.cc -> oracle/_ref/libfluid_ref.so), and tests/test_ref_pin.py checks BIT FOR BIT that
+ * (a) every function of the step body (P2Gtransfer, interpolate, setRHS, setDiver, setA, setA2 + the matrix
+ * handed to Eigen, cg.solve, velUpdate, setOnlyB, FLIPadvect, extrapolate, advect, interpFromGrid) returns
+ * what this restatement returns on three adversarial 121^3 scenes (walls, interior obstacle, strays outside
+ * the box, round() ties), and (b) the reference's own main() run for three steps of its own loop on its own
+ * scene ends in the same particles, grid velocities, cell numbering, pass counts and dt as oracle_step x 3.
+ * Also: the known-answer tests the reference tree holds next to the path
+ * (openvdb/unittest/TestConjGradient.cc:57-101, TestPoissonSolver.cc:215-290) and the hand analysis of
+ * SURVEY.md 3.2 (tests/test_oracle.py).  Only the scatterer's voxel visiting order (VDB tree order) is not
+ * reproduced: initial positions are distribution-equivalent (irrelevant to parity, both sides get the same arrays).
  *
  * Layout: grid arrays are flat, idx = (k*ny + j)*nx + i with i = x + ox etc. (x fastest);
  * reference coordinate c = (i-ox, j-oy, k-oz).  Loops that carry sequential semantics
@@ -104,6 +110,9 @@ const uint8_t* oracle_solid(oracle_ctx*);
 int            oracle_num_active(oracle_ctx*);
 const double*  oracle_b(oracle_ctx*);       /* numActive */
 const double*  oracle_p(oracle_ctx*);       /* numActive */
+const double*  oracle_b2(oracle_ctx*);      /* numActive: setOnlyB's vector (fluid.cc:1481) */
+/* the triplet list setA2 hands to setFromTriplets (fluid.cc:498-540), in push order; returns its length */
+int64_t oracle_triplets(oracle_ctx*, const int32_t** rows, const int32_t** cols, const double** vals);
 
 /* Known-answer helper: solve a small dense SPD system with the reference's solver type
  * (used with openvdb/unittest/TestConjGradient.cc:66-92).  Returns iterations, <0 if no Eigen. */

@@ -46,8 +46,11 @@ _lib = None
 
 
 def build(force=False):
-    """Run oracle/Makefile (port always; _ref only when /root/reference is present)."""
-    if force or not os.path.exists(PORT_LIB) or (os.path.isdir("/root/reference/Eigen") and not os.path.exists(REF_LIB)):
+    """Run oracle/Makefile (make decides what is stale): the port always; oracle/_ref (restatement + the
+    reference's Eigen, and the reference's own fluid.cc over oracle/shim) only when /root/reference is
+    present -- on the GPU box the prebuilt files are used as they travelled."""
+    have_ref = os.path.isdir("/root/reference/Eigen")
+    if force or have_ref or not os.path.exists(PORT_LIB):
         subprocess.check_call(["make", "-s", "-C", _HERE, "all"], env={**os.environ, "CXX": "/usr/bin/g++"})
 
 
@@ -107,6 +110,10 @@ def load(prefer_ref=True):
     lib.oracle_b.restype = dp
     lib.oracle_p.argtypes = [C.c_void_p]
     lib.oracle_p.restype = dp
+    lib.oracle_b2.argtypes = [C.c_void_p]
+    lib.oracle_b2.restype = dp
+    lib.oracle_triplets.argtypes = [C.c_void_p, C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(dp)]
+    lib.oracle_triplets.restype = C.c_int64
     lib.oracle_kat_solve_dense.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.oracle_kat_solve_dense.restype = C.c_int
     _lib = lib
@@ -200,6 +207,20 @@ class Oracle:
     def p(self):
         n = self.num_active
         return np.ctypeslib.as_array(self.lib.oracle_p(self.h), shape=(n,)) if n else np.zeros(0)
+
+    @property
+    def b2(self):
+        n = self.num_active
+        return np.ctypeslib.as_array(self.lib.oracle_b2(self.h), shape=(n,)) if n else np.zeros(0)
+
+    def triplets(self):
+        """(rows, cols, vals) of the list setA2 builds (fluid.cc:498-540), push order."""
+        r = C.POINTER(C.c_int32)(); c_ = C.POINTER(C.c_int32)(); v = C.POINTER(C.c_double)()
+        n = self.lib.oracle_triplets(self.h, C.byref(r), C.byref(c_), C.byref(v))
+        if n == 0:
+            return np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0)
+        return (np.ctypeslib.as_array(r, shape=(n,)).copy(), np.ctypeslib.as_array(c_, shape=(n,)).copy(),
+                np.ctypeslib.as_array(v, shape=(n,)).copy())
 
     # stages
     def clear_vel(self): self.lib.oracle_clear_vel(self.h)

@@ -1,0 +1,3 @@
+/* oracle/shim stand-in (TEST INFRASTRUCTURE): fluid.cc includes <openvdb/points/PointCount.h> but uses no symbol
+ * that is not already provided by the dense-array stand-in <openvdb/openvdb.h> of this directory. */
+#include <openvdb/openvdb.h>
