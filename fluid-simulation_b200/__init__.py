@@ -64,6 +64,7 @@ EXPORTS = [
     "flipb200_host_alloc", "flipb200_host_free",
     "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
     "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab", "flipb200_halo_mode", "flipb200_debug_info",
+    "flipb200_profile_iteration",
 ]
 
 _lib = None
@@ -121,6 +122,7 @@ def load():
     lib.flipb200_get_particle_ids.argtypes = [vp, vp, C.c_int64]
     lib.flipb200_halo_mode.argtypes = [vp]
     lib.flipb200_debug_info.argtypes = [vp, ip]
+    lib.flipb200_profile_iteration.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, ip]
     lib.flipb200_step_host_slab.argtypes = [vp] + [vp] * 6 + [C.c_int64, C.c_int64, C.POINTER(C.c_int64), dp, vp,
                                                               C.POINTER(Stats)]
     _lib = lib
@@ -340,6 +342,16 @@ class Flip:
         if a.shape != self.shape:
             raise ValueError("grid shape")
         _check(self.lib.flipb200_set_grid(self.h, which, _ptr(a), a.nbytes), "set_grid")
+
+    def profile_iteration(self, iters=10):
+        """[(stage name, microseconds)] of one PCG iteration, in launch order (plain launches, CUDA events)."""
+        cap, W = 96, 40
+        names = C.create_string_buffer(cap * W)
+        us = (C.c_float * cap)()
+        n = C.c_int32(0)
+        _check(self.lib.flipb200_profile_iteration(self.h, iters, cap, names, us, C.byref(n)), "profile_iteration")
+        raw = names.raw
+        return [(raw[m * W:(m + 1) * W].split(b"\0", 1)[0].decode(), float(us[m])) for m in range(n.value)]
 
     def time_kernel(self, which, iters):
         ms = C.c_float(0)

@@ -462,6 +462,7 @@ PeerHalo fb_halo_make(flipb200_ctx* c, int lin, int ain, int lout, int aout, siz
   HaloState& hs = c->halo;
   if (hs.mode == 0) return h;
   h.mode = hs.mode; h.kdn = kdn; h.kup = kup; h.nb = nb;
+  h.acq_sys = hs.acq_sys;
   if (hs.dbg) { h.dbg = hs.dbg + 8 * (hs.dbg_n % HALO_DBG_MAX); hs.dbg_n++; }
   h.my_flags = hs.flags; h.cnt = hs.flags + 2;
   h.sig_dn = hs.peer_flags[0] ? hs.peer_flags[0] + 1 : nullptr;
@@ -527,6 +528,7 @@ void fb_gather_wait(flipb200_ctx* c, PeerHalo* h) {
   HaloState& hs = c->halo;
   if (!hs.gather_on || hs.mode != 2) return;
   h->mode = 2;
+  h->acq_sys = hs.acq_sys;
   h->gat_flags = hs.mail->gflag_ptr();
   h->gat_n = c->world; h->gat_self = c->rank;
   h->gat_rel = (int)(hs.gather_seq - hs.seg_base);
@@ -566,6 +568,7 @@ int fb_halo_setup(flipb200_ctx* c) {
   if (c->world == 1 || !c->comm || c->mg_levels < 2 || c->mg_nd < 1) return 0;
   const char* e = getenv("FLIPB200_FUSED_HALO");
   if (e && e[0] == '0') return 0;
+  { const char* a = getenv("FLIPB200_HALO_ACQ"); hs.acq_sys = (a && a[0] == 'g') ? 0 : 1; }   // halo.cuh: consumer-side acquire scope
   CK(cudaMalloc((void**)&hs.flags, 8 * sizeof(unsigned)));   // [0,1] flags, [2,3] push counters, [4] gather counter
   {
     const char* de = getenv("FLIPB200_HALO_DEBUG");

@@ -121,6 +121,10 @@ struct IterProf {
   const char* name[PROF_MAX];
   double acc[PROF_MAX];
   int iters;
+  bool request;                // flipb200_profile_iteration: profile the next fb_pcg_time(PCG_ITER) and keep the result below
+  int out_n;                   // stages of the last profiled run
+  float out_us[PROF_MAX];
+  const char* out_name[PROF_MAX];
 };
 struct Comm;   // comm.cu: NCCL (one process per GPU) or in-process threaded ranks (tests)
 
@@ -131,6 +135,7 @@ struct HaloState {
   unsigned long long* dbg;   // FLIPB200_HALO_DEBUG=1: 8 timestamps per fb_halo_make call of an iteration
   int dbg_n;
   int mode;                          // 0 off (halo copies), 1 push + host barrier (in-process ranks), 2 push + device flags
+  int acq_sys;                       // consumer acquires at system scope (default 1; FLIPB200_HALO_ACQ=gpu -> 0), halo.cuh
   unsigned* flags;                   // device: [0..1] flags written by the lower / upper neighbour, [2..3] block counters
   unsigned* peer_flags[2];           // the neighbours' flag blocks (peer mappings): [0] lower, [1] upper
   void* peer[2][MG_MAX_LEVELS][3];   // the neighbours' arrays: [dir][level][HA_*]

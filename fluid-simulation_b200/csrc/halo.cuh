@@ -49,6 +49,10 @@ struct PeerHalo {
   // pushed its planes (GatherPush below): gat_flags[r] >= halo_base + gat_rel for r != gat_self
   const unsigned* gat_flags;
   int gat_n, gat_self, gat_rel;
+  // consumer-side acquire: 1 (default) = after the relaxed spin ONE ld.acquire.sys of the flag, so that the
+  // acquire's scope covers the releasing thread on the other GPU (PTX memory model: synchronizes-with needs
+  // a scope that includes both threads); 0 (FLIPB200_HALO_ACQ=gpu) = the round-1 gpu-scope fence.
+  int acq_sys;
 };
 __device__ __forceinline__ unsigned long long halo_now() {
   unsigned long long t;
@@ -93,7 +97,7 @@ __device__ __forceinline__ void halo_wait(const PeerHalo& H, DevScalars* ds, boo
       const long long t0 = clock64();
       while ((int)(ld_relaxed_sys(&H.gat_flags[t]) - need) < 0)
         if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
-      fence_acq_rel_gpu();
+      if (H.acq_sys) (void)ld_acquire_sys(&H.gat_flags[t]); else fence_acq_rel_gpu();
     }
     __syncthreads();
   }
@@ -116,11 +120,17 @@ __device__ __forceinline__ void halo_wait(const PeerHalo& H, DevScalars* ds, boo
       while ((int)(ld_relaxed_sys(&H.my_flags[1]) - need) < 0)
         if (clock64() - t0 > HALO_SPIN_LIMIT) { ds->pcg_status = FLIPB200_ERR_COMM; break; }
     }
-    // The ghost planes and the flag live in THIS GPU's memory; the neighbour ordered them with a
-    // system-scope release.  What is left to do here is to keep this SM's later loads behind the flag
-    // load and away from stale L1 lines: a gpu-scope fence (0.7 us; the system-scope one costs 3.5 us
-    // of round trip that orders nothing more on the reading side).
-    fence_acq_rel_gpu();
+    // The neighbour (another GPU) ordered its plane stores before the flag with a system-scope release.
+    // The acquire that pairs with it must be at a scope that includes that thread: ONE ld.acquire.sys of
+    // the flag after the relaxed spin (the polls themselves stay relaxed: an acquire per poll is a
+    // system-scope round trip each time).  It reads the value the spin saw (or a later one of the same
+    // release sequence), so it synchronizes-with the release; bar.sync below extends that to the block.
+    // FLIPB200_HALO_ACQ=gpu keeps round 1's gpu-scope fence (works on this box, not guaranteed by the model).
+    if (H.acq_sys) {
+      if (w0) (void)ld_acquire_sys(&H.my_flags[0]);
+      if (w1) (void)ld_acquire_sys(&H.my_flags[1]);
+    } else
+      fence_acq_rel_gpu();
     if (H.dbg && blockIdx.x == 0 && blockIdx.y == 0) H.dbg[w0 ? 2 : 3] = halo_now();
   }
   __syncthreads();

@@ -747,7 +747,8 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   }
   bool graph = false;
   const char* pe = getenv("FLIPB200_PROFILE_ITER");
-  const bool prof = pe && pe[0] == '1' && which == FLIPB200_KERNEL_PCG_ITER;
+  const bool prof_env = pe && pe[0] == '1';
+  const bool prof = (prof_env || (c->prof && c->prof->request)) && which == FLIPB200_KERNEL_PCG_ITER;
   if (prof && !c->prof) c->prof = (IterProf*)calloc(1, sizeof(IterProf));
   if (which == FLIPB200_KERNEL_PCG_ITER && !prof) graph = get_iteration_graph(c, S, cf, use_mg, dt, 1);
   for (int it = 0; it < 3 + iters; ++it) {
@@ -776,11 +777,16 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     IterProf* p = c->prof;
     double tot = 0.0;
     for (int m = 1; m < p->n; ++m) tot += p->acc[m] / p->iters;
+    p->out_n = 0;
+    for (int m = 1; m < p->n; ++m) { p->out_us[p->out_n] = (float)(p->acc[m] / p->iters * 1e3); p->out_name[p->out_n] = p->name[m]; p->out_n++; }
+    p->request = false;
+    if (prof_env) {
     fprintf(stderr, "flipb200 rank %d: PCG iteration profile over %d iterations (plain launches), total %.1f us\n", c->rank, p->iters, tot * 1e3);
     for (int m = 1; m < p->n; ++m) fprintf(stderr, "  r%d %-28s %8.1f us\n", c->rank, p->name[m], p->acc[m] / p->iters * 1e3);
+    }
     for (int m = 0; m < PROF_MAX; ++m) p->acc[m] = 0.0;
     p->iters = 0;
-    if (c->halo.dbg) {   // boundary-block timestamps of the last profiled iteration (ns, relative to the first)
+    if (c->halo.dbg && prof_env) {   // boundary-block timestamps of the last profiled iteration (ns, relative to the first)
       unsigned long long h[8 * HALO_DBG_MAX];
       CK(cudaMemcpy(h, c->halo.dbg, sizeof(h), cudaMemcpyDeviceToHost));
       unsigned long long t0 = ~0ull;

@@ -254,4 +254,24 @@ int flipb200_time_kernel(flipb200_ctx* c, int which, int32_t iters, float* ms_pe
   }
 }
 
+int flipb200_profile_iteration(flipb200_ctx* c, int32_t iters, int32_t cap, char* names, float* us, int32_t* n_out) {
+  if (!c || !names || !us || !n_out || iters < 1 || cap < 1) return FLIPB200_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  if (!c->prof) c->prof = (IterProf*)calloc(1, sizeof(IterProf));
+  if (!c->prof) return FLIPB200_ERR_ARG;
+  c->prof->request = true;
+  c->prof->out_n = 0;
+  float ms = 0.f; int64_t units = 0;
+  int rc = fb_pcg_time(c, FLIPB200_KERNEL_PCG_ITER, iters, &ms, &units);
+  c->prof->request = false;
+  if (rc) return rc;
+  const int n = c->prof->out_n < cap ? c->prof->out_n : cap;
+  for (int m = 0; m < n; ++m) {
+    us[m] = c->prof->out_us[m];
+    snprintf(names + (size_t)m * FLIPB200_PROFILE_NAME, FLIPB200_PROFILE_NAME, "%s", c->prof->out_name[m]);
+  }
+  *n_out = n;
+  return FLIPB200_OK;
+}
+
 }  // extern "C"

@@ -174,6 +174,13 @@ enum { FLIPB200_KERNEL_SPMV = 0, FLIPB200_KERNEL_PCG_ITER = 1, FLIPB200_KERNEL_P
        FLIPB200_KERNEL_G2P = 3, FLIPB200_KERNEL_SORT = 4 };
 int  flipb200_time_kernel(flipb200_ctx*, int which, int32_t iters, float* ms_per_launch, int64_t* units);
 
+/* Stage-by-stage device times of ONE PCG iteration (plain launches with a CUDA event between the stages,
+ * averaged over `iters` iterations of the current system, no convergence exit): names[m] (FLIPB200_PROFILE_NAME
+ * bytes each, e.g. "k_spmv", "L0 halo+smooth", "tail (small levels + coarsest)") and us[m], m < *n <= cap.
+ * A stage name can occur more than once (levels >= 2 share one name).  bench.py's roofline.by_kernel. */
+#define FLIPB200_PROFILE_NAME 40
+int  flipb200_profile_iteration(flipb200_ctx*, int32_t iters, int32_t cap, char* names, float* us, int32_t* n);
+
 /* Pinned host memory helpers for the e2e path (cudaHostAlloc / cudaFreeHost). */
 int  flipb200_host_alloc(void** ptr, size_t bytes);
 int  flipb200_host_free(void* ptr);

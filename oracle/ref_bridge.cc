@@ -120,6 +120,8 @@ extern "C" {
 int ref_grid_dim(void) { return RD; }
 int ref_grid_origin(void) { return RB; }
 double ref_spline(double x) { return spline(x); }
+/* threads of the tbb::parallel_for stand-in (1 = serial, deterministic; > 1 for timing the reference arm) */
+void ref_set_threads(int t) { openvdb::shim::state().threads = t < 1 ? 1 : t; }
 
 void* ref_world_create(void) { return new World(); }
 void ref_world_destroy(void* h) { delete static_cast<World*>(h); }

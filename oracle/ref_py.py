@@ -40,6 +40,7 @@ def load():
     lib = C.CDLL(LIB)
     vp, d, i64 = C.c_void_p, C.c_double, C.c_int64
     lib.ref_spline.restype = d; lib.ref_spline.argtypes = [d]
+    lib.ref_set_threads.argtypes = [C.c_int]
     lib.ref_world_create.restype = vp
     lib.ref_world_destroy.argtypes = [vp]
     for nm in ("ref_get_fgrid", "ref_set_fgrid"):
@@ -85,6 +86,11 @@ def load():
 
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+def set_threads(t):
+    """threads of the tbb::parallel_for stand-in: 1 = serial in index order (pinning), > 1 = timing runs"""
+    load().ref_set_threads(int(t))
 
 
 def spline(x):

@@ -43,6 +43,7 @@
 #include <random>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #ifndef SHIM_LIM
@@ -130,6 +131,7 @@ struct State {
   std::vector<void*> point_lists;                 /* the PointAccessor handed to UniformPointScatter */
   std::vector<Vec3d> last_scatter;                /* points offered to PointList::add by the last operator() */
   std::function<void(const std::string&)> on_file_write;
+  int threads = 1;                                /* tbb::parallel_for stand-in: 1 = serial in index order (parity runs) */
 };
 inline State& state() { static State s; return s; }
 struct StopRun {};                                /* thrown by the hook to leave ref_main after K steps */
@@ -283,9 +285,24 @@ class UniformPointScatter {
 }  // namespace openvdb
 
 namespace tbb {
+/* threads == 1: serial, index order (deterministic; what the pinning tests use).  threads > 1 (timing runs of
+ * the reference arm only): contiguous chunks on std::threads -- the reference's own per-node mutexes
+ * (fluid.cc:290-294, :872-874) and its maxSpeed mutex (:984-989) are what make its bodies safe under TBB,
+ * and they are just as safe here; chunk boundaries are multiples of 64 so that the vector<bool> bodies
+ * (:899-902) never share a word. */
 template <typename I0, typename I1, typename F>
 inline void parallel_for(I0 first, I1 last, const F& f) {
-  for (size_t i = (size_t)first; i < (size_t)last; ++i) f(i);
+  const size_t a = (size_t)first, b = (size_t)last;
+  const int T = openvdb::shim::state().threads;
+  if (T <= 1 || b - a < 4096) { for (size_t i = a; i < b; ++i) f(i); return; }
+  const size_t chunk = (((b - a) + T - 1) / T + 63) & ~(size_t)63;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < T; ++t) {
+    const size_t lo = a + (size_t)t * chunk, hi = std::min(b, lo + chunk);
+    if (lo >= hi) break;
+    pool.emplace_back([lo, hi, &f]() { for (size_t i = lo; i < hi; ++i) f(i); });
+  }
+  for (std::thread& th : pool) th.join();
 }
 }  // namespace tbb
 
