@@ -622,7 +622,7 @@ def bench_cube_drop(job, n, steps, warmup):
         first.append(st.as_dict())
     dev_s, wall, stats, clocks, launches, dt = run_steps(job, f, steps, max(0, warmup - NCHK), dt=dt, sample_clocks=False)
     check = {"steps": step_consistency(job, f, stats, total)}
-    nf0 = (side + 1) ** 3                                   # nodes the splat of a free-floating cube reaches
+    nf0 = (side + 2) ** 3                                   # nodes the splat of a free-floating cube reaches: voxels lo..hi -> nodes lo-1..hi+1
     check["first_step_cells"] = {"ok": bool(first[0]["n_fluid"] == nf0) if first else True, "n_fluid": first[0]["n_fluid"] if first else None, "closed_form": nf0}
     if world > 1 and rank == 0 and ref_stats and first:
         worst = 0.0

@@ -73,6 +73,8 @@ struct DevScalars {
   int pcg_it;                        // current iteration (kernels launched from a CUDA graph read it here)
   int n_invalid;                     // particles whose support lies outside the box
   int x_pending;                     // the stop test fired before k_update_p<1> applied x += alpha p (k_pcg_finish_x)
+  double warm_gamma;                 // warm start: x0 = gamma * guess (residual-minimising scale)
+  double warm_rr0;                   // |b - A x0|^2 as accumulated by the warm init (exact)
   // z-slab runs: kernels accumulate this rank's share of the current dot products here; after the
   // all-reduce k_pcg_publish moves the sum into the ring slot (single GPU: straight into the ring)
   double part[4];                    // [0] p.Ap  [1] r.z  [2] r.r
@@ -180,6 +182,11 @@ struct flipb200_ctx {
   float  *bf[2];           // diver (= b) ping-pong: [cur] is b of this pass, [cur^1] receives b2
   int     bcur;
   double *x, *r, *pd, *Ap; // PCG vectors (x = pressure on the grid)
+  double *xprev;           // warm start: the solution of the pass before the last one (params.warm_start)
+  bool x_valid;            // c->x holds a converged solution (0 off the current fluid cells: k_classify keeps that invariant)
+  int pass_idx;            // relaxation pass of the solve about to run (0 = first of the step; set by the step loop)
+  int xprev_pass;          // pass whose solution xprev holds (-1: none in this step)
+  double last_rate;        // decimal digits of |r|^2 gained per iteration in the previous solve (sizes the first launch batch)
   MgLevel mg[MG_MAX_LEVELS];
   int mg_levels;           // 0 => hierarchy not allocated (precond != 1)
   int mg_nd;               // levels [0, mg_nd) are slab-distributed, [mg_nd, mg_levels) replicated (0 when world == 1)

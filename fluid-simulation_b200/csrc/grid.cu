@@ -18,7 +18,7 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
            double* __restrict__ u0, double* __restrict__ u1, double* __restrict__ u2,
            double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
            double* __restrict__ xpress,
-           const uint8_t* __restrict__ fs, uint8_t* __restrict__ fl, DevScalars* __restrict__ ds) {
+           const uint8_t* __restrict__ fs, uint8_t* __restrict__ fl, DevScalars* __restrict__ ds, int keep_x) {
   __shared__ int sred[7][8];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -35,11 +35,13 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
       u0[q] = a; u1[q] = b; u2[q] = cc;
     }
     b0[q] = a; b1[q] = b; b2[q] = cc;
-    xpress[q] = 0.0;
     uint8_t f = fs[q];
     // a fluid cell whose six neighbours are all solid has Adiag == 0 and no row in the
     // reference's matrix (fluid.cc:498); it is left out of the system here as well.
     bool fluid = !(f & FB_SOLID) && w > 0.0f && (f & FB_SMASK) != FB_SMASK;
+    // pressure: 0 off the fluid cells (every solver kernel relies on it); with params.warm_start the value of a
+    // cell that stays fluid survives as the next solve's initial guess (pcg.cu)
+    if (!(keep_x && fluid)) xpress[q] = 0.0;
     if (fluid) {
       f |= FB_FLUID; cnt = 1;
       mnx = mxx = i; mny = mxy = j; mnz = mxz = k + g.kg0;   // bbox in GLOBAL planes
@@ -153,7 +155,7 @@ int fb_classify(flipb200_ctx* c) {
   k_reset_classify<<<1, 1, 0, c->stream>>>(c->ds);
   dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.k1 - g.k0);
   k_classify<<<grd, blk, 0, c->stream>>>(g, c->wacc, c->wf, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1],
-                                         c->ub[2], c->x, c->flags_static, c->flags, c->ds);
+                                         c->ub[2], c->x, c->flags_static, c->flags, c->ds, (c->P.warm_start && c->x_valid) ? 1 : 0);
   CK_LAUNCH(); c->launches += 2;
   int rc;
   if (c->P.extrapolate && (rc = fb_extrapolate(c))) return rc;

@@ -926,6 +926,76 @@ k_g2p_advect_cell(Grid g, const int32_t* __restrict__ start, const uint8_t* __re
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// G2P + advection in ONE pass, one thread per PARTICLE (round 2).  The per-cell kernels above issue 8-byte
+// loads 64 B apart (32 sectors per warp request) and cannot write the advected positions without the same
+// scatter; the one-pass per-cell kernel measured 7.1 ms against 4.7 ms for the two kernels
+// (profiles/r2a_variants_ab.txt).  Here consecutive lanes take consecutive particles: six fully coalesced
+// loads, six fully coalesced stores into the alternate buffers; the 8 x 3 cell-centred deltas are gathered
+// with read-only loads that hit L1 (cell-sorted order: a warp touches ~4 cells).  dt is a function of the
+// global max speed (fluid.cc:992-999), so the kernel bets on dt == dt_max (true whenever
+// maxSpeed <= dx / dt_max; tried only when the previous step ended that way) exactly like
+// g2p_advect_fused: the inputs stay untouched until the bet is known to hold.  Same operation sequence per
+// particle as k_g2p followed by k_advect.  Works on any particle order (sorted or not).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_g2p_advect_pp(Grid g, int64_t n, const uint8_t* __restrict__ fl,
+                const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
+                const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
+                double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
+                double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
+                const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
+                DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest,
+                uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
+  __shared__ double red[8];
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double speed = 0.0;
+  if (t < n) {
+    double x = __ldg(px + t), y = __ldg(py + t), z = __ldg(pz + t);
+    double a = __ldg(vx + t), b = __ldg(vy + t), cc = __ldg(vz + t);
+    const uint32_t kq = particle_key(g, x, y, z);
+    if (kq < (uint32_t)g.total) {
+      const int q = (int)kq;
+      const int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
+      const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+      const double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
+      const double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
+      const double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+      double wsum = 0, dx = 0, dy = 0, dz = 0;
+#pragma unroll
+      for (int m = 0; m < 8; ++m) {
+        const int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
+        const int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
+        const bool in = inside_shell(g, ii, jj, kk);                 // fluid.cc:237 (no solid test)
+        const double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
+        const double ex = in ? __ldg(dcx + qq) : 0.0, ey = in ? __ldg(dcy + qq) : 0.0, ez = in ? __ldg(dcz + qq) : 0.0;
+        if (in) wsum += cw;
+        dx += ex * cw; dy += ey * cw; dz += ez * cw;
+      }
+      if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }            // PIC/FLIP blend (see k_cell_delta)
+      if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }   // as k_g2p_cell
+    } else if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }
+    speed = a * a + b * b + cc * cc;                                       // before the collision, fluid.cc:982
+    advect_one(g, fl, timestep, e_rest, x, y, z, a, b, cc, x, y, z);
+    opx[t] = x; opy[t] = y; opz[t] = z; ovx[t] = a; ovy[t] = b; ovz[t] = cc;
+    if (key) {                                  // the next step's cell key and in-cell rank (what k_key_count computes)
+      const uint32_t kx = particle_key(g, x, y, z);
+      key[t] = kx; rank[t] = (uint32_t)atomicAdd(&count[kx], 1);
+    }
+  }
+  speed = sqrt(warp_max(speed));
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = speed;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double m = red[0];
+#pragma unroll
+    for (int q2 = 1; q2 < 8; ++q2) m = fmax(m, red[q2]);
+    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
+  }
+}
+
 // the trailing "outside the box" bucket of the fused path: no grid contact (k_speed_tail), then advection
 __global__ void k_g2p_advect_tail(Grid g, const int32_t* __restrict__ start, int64_t n /* = n_sorted */, const uint8_t* __restrict__ fl,
                                   const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
@@ -1004,6 +1074,21 @@ static int g2p_advect_fused(flipb200_ctx* c, int W, bool capped, bool* done) {
   if (emit) { int rc = clear_cell_count(c); if (rc) return rc; }
 #define FUSED_ARGS g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2], \
                    pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec, c->P.restitution, ekey, erank, ecount
+  if (W == 0) {
+    k_g2p_advect_pp<<<(unsigned)((pt.n + 255) / 256), 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1],
+                                                                         pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec,
+                                                                         c->P.restitution, ekey, erank, ecount);
+    k_set_dt<<<1, 1, 0, c->stream>>>(c->ds, c->P.dt_max, c->P.dx);
+    CK_LAUNCH(); c->launches += 2;
+    int rc0 = fb_fetch_scalars(c);
+    if (rc0) return rc0;
+    if (c->hs->dt_out != dt_spec) return 0;          // bet lost: pt.a is untouched
+    for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
+    c->sorted = false;
+    c->keys_ready = emit;
+    *done = true;
+    return 0;
+  }
   if (W == 4 && capped) k_g2p_advect_cell<4, 4><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
   else if (W == 4) k_g2p_advect_cell<4, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
   else k_g2p_advect_cell<1, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
@@ -1036,7 +1121,7 @@ int fb_g2p_advect(flipb200_ctx* c) {
   if (mode && mode[0] == 'f' && c->world == 1 && c->sorted && pt.n == c->n_sorted && pt.n > 0 &&
       (c->hs->dt_out == c->P.dt_max || c->hs->dt_out == 0.0)) {
     bool done = false;
-    int rc = g2p_advect_fused(c, mode[1] == '4' ? 4 : 1, mode[1] == '4' && mode[2] == 'c', &done);
+    int rc = g2p_advect_fused(c, mode[1] == 'p' ? 0 : (mode[1] == '4' ? 4 : 1), mode[1] == '4' && mode[2] == 'c', &done);
     if (rc || done) return rc;
     k_reset_max<<<1, 1, 0, c->stream>>>(c->ds);
     c->launches++;

@@ -68,6 +68,125 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
   if (MODE == 1) halo_signal(H, ds, k == H.kdn, k == H.kup);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Warm start (params.warm_start; Eigen's cg.solve() starts from x = 0, ConjugateGradient.h:233-237, the stop
+// rule |r|^2 < tol^2 |b|^2 is unchanged).  The guess g is the previous solution, which k_classify keeps only
+// on cells that are still fluid; over the relaxation passes of one step the right-hand sides obey
+// b_{k+1} = th b_k + G with th = 1 - 1/relax_div (fluid.cc:1475: velUpdate applies a tenth of the gradient), so
+// from pass 3 on g = x_k + th (x_k - x_{k-1}) (k_warm_extrap).  x0 = gamma g with the residual-minimising
+// gamma = (b . A g) / (A g . A g); then |r0|^2 = |b|^2 - gamma (b . A g) is known from the two dot products
+// before r0 itself is formed, which gives the fp32 / fp16 V-cycle input its O(1) scale in the same pass.
+//   k_warm_extrap   g = x + th (x - xprev), xprev = x                         (passes >= 3)   32 B/node
+//   k_warm_ax       Ap = A g, (b . Ap), (Ap . Ap)                                             21 B/node
+//   k_warm_scalars  gamma, |r0|^2 estimate -> ring slot 2 (scale of the first V-cycle)
+//   k_warm_init     x = gamma g, r = b - gamma Ap, |r|^2 -> ring slot 3; MG: b0, x1; Jacobi: p, r.z   45 B/node
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32 * SW_BY)
+k_warm_extrap(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, double* __restrict__ x, double* __restrict__ xprev,
+              double theta, int have_prev) {
+  STREAM_PROLOGUE(S)
+  if (!act) return;
+  const double2 xv = ld2<double>(x + q);
+  if (have_prev) {
+    const double2 pv = ld2<double>(xprev + q);
+    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    const double g0 = (f.x & FB_FLUID) ? xv.x + theta * (xv.x - pv.x) : 0.0;
+    const double g1 = (f.y & FB_FLUID) ? xv.y + theta * (xv.y - pv.y) : 0.0;
+    st2<double>(x + q, g0, g1);
+  }
+  st2<double>(xprev + q, xv.x, xv.y);
+}
+
+__global__ void __launch_bounds__(32 * ST_BY)
+k_warm_ax(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+          const float* __restrict__ b, const double* __restrict__ x, double* __restrict__ Ap, DevScalars* __restrict__ ds) {
+  __shared__ double sm[64];
+  double acc[2] = {0.0, 0.0};
+  StencilMarch<double> m;
+  if (m.begin(S, x)) {
+    const int kend = min(m.k + ST_ZP, S.box.z1);
+#pragma unroll
+    for (int z = 0; z < ST_ZP; ++z) {
+      if (m.k >= kend) break;
+      m.load(S, x);
+      uchar2 f = m.act ? *reinterpret_cast<const uchar2*>(fl + m.q) : make_uchar2(0, 0);
+      const float2 bv = m.act ? ld2<float>(b + m.q) : make_float2(0.f, 0.f);
+      double a0 = 0.0, a1 = 0.0;
+      if (f.x & FB_FLUID) { a0 = cf.diag[6 - __popc(f.x & FB_SMASK)] * m.c0() + cf.off * m.sum0(); acc[0] += (double)bv.x * a0; acc[1] += a0 * a0; }
+      if (f.y & FB_FLUID) { a1 = cf.diag[6 - __popc(f.y & FB_SMASK)] * m.c1() + cf.off * m.sum1(); acc[0] += (double)bv.y * a1; acc[1] += a1 * a1; }
+      if (m.act) st2<double>(Ap + m.q, a0, a1);
+      m.advance(S);
+    }
+  }
+  block_sum<2>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    if (acc[0] != 0.0) atomicAdd(&ds->part[PART_PAP], acc[0]);
+    if (acc[1] != 0.0) atomicAdd(&ds->part[PART_RZ], acc[1]);
+  }
+}
+
+__global__ void k_warm_scalars(DevScalars* ds, double bnorm2) {
+  const double bAg = ds->part[PART_PAP], AgAg = ds->part[PART_RZ];
+  ds->part[PART_PAP] = 0.0; ds->part[PART_RZ] = 0.0;
+  double gamma = AgAg > 0.0 ? bAg / AgAg : 0.0;
+  if (!(gamma == gamma) || !(fabs(gamma) < 1e300)) gamma = 0.0;
+  double rr = bnorm2 - gamma * bAg;                     // |b - gamma A g|^2 at the optimal gamma
+  const double floor_rr = bnorm2 * 1e-24;               // cancellation guard: the estimate only scales the V-cycle input
+  if (!(rr > floor_rr)) rr = floor_rr > 0.0 ? floor_rr : bnorm2;
+  ds->warm_gamma = gamma;
+  ds->rr[2] = rr;                                       // "iteration -1" scale read by the first direction update
+  ds->rr[3] = 0.0;                                      // k_warm_init accumulates the exact |r0|^2 here
+}
+
+template <int MODE, typename TB = float>
+__global__ void __launch_bounds__(32 * SW_BY)
+k_warm_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
+            const float* __restrict__ b, double* __restrict__ x, double* __restrict__ r, double* __restrict__ p,
+            const double* __restrict__ Ap, TB* __restrict__ b0, float* __restrict__ x1, double bscale,
+            DevScalars* __restrict__ ds, int dist, const __grid_constant__ PeerHalo H) {
+  __shared__ double sm[64];
+  const double gamma = ds->warm_gamma;
+  const double rr_est = ds->rr[2];
+  const double sc = (rr_est > 0.0 ? rsqrt(rr_est) : 1.0) * bscale;
+  STREAM_PROLOGUE(S)
+  double acc[2] = {0.0, 0.0};
+  if (act) {
+    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    const float2 bv = ld2<float>(b + q);
+    const double2 xv = ld2<double>(x + q), av = ld2<double>(Ap + q);
+    const bool f0 = f.x & FB_FLUID, f1 = f.y & FB_FLUID;
+    const double r0 = f0 ? (double)bv.x - gamma * av.x : 0.0, r1 = f1 ? (double)bv.y - gamma * av.y : 0.0;
+    st2<double>(x + q, f0 ? gamma * xv.x : 0.0, f1 ? gamma * xv.y : 0.0);
+    st2<double>(r + q, r0, r1);
+    acc[0] = r0 * r0 + r1 * r1;
+    const int k0 = 6 - __popc(f.x & FB_SMASK), k1 = 6 - __popc(f.y & FB_SMASK);
+    if (MODE == 0) {
+      const double p0 = r0 * cf.inv[k0], p1 = r1 * cf.inv[k1];
+      st2<double>(p + q, p0, p1);
+      acc[1] = r0 * p0 + r1 * p1;
+    } else {
+      const float s0 = (float)(r0 * sc), s1 = (float)(r1 * sc);
+      stq2<TB>(b0 + q, s0, s1);
+      st2<float>(x1 + q, cf.winv[k0] * s0, cf.winv[k1] * s1);
+      halo_push2<float>(H, q, k, cf.winv[k0] * s0, cf.winv[k1] * s1);
+      st2<double>(p + q, 0.0, 0.0);
+    }
+  }
+  block_sum<2>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    if (acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RR] : &ds->rr[3], acc[0]);
+    if (MODE == 0 && acc[1] != 0.0) atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[3], acc[1]);
+  }
+  if (MODE == 1) halo_signal(H, ds, k == H.kdn, k == H.kup);
+}
+
+// stop test on the warm start's own residual (0 iterations) and the scale of iteration 0
+__global__ void k_warm_check(DevScalars* ds) {
+  const double rr = ds->rr[3];
+  ds->warm_rr0 = rr;
+  if (rr < ds->threshold) { ds->pcg_done = 1; ds->pcg_iters = 0; ds->rr_final = rr; ds->x_pending = 0; }
+}
+
 // K1: Ap = A p and p.Ap (STENCIL shape: z-march in registers, x neighbours by shuffle)
 __global__ void __launch_bounds__(32 * ST_BY)
 k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
@@ -538,7 +657,7 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     fb_prof(c, "allreduce rr");
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
-    const bool up4_on = [] { const char* e = getenv("FLIPB200_UP4"); return e && e[0] == '1'; }();   // experimental, see k_update_p4
+    const bool up4_on = true;                       // four nodes per lane whenever the rows are wide enough (k_update_p4)
     if (p32) fb_p32_update_p(c, L0.xb, it_arg, noexit, h16 ? 1.0 / bscale : 1.0, true);
     else if ((up4_on || h16) && st4_on && S4.xe - S4.box.x0 >= 128) {
       const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
@@ -623,9 +742,37 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   }
   c->halo.seg_base = c->halo.abs_seq;
   k_pcg_reset<<<1, 1, 0, c->stream>>>(c->ds, bnorm2, threshold, max_iter, (int)c->halo.seg_base);
-  const bool h16 = use_mg && mg_h16_active(c);              // experimental fp16 storage of b0 / the level-0 residual (pcg.cuh)
+  const bool h16 = use_mg && mg_h16_active(c);              // fp16 storage of b0 / the level-0 residual (pcg.cuh)
   const double bscale = h16 ? mg_h16_bscale(c) : 1.0;
-  if (h16)
+  // warm start: only from a converged previous solution, and never for b = 0 (Eigen returns x = 0 there)
+  const bool warm = c->P.warm_start && c->x_valid && c->xprev && bnorm2 > 0.0 && bnorm2 == bnorm2 && max_iter > 0;
+  c->x_valid = false;
+  if (warm) {
+    const double theta = 1.0 - 1.0 / (double)c->P.relax_div;
+    // passes >= 3 of a step: extrapolate along b_{k+1} - b_k = theta (b_k - b_{k-1}); pass 2 only remembers x_1
+    if (c->pass_idx >= 1) {
+      const int have = (c->pass_idx >= 2 && c->xprev_pass == c->pass_idx - 2) ? 1 : 0;
+      k_warm_extrap<<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->xprev, theta, have);
+      c->xprev_pass = c->pass_idx - 1;
+      c->launches++;
+    } else c->xprev_pass = -1;
+    int rc = fb_halo_fill(c, c->g, c->x, sizeof(double), 1, 1);     // z-slabs: ghost planes of the guess
+    if (rc) return rc;
+    k_warm_ax<<<stencil_grid(S), STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->Ap, c->ds);
+    if (dist && (rc = fb_allreduce(c, &c->ds->part[PART_PAP], 2, FB_F64, FB_SUM))) return rc;    // (b.Ag, Ag.Ag) are adjacent
+    k_warm_scalars<<<1, 1, 0, c->stream>>>(c->ds, bnorm2);
+    const PeerHalo Hw = (use_mg && fused) ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off();
+    if (h16) k_warm_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, reinterpret_cast<__half*>(L0.b), L0.xa, bscale, c->ds, dist, Hw);
+    else if (use_mg) k_warm_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, 1.0, c->ds, dist, Hw);
+    else k_warm_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, (float*)nullptr, nullptr, 1.0, c->ds, dist, halo_off());
+    if (dist) {
+      if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 2, FB_F64, FB_SUM))) return rc;           // r.z (Jacobi) and r.r are adjacent
+      fb_pcg_publish(c, use_mg ? (1 << PART_RR) : ((1 << PART_RZ) | (1 << PART_RR)), -1);
+    }
+    k_warm_check<<<1, 1, 0, c->stream>>>(c->ds);
+    CK_LAUNCH(); c->launches += 5;
+    if ((rc = fb_fetch_scalars(c))) return rc;          // one round trip: |r0|^2 sizes the first batch, and the guess may already pass
+  } else if (h16)
     k_pcg_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, reinterpret_cast<__half*>(L0.b), L0.xa,
                                                               (bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0) * bscale, c->ds, dist, halo_off());
   else if (use_mg)
@@ -643,7 +790,8 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   CK_LAUNCH(); c->launches += 2;
   if (bnorm2 == 0.0) return 0;                     // rhsNorm2 == 0 => x = 0, 0 iterations (ConjugateGradient.h:46-52)
   if (!(bnorm2 == bnorm2)) return FLIPB200_ERR_BREAKDOWN;
-  bool done = max_iter == 0;
+  bool done = max_iter == 0 || (warm && c->hs->pcg_done != 0);
+  const double rr_start = warm ? c->hs->warm_rr0 : bnorm2;
   if (use_mg && !done) {
     int rc = fb_mg_vcycle(c, -1);                  // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
@@ -661,6 +809,10 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   // first batch: as many iterations as the previous solve needed (consecutive solves of a scene need
   // the same number +-1: usually one batch, one host round trip), then small batches
   int batch = c->last_iters > 4 ? c->last_iters : (use_mg ? 8 : 32);
+  if (warm && c->last_rate > 0.0 && rr_start > threshold) {      // digits still to gain / digits per iteration of the last solve
+    const int need = (int)ceil(log10(rr_start / threshold) / c->last_rate) + 1;
+    batch = need < 2 ? 2 : need;
+  }
   int it = 0;
   while (!done) {
     int stop = min(it + batch, max_iter);
@@ -687,6 +839,12 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     CK_LAUNCH(); c->launches++;
   }
   c->last_iters = c->hs->pcg_iters;
+  if (c->hs->pcg_iters > 0 && c->hs->rr_final > 0.0 && rr_start > c->hs->rr_final)
+    c->last_rate = log10(rr_start / c->hs->rr_final) / c->hs->pcg_iters;
+  c->x_valid = c->hs->pcg_status == 0 && c->hs->pcg_done != 0;
+  if (getenv("FLIPB200_WARM_DEBUG"))
+    fprintf(stderr, "flipb200 solve: pass %d warm %d gamma %.6g |r0|/|b| %.3e iters %d rate %.3f digits/it\n", c->pass_idx, (int)warm,
+            warm ? c->hs->warm_gamma : 0.0, sqrt(rr_start / bnorm2), c->hs->pcg_iters, c->last_rate / 2);
   if (iters_out) *iters_out = c->hs->pcg_iters;
   if (rel_out) *rel_out = sqrt(c->hs->rr_final / bnorm2);          // cg.error(), ConjugateGradient.h:88
   if (c->hs->pcg_status == FLIPB200_ERR_BREAKDOWN) return FLIPB200_ERR_BREAKDOWN;
@@ -700,6 +858,7 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
 int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units) {
   const Sweep S = make_sweep(c->g, c->box);
   if (sweep_empty(S)) return FLIPB200_ERR_STATE;
+  c->x_valid = false;                              // the timing loop overwrites x
   const double dt = c->P.dt_max;
   PcgCoef cf; fb_make_coef(c, dt, &cf);
   const dim3 sg = stream_grid(S), tg = stencil_grid(S);

@@ -30,7 +30,7 @@ static inline MgCoef make_mg_coef(double h2inv, double omega) {
 #define IT_DEV (-1000)
 __device__ __forceinline__ int pcg_iter(const DevScalars* ds, int it_arg) { return it_arg == IT_DEV ? ds->pcg_it : it_arg; }
 
-// FLIPB200_MG_H16=1 (experimental, OFF by default, unmeasured on the GPU): the level-0 right-hand side b0 and the
+// params.mixed bit 1 (default ON since round 2: measured -26 us per iteration at 256^3, profiles/r2a_variants_ab.txt): the level-0 right-hand side b0 and the
 // level-0 residual handed to the restriction are STORED as fp16 (arithmetic stays fp32).  Prototype
 // (tools/mg_proto7.py, full tank 128^3): 21 CG iterations either way, with r.z taken from the stored b0
 // as the fused dot does; fp16 storage of the iterates x costs 2 iterations, bf16 of anything more.
@@ -39,8 +39,7 @@ __device__ __forceinline__ int pcg_iter(const DevScalars* ds, int it_arg) { retu
 // V-cycle is linear, k_update_p4 divides z by it again and the fused r.z by its square.
 // Single GPU, four-node sweeps only (rows >= 128 nodes); the direction update runs as k_update_p4.
 static inline bool mg_h16_active(const flipb200_ctx* c) {
-  const char* e = getenv("FLIPB200_MG_H16");
-  if (!(e && e[0] == '1') || c->world != 1 || c->mg_levels < 2) return false;
+  if (!(c->P.mixed & 2) || c->world != 1 || c->mg_levels < 2) return false;
   const char* s4 = getenv("FLIPB200_ST4");
   if (s4 && s4[0] == '0') return false;
   const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
@@ -63,11 +62,10 @@ void fb_h16_resid4(flipb200_ctx* c, dim3 g, const Sweep& S, const MgCoef& m, con
 void fb_h16_restrict4(flipb200_ctx* c, dim3 g, dim3 blk, const Grid& gf, const Box& fbox, const Grid& gc, const Box& cbox, const MgCoef& mcc,
                       const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc);
 
-// FLIPB200_P32=1 (experimental, OFF by default, unmeasured; pcg_p32.cu): the CG search direction stored as fp32.
+// params.mixed bit 0 (default ON since round 2: measured -32 us per iteration, same iteration counts; pcg_p32.cu): the CG search direction stored as fp32.
 // Same conditions as the fp16 variant: single GPU, multigrid on, four-node sweeps.
 static inline bool pcg_p32_active(const flipb200_ctx* c) {
-  const char* e = getenv("FLIPB200_P32");
-  if (!(e && e[0] == '1') || c->world != 1 || c->mg_levels < 2) return false;
+  if (!(c->P.mixed & 1) || c->world != 1 || c->mg_levels < 2) return false;
   const char* s4 = getenv("FLIPB200_ST4");
   if (s4 && s4[0] == '0') return false;
   const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)

@@ -24,6 +24,7 @@ int relax_loop(flipb200_ctx* c, double dt, flipb200_stats* st, float* ms_pcg) {
   do {
     int iters = 0; double rel = 0.0;
     cudaEventRecord(c->ev[4], c->stream);
+    c->pass_idx = passes;
     rc = fb_pcg_solve(c, dt, &iters, &rel);
     cudaEventRecord(c->ev[5], c->stream);
     if (rc) return rc;
@@ -177,6 +178,7 @@ int flipb200_pcg_solve(flipb200_ctx* c, double dt, int32_t* iters, double* rel_r
   if (c->stage < 3) return FLIPB200_ERR_STATE;
   CK(cudaSetDevice(c->device));
   int it = 0; double rel = 0.0;
+  c->pass_idx = 0;
   int rc = fb_pcg_solve(c, dt, &it, &rel);
   if (iters) *iters = it;
   if (rel_resid) *rel_resid = rel;

@@ -60,6 +60,15 @@ typedef struct {
                                 extrapolate (fluid.cc:705-802) on the P2G velocities -- layer by layer every
                                 air node gets the average of the nodes defined one layer earlier (single GPU) */
   int64_t max_particles;     /* capacity to reserve; 0 => grow on set_particles               */
+  /* ---- solver options without a counterpart in the reference (round 2) ---- */
+  int32_t warm_start;        /* 1 (default): CG starts from the previous pressure -- the last pass's / step's solution on the
+                                cells that are still fluid, extrapolated over the relaxation passes (b_{k+1} = (1 - 1/relax_div) b_k + G
+                                within a step) and scaled by the residual-minimising factor; same stop rule |r|^2 < tol^2 |b|^2.
+                                0: x0 = 0, what cg.solve() does (Eigen ConjugateGradient.h:233-237)                               */
+  int32_t mixed;             /* storage precision INSIDE the fp64 solve (arithmetic stays fp64 / fp32): bit 0 = CG search direction
+                                stored as fp32, bit 1 = level-0 multigrid right-hand side and residual stored as fp16.
+                                default 3; 0 = everything at full width.  Single GPU, rows >= 128 nodes; ignored otherwise.       */
+  int32_t reserved[6];
 } flipb200_params;
 
 /* per-step statistics (the reference prints none of these except dt and error) */

@@ -47,7 +47,7 @@ class Flip:
         if tuple(lo) == (2, 2, 2) and hi[0] == s.nx - 3:
             s.nf = (s.nx - 4) * (s.ny - 5) * (s.nz - 4)
         else:
-            s.nf = (hi[0] - lo[0] + 2) * (hi[1] - lo[1] + 2) * (hi[2] - lo[2] + 2)
+            s.nf = (hi[0] - lo[0] + 3) * (hi[1] - lo[1] + 3) * (hi[2] - lo[2] + 3)
 
     @property
     def num_particles(s): return s.n

@@ -1,21 +1,19 @@
 #!/bin/bash
-# multi-GPU round: NCCL slab test + scaling bench.  usage: tools/gpu_multi.sh <tag> <ngpu> [n]
-TAG=${1:-m}; NG=${2:-2}; N=${3:-256}
+# usage: gpurun --gpus N --timeout 1500 -- 'bash tools/gpu_multi.sh <tag> <N> [steps] [extra bench args]'
+TAG=${1:-r2m}; N=${2:-2}; STEPS=${3:-5}; shift 3
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=index,name --format=csv > gpurun_out/${TAG}_smi.txt 2>&1
-if [ "${SKIP_TEST:-0}" = "0" ]; then timeout 600 python -m pytest tests/test_gpu_nccl.py -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest.log; fi
-timeout 300 python bench.py --grid-n $N --steps 3 --warmup 3 --no-cpu > gpurun_out/${TAG}_bench_1.json 2> gpurun_out/${TAG}_bench_1.err; echo "bench1 rc=$?"
-G=2
-while [ $G -le $NG ]; do
-  NCCL_DEBUG=WARN timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $G --master-addr 127.0.0.1 --master-port 29517 bench.py --grid-n $N --gpus $G --steps 3 --warmup 3 --no-cpu > gpurun_out/${TAG}_bench_$G.json 2> gpurun_out/${TAG}_bench_$G.err; echo "bench$G rc=$?"
-  tail -3 gpurun_out/${TAG}_bench_$G.err
-  G=$((G*2))
-done
-for f in gpurun_out/${TAG}_bench_*.json; do echo $f; python - "$f" <<'PY'
-import json,sys
+timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps $STEPS --warmup 3 "$@" > gpurun_out/${TAG}_bench_n${N}.json 2> gpurun_out/${TAG}_bench_n${N}.err; echo "bench N=$N rc=$?"
+tail -c 1500 gpurun_out/${TAG}_bench_n${N}.err
+python - <<PY
+import json
 try:
-    d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
-    print({k:d.get(k) for k in ['value','ms_per_step','n_gpus']}, d['e2e'] and d['e2e']['value'], d['kernels'], d['per_step'][-1])
-except Exception as e: print('ERR',e)
+    d=json.loads(open('gpurun_out/${TAG}_bench_n${N}.json').read().strip().splitlines()[-1])
+    print('value %.4g ms/step %.2f e2e %s checks_ok %s' % (d['value'], d['ms_per_step'], d.get('e2e') and '%.4g' % d['e2e']['value'], d['checks_ok']))
+    print('check', json.dumps(d['check'])[:1200])
+    print('iter us', d['roofline']['by_kernel']['pcg_iteration']['us'])
+    for k in ('pcg','dam_break_column','cube_drop_512'):
+        if k in d: print(k, 'value %.4g ms/step %.2f' % (d[k]['value'], d[k]['ms_per_step']), json.dumps(d[k]['check'])[:1400])
+    print([ (s['passes'], s['pcg_iters_total'], round(s['ms_total'],1)) for s in d['per_step']])
+except Exception as e:
+    print('parse failed', e)
 PY
-done
