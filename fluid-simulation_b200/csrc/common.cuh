@@ -183,6 +183,10 @@ struct flipb200_ctx {
   int     bcur;
   double *x, *r, *pd, *Ap; // PCG vectors (x = pressure on the grid)
   double *xprev;           // warm start: the solution of the pass before the last one (params.warm_start)
+  double *xfirst;          // warm start: the first pass's solution of the previous step (guess of the next step's first pass)
+  double *xG;              // warm start: A^-1 G of the previous step (x_2 - th x_1), guess of the second pass: x_2 = th x_1 + xG
+  bool have_first, have_G; // xfirst / xG hold data
+  int last_step_passes;    // passes of the last finished step (0: unknown): 1 => x is that step's first solution, 2 => (xprev, x) = (x_1, x_2)
   bool x_valid;            // c->x holds a converged solution (0 off the current fluid cells: k_classify keeps that invariant)
   int pass_idx;            // relaxation pass of the solve about to run (0 = first of the step; set by the step loop)
   int xprev_pass;          // pass whose solution xprev holds (-1: none in this step)

@@ -211,7 +211,7 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
     if (alloc_n(c, &c->u[a], T) || alloc_n(c, &c->ub[a], T)) goto fail;
   if (alloc_n(c, &c->wacc, T) || alloc_n(c, &c->wf, T) || alloc_n(c, &c->bf[0], T) || alloc_n(c, &c->bf[1], T)) goto fail;
   if (alloc_n(c, &c->x, T) || alloc_n(c, &c->r, T) || alloc_n(c, &c->pd, T) || alloc_n(c, &c->Ap, T)) goto fail;
-  if (c->P.warm_start && alloc_n(c, &c->xprev, T)) goto fail;
+  if (c->P.warm_start && (alloc_n(c, &c->xprev, T) || alloc_n(c, &c->xfirst, T) || alloc_n(c, &c->xG, T))) goto fail;
   if (alloc_n(c, &c->cell_count, T + 8) || alloc_n(c, &c->cell_start, T + 8) || alloc_n(c, &c->scan_tmp, T / 2048 + 64)) goto fail;
   if (alloc_n(c, &c->ds, 1)) goto fail;
   if (world > 1 && alloc_n(c, &c->halo_tmp, 4 * (size_t)plane)) goto fail;
@@ -282,7 +282,7 @@ void flipb200_destroy(flipb200_ctx* c) {
   cudaFree(c->solid); cudaFree(c->flags); cudaFree(c->flags_static); cudaFree(c->ext_layer);
   for (int a = 0; a < 3; ++a) { cudaFree(c->u[a]); cudaFree(c->ub[a]); }
   cudaFree(c->wacc); cudaFree(c->wf); cudaFree(c->bf[0]); cudaFree(c->bf[1]);
-  cudaFree(c->x); cudaFree(c->r); cudaFree(c->pd); cudaFree(c->Ap); cudaFree(c->xprev);
+  cudaFree(c->x); cudaFree(c->r); cudaFree(c->pd); cudaFree(c->Ap); cudaFree(c->xprev); cudaFree(c->xfirst); cudaFree(c->xG);
   cudaFree(c->cell_count); cudaFree(c->cell_start); cudaFree(c->scan_tmp);
   for (int q = 0; q < 6; ++q) { cudaFree(c->pt.a[q]); cudaFree(c->pt.b[q]); }
   cudaFree(c->pt.key); cudaFree(c->pt.rank); cudaFree(c->pt.id); cudaFree(c->pt.id_b);

@@ -81,20 +81,35 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
 //   k_warm_scalars  gamma, |r0|^2 estimate -> ring slot 2 (scale of the first V-cycle)
 //   k_warm_init     x = gamma g, r = b - gamma Ap, |r|^2 -> ring slot 3; MG: b0, x1; Jacobi: p, r.z   45 B/node
 // ---------------------------------------------------------------------------------------------
+// guess of pass k of a step (th = 1 - 1/relax_div); all guesses are masked to the current fluid cells
+//   MODE 0 (first pass):   if pendG: xG = x - th xprev (the last step ended after two passes);  x = src (x itself or xfirst)
+//   MODE 1 (second pass):  xprev = xfirst = x (= x_1);  x = th x_1 + xG
+//   MODE 2 (third pass):   xG = x - th xprev;  g = x + th (x - xprev);  xprev = x
+//   MODE 3 (later passes): g = x + th (x - xprev);  xprev = x
+template <int MODE>
 __global__ void __launch_bounds__(32 * SW_BY)
-k_warm_extrap(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, double* __restrict__ x, double* __restrict__ xprev,
-              double theta, int have_prev) {
+k_warm_guess(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, double* __restrict__ x, double* __restrict__ xprev,
+             double* __restrict__ xfirst, double* __restrict__ xG, double theta, int pendG, int src_first, int have_G) {
   STREAM_PROLOGUE(S)
   if (!act) return;
+  const uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+  const bool f0 = f.x & FB_FLUID, f1 = f.y & FB_FLUID;
   const double2 xv = ld2<double>(x + q);
-  if (have_prev) {
+  if (MODE == 0) {
+    if (pendG) { const double2 pv = ld2<double>(xprev + q); st2<double>(xG + q, xv.x - theta * pv.x, xv.y - theta * pv.y); }
+    if (src_first) { const double2 sv = ld2<double>(xfirst + q); st2<double>(x + q, f0 ? sv.x : 0.0, f1 ? sv.y : 0.0); }
+  } else if (MODE == 1) {
+    st2<double>(xprev + q, xv.x, xv.y);
+    st2<double>(xfirst + q, xv.x, xv.y);
+    double g0 = theta * xv.x, g1 = theta * xv.y;
+    if (have_G) { const double2 gv = ld2<double>(xG + q); g0 += gv.x; g1 += gv.y; }
+    st2<double>(x + q, f0 ? g0 : 0.0, f1 ? g1 : 0.0);
+  } else {
     const double2 pv = ld2<double>(xprev + q);
-    uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
-    const double g0 = (f.x & FB_FLUID) ? xv.x + theta * (xv.x - pv.x) : 0.0;
-    const double g1 = (f.y & FB_FLUID) ? xv.y + theta * (xv.y - pv.y) : 0.0;
-    st2<double>(x + q, g0, g1);
+    if (MODE == 2) st2<double>(xG + q, xv.x - theta * pv.x, xv.y - theta * pv.y);
+    st2<double>(x + q, f0 ? xv.x + theta * (xv.x - pv.x) : 0.0, f1 ? xv.y + theta * (xv.y - pv.y) : 0.0);
+    st2<double>(xprev + q, xv.x, xv.y);
   }
-  st2<double>(xprev + q, xv.x, xv.y);
 }
 
 __global__ void __launch_bounds__(32 * ST_BY)
@@ -749,13 +764,27 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   c->x_valid = false;
   if (warm) {
     const double theta = 1.0 - 1.0 / (double)c->P.relax_div;
-    // passes >= 3 of a step: extrapolate along b_{k+1} - b_k = theta (b_k - b_{k-1}); pass 2 only remembers x_1
-    if (c->pass_idx >= 1) {
-      const int have = (c->pass_idx >= 2 && c->xprev_pass == c->pass_idx - 2) ? 1 : 0;
-      k_warm_extrap<<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->xprev, theta, have);
-      c->xprev_pass = c->pass_idx - 1;
-      c->launches++;
-    } else c->xprev_pass = -1;
+    // guess (see k_warm_guess): first pass from the previous step's first solution, second pass th x_1 + A^-1 G of the
+    // previous step, later passes extrapolated along b_{k+1} - b_k = th (b_k - b_{k-1})
+    const int pk = c->pass_idx;
+    if (pk == 0) {
+      const int pendG = c->last_step_passes == 2 ? 1 : 0;
+      const int src_first = (c->last_step_passes != 1 && c->have_first) ? 1 : 0;
+      if (pendG || src_first) {
+        k_warm_guess<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->xprev, c->xfirst, c->xG, theta, pendG, src_first, 0);
+        c->launches++;
+      }
+      if (pendG) c->have_G = true;
+      c->last_step_passes = 0;
+      c->xprev_pass = -1;
+    } else if (pk == 1) {
+      k_warm_guess<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->xprev, c->xfirst, c->xG, theta, 0, 0, c->have_G ? 1 : 0);
+      c->have_first = true; c->xprev_pass = 0; c->launches++;
+    } else if (c->xprev_pass == pk - 2) {
+      if (pk == 2) { k_warm_guess<2><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->xprev, c->xfirst, c->xG, theta, 0, 0, 0); c->have_G = true; }
+      else k_warm_guess<3><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, c->x, c->xprev, c->xfirst, c->xG, theta, 0, 0, 0);
+      c->xprev_pass = pk - 1; c->launches++;
+    }
     int rc = fb_halo_fill(c, c->g, c->x, sizeof(double), 1, 1);     // z-slabs: ghost planes of the guess
     if (rc) return rc;
     k_warm_ax<<<stencil_grid(S), STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->Ap, c->ds);

@@ -40,6 +40,7 @@ int relax_loop(flipb200_ctx* c, double dt, flipb200_stats* st, float* ms_pcg) {
   } while (error > c->P.relax_tol);                                     // :1484
   st->passes = passes;
   st->last_error = error;
+  c->last_step_passes = passes;          // warm start (pcg.cu): which solutions x / xprev hold for the next step
   return 0;
 }
 
@@ -179,6 +180,7 @@ int flipb200_pcg_solve(flipb200_ctx* c, double dt, int32_t* iters, double* rel_r
   CK(cudaSetDevice(c->device));
   int it = 0; double rel = 0.0;
   c->pass_idx = 0;
+  c->last_step_passes = 1;               // stage-level call: the guess is whatever the last solve left in x
   int rc = fb_pcg_solve(c, dt, &it, &rel);
   if (iters) *iters = it;
   if (rel_resid) *rel_resid = rel;
