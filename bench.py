@@ -353,8 +353,24 @@ def per_step(stats):
     return [{k: (round(s[k], 3) if isinstance(s[k], float) else s[k]) for k in keys} for s in stats]
 
 
-def iteration_profile(job, f, nodes):
+def stage_bytes(mixed):
+    """STAGE_BYTES with the storage choices of params.mixed: bit 0 = CG search direction as fp32, bit 1 = level-0 b0 and residual as fp16"""
+    b = dict(STAGE_BYTES)
+    if mixed & 1:
+        b["k_spmv"] = 13.0          # read p 4, flag 1; write Ap 8
+        b["k_update_p"] = 29.0      # read p 4, x 8, z 4, flag 1; write p 4, x 8
+    if mixed & 2:
+        b["k_update_xr"] = 31.0     # b0 as fp16
+        for k in ("L0 halo+smooth", "L0 halo+smooth (post 1)", "L0 halo+smooth (post 2)"):
+            b[k] = 11.0             # read b0 2, x 4, flag 1; write x' 4
+        b["L0 halo+resid"] = 10.0   # read b0 2, x 4, flag + normaliser 2; write residual 2
+        b["L0 halo+restrict"] = 2.5
+    return b
+
+
+def iteration_profile(job, f, nodes, mixed=0):
     """stage profile of one PCG iteration -> by_kernel entries + the list of small-level stages"""
+    SB = stage_bytes(mixed)
     prof = f.profile_iteration(10)
     by = {}
     agg = {}
@@ -364,8 +380,8 @@ def iteration_profile(job, f, nodes):
     total = sum(us for _n, us in prof)
     for name, (us, cnt) in agg.items():
         e = {"us_per_iteration": us, "launches_per_iteration": cnt}
-        if name in STAGE_BYTES and us > 0:
-            bpn = STAGE_BYTES[name]
+        if name in SB and us > 0:
+            bpn = SB[name]
             e["bytes_per_node"] = bpn
             e["gbs"] = bpn * nodes * cnt / (us * 1e-6) / 1e9
             e["frac"] = e["gbs"] / job.peak
@@ -413,12 +429,18 @@ def bench_flip(job, n, fill, steps, warmup, headline, tag):
     ms_iter, _ = f.time_kernel(fb.KERNEL_PCG_ITER, args.kernel_iters)
     ms_p2g, npart = f.time_kernel(fb.KERNEL_P2G, 5)
     ms_sort, _ = f.time_kernel(fb.KERNEL_SORT, 5)
-    ach = 17.0 * nodes / (ms_spmv * 1e-3) / 1e9
+    # params.mixed (single GPU, rows >= 128 nodes): the product's stencil reads the search direction as fp32
+    mixed = int(getattr(f.params, "mixed", 0)) if (world == 1 and n >= 128 and args.precond == 1) else 0
+    if os.environ.get("FLIPB200_MIXED") is not None and mixed:
+        mixed = int(os.environ["FLIPB200_MIXED"])
+    SB = stage_bytes(mixed)
+    spmv_bytes = SB["k_spmv"]
+    ach = spmv_bytes * nodes / (ms_spmv * 1e-3) / 1e9
     traffic = None          # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu capture
     tj_all = {}
     try:
         tj_all = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        tj = tj_all["k_spmv"]
+        tj = tj_all["k_spmv4f" if mixed & 1 else "k_spmv"]
         if tj["grid"] == [n, n, n] and world == 1:
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
     except Exception:
@@ -439,7 +461,7 @@ def bench_flip(job, n, fill, steps, warmup, headline, tag):
     by["sort"] = pk(0.0, npart, ms_sort_step, unit="particle", what="cell sort: overhead, no algorithmic bytes (SURVEY 8d)")
     by["particle_phase"] = pk(151.1, npart, ms_part_step, unit="particle", what="(52 + 99.1) B x particles / (ms_sort + ms_p2g + ms_g2p)")
     try:
-        stage, us_total = iteration_profile(job, f, nodes)
+        stage, us_total = iteration_profile(job, f, nodes, mixed)
     except Exception as e:          # Jacobi mode has no stage marks beyond the three CG kernels
         stage, us_total = {}, 0.0
     coarse_us = 0.0
@@ -451,7 +473,7 @@ def bench_flip(job, n, fill, steps, warmup, headline, tag):
     by["pcg_iteration"] = {"us": ms_iter * 1e3, "iters_per_s": 1e3 / ms_iter, "share_of_step": ms_iter * iters_step / ms_total_step if ms_total_step > 0 else None,
                            "us_plain_launch_sum": us_total, "us_levels_below_0": coarse_us,
                            "jacobi_equivalent_bytes_per_node": 91, "jacobi_equivalent_frac": 91.0 * nodes / (ms_iter * 1e-3) / 1e9 / peak,
-                           "level0_algorithmic_bytes_per_node": sum(STAGE_BYTES[k] * stage[k]["launches_per_iteration"] for k in STAGE_BYTES if k in stage),
+                           "level0_algorithmic_bytes_per_node": sum(SB[k] * stage[k]["launches_per_iteration"] for k in SB if k in stage),
                            "what": "CUDA-graph replay of the whole iteration, flipb200_time_kernel(PCG_ITER)"}
     # dominant = the kernel family with the largest share of the step's device time
     fam = {"k_mg_smooth (level 0, pre + 2 post sweeps)": sum(stage[k]["us_per_iteration"] for k in stage if k.startswith("L0 halo+smooth")),
@@ -468,11 +490,13 @@ def bench_flip(job, n, fill, steps, warmup, headline, tag):
     dominant = {"kernel": dom, "ms_per_step": fam_ms[dom], "share_of_step": fam_ms[dom] / ms_total_step if ms_total_step > 0 else None}
     if dom.startswith("k_mg_smooth"):
         us = fam[dom]; cnt = sum(stage[k]["launches_per_iteration"] for k in stage if k.startswith("L0 halo+smooth"))
-        g = 13.0 * nodes * cnt / (us * 1e-6) / 1e9
-        dominant.update({"bytes_per_node": 13.0, "launches_per_iteration": cnt, "gbs": g, "frac": g / peak})
-    line["roofline"] = {"bound": "hbm", "kernel": "k_spmv (7-pt matrix-free A.p + p.Ap)", "achieved": ach, "peak": peak, "unit": "GB/s",
+        g = SB["L0 halo+smooth"] * nodes * cnt / (us * 1e-6) / 1e9
+        dominant.update({"bytes_per_node": SB["L0 halo+smooth"], "launches_per_iteration": cnt, "gbs": g, "frac": g / peak})
+    line["roofline"] = {"bound": "hbm", "kernel": "k_spmv (7-pt matrix-free A.p + p.Ap" + ("; search direction stored as fp32, A.p and p.Ap evaluated in fp64)" if mixed & 1 else ")"),
+                        "achieved": ach, "peak": peak, "unit": "GB/s",
                         "frac": ach / peak, "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu, per launch)" if traffic else None,
-                        "algorithmic_bytes": 17 * nodes, "peak_source": job.peak_src, "algorithmic_bytes_per_node": 17, "swept_nodes": nodes,
+                        "algorithmic_bytes": spmv_bytes * nodes, "peak_source": job.peak_src, "algorithmic_bytes_per_node": spmv_bytes, "swept_nodes": nodes,
+                        "mixed": mixed,
                         "us_per_launch": ms_spmv * 1e3, "dominant": dominant, "by_kernel": by,
                         "ncu_traffic": {k: v for k, v in tj_all.items() if isinstance(v, dict)} if world == 1 and n == 256 else None}
     line["per_step"] = per_step(stats)
@@ -572,7 +596,9 @@ def bench_pcg(job, n):
     it_s = PCG_BLOCK * blocks / (ms_block * 1e-3)
     ms_spmv, _ = f.time_kernel(fb.KERNEL_SPMV, args.kernel_iters)
     ms_spmv = job.reduce(ms_spmv)
-    ach = 17.0 * nodes / (ms_spmv * 1e-3) / 1e9
+    mixed = int(getattr(f.params, "mixed", 0)) if (world == 1 and n >= 128 and args.precond == 1) else 0
+    spmv_bytes = 13.0 if mixed & 1 else 17.0
+    ach = spmv_bytes * nodes / (ms_spmv * 1e-3) / 1e9
     its = job.gather_ints([iters_tol, n_fluid])
     check["same_on_all_ranks"] = {"ok": all(v == its[0] for v in its)}
     check["ok"] = all(v["ok"] for v in check.values() if isinstance(v, dict))
@@ -584,7 +610,7 @@ def bench_pcg(job, n):
                                    f"iterations without convergence exit (BASELINE configs[4])", "grid": [n, n, nzg], "engine": info},
             "us_per_iteration": ms_block / (PCG_BLOCK * blocks) * 1e3, "iterations_to_tolerance": iters_tol, "rel_residual": rel,
             "unknowns": n_fluid, "swept_nodes_per_gpu": nodes, "node_updates_per_s": it_s * nodes * world,
-            "stencil": {"kernel": "k_spmv", "us_per_launch": ms_spmv * 1e3, "gbs_per_gpu": ach, "frac": ach / job.peak, "bytes_per_node": 17},
+            "stencil": {"kernel": "k_spmv", "us_per_launch": ms_spmv * 1e3, "gbs_per_gpu": ach, "frac": ach / job.peak, "bytes_per_node": spmv_bytes},
             "jacobi_equivalent_frac": 91.0 * nodes * it_s / 1e9 / job.peak, "peak": job.peak,
             "gpu_launches": int(info["kernels_per_iteration"] * PCG_BLOCK * blocks), "check": check}
 

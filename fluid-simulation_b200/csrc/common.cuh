@@ -202,7 +202,7 @@ struct flipb200_ctx {
   Particles pt;
   int64_t n_sorted;        // particles [0, n_sorted) are in cell order; [n_sorted, n) arrived by migration this step
   bool sorted;             // particle arrays are in cell order and cell_start is valid
-  bool keys_ready;         // FLIPB200_SORT=k: pt.key / pt.rank / cell_count describe the CURRENT positions (written by the last advection)
+  char opt_p2g, opt_g2p;   // kernel variants (FLIPB200_P2G / FLIPB200_G2P, read once at create): see particles.cu
   DevScalars* ds;          // device
   DevScalars* hs;          // pinned host mirror
   Box box;                 // sweep box of this step (local planes, clipped to the owned range)
@@ -253,6 +253,28 @@ __device__ __forceinline__ double spline_ref(double x) {
     return 1.5 * ((-4.0 / 3.0) * (x * x * x) + 4.0 * x * x - 4.0 * x + 4.0 / 3.0);
   }
   return 0.0;
+}
+
+// The two non-zero 1-D weights of a particle along one axis: w0 = spline(x - n0), w1 = spline(x - (n0 + 1)) with n0 the
+// base node (x - n0 in [0, 1)).  |x - n0| + |x - n0 - 1| = 1, so one argument takes the inner polynomial of
+// fluid.cc:22-37 and the other the outer one: evaluating spline_ref twice makes a warp run BOTH branches for both
+// calls (lanes disagree), 28 fp64 operations and 6 branches per axis; here each polynomial is evaluated once on
+// the argument it belongs to, and selects put the results back in node order.  Same expressions as spline_ref;
+// the rare cases (support edge, ties at 0.5, arguments outside [0, 1]) fall back to spline_ref itself.
+__device__ __forceinline__ void spline_pair(double x, double n0, double& w0, double& w1) {
+  const double d0 = x - n0, d1 = x - (n0 + 1.0);
+  const double a0 = fabs(d0), a1 = fabs(d1);
+  const double lo = fmin(a0, a1), hi = fmax(a0, a1);
+  if (lo < 0.5 && hi >= 0.5 && hi <= 1.0 - 1e-4) {
+    const double wl = 1.5 * (4.0 * lo * lo * lo - 4.0 * lo * lo + 2.0 / 3.0);
+    const double wh = 1.5 * ((-4.0 / 3.0) * (hi * hi * hi) + 4.0 * hi * hi - 4.0 * hi + 4.0 / 3.0);
+    const bool first_near = a0 <= a1;
+    w0 = first_near ? wl : wh;
+    w1 = first_near ? wh : wl;
+  } else {
+    w0 = spline_ref(d0);
+    w1 = spline_ref(d1);
+  }
 }
 
 // Base cell (lower corner of the 2x2x2 non-zero support) of a coordinate along one axis.

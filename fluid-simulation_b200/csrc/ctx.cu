@@ -101,7 +101,7 @@ int fb_reserve_particles(flipb200_ctx* c, int64_t n) {
   for (int q = 0; q < 6; ++q) { cudaFree(pt.a[q]); cudaFree(pt.b[q]); pt.a[q] = na[q]; pt.b[q] = nb[q]; }
   cudaFree(pt.key); cudaFree(pt.rank); cudaFree(pt.id); cudaFree(pt.id_b);
   pt.key = nk; pt.rank = nr; pt.id = ni; pt.id_b = nib; pt.cap = ncap;
-  c->keys_ready = false;   // key / rank arrays were reallocated
+    // key / rank arrays were reallocated
   return 0;
 }
 
@@ -175,6 +175,9 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
   // experiment switches are read ONCE, here; after that only c->P / c->opt decide (two contexts of one process can differ)
   if (const char* e = getenv("FLIPB200_WARM")) c->P.warm_start = atoi(e);
   if (const char* e = getenv("FLIPB200_MIXED")) c->P.mixed = atoi(e);
+  c->opt_p2g = 'c'; c->opt_g2p = 't';
+  if (const char* e = getenv("FLIPB200_P2G")) if (e[0] == 'c' || e[0] == 'p' || e[0] == 't') c->opt_p2g = e[0];
+  if (const char* e = getenv("FLIPB200_G2P")) if (e[0] == 'c' || e[0] == 'p' || e[0] == 't') c->opt_g2p = e[0];
   c->rank = rank; c->world = world;
   if (slab_split(p->nz, world, c->zsplit, &c->slab_align)) { free(c); return FLIPB200_ERR_ARG; }
   c->gz0 = c->zsplit[rank]; c->gz1 = c->zsplit[rank + 1];
@@ -307,7 +310,7 @@ int flipb200_set_particles(flipb200_ctx* c, const double* px, const double* py, 
   if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->sorted = false;
-  c->keys_ready = false;
+ 
   if (c->world > 1) {
     // every rank is handed the whole scene and keeps the particles whose base plane it owns
     int rc = fb_sort_particles_ex(c, 1);

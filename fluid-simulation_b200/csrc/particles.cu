@@ -119,11 +119,8 @@ int fb_sort_particles_ex(flipb200_ctx* c, int filter) {
   const Grid& g = c->g;
   Particles& pt = c->pt;
   const int nb = g.total + 3;                 // cells + "outside the box" + "to lower rank" + "to upper rank"
-  // FLIPB200_SORT=k: the last advection already wrote key / rank / histogram of these very positions
-  const bool have_keys = c->keys_ready && c->world == 1 && !filter && pt.n > 0;
-  c->keys_ready = false;
-  if (!have_keys) CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(nb + 1) * sizeof(int32_t), c->stream));
-  if (pt.n > 0 && !have_keys) {
+  CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(nb + 1) * sizeof(int32_t), c->stream));
+  if (pt.n > 0) {
     int blocks = (int)((pt.n + 255) / 256);
     k_key_count<<<blocks, 256, 0, c->stream>>>(g, pt.n, pt.a[0], pt.a[1], pt.a[2], pt.key, pt.rank, c->cell_count,
                                                (filter && c->rank != 0) ? 1 : 0);
@@ -201,174 +198,18 @@ k_p2g_cell(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __
 #pragma unroll
   for (int m = 0; m < 8; ++m) { aw[m] = 0; ax[m] = 0; ay[m] = 0; az[m] = 0; }
   const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
+  // (measured and dropped in round 2, profiles/r2_particles.md: issuing the loads of particle n + 1 before the arithmetic
+  //  of particle n, and handing the x+1 partial sums to the next lane so that a cell sends 16 REDs instead of 32 --
+  //  2.10 and 2.24 ms against 2.06 ms: the kernel is bound by neither the loads in flight nor the RED rate)
   for (int n = s; n < e; ++n) {
     double x = px[n], y = py[n], z = pz[n];
     double a = vx[n], b = vy[n], cc = vz[n];
-    double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-    double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-    double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+    double wx0, wx1, wy0, wy1, wz0, wz1;
+    spline_pair(x, nx0, wx0, wx1); spline_pair(y, ny0, wy0, wy1); spline_pair(z, nz0, wz0, wz1);
 #pragma unroll
     for (int m = 0; m < 8; ++m) {
       double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);   // (sx*sy)*sz, fluid.cc:291
       aw[m] += cw; ax[m] += cw * a; ay[m] += cw * b; az[m] += cw * cc;
-    }
-  }
-#pragma unroll
-  for (int m = 0; m < 8; ++m) {
-    int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
-    if (fl[qq] & FB_SOLID) continue;            // fluid.cc:288
-    atomicAdd(&wacc[qq], aw[m]);
-    atomicAdd(&ux[qq], ax[m]);
-    atomicAdd(&uy[qq], ay[m]);
-    atomicAdd(&uz[qq], az[m]);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Row-staged variants (FLIPB200_P2G=row / FLIPB200_G2P=row; parity-tested, not the default).  A warp owns 32 consecutive base cells of one x-row; because the
-// particles are cell-sorted, the particles of those cells are ONE contiguous range of the SoA arrays.
-// The warp streams that range into shared memory with 8-byte cp.async (fully coalesced, no
-// registers held while the loads fly), then every lane walks the particles of its own cell out of
-// shared memory and accumulates in registers exactly like the per-cell kernels.  The per-cell
-// kernels issue one dependent 8-byte load per lane and iteration with a 64-byte stride between
-// lanes (ncu: 25 % occupancy, 37 % DRAM utilisation, LSU wavefronts 66 %, fp64 pipe 40 %).  Measured on
-// B200 at 256^3 / 8 ppc the staged kernels are NOT faster (P2G 2.68 vs 2.45 ms): with 128 registers and 55 KB
-// of shared memory per block only 12 warps are resident and the fp64 pipe starves during the load phases.  Shared-memory index t of a
-// chunk is padded to t + t/8: with ~8 particles per cell the lanes' walks start 8 apart, which
-// would put them on two banks.
-// ---------------------------------------------------------------------------------------------
-#define ROW_CH 256                                   // particles per staged chunk
-#define ROW_PAD(t) ((t) + ((t) >> 3))
-#define ROW_STRIDE (ROW_CH + ROW_CH / 8 + 2)         // doubles per attribute and warp
-#define ROW_WARPS 4
-#define ROW_SMEM(nattr) ((size_t)ROW_WARPS * (nattr) * ROW_STRIDE * sizeof(double))
-
-__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
-  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
-__global__ void __launch_bounds__(32 * ROW_WARPS)
-k_p2g_row(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
-          const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-          const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
-          double* __restrict__ wacc, double* __restrict__ ux, double* __restrict__ uy, double* __restrict__ uz) {
-  extern __shared__ double rsm[];
-  const int lane = threadIdx.x;
-  double* sm = rsm + (size_t)threadIdx.y * 6 * ROW_STRIDE;
-  const int i = box.x0 + blockIdx.x * 32 + lane;
-  const int j = box.y0 + blockIdx.y * ROW_WARPS + threadIdx.y;
-  const int k = box.z0 + blockIdx.z;
-  if (j >= box.y1 || j > g.ny - 2 || k + g.kg0 > g.gnz - 2) return;          // whole warp
-  const bool valid = i < box.x1 && i <= g.nx - 2;
-  const int q0 = gidx(g, box.x0 + blockIdx.x * 32, j, k);
-  const int q = q0 + lane;
-  int s = 0, e = 0;
-  if (valid) { s = start[q]; e = start[q + 1]; }
-  const unsigned vm = __ballot_sync(0xffffffffu, valid);
-  if (vm == 0) return;
-  const int S = __shfl_sync(0xffffffffu, s, 0), E = __shfl_sync(0xffffffffu, e, 31 - __clz(vm));
-  if (E == S) return;
-  double aw[8], ax[8], ay[8], az[8];
-#pragma unroll
-  for (int m = 0; m < 8; ++m) { aw[m] = 0; ax[m] = 0; ay[m] = 0; az[m] = 0; }
-  const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-  for (int cs = S; cs < E; cs += ROW_CH) {
-    const int cn = min(ROW_CH, E - cs);
-    for (int t = lane; t < cn; t += 32) {
-      const int u = ROW_PAD(t);
-      cp_async8(sm + 0 * ROW_STRIDE + u, px + cs + t); cp_async8(sm + 1 * ROW_STRIDE + u, py + cs + t);
-      cp_async8(sm + 2 * ROW_STRIDE + u, pz + cs + t); cp_async8(sm + 3 * ROW_STRIDE + u, vx + cs + t);
-      cp_async8(sm + 4 * ROW_STRIDE + u, vy + cs + t); cp_async8(sm + 5 * ROW_STRIDE + u, vz + cs + t);
-    }
-    cp_async_wait_all();
-    __syncwarp();
-    const int n0 = max(s, cs), n1 = min(e, cs + cn);
-    for (int n = n0; n < n1; ++n) {
-      const int u = ROW_PAD(n - cs);
-      double x = sm[u], y = sm[ROW_STRIDE + u], z = sm[2 * ROW_STRIDE + u];
-      double a = sm[3 * ROW_STRIDE + u], b = sm[4 * ROW_STRIDE + u], cc = sm[5 * ROW_STRIDE + u];
-      double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-      double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-      double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
-#pragma unroll
-      for (int m = 0; m < 8; ++m) {
-        double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);   // (sx*sy)*sz, fluid.cc:291
-        aw[m] += cw; ax[m] += cw * a; ay[m] += cw * b; az[m] += cw * cc;
-      }
-    }
-    __syncwarp();
-  }
-  if (s == e) return;
-#pragma unroll
-  for (int m = 0; m < 8; ++m) {
-    int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
-    if (fl[qq] & FB_SOLID) continue;            // fluid.cc:288
-    atomicAdd(&wacc[qq], aw[m]);
-    atomicAdd(&ux[qq], ax[m]);
-    atomicAdd(&uy[qq], ay[m]);
-    atomicAdd(&uz[qq], az[m]);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// 256-bit variants of the per-cell kernels (FLIPB200_P2G=v4 / FLIPB200_G2P=v4; NOT the default and not
-// yet measured -- written after the GPU budget of round 1 was spent, first A/B of round 2).
-// Why: k_p2g_cell / k_g2p_cell keep 16 warps per SM (122 / 117 registers) with six 8-byte loads in
-// flight per lane = 24 KB per SM, about half of what 6.5 TB/s x ~1 us of latency needs per SM (44 KB);
-// ncu shows 37 % DRAM utilisation and the LSU busy with 16 cache lines per warp request (lanes are 64 B
-// apart).  Here a lane fetches the aligned groups of four particles that cover its cell's range
-// [s, e) with LDG.256 (ld.global.v4.f64): a quarter of the requests, four times the bytes in flight;
-// slots outside [s, e) belong to the neighbouring cells and are skipped.  Accumulation order is the
-// particle order, as in k_p2g_cell: identical bits.  Needs 32-byte aligned arrays (cudaMalloc) and a
-// capacity that is a multiple of 4 (fb_reserve_particles rounds to 64).
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void ld4_nc(const double* p, double (&v)[4]) {
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
-}
-__device__ __forceinline__ void ld4(const double* p, double (&v)[4]) {
-  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p) : "memory");
-}
-__device__ __forceinline__ void st4(double* p, const double (&v)[4]) {
-  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
-}
-
-// MINB = 4 (FLIPB200_P2G=v4c) caps the kernel at 128 registers (16 warps per SM; ptxas spills 48 bytes),
-// MINB = 1 lets it take ~150 (12 warps per SM)
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB)
-k_p2g_cell4(Grid g, Box box, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
-            const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-            const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
-            double* __restrict__ wacc, double* __restrict__ ux, double* __restrict__ uy, double* __restrict__ uz) {
-  int i = box.x0 + blockIdx.x * blockDim.x + threadIdx.x;
-  int j = box.y0 + blockIdx.y * blockDim.y + threadIdx.y;
-  int k = box.z0 + blockIdx.z;
-  if (i >= box.x1 || j >= box.y1 || i > g.nx - 2 || j > g.ny - 2 || k + g.kg0 > g.gnz - 2) return;
-  int q = gidx(g, i, j, k);
-  int s = start[q], e = start[q + 1];
-  if (s == e) return;
-  double aw[8], ax[8], ay[8], az[8];
-#pragma unroll
-  for (int m = 0; m < 8; ++m) { aw[m] = 0; ax[m] = 0; ay[m] = 0; az[m] = 0; }
-  const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-  for (int g0 = s & ~3; g0 < e; g0 += 4) {
-    double X[4], Y[4], Z[4], A[4], B[4], C[4];
-    ld4_nc(px + g0, X); ld4_nc(py + g0, Y); ld4_nc(pz + g0, Z);
-    ld4_nc(vx + g0, A); ld4_nc(vy + g0, B); ld4_nc(vz + g0, C);
-#pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const int n = g0 + t;
-      if (n < s || n >= e) continue;              // a neighbouring cell's particle (or past the end)
-      double wx0 = spline_ref(X[t] - nx0), wx1 = spline_ref(X[t] - (nx0 + 1.0));
-      double wy0 = spline_ref(Y[t] - ny0), wy1 = spline_ref(Y[t] - (ny0 + 1.0));
-      double wz0 = spline_ref(Z[t] - nz0), wz1 = spline_ref(Z[t] - (nz0 + 1.0));
-#pragma unroll
-      for (int m = 0; m < 8; ++m) {
-        double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);   // (sx*sy)*sz, fluid.cc:291
-        aw[m] += cw; ax[m] += cw * A[t]; ay[m] += cw * B[t]; az[m] += cw * C[t];
-      }
     }
   }
 #pragma unroll
@@ -397,9 +238,8 @@ __global__ void k_p2g_particle(Grid g, int64_t n, const uint8_t* __restrict__ fl
   int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
   double a = vx[t], b = vy[t], cc = vz[t];
   const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-  double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-  double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-  double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+  double wx0, wx1, wy0, wy1, wz0, wz1;
+  spline_pair(x, nx0, wx0, wx1); spline_pair(y, ny0, wy0, wy1); spline_pair(z, nz0, wz0, wz1);
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
     int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
@@ -412,8 +252,12 @@ __global__ void k_p2g_particle(Grid g, int64_t n, const uint8_t* __restrict__ fl
   }
 }
 
+int fb_p2g_rows(flipb200_ctx* c);                          // rows.cu
 // bounding box (in base cells) of the particles, from the sorted cell histogram is expensive;
 // P2G sweeps every base cell of the box instead -- a cell with no particles costs two int loads.
+// c->opt_p2g (FLIPB200_P2G, read once at create; the parity tests cross-check the variants):
+//   'c' one thread per cell (default: 2.06 ms at 256^3 / 127 M particles), 't' rows staged by TMA (rows.cu, 2.16 ms),
+//   'p' one thread per particle with 32 REDs each (reference-shaped; also the path of unsorted input)
 int fb_p2g(flipb200_ctx* c) {
   const Grid& g = c->g;
   const size_t T = (size_t)g.total;
@@ -421,8 +265,8 @@ int fb_p2g(flipb200_ctx* c) {
   CK(cudaMemsetAsync(c->wacc, 0, T * sizeof(double), c->stream));
   for (int a = 0; a < 3; ++a) CK(cudaMemsetAsync(c->u[a], 0, T * sizeof(double), c->stream));
   Particles& pt = c->pt;
-  const char* mode = getenv("FLIPB200_P2G");
-  if (mode && mode[0] == 'p' && c->world == 1) {
+  const char mode = c->opt_p2g;
+  if (mode == 'p' && c->world == 1) {
     if (pt.n == 0) return 0;
     int blocks = (int)((pt.n + 127) / 128);
     k_p2g_particle<<<blocks, 128, 0, c->stream>>>(g, pt.n, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
@@ -432,25 +276,16 @@ int fb_p2g(flipb200_ctx* c) {
   }
   if (!c->sorted) { int rc = fb_sort_particles(c); if (rc) return rc; }
   if (c->n_sorted > 0) {
-    Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
-    dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
-    if (mode && mode[0] == 'v' && mode[1] && mode[2] == 'c')   // FLIPB200_P2G=v4c: 256-bit loads, capped at 128 registers
-      k_p2g_cell4<4><<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                                 pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
-    else if (mode && mode[0] == 'v')   // FLIPB200_P2G=v4: 256-bit loads (unmeasured, see k_p2g_cell4)
-      k_p2g_cell4<1><<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                                 pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
-    else if (!(mode && mode[0] == 'r'))   // default: per-cell kernel; FLIPB200_P2G=row: shared-memory staged variant (measured 9 % slower at 8 ppc)
+    if (mode == 't') {
+      int rc = fb_p2g_rows(c);
+      if (rc) return rc;
+    } else {
+      Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
+      dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
       k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
                                              pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
-    else {
-      static bool attr_set = false;
-      if (!attr_set) { CK(cudaFuncSetAttribute(k_p2g_row, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROW_SMEM(6))); attr_set = true; }
-      k_p2g_row<<<grd, dim3(32, ROW_WARPS, 1), ROW_SMEM(6), c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1],
-                                                                         pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->wacc, c->u[0],
-                                                                         c->u[1], c->u[2]);
+      CK_LAUNCH(); c->launches++;
     }
-    CK_LAUNCH(); c->launches++;
   }
   if (pt.n > c->n_sorted) {   // particles that migrated in this step (unsorted tail)
     const int64_t o = c->n_sorted, m = pt.n - o;
@@ -488,9 +323,8 @@ k_g2p(Grid g, int64_t n, const uint8_t* __restrict__ fl,
       int q = (int)key;
       int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
       const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-      double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-      double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-      double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+      double wx0, wx1, wy0, wy1, wz0, wz1;
+      spline_pair(x, nx0, wx0, wx1); spline_pair(y, ny0, wy0, wy1); spline_pair(z, nz0, wz0, wz1);
       double wsum = 0, dx = 0, dy = 0, dz = 0;
 #pragma unroll
       for (int m = 0; m < 8; ++m) {
@@ -554,9 +388,8 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
     for (int n = s; n < e; ++n) {
       double x = px[n], y = py[n], z = pz[n];
       double a = vx[n], b = vy[n], cc = vz[n];
-      double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-      double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-      double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
+      double wx0, wx1, wy0, wy1, wz0, wz1;
+      spline_pair(x, nx0, wx0, wx1); spline_pair(y, ny0, wy0, wy1); spline_pair(z, nz0, wz0, wz1);
       double wsum = 0, dx = 0, dy = 0, dz = 0;
 #pragma unroll
       for (int m = 0; m < 8; ++m) {
@@ -578,166 +411,6 @@ k_g2p_cell(Grid g, const int32_t* __restrict__ start,
   __syncthreads();
   if (tid == 0) {
     double m = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
-    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
-  }
-}
-
-// k_g2p_cell with 256-bit particle accesses (see k_p2g_cell4).  A group of four that lies wholly inside
-// the cell's range is written back with one 256-bit store, the partial groups at either end
-// element by element (their other slots belong to the neighbouring cells' threads).
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB)
-k_g2p_cell4(Grid g, const int32_t* __restrict__ start,
-            const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-            double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
-            const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-            DevScalars* __restrict__ ds, double ratio) {
-  __shared__ double red[4];
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = g.k0 + blockIdx.z;
-  double speed = 0.0;
-  int s = 0, e = 0, q = 0;
-  if (i <= g.nx - 2 && j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
-  if (s < e) {
-    double ddx[8], ddy[8], ddz[8];
-    unsigned inmask = 0;
-#pragma unroll
-    for (int m = 0; m < 8; ++m) {
-      int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
-      int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
-      bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
-      ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
-      if (in) inmask |= 1u << m;
-    }
-    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-    for (int g0 = s & ~3; g0 < e; g0 += 4) {
-      double X[4], Y[4], Z[4], A[4], B[4], C[4];
-      ld4_nc(px + g0, X); ld4_nc(py + g0, Y); ld4_nc(pz + g0, Z);
-      ld4(vx + g0, A); ld4(vy + g0, B); ld4(vz + g0, C);          // written by this kernel: no .nc
-      unsigned wr = 0;                                            // slots whose velocity changed
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const int n = g0 + t;
-        if (n < s || n >= e) continue;
-        double wx0 = spline_ref(X[t] - nx0), wx1 = spline_ref(X[t] - (nx0 + 1.0));
-        double wy0 = spline_ref(Y[t] - ny0), wy1 = spline_ref(Y[t] - (ny0 + 1.0));
-        double wz0 = spline_ref(Z[t] - nz0), wz1 = spline_ref(Z[t] - (nz0 + 1.0));
-        double wsum = 0, dx = 0, dy = 0, dz = 0;
-#pragma unroll
-        for (int m = 0; m < 8; ++m) {
-          double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
-          if (inmask & (1u << m)) wsum += cw;
-          dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
-        }
-        double a = A[t], b = B[t], cc = C[t];
-        if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }          // PIC/FLIP blend (see k_cell_delta)
-        if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }   // as k_g2p_cell
-        if (wsum != 0.0 || ratio != 1.0) { A[t] = a; B[t] = b; C[t] = cc; wr |= 1u << t; }
-        speed = fmax(speed, a * a + b * b + cc * cc);
-      }
-      if (g0 >= s && g0 + 4 <= e) {               // all four slots are this cell's
-        if (wr) { st4(vx + g0, A); st4(vy + g0, B); st4(vz + g0, C); }
-      } else {
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-          if (wr & (1u << t)) { vx[g0 + t] = A[t]; vy[g0 + t] = B[t]; vz[g0 + t] = C[t]; }
-      }
-    }
-  }
-  speed = sqrt(warp_max(speed));                               // fluid.cc:982 (Vec3::length)
-  int tid = threadIdx.x + blockDim.x * threadIdx.y, lane = tid & 31, w = tid >> 5;
-  if (lane == 0) red[w] = speed;
-  __syncthreads();
-  if (tid == 0) {
-    double m = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
-    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
-  }
-}
-
-// Row-staged G2P (see k_p2g_row): positions and velocities of a row's particles are staged in
-// shared memory with coalesced cp.async, every lane updates the particles of its own cell there, and
-// the new velocities go back to HBM with coalesced stores.
-__global__ void __launch_bounds__(32 * ROW_WARPS)
-k_g2p_row(Grid g, const int32_t* __restrict__ start,
-          const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-          double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
-          const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-          DevScalars* __restrict__ ds, double ratio) {
-  extern __shared__ double rsm[];
-  __shared__ double red[ROW_WARPS];
-  const int lane = threadIdx.x;
-  double* sm = rsm + (size_t)threadIdx.y * 6 * ROW_STRIDE;
-  const int i = blockIdx.x * 32 + lane;
-  const int j = blockIdx.y * ROW_WARPS + threadIdx.y;
-  const int k = g.k0 + blockIdx.z;
-  double speed = 0.0;
-  const bool row = j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2;                 // whole warp
-  const bool valid = row && i <= g.nx - 2;
-  const int q = gidx(g, i, j, k);
-  int s = 0, e = 0;
-  if (valid) { s = start[q]; e = start[q + 1]; }
-  const unsigned vm = __ballot_sync(0xffffffffu, valid);
-  const int S = __shfl_sync(0xffffffffu, s, 0), E = vm ? __shfl_sync(0xffffffffu, e, 31 - __clz(vm | 1u)) : S;
-  if (vm != 0 && E > S) {
-    double ddx[8], ddy[8], ddz[8];
-    unsigned inmask = 0;
-    if (s < e) {
-#pragma unroll
-      for (int m = 0; m < 8; ++m) {
-        int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
-        int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
-        bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
-        ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
-        if (in) inmask |= 1u << m;
-      }
-    }
-    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-    for (int cs = S; cs < E; cs += ROW_CH) {
-      const int cn = min(ROW_CH, E - cs);
-      for (int t = lane; t < cn; t += 32) {
-        const int u = ROW_PAD(t);
-        cp_async8(sm + 0 * ROW_STRIDE + u, px + cs + t); cp_async8(sm + 1 * ROW_STRIDE + u, py + cs + t);
-        cp_async8(sm + 2 * ROW_STRIDE + u, pz + cs + t); cp_async8(sm + 3 * ROW_STRIDE + u, vx + cs + t);
-        cp_async8(sm + 4 * ROW_STRIDE + u, vy + cs + t); cp_async8(sm + 5 * ROW_STRIDE + u, vz + cs + t);
-      }
-      cp_async_wait_all();
-      __syncwarp();
-      const int n0 = max(s, cs), n1 = min(e, cs + cn);
-      for (int n = n0; n < n1; ++n) {
-        const int u = ROW_PAD(n - cs);
-        double x = sm[u], y = sm[ROW_STRIDE + u], z = sm[2 * ROW_STRIDE + u];
-        double a = sm[3 * ROW_STRIDE + u], b = sm[4 * ROW_STRIDE + u], cc = sm[5 * ROW_STRIDE + u];
-        double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-        double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-        double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
-        double wsum = 0, dx = 0, dy = 0, dz = 0;
-#pragma unroll
-        for (int m = 0; m < 8; ++m) {
-          double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
-          if (inmask & (1u << m)) wsum += cw;
-          dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
-        }
-        if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }        // PIC/FLIP blend (see k_cell_delta)
-        if (wsum != 0.0) { a += dx / wsum; b += dy / wsum; cc += dz / wsum; }   // fluid.cc:258-262, 981
-        if (wsum != 0.0 || ratio != 1.0) { sm[3 * ROW_STRIDE + u] = a; sm[4 * ROW_STRIDE + u] = b; sm[5 * ROW_STRIDE + u] = cc; }
-        speed = fmax(speed, sqrt(a * a + b * b + cc * cc));          // fluid.cc:982
-      }
-      __syncwarp();
-      for (int t = lane; t < cn; t += 32) {
-        const int u = ROW_PAD(t);
-        vx[cs + t] = sm[3 * ROW_STRIDE + u]; vy[cs + t] = sm[4 * ROW_STRIDE + u]; vz[cs + t] = sm[5 * ROW_STRIDE + u];
-      }
-      __syncwarp();
-    }
-  }
-  speed = warp_max(speed);
-  if (lane == 0) red[threadIdx.y] = speed;
-  __syncthreads();
-  if (threadIdx.y == 0 && lane == 0) {
-    double m = red[0];
-#pragma unroll
-    for (int w = 1; w < ROW_WARPS; ++w) m = fmax(m, red[w]);
     if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
   }
 }
@@ -801,19 +474,6 @@ k_advect(Grid g, int64_t n, const uint8_t* __restrict__ fl, double dt_max, doubl
 
 __global__ void k_reset_max(DevScalars* ds) { ds->max_speed_bits = 0ull; }
 
-// ---------------------------------------------------------------------------------------------
-// G2P and advection in ONE pass (FLIPB200_G2P=f1 / f4; NOT the default and not yet measured -- written
-// after the GPU budget of round 1 was spent, first A/B of round 2).  The two-kernel path moves
-// 48 + 24 B (k_g2p_cell) and 48 + 24 B (k_advect) per particle because FLIPadvect's dt is a function
-// of the global max speed (fluid.cc:992-999).  But dt = min(dt_max, dx / maxSpeed) IS dt_max whenever
-// maxSpeed <= dx / dt_max, which the host can bet on when the previous step ended that way: the
-// fused kernel advects with dt_max and writes positions AND velocities into the alternate (sort)
-// buffers -- 48 B read + 48 B written, the algorithmic 96 B -- while accumulating the max speed.
-// If the bet holds (checked on the host with the same expression) the buffers are swapped; if not,
-// the inputs are untouched and the two-kernel path runs as if nothing had happened.  Same operation
-// sequence per particle as k_g2p_cell followed by k_advect: identical bits.  W = particles per load
-// (1: 8-byte accesses, 4: 256-bit, see k_p2g_cell4).  Single GPU, cell-sorted particles only.
-// ---------------------------------------------------------------------------------------------
 // one particle of FLIPadvect phase 2 (fluid.cc:1000-1036), exactly as k_advect does it
 __device__ __forceinline__ void advect_one(const Grid& g, const uint8_t* __restrict__ fl, double timestep, double e,
                                            double x, double y, double z, double& a, double& b, double& cc,
@@ -837,173 +497,13 @@ __device__ __forceinline__ void advect_one(const Grid& g, const uint8_t* __restr
   }
 }
 
-template <int W> __device__ __forceinline__ void ldw_nc(const double* p, double (&v)[W]);
-template <> __device__ __forceinline__ void ldw_nc<1>(const double* p, double (&v)[1]) { v[0] = __ldg(p); }
-template <> __device__ __forceinline__ void ldw_nc<4>(const double* p, double (&v)[4]) { ld4_nc(p, v); }
-
-template <int W, int MINB>
-__global__ void __launch_bounds__(128, MINB)
-k_g2p_advect_cell(Grid g, const int32_t* __restrict__ start, const uint8_t* __restrict__ fl,
-                  const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-                  const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
-                  double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
-                  double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
-                  const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest,
-                  uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
-  __shared__ double red[4];
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = g.k0 + blockIdx.z;
-  double speed = 0.0;
-  int s = 0, e = 0, q = 0;
-  if (i <= g.nx - 2 && j <= g.ny - 2 && k + g.kg0 <= g.gnz - 2) { q = gidx(g, i, j, k); s = start[q]; e = start[q + 1]; }
-  if (s < e) {
-    double ddx[8], ddy[8], ddz[8];
-    unsigned inmask = 0;
-#pragma unroll
-    for (int m = 0; m < 8; ++m) {
-      int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
-      int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
-      bool in = inside_shell(g, ii, jj, kk);                     // fluid.cc:237 (no solid test)
-      ddx[m] = in ? dcx[qq] : 0.0; ddy[m] = in ? dcy[qq] : 0.0; ddz[m] = in ? dcz[qq] : 0.0;
-      if (in) inmask |= 1u << m;
-    }
-    const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-    for (int g0 = s & ~(W - 1); g0 < e; g0 += W) {
-      double X[W], Y[W], Z[W], A[W], B[W], C[W];
-      ldw_nc<W>(px + g0, X); ldw_nc<W>(py + g0, Y); ldw_nc<W>(pz + g0, Z);
-      ldw_nc<W>(vx + g0, A); ldw_nc<W>(vy + g0, B); ldw_nc<W>(vz + g0, C);
-#pragma unroll
-      for (int t = 0; t < W; ++t) {
-        const int n = g0 + t;
-        if (n < s || n >= e) continue;
-        double wx0 = spline_ref(X[t] - nx0), wx1 = spline_ref(X[t] - (nx0 + 1.0));
-        double wy0 = spline_ref(Y[t] - ny0), wy1 = spline_ref(Y[t] - (ny0 + 1.0));
-        double wz0 = spline_ref(Z[t] - nz0), wz1 = spline_ref(Z[t] - (nz0 + 1.0));
-        double wsum = 0, dx = 0, dy = 0, dz = 0;
-#pragma unroll
-        for (int m = 0; m < 8; ++m) {
-          double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
-          if (inmask & (1u << m)) wsum += cw;
-          dx += ddx[m] * cw; dy += ddy[m] * cw; dz += ddz[m] * cw;
-        }
-        double a = A[t], b = B[t], cc = C[t];
-        if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }          // PIC/FLIP blend (see k_cell_delta)
-        if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }   // as k_g2p_cell
-        speed = fmax(speed, a * a + b * b + cc * cc);                       // before the collision, fluid.cc:982
-        advect_one(g, fl, timestep, e_rest, X[t], Y[t], Z[t], a, b, cc, X[t], Y[t], Z[t]);
-        A[t] = a; B[t] = b; C[t] = cc;
-        if (key) {                                  // FLIPB200_SORT=k: the next step's cell key and in-cell rank (k_key_count)
-          const uint32_t kx = particle_key(g, X[t], Y[t], Z[t]);
-          key[n] = kx; rank[n] = (uint32_t)atomicAdd(&count[kx], 1);
-        }
-      }
-      bool stored = false;
-      if constexpr (W == 4) {
-        if (g0 >= s && g0 + 4 <= e) {             // all four slots are this cell's
-          st4(opx + g0, X); st4(opy + g0, Y); st4(opz + g0, Z); st4(ovx + g0, A); st4(ovy + g0, B); st4(ovz + g0, C);
-          stored = true;
-        }
-      }
-      if (!stored) {
-#pragma unroll
-        for (int t = 0; t < W; ++t) {
-          const int n = g0 + t;
-          if (n < s || n >= e) continue;
-          opx[n] = X[t]; opy[n] = Y[t]; opz[n] = Z[t]; ovx[n] = A[t]; ovy[n] = B[t]; ovz[n] = C[t];
-        }
-      }
-    }
-  }
-  speed = sqrt(warp_max(speed));                               // fluid.cc:982 (Vec3::length)
-  int tid = threadIdx.x + blockDim.x * threadIdx.y, lane = tid & 31, w = tid >> 5;
-  if (lane == 0) red[w] = speed;
-  __syncthreads();
-  if (tid == 0) {
-    double m = fmax(fmax(red[0], red[1]), fmax(red[2], red[3]));
-    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
-  }
-}
-
-
-// ---------------------------------------------------------------------------------------------
-// G2P + advection in ONE pass, one thread per PARTICLE (round 2).  The per-cell kernels above issue 8-byte
-// loads 64 B apart (32 sectors per warp request) and cannot write the advected positions without the same
-// scatter; the one-pass per-cell kernel measured 7.1 ms against 4.7 ms for the two kernels
-// (profiles/r2a_variants_ab.txt).  Here consecutive lanes take consecutive particles: six fully coalesced
-// loads, six fully coalesced stores into the alternate buffers; the 8 x 3 cell-centred deltas are gathered
-// with read-only loads that hit L1 (cell-sorted order: a warp touches ~4 cells).  dt is a function of the
-// global max speed (fluid.cc:992-999), so the kernel bets on dt == dt_max (true whenever
-// maxSpeed <= dx / dt_max; tried only when the previous step ended that way) exactly like
-// g2p_advect_fused: the inputs stay untouched until the bet is known to hold.  Same operation sequence per
-// particle as k_g2p followed by k_advect.  Works on any particle order (sorted or not).
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-k_g2p_advect_pp(Grid g, int64_t n, const uint8_t* __restrict__ fl,
-                const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
-                const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
-                double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
-                double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
-                const double* __restrict__ dcx, const double* __restrict__ dcy, const double* __restrict__ dcz,
-                DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest,
-                uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
-  __shared__ double red[8];
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  double speed = 0.0;
-  if (t < n) {
-    double x = __ldg(px + t), y = __ldg(py + t), z = __ldg(pz + t);
-    double a = __ldg(vx + t), b = __ldg(vy + t), cc = __ldg(vz + t);
-    const uint32_t kq = particle_key(g, x, y, z);
-    if (kq < (uint32_t)g.total) {
-      const int q = (int)kq;
-      const int k = q / g.plane, rem = q - k * g.plane, j = rem / g.px, i = rem - j * g.px;
-      const double nx0 = (double)(i - g.ox), ny0 = (double)(j - g.oy), nz0 = (double)(k - g.oz);
-      const double wx0 = spline_ref(x - nx0), wx1 = spline_ref(x - (nx0 + 1.0));
-      const double wy0 = spline_ref(y - ny0), wy1 = spline_ref(y - (ny0 + 1.0));
-      const double wz0 = spline_ref(z - nz0), wz1 = spline_ref(z - (nz0 + 1.0));
-      double wsum = 0, dx = 0, dy = 0, dz = 0;
-#pragma unroll
-      for (int m = 0; m < 8; ++m) {
-        const int ii = i + (m & 1), jj = j + ((m >> 1) & 1), kk = k + ((m >> 2) & 1);
-        const int qq = q + (m & 1) + ((m & 2) ? g.px : 0) + ((m & 4) ? g.plane : 0);
-        const bool in = inside_shell(g, ii, jj, kk);                 // fluid.cc:237 (no solid test)
-        const double cw = ((m & 1) ? wx1 : wx0) * ((m & 2) ? wy1 : wy0) * ((m & 4) ? wz1 : wz0);
-        const double ex = in ? __ldg(dcx + qq) : 0.0, ey = in ? __ldg(dcy + qq) : 0.0, ez = in ? __ldg(dcz + qq) : 0.0;
-        if (in) wsum += cw;
-        dx += ex * cw; dy += ey * cw; dz += ez * cw;
-      }
-      if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }            // PIC/FLIP blend (see k_cell_delta)
-      if (wsum != 0.0) { const double iw = 1.0 / wsum; a += dx * iw; b += dy * iw; cc += dz * iw; }   // as k_g2p_cell
-    } else if (ratio != 1.0) { a *= ratio; b *= ratio; cc *= ratio; }
-    speed = a * a + b * b + cc * cc;                                       // before the collision, fluid.cc:982
-    advect_one(g, fl, timestep, e_rest, x, y, z, a, b, cc, x, y, z);
-    opx[t] = x; opy[t] = y; opz[t] = z; ovx[t] = a; ovy[t] = b; ovz[t] = cc;
-    if (key) {                                  // the next step's cell key and in-cell rank (what k_key_count computes)
-      const uint32_t kx = particle_key(g, x, y, z);
-      key[t] = kx; rank[t] = (uint32_t)atomicAdd(&count[kx], 1);
-    }
-  }
-  speed = sqrt(warp_max(speed));
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  if (lane == 0) red[w] = speed;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double m = red[0];
-#pragma unroll
-    for (int q2 = 1; q2 < 8; ++q2) m = fmax(m, red[q2]);
-    if (m > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(m));
-  }
-}
-
 // the trailing "outside the box" bucket of the fused path: no grid contact (k_speed_tail), then advection
 __global__ void k_g2p_advect_tail(Grid g, const int32_t* __restrict__ start, int64_t n /* = n_sorted */, const uint8_t* __restrict__ fl,
                                   const double* __restrict__ px, const double* __restrict__ py, const double* __restrict__ pz,
                                   const double* __restrict__ vx, const double* __restrict__ vy, const double* __restrict__ vz,
                                   double* __restrict__ opx, double* __restrict__ opy, double* __restrict__ opz,
                                   double* __restrict__ ovx, double* __restrict__ ovy, double* __restrict__ ovz,
-                                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest,
-                                  uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
+                                  DevScalars* __restrict__ ds, double ratio, double timestep, double e_rest) {
   double speed = 0.0;
   for (int64_t t = (int64_t)start[g.total] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n;
        t += (int64_t)gridDim.x * blockDim.x) {
@@ -1013,44 +513,9 @@ __global__ void k_g2p_advect_tail(Grid g, const int32_t* __restrict__ start, int
     speed = fmax(speed, sqrt(a * a + b * b + cc * cc));
     advect_one(g, fl, timestep, e_rest, x, y, z, a, b, cc, x, y, z);
     opx[t] = x; opy[t] = y; opz[t] = z; ovx[t] = a; ovy[t] = b; ovz[t] = cc;
-    if (key) { const uint32_t kx = particle_key(g, x, y, z); key[t] = kx; rank[t] = (uint32_t)atomicAdd(&count[kx], 1); }
   }
   speed = warp_max(speed);
   if ((threadIdx.x & 31) == 0 && speed > 0.0) atomicMax(&ds->max_speed_bits, (unsigned long long)__double_as_longlong(speed));
-}
-
-// FLIPB200_SORT=k (NOT the default, unmeasured): the advection kernel also emits what k_key_count would
-// compute at the start of the next step -- the cell key of the NEW position and the particle's rank
-// in its cell (histogram atomic) -- so the next sort skips k_key_count and its 24 B/particle re-read
-// of the positions.  Single GPU.  k_advect_key = k_advect + that emission (same arithmetic: advect_one).
-__global__ void __launch_bounds__(256)
-k_advect_key(Grid g, int64_t n, const uint8_t* __restrict__ fl, double dt_max, double dxc, double e,
-             double* __restrict__ px, double* __restrict__ py, double* __restrict__ pz,
-             double* __restrict__ vx, double* __restrict__ vy, double* __restrict__ vz,
-             DevScalars* __restrict__ ds, uint32_t* __restrict__ key, uint32_t* __restrict__ rank, int32_t* __restrict__ count) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  double maxSpeed = __longlong_as_double((long long)ds->max_speed_bits);
-  double timestep = dt_max;                                   // fluid.cc:992-999
-  if (maxSpeed != 0.0) timestep = dt_max < dxc / maxSpeed ? dt_max : dxc / maxSpeed;
-  if (t == 0) ds->dt_out = timestep;
-  if (t >= n) return;
-  double x = px[t], y = py[t], z = pz[t];
-  double a = vx[t], b = vy[t], cc = vz[t];
-  const double a0 = a, b0 = b, c0 = cc;
-  advect_one(g, fl, timestep, e, x, y, z, a, b, cc, x, y, z);
-  px[t] = x; py[t] = y; pz[t] = z;
-  if (__double_as_longlong(a) != __double_as_longlong(a0) || __double_as_longlong(b) != __double_as_longlong(b0) ||
-      __double_as_longlong(cc) != __double_as_longlong(c0)) { vx[t] = a; vy[t] = b; vz[t] = cc; }
-  const uint32_t kx = particle_key(g, x, y, z);
-  key[t] = kx; rank[t] = (uint32_t)atomicAdd(&count[kx], 1);
-}
-static bool sort_emit_keys(const flipb200_ctx* c) {
-  const char* m = getenv("FLIPB200_SORT");
-  return m && m[0] == 'k' && c->world == 1;
-}
-static int clear_cell_count(flipb200_ctx* c) {
-  CK(cudaMemsetAsync(c->cell_count, 0, (size_t)(c->g.total + 3 + 1) * sizeof(int32_t), c->stream));   // as fb_sort_particles_ex
-  return 0;
 }
 
 // dt of fluid.cc:992-999 from the collected max speed (the two-kernel path does this inside k_advect)
@@ -1061,54 +526,14 @@ __global__ void k_set_dt(DevScalars* ds, double dt_max, double dxc) {
   ds->dt_out = timestep;
 }
 
-// returns 0 and *done = true when the bet on dt == dt_max held (buffers swapped, step finished);
-// *done = false: nothing was changed, the caller runs the two-kernel path
-static int g2p_advect_fused(flipb200_ctx* c, int W, bool capped, bool* done) {
-  const Grid& g = c->g;
-  Particles& pt = c->pt;
-  *done = false;
-  const double dt_spec = c->P.dt_max;
-  dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
-  const bool emit = sort_emit_keys(c);
-  uint32_t* ekey = emit ? pt.key : nullptr; uint32_t* erank = emit ? pt.rank : nullptr; int32_t* ecount = emit ? c->cell_count : nullptr;
-  if (emit) { int rc = clear_cell_count(c); if (rc) return rc; }
-#define FUSED_ARGS g, c->cell_start, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1], pt.b[2], \
-                   pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec, c->P.restitution, ekey, erank, ecount
-  if (W == 0) {
-    k_g2p_advect_pp<<<(unsigned)((pt.n + 255) / 256), 256, 0, c->stream>>>(g, pt.n, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], pt.b[0], pt.b[1],
-                                                                         pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio, dt_spec,
-                                                                         c->P.restitution, ekey, erank, ecount);
-    k_set_dt<<<1, 1, 0, c->stream>>>(c->ds, c->P.dt_max, c->P.dx);
-    CK_LAUNCH(); c->launches += 2;
-    int rc0 = fb_fetch_scalars(c);
-    if (rc0) return rc0;
-    if (c->hs->dt_out != dt_spec) return 0;          // bet lost: pt.a is untouched
-    for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
-    c->sorted = false;
-    c->keys_ready = emit;
-    *done = true;
-    return 0;
-  }
-  if (W == 4 && capped) k_g2p_advect_cell<4, 4><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
-  else if (W == 4) k_g2p_advect_cell<4, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
-  else k_g2p_advect_cell<1, 1><<<grd, blk, 0, c->stream>>>(FUSED_ARGS);
-#undef FUSED_ARGS
-  k_g2p_advect_tail<<<64, 256, 0, c->stream>>>(g, c->cell_start, c->n_sorted, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                               pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->ds, c->P.flip_ratio, dt_spec,
-                                               c->P.restitution, ekey, erank, ecount);
-  k_set_dt<<<1, 1, 0, c->stream>>>(c->ds, c->P.dt_max, c->P.dx);
-  CK_LAUNCH(); c->launches += 3;
-  int rc = fb_fetch_scalars(c);
-  if (rc) return rc;
-  if (c->hs->dt_out != dt_spec) return 0;          // bet lost: pt.a is untouched
-  for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
-  c->sorted = false;   // positions moved: cell order is stale
-  c->keys_ready = emit;
-  *done = true;
-  return 0;
-}
+int fb_g2p_advect_rows(flipb200_ctx* c, double timestep);   // rows.cu
 
-
+// c->opt_g2p (FLIPB200_G2P, read once at create):
+//   't' (default) ONE pass over the particles: G2P + advection with the rows staged by TMA (rows.cu), betting on
+//       dt == dt_max (true whenever maxSpeed <= dx / dt_max; tried when the previous step ended that way); the new state
+//       goes to the alternate buffers, so a lost bet costs one wasted pass and the two-kernel path below runs on the
+//       untouched inputs.  96 B / particle instead of 72 + 72: 3.0 ms against 4.5 ms at 256^3 / 127 M particles.
+//   'c' two kernels: k_g2p_cell (one thread per cell) then k_advect;  'p' k_g2p (one thread per particle) then k_advect
 int fb_g2p_advect(flipb200_ctx* c) {
   const Grid& g = c->g;
   Particles& pt = c->pt;
@@ -1116,36 +541,34 @@ int fb_g2p_advect(flipb200_ctx* c) {
   c->launches++;
   int blocks = (int)((pt.n + 255) / 256);
   if (blocks == 0) blocks = 1;
-  const char* mode = getenv("FLIPB200_G2P");
-  // FLIPB200_G2P=f1 / f4 / f4c: one-pass G2P + advection, betting on dt == dt_max when the previous step ended that way
-  if (mode && mode[0] == 'f' && c->world == 1 && c->sorted && pt.n == c->n_sorted && pt.n > 0 &&
-      (c->hs->dt_out == c->P.dt_max || c->hs->dt_out == 0.0)) {
-    bool done = false;
-    int rc = g2p_advect_fused(c, mode[1] == 'p' ? 0 : (mode[1] == '4' ? 4 : 1), mode[1] == '4' && mode[2] == 'c', &done);
-    if (rc || done) return rc;
-    k_reset_max<<<1, 1, 0, c->stream>>>(c->ds);
+  const char mode = c->opt_g2p;
+  int rc;
+  if (mode == 't' && c->sorted && pt.n == c->n_sorted && pt.n > 0 && (c->hs->dt_out == c->P.dt_max || c->hs->dt_out == 0.0)) {
+    const double dt_spec = c->P.dt_max;
+    if ((rc = fb_g2p_advect_rows(c, dt_spec))) return rc;
+    // the trailing bucket (key == total) holds the particles outside the box: no grid contact, free flight
+    k_g2p_advect_tail<<<64, 256, 0, c->stream>>>(g, c->cell_start, c->n_sorted, c->flags, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                                 pt.b[0], pt.b[1], pt.b[2], pt.b[3], pt.b[4], pt.b[5], c->ds, c->P.flip_ratio, dt_spec,
+                                                 c->P.restitution);
+    CK_LAUNCH(); c->launches++;
+    if ((rc = fb_allreduce(c, &c->ds->max_speed_bits, 1, FB_U64, FB_MAX))) return rc;   // maxSpeed is global (fluid.cc:976-991)
+    k_set_dt<<<1, 1, 0, c->stream>>>(c->ds, c->P.dt_max, c->P.dx);
+    CK_LAUNCH(); c->launches++;
+    if ((rc = fb_fetch_scalars(c))) return rc;
+    if (c->hs->dt_out == dt_spec) {                  // bet won: the alternate buffers hold the new state
+      for (int q = 0; q < 6; ++q) { double* t = pt.a[q]; pt.a[q] = pt.b[q]; pt.b[q] = t; }
+      c->sorted = false;                             // positions moved: cell order is stale (ids did not move: same index)
+      return 0;
+    }
+    k_reset_max<<<1, 1, 0, c->stream>>>(c->ds);     // bet lost: pt.a is untouched
     c->launches++;
   }
-  if (c->sorted && !(mode && mode[0] == 'p' && c->world == 1)) {
+  if (c->sorted && !(mode == 'p' && c->world == 1)) {
     if (c->n_sorted > 0) {
       dim3 blk(32, 4, 1), grd(cdiv(g.nx - 1, 32), cdiv(g.ny - 1, 4), g.k1 - g.k0);
-      if (mode && mode[0] == 'v' && mode[1] && mode[2] == 'c')   // FLIPB200_G2P=v4c: capped at 128 registers
-        k_g2p_cell4<4><<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                                   c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
-      else if (mode && mode[0] == 'v')     // FLIPB200_G2P=v4: 256-bit accesses (unmeasured, see k_g2p_cell4)
-        k_g2p_cell4<1><<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                                   c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
-      else if (!(mode && mode[0] == 'r'))  // default: per-cell kernel; FLIPB200_G2P=row: shared-memory staged variant (measured 3 % slower)
-        k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
-                                               c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);   // dc arrays written by fb_cell_delta
-      else {
-        static bool attr_set = false;
-        if (!attr_set) { CK(cudaFuncSetAttribute(k_g2p_row, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ROW_SMEM(6))); attr_set = true; }
-        k_g2p_row<<<grd, dim3(32, ROW_WARPS, 1), ROW_SMEM(6), c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
-                                                                           pt.a[4], pt.a[5], c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);
-      }
+      k_g2p_cell<<<grd, blk, 0, c->stream>>>(g, c->cell_start, pt.a[0], pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5],
+                                             c->r, c->pd, c->Ap, c->ds, c->P.flip_ratio);   // dc arrays written by fb_cell_delta
       c->launches++;
-      // the trailing bucket (key == total) holds the particles outside the box (usually none)
       k_speed_tail<<<64, 256, 0, c->stream>>>(c->cell_start, g.total, c->n_sorted, pt.a[3], pt.a[4], pt.a[5], c->ds, c->P.flip_ratio);
       c->launches++;
     }
@@ -1162,17 +585,7 @@ int fb_g2p_advect(flipb200_ctx* c) {
   }
   CK_LAUNCH();
   // maxSpeed is a global max (fluid.cc:976-991): every rank advects with the same dt
-  int rc = fb_allreduce(c, &c->ds->max_speed_bits, 1, FB_U64, FB_MAX);
-  if (rc) return rc;
-  if (sort_emit_keys(c) && pt.n > 0) {   // FLIPB200_SORT=k: advection also emits the next step's keys (k_advect_key)
-    if ((rc = clear_cell_count(c))) return rc;
-    k_advect_key<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
-                                                pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds, pt.key, pt.rank, c->cell_count);
-    CK_LAUNCH(); c->launches++;
-    c->sorted = false;
-    c->keys_ready = true;
-    return 0;
-  }
+  if ((rc = fb_allreduce(c, &c->ds->max_speed_bits, 1, FB_U64, FB_MAX))) return rc;
   k_advect<<<blocks, 256, 0, c->stream>>>(g, pt.n, c->flags, c->P.dt_max, c->P.dx, c->P.restitution, pt.a[0],
                                           pt.a[1], pt.a[2], pt.a[3], pt.a[4], pt.a[5], c->ds);
   CK_LAUNCH(); c->launches++;
@@ -1234,7 +647,6 @@ int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint6
   CK(cudaStreamSynchronize(c->stream));
   c->pt.n = base + add;
   c->sorted = false;
-  c->keys_ready = false;
   return 0;
 }
 

@@ -943,7 +943,7 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
     if (prof && it >= 3) { c->prof->on = true; c->prof->n = 0; c->halo.dbg_n = 0; }
     if (it == 3) CK(cudaEventRecord(c->ev[6], c->stream));
     if (which != FLIPB200_KERNEL_PCG_ITER) {
-      launch_spmv(c, cf, it, 1, 0, halo_off());
+      launch_spmv(c, cf, it, 1, 0, halo_off(), c->mg_levels >= 2 && pcg_p32_active(c));   // the stencil the product runs
       c->launches++;
     } else if (graph) {
       if (cudaGraphLaunch(c->it_exec, c->stream) != cudaSuccess) { fb_graph_invalidate(c); return FLIPB200_ERR_CUDA; }

@@ -41,6 +41,7 @@ class Flip:
         s.z0, s.z1 = 0, s.nz
         s.N = s.nx * s.ny * s.nz // world
         s.nf = 0
+        s.params = types.SimpleNamespace(mixed=3)
 
     def seed_box(s, lo, hi, seed=0):
         s.n = (hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1) * 8

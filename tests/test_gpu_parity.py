@@ -13,11 +13,10 @@ pytestmark = pytest.mark.gpu
 
 TOL_GRID = 1e-5      # north_star: single-step grid velocity / pressure rel-L2
 TOL_POS10 = 1e-4     # north_star: positions after 10 steps rel-L2
-# kernel variants that have not run on a GPU yet join the parametrised tests only on request
-# (FLIPB200_TEST_EXPERIMENTAL=1), so that an unmeasured variant can never turn the suite red
-_EXP = os.environ.get("FLIPB200_TEST_EXPERIMENTAL") == "1"
-PARTICLE_MODES = ["row", "cell", "particle"] + (["v4", "v4c"] if _EXP else [])
-G2P_MODES = PARTICLE_MODES + (["f1", "f4", "f4c"] if _EXP else [])      # one-pass G2P + advection (bet on dt == dt_max)
+# kernel variants kept after the round-2 measurements (FLIPB200_P2G / FLIPB200_G2P are read once, at create):
+# cell = one thread per cell, particle = one thread per particle, tma = rows staged in shared memory by TMA bulk copies
+PARTICLE_MODES = ["cell", "particle", "tma"]
+G2P_MODES = ["tma", "cell", "particle"]      # tma: ONE pass G2P + advection betting on dt == dt_max, two kernels when the bet is lost
 
 
 @pytest.fixture(scope="module")
@@ -98,11 +97,14 @@ def test_rhs_div_pcg_velupdate_relax(fb, oracle_mod, scenes):
     assert e == pytest.approx(eo, rel=1e-12)
 
 
+@pytest.mark.parametrize("vscale", [6.0, 1.5])
 @pytest.mark.parametrize("mode", G2P_MODES)
-def test_g2p_advect(fb, oracle_mod, scenes, mode, monkeypatch):
-    """a17/a18 from identical grids; includes particles that hit the solid shell (both G2P kernels)."""
+def test_g2p_advect(fb, oracle_mod, scenes, mode, vscale, monkeypatch):
+    """a17/a18 from identical grids; includes particles that hit the solid shell (all G2P kernels).
+    vscale 6: max speed > dx / dt_max, dt comes from the speed (the one-pass kernel's bet is lost, two kernels run);
+    vscale 1.5: dt == dt_max, the one-pass kernel's result is the one compared."""
     monkeypatch.setenv("FLIPB200_G2P", mode)
-    sc = random_velocity_scene(scenes, n=21, half=8, vscale=6.0)   # fast particles touching the wall (shell at |c| >= 9)
+    sc = random_velocity_scene(scenes, n=21, half=8, vscale=vscale)   # particles touching the wall (shell at |c| >= 9)
     f, o = _pair(fb, oracle_mod, sc)
     dt = 0.1
     f.p2g(); f.classify()
@@ -114,6 +116,7 @@ def test_g2p_advect(fb, oracle_mod, scenes, mode, monkeypatch):
     dt_g = f.g2p_advect()
     dt_o = o.flip_advect(dt)
     assert dt_g == pytest.approx(dt_o, rel=1e-13)
+    assert (dt_o == 0.1) == (vscale < 2.0)
     pg, vg = f.get_particles(); po, vo = o.get_particles()
     assert rel_l2(vg, vo) < 1e-12
     assert rel_l2(pg, po) < 1e-13
