@@ -148,6 +148,12 @@ __device__ __forceinline__ void halo_push4(const PeerHalo& H, int q, int k, floa
   if (H.push_dn && k == H.kdn) *reinterpret_cast<float4*>(reinterpret_cast<float*>(H.dst_dn) + q) = v;
   if (H.push_up && k == H.kup) *reinterpret_cast<float4*>(reinterpret_cast<float*>(H.dst_up) + q) = v;
 }
+// four values stored as fp16 (the level-0 residual of the V-cycle with params.mixed bit 1; q counts halves)
+__device__ __forceinline__ void halo_push4h(const PeerHalo& H, int q, int k, float4 v) {
+  if (H.mode == 0) return;
+  if (H.push_dn && k == H.kdn) stq4<__half>(reinterpret_cast<__half*>(H.dst_dn) + q, v);
+  if (H.push_up && k == H.kup) stq4<__half>(reinterpret_cast<__half*>(H.dst_up) + q, v);
+}
 template <typename T>
 __device__ __forceinline__ void halo_push1(const PeerHalo& H, int q, int k, T v) {
   if (H.mode == 0) return;

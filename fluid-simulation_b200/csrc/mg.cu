@@ -1044,19 +1044,23 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     {
       PeerHalo Hs = fb_halo_make(c, l, HA_XA, l, HA_XB, F, k0, k1, nbs);
       if (gathered) { fb_gather_wait(c, &Hs); gathered = false; }
-      if (l == 0 && h16) fb_h16_smooth4(c, 0, tg, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, it, rzs);
+      if (l == 0 && h16) fb_h16_smooth4(c, 0, tg, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, it, rzs, dist, Hs);
       else if (w4[l]) launch_smooth4<0>(tg, c->stream, Hs, S4[l], mc2[l], L.flags, L.b, L.xa, L.xb, (const double*)nullptr, c->ds, it, dist);
       else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc2[l], L.flags, L.b, L.xa, L.xb, nullptr, c->ds, it, dist, Hs);
     }
     fb_prof(c, l == 0 ? "L0 halo+smooth" : (l == 1 ? "L1 halo+smooth" : "L2+ halo+smooth"));
     HALO(L, L.xb);
     {
-      const PeerHalo Hr = fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs);
-      if (l == 0 && h16) fb_h16_resid4(c, tg, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa);
+      // the level-0 residual is stored (and pushed to the neighbours' ghost planes) as fp16 with params.mixed bit 1
+      const PeerHalo Hr = fb_halo_make(c, l, HA_XB, l, HA_XA, (l == 0 && h16) ? sizeof(__half) : F, k0, k1, nbs);
+      if (l == 0 && h16) fb_h16_resid4(c, tg, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, Hr);
       else if (w4[l]) launch_resid4(tg, c->stream, Hr, sweep_down(S4[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds);
       else k_mg_resid<<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc[l], L.flags, L.nrm, L.b, L.xb, L.xa, c->ds, Hr);
     }
     fb_prof(c, l == 0 ? "L0 halo+resid" : (l == 1 ? "L1 halo+resid" : "L2+ halo+resid"));
+    if (l == 0 && h16) {   // the residual in L.xa is an array of halves: its planes are half as wide in bytes
+      if (L.dist) { int rc__ = fused ? fb_halo_point(c) : fb_halo_fill(c, L.g, L.xa, sizeof(__half), 1, 1); if (rc__) return rc__; }
+    } else
     HALO(L, L.xa);
     Box cb = C.box;
     int ck0 = C.g.k0, ck1 = C.g.k1 - 1;          // boundary planes in the coarse index space
@@ -1077,7 +1081,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
       const GatherPush G = gathered ? fb_gather_make(c, some ? cg.x * cg.y * cg.z : 1) : gather_off();
       if (some) {
         if (l == 0 && h16 && !r4) return FLIPB200_ERR_STATE;       // the fp16 residual has no two-node reader
-        if (l == 0 && h16) fb_h16_restrict4(c, cg, pblk, L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, zc);
+        if (l == 0 && h16) fb_h16_restrict4(c, cg, pblk, L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, zc, H, G);
         else if (r4) k_mg_restrict4<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
         else k_mg_restrict<<<cg, pblk, 0, c->stream>>>(L.g, L.boxe, C.g, cb, mc[l + 1], C.flags, L.xa, C.b, C.xa, c->ds, zc, H, G);
       } else if (gathered && G.mode == 2) k_mg_gather_signal<<<1, 32, 0, c->stream>>>(c->ds, G);
@@ -1134,7 +1138,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     HALO(L, L.xb);
     {
       const PeerHalo H1 = fb_halo_make(c, l, HA_XB, l, HA_XA, F, k0, k1, nbs);
-      if (l == 0 && h16) fb_h16_smooth4(c, 0, tg, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, it, rzs);
+      if (l == 0 && h16) fb_h16_smooth4(c, 0, tg, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, it, rzs, dist, H1);
       else if (w4[l]) launch_smooth4<0>(tg, c->stream, H1, sweep_down(S4[l]), mc2[l], L.flags, L.b, L.xb, L.xa, (const double*)nullptr, c->ds, it, dist);
       else k_mg_smooth<0><<<tg, STENCIL_BLOCK, 0, c->stream>>>(sweep_down(S[l]), mc2[l], L.flags, L.b, L.xb, L.xa, nullptr, c->ds, it, dist, H1);
     }
@@ -1143,7 +1147,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     // the last sweep's output is read through ghosts only as the coarse correction of the level above
     if (l == 0) {
       const PeerHalo Hd = fb_halo_make(c, l, HA_XA, -1, -1, F, k0, k1, nbs);
-      if (h16) fb_h16_smooth4(c, 2, tg, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, it, rzs);
+      if (h16) fb_h16_smooth4(c, 2, tg, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, it, rzs, dist, Hd);
       else if (w4[l] && rz64) launch_smooth4<1>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
       else if (w4[l]) launch_smooth4<2>(tg, c->stream, Hd, S4[l], mc[l], L.flags, L.b, L.xa, L.xb, (const double*)c->r, c->ds, it, dist);
       else if (rz64) k_mg_smooth<1><<<tg, STENCIL_BLOCK, 0, c->stream>>>(S[l], mc[l], L.flags, L.b, L.xa, L.xb, c->r, c->ds, it, dist, Hd);

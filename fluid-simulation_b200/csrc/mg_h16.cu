@@ -1,4 +1,4 @@
-// mg_h16.cu -- FLIPB200_MG_H16=1 (experimental, OFF by default, not yet measured on a GPU; see pcg.cuh).
+// mg_h16.cu -- params.mixed bit 1 (default ON since round 2; see pcg.cuh).
 // Level-0 V-cycle sweeps that keep the right-hand side b0 and the residual handed to the restriction
 // in fp16 (arithmetic in fp32): copies of k_mg_smooth4 / k_mg_resid4 / k_mg_restrict4 of mg.cu with the
 // loads / stores of those two arrays swapped.  They live in their own translation unit, behind host
@@ -96,7 +96,7 @@ k_mg_resid4h(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
       o.y = resid_node(mc, (f >> 8) & 0xffu, (nn >> 8) & 0xffu, m.pc.y, bv.y, m.sum1());
       o.z = resid_node(mc, (f >> 16) & 0xffu, (nn >> 16) & 0xffu, m.pc.z, bv.z, m.sum2());
       o.w = resid_node(mc, f >> 24, nn >> 24, m.pc.w, bv.w, m.sum3());
-      if (m.act) { stq4<__half>(rn + m.q, o); if (PEER) halo_push4(H, m.q, m.k, o); }
+      if (m.act) { stq4<__half>(rn + m.q, o); if (PEER) halo_push4h(H, m.q, m.k, o); }
       m.advance(S);
     }
   }
@@ -177,18 +177,24 @@ k_mg_restrict4h(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t*
 }
 
 
-// host wrappers (single GPU: no peer code)
+// host wrappers; H.mode != 0 on z-slab runs (ghost planes pushed by the producing kernel, halo.cuh)
 void fb_h16_smooth4(flipb200_ctx* c, int dot, dim3 g, const Sweep& S, const MgCoef& m, const uint8_t* fl, const float* b0,
-                    const float* xi, float* xo, int it, float rzs) {
+                    const float* xi, float* xo, int it, float rzs, int dist, const PeerHalo& H) {
   const __half* b = reinterpret_cast<const __half*>(b0);
-  if (dot == 2) k_mg_smooth4h<2, false><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, b, xi, xo, nullptr, c->ds, it, 0, halo_off(), rzs);
-  else k_mg_smooth4h<0, false><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, b, xi, xo, nullptr, c->ds, it, 0, halo_off(), rzs);
+  if (H.mode) {
+    if (dot == 2) k_mg_smooth4h<2, true><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, b, xi, xo, nullptr, c->ds, it, dist, H, rzs);
+    else k_mg_smooth4h<0, true><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, b, xi, xo, nullptr, c->ds, it, dist, H, rzs);
+  } else {
+    if (dot == 2) k_mg_smooth4h<2, false><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, b, xi, xo, nullptr, c->ds, it, dist, H, rzs);
+    else k_mg_smooth4h<0, false><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, b, xi, xo, nullptr, c->ds, it, dist, H, rzs);
+  }
 }
 void fb_h16_resid4(flipb200_ctx* c, dim3 g, const Sweep& S, const MgCoef& m, const uint8_t* fl, const uint8_t* nrm, const float* b0,
-                   const float* x, float* rn) {
-  k_mg_resid4h<false><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, nrm, reinterpret_cast<const __half*>(b0), x, reinterpret_cast<__half*>(rn), c->ds, halo_off());
+                   const float* x, float* rn, const PeerHalo& H) {
+  if (H.mode) k_mg_resid4h<true><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, nrm, reinterpret_cast<const __half*>(b0), x, reinterpret_cast<__half*>(rn), c->ds, H);
+  else k_mg_resid4h<false><<<g, STENCIL_BLOCK, 0, c->stream>>>(S, m, fl, nrm, reinterpret_cast<const __half*>(b0), x, reinterpret_cast<__half*>(rn), c->ds, H);
 }
 void fb_h16_restrict4(flipb200_ctx* c, dim3 g, dim3 blk, const Grid& gf, const Box& fbox, const Grid& gc, const Box& cbox, const MgCoef& mcc,
-                      const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc) {
-  k_mg_restrict4h<<<g, blk, 0, c->stream>>>(gf, fbox, gc, cbox, mcc, fc, reinterpret_cast<const __half*>(rn), bc, x1c, c->ds, zc, halo_off(), gather_off());
+                      const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc, const PeerHalo& H, const GatherPush& G) {
+  k_mg_restrict4h<<<g, blk, 0, c->stream>>>(gf, fbox, gc, cbox, mcc, fc, reinterpret_cast<const __half*>(rn), bc, x1c, c->ds, zc, H, G);
 }

@@ -275,7 +275,7 @@ k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, con
 
 // launch K1 in the shape that fits the sweep (FLIPB200_ST4=0: always two nodes per lane)
 static void launch_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit, int dist, const PeerHalo& H, bool p32 = false) {
-  if (p32) { fb_p32_spmv(c, cf, it_arg, noexit); return; }       // experimental fp32 search direction (pcg_p32.cu)
+  if (p32) { fb_p32_spmv(c, cf, it_arg, noexit, dist, H); return; }       // fp32 search direction (pcg_p32.cu)
   const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
   const Sweep S4 = make_sweep(c->g, c->box, 4);
   if (st4_on && S4.xe - S4.box.x0 >= 128) {
@@ -639,10 +639,11 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   const double bscale = h16 ? mg_h16_bscale(c) : 1.0;
   int rc;
   fb_prof(c, "start");
-  if (fused) rc = fb_halo_point(c); else rc = fb_halo_fill(c, c->g, c->pd, sizeof(double), 1, 1);
+  const bool p32 = use_mg && pcg_p32_active(c);
+  const size_t pel = p32 ? sizeof(float) : sizeof(double);      // storage width of the search direction
+  if (fused) rc = fb_halo_point(c); else rc = fb_halo_fill(c, c->g, c->pd, pel, 1, 1);
   if (rc) return rc;
   fb_prof(c, "halo pd");
-  const bool p32 = use_mg && pcg_p32_active(c);
   launch_spmv(c, cf, it_arg, noexit, dist, fused ? fb_halo_make(c, 0, HA_PD, -1, -1, 0, k0, k1, tg.x * tg.y) : halo_off(), p32);
   fb_prof(c, "k_spmv");
   if (dist) {
@@ -659,7 +660,8 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     if (st4_on && S4.xe - S4.box.x0 >= 128) {
       const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
       if (h16) k_update_xr4<__half><<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), cf, c->flags, c->r, c->Ap, reinterpret_cast<__half*>(L0.b), L0.xa, c->ds,
-                                                                         it_arg, noexit, dist, halo_off(), bscale);
+                                                                         it_arg, noexit, dist,
+                                                                         fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off(), bscale);
       else
       k_update_xr4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), cf, c->flags, c->r, c->Ap, L0.b, L0.xa, c->ds, it_arg, noexit, dist,
                                                         fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off(), 1.0);
@@ -673,8 +675,11 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
     rc = fb_mg_vcycle(c, it_arg);
     if (rc) return rc;
     const bool up4_on = true;                       // four nodes per lane whenever the rows are wide enough (k_update_p4)
-    if (p32) fb_p32_update_p(c, L0.xb, it_arg, noexit, h16 ? 1.0 / bscale : 1.0, true);
-    else if ((up4_on || h16) && st4_on && S4.xe - S4.box.x0 >= 128) {
+    if (p32) {
+      const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
+      fb_p32_update_p(c, L0.xb, it_arg, noexit, h16 ? 1.0 / bscale : 1.0, true,
+                      fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off());
+    } else if ((up4_on || h16) && st4_on && S4.xe - S4.box.x0 >= 128) {
       const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
       k_update_p4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(sweep_down(S4), c->flags, L0.xb, c->pd, c->x, c->ds, it_arg, noexit,
                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg4.x * sg4.y) : halo_off(),
@@ -803,7 +808,8 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     if ((rc = fb_fetch_scalars(c))) return rc;          // one round trip: |r0|^2 sizes the first batch, and the guess may already pass
   } else if (h16)
     k_pcg_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, reinterpret_cast<__half*>(L0.b), L0.xa,
-                                                              (bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0) * bscale, c->ds, dist, halo_off());
+                                                              (bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0) * bscale, c->ds, dist,
+                                                              fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
   else if (use_mg)
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, L0.b, L0.xa,
                                                       bnorm2 > 0.0 ? 1.0 / sqrt(bnorm2) : 1.0, c->ds, dist,
@@ -824,11 +830,15 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (use_mg && !done) {
     int rc = fb_mg_vcycle(c, -1);                  // z0 = M^-1 r0, rz[3] = r0.z0
     if (rc) return rc;
-    if (pcg_p32_active(c)) fb_p32_update_p(c, L0.xb, -1, 0, h16 ? 1.0 / bscale : 1.0, false);
-    else if (h16) {
-      const Sweep S4 = make_sweep(c->g, c->box, 4);
-      k_update_p4<<<dim3(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z), STREAM_BLOCK, 0, c->stream>>>(S4, c->flags, L0.xb, c->pd, c->x, c->ds, -1, 0, halo_off(), 1.0 / bscale);
-    } else
+    const Sweep S4p = make_sweep(c->g, c->box, 4);
+    const dim3 sg4p(cdiv(S4p.xe - S4p.box.x0, 128), sg.y, sg.z);
+    if (pcg_p32_active(c))
+      fb_p32_update_p(c, L0.xb, -1, 0, h16 ? 1.0 / bscale : 1.0, false,
+                      fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(float), k0, k1, sg4p.x * sg4p.y) : halo_off());
+    else if (h16)
+      k_update_p4<<<sg4p, STREAM_BLOCK, 0, c->stream>>>(S4p, c->flags, L0.xb, c->pd, c->x, c->ds, -1, 0,
+                                                        fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg4p.x * sg4p.y) : halo_off(), 1.0 / bscale);
+    else
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, -1, 0,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 0, halo_seg_close(c));
@@ -909,19 +919,26 @@ int fb_pcg_time(flipb200_ctx* c, int which, int iters, float* ms, int64_t* units
   const double bscale = h16 ? mg_h16_bscale(c) : 1.0;
   if (h16) {
     k_pcg_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, reinterpret_cast<__half*>(L0.b), L0.xa,
-                                                              bscale / sqrt(bn), c->ds, dist, halo_off());
+                                                              bscale / sqrt(bn), c->ds, dist,
+                                                              fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     int rc = fb_mg_vcycle(c, -1); if (rc) return rc;
     const Sweep S4 = make_sweep(c->g, c->box, 4);
-    if (pcg_p32_active(c)) fb_p32_update_p(c, L0.xb, -1, 1, 1.0 / bscale, false);
+    const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
+    if (pcg_p32_active(c)) fb_p32_update_p(c, L0.xb, -1, 1, 1.0 / bscale, false,
+                                           fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off());
     else
-    k_update_p4<<<dim3(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z), STREAM_BLOCK, 0, c->stream>>>(S4, c->flags, L0.xb, c->pd, c->x, c->ds, -1, 1, halo_off(), 1.0 / bscale);
+    k_update_p4<<<sg4, STREAM_BLOCK, 0, c->stream>>>(S4, c->flags, L0.xb, c->pd, c->x, c->ds, -1, 1,
+                                                     fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg4.x * sg4.y) : halo_off(), 1.0 / bscale);
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1, halo_seg_close(c));
   } else if (use_mg) {
     k_pcg_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->bf[c->bcur], c->x, c->r, c->pd, L0.b, L0.xa, 1.0 / sqrt(bn), c->ds, dist,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off());
     int rc = fb_mg_vcycle(c, -1); if (rc) return rc;
-    if (pcg_p32_active(c)) fb_p32_update_p(c, L0.xb, -1, 1, 1.0, false);
-    else
+    if (pcg_p32_active(c)) {
+      const Sweep S4 = make_sweep(c->g, c->box, 4);
+      const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
+      fb_p32_update_p(c, L0.xb, -1, 1, 1.0, false, fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(float), k0, k1, sg4.x * sg4.y) : halo_off());
+    } else
     k_update_p<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, c->r, L0.xb, c->pd, c->x, c->ds, -1, 1,
                                                       fused ? fb_halo_make(c, -1, -1, 0, HA_PD, sizeof(double), k0, k1, sg.x * sg.y) : halo_off());
     k_pcg_advance<<<1, 1, 0, c->stream>>>(c->ds, -1, 1, halo_seg_close(c));

@@ -37,9 +37,10 @@ __device__ __forceinline__ int pcg_iter(const DevScalars* ds, int it_arg) { retu
 // Saves 14 of the ~88 B/node the level-0 part of an iteration moves.  fp16 needs O(1) entries: the
 // scaled residual (|b0| = 1, entries ~ 1/sqrt(N)) is multiplied by bscale = 2^floor(log2 sqrt(N)) / 4; the
 // V-cycle is linear, k_update_p4 divides z by it again and the fused r.z by its square.
-// Single GPU, four-node sweeps only (rows >= 128 nodes); the direction update runs as k_update_p4.
+// Four-node sweeps only (rows >= 128 nodes); the direction update runs as k_update_p4.  z-slab runs: the fp16 residual's
+// ghost planes travel as fp16 (halo_push4h).
 static inline bool mg_h16_active(const flipb200_ctx* c) {
-  if (!(c->P.mixed & 2) || c->world != 1 || c->mg_levels < 2) return false;
+  if (!(c->P.mixed & 2) || c->mg_levels < 2) return false;
   const char* s4 = getenv("FLIPB200_ST4");
   if (s4 && s4[0] == '0') return false;
   const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
@@ -55,23 +56,25 @@ static inline double mg_h16_bscale(const flipb200_ctx* c) {
 }
 // mg_h16.cu: host wrappers of the fp16-storage copies of the level-0 sweeps
 struct Sweep;
+struct PeerHalo;
+struct GatherPush;
 void fb_h16_smooth4(flipb200_ctx* c, int dot, dim3 g, const Sweep& S, const MgCoef& m, const uint8_t* fl, const float* b0,
-                    const float* xi, float* xo, int it, float rzs);
+                    const float* xi, float* xo, int it, float rzs, int dist, const PeerHalo& H);
 void fb_h16_resid4(flipb200_ctx* c, dim3 g, const Sweep& S, const MgCoef& m, const uint8_t* fl, const uint8_t* nrm, const float* b0,
-                   const float* x, float* rn);
+                   const float* x, float* rn, const PeerHalo& H);
 void fb_h16_restrict4(flipb200_ctx* c, dim3 g, dim3 blk, const Grid& gf, const Box& fbox, const Grid& gc, const Box& cbox, const MgCoef& mcc,
-                      const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc);
+                      const uint8_t* fc, const float* rn, float* bc, float* x1c, int zc, const PeerHalo& H, const GatherPush& G);
 
 // params.mixed bit 0 (default ON since round 2: measured -32 us per iteration, same iteration counts; pcg_p32.cu): the CG search direction stored as fp32.
-// Same conditions as the fp16 variant: single GPU, multigrid on, four-node sweeps.
+// Same conditions as the fp16 variant: multigrid on, four-node sweeps; on z-slabs the ghost planes of p travel as fp32.
 static inline bool pcg_p32_active(const flipb200_ctx* c) {
-  if (!(c->P.mixed & 1) || c->world != 1 || c->mg_levels < 2) return false;
+  if (!(c->P.mixed & 1) || c->mg_levels < 2) return false;
   const char* s4 = getenv("FLIPB200_ST4");
   if (s4 && s4[0] == '0') return false;
   const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
   return xe - x0 >= 128;
 }
 struct PcgCoef;
-void fb_p32_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit);
-void fb_p32_update_p(flipb200_ctx* c, const float* zf, int it_arg, int noexit, double inv_bscale, bool down);
+void fb_p32_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit, int dist, const PeerHalo& H);
+void fb_p32_update_p(flipb200_ctx* c, const float* zf, int it_arg, int noexit, double inv_bscale, bool down, const PeerHalo& H);
 void fb_p32_finish_x(flipb200_ctx* c);
