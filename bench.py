@@ -270,7 +270,7 @@ class Job:
         self.dist.all_gather(out, t)
         return [o.cpu().tolist() for o in out]
 
-    def make(self, n, nzg, cap, world=None, rank=None, origin=None):
+    def make(self, n, nzg, cap, world=None, rank=None, origin=None, zsplit=None):
         world = self.world if world is None else world
         rank = self.rank if rank is None else rank
         o = origin if origin is not None else (n // 2, n // 2, nzg // 2)
@@ -278,7 +278,7 @@ class Job:
             return self.fb.Flip(nx=n, ny=n, nz=nzg, ox=o[0], oy=o[1], oz=o[2], max_particles=cap, precond=self.args.precond,
                                 device=self.local_rank)
         return self.fdist.create_slab_flip(self.fb, rank, world, device=self.local_rank, nx=n, ny=n, nz=nzg, ox=o[0], oy=o[1], oz=o[2],
-                                           max_particles=cap, precond=self.args.precond)
+                                           max_particles=cap, precond=self.args.precond, zsplit=zsplit)
 
     def finish(self):
         if self.world > 1:
@@ -623,7 +623,9 @@ def bench_cube_drop(job, n, steps, warmup):
     lo, hi = cube_box(n)
     side = hi[0] - lo[0] + 1
     total = side ** 3 * 8
-    zs, _a = job.fdist.slab_split(n, world)
+    # static load balancing along z: the cube only occupies the planes lo-1 .. hi+1, so the slab boundaries are chosen to
+    # give every rank the same share of THOSE planes (flipb200_create_slab_split); --even-split keeps the even cut
+    zs = job.fdist.slab_split(n, world)[0] if (args.even_split or world == 1) else job.fdist.balanced_split(n, world, lo[2] - 1, hi[2] + 2)
     own = max(0, min(hi[2] + 1, zs[rank + 1]) - max(lo[2], zs[rank]))
     cap = int((side * side * own * 8 + side * side * 8 * 4) * 1.5) + 65536
     NCHK = 3
@@ -639,7 +641,7 @@ def bench_cube_drop(job, n, steps, warmup):
                 ref_stats.append(st.as_dict())
             g.close()
         job.barrier()
-    f = job.make(n, n, cap)
+    f = job.make(n, n, cap, zsplit=None if (args.even_split or world == 1) else zs)
     f.seed_box(lo, hi, seed=1234)
     first = []
     dt = 0.1
@@ -672,8 +674,9 @@ def bench_cube_drop(job, n, steps, warmup):
             "ms_per_step": dev_s / steps * 1e3, "wall_ms_per_step": wall / steps * 1e3,
             "config": {"workload": f"cube-drop FLIP, {n}^3 grid, cube of side {side} voxels, 8 particles/cell ({total} particles), fp64, "
                                    f"{'MG-' if args.precond == 1 else 'Jacobi-'}PCG to 2.2e-16 (BASELINE configs[3])", "grid": [n, n, n], "particles_total": total,
-                       "parallelism": "single GPU" if world == 1 else f"{world} z-slabs of ~{n // world} planes, halo exchange + PCG all-reduces + particle migration",
-                       "engine": info},
+                       "parallelism": "single GPU" if world == 1 else f"{world} z-slabs with boundaries {zs} ({'even' if args.even_split else 'balanced over the planes that hold the cube'}), "
+                                                                                  "halo exchange + PCG all-reduces + particle migration",
+                       "slab_boundaries": zs, "engine": info},
             "gpu_launches": int(launches), "check": check, "per_step": per_step(stats), "ms_sort_mean": float(np.mean(moved)) if moved else None}
 
 
@@ -690,6 +693,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="headline workload only (no pcg / cube_drop_512 / column / 128 / default scene)")
+    ap.add_argument("--even-split", action="store_true", help="cube-drop on N GPUs: even z-slabs instead of the load-balanced boundaries")
     ap.add_argument("--kernel-iters", type=int, default=50)
     ap.add_argument("--precond", type=int, default=int(os.environ.get("FLIPB200_PRECOND", "1")), help="0 Jacobi, 1 multigrid V-cycle")
     args = ap.parse_args()

@@ -65,7 +65,7 @@ EXPORTS = [
     "flipb200_host_alloc", "flipb200_host_free",
     "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
     "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab", "flipb200_halo_mode", "flipb200_debug_info",
-    "flipb200_profile_iteration",
+    "flipb200_profile_iteration", "flipb200_create_slab_split",
 ]
 
 _lib = None
@@ -116,6 +116,7 @@ def load():
     lib.flipb200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     lib.flipb200_host_free.argtypes = [vp]
     lib.flipb200_create_slab.argtypes = [C.POINTER(Params), vp, C.c_int32, C.c_int32, C.POINTER(vp)]
+    lib.flipb200_create_slab_split.argtypes = [C.POINTER(Params), vp, C.c_int32, C.c_int32, ip, C.POINTER(vp)]
     lib.flipb200_slab_range.argtypes = [vp, ip, ip]
     lib.flipb200_comm_unique_id.argtypes = [vp]
     lib.flipb200_comm_init_nccl.argtypes = [vp, vp]
@@ -174,8 +175,9 @@ def pinned_free(p):
 class Flip:
     """One simulation context on one GPU.  Grid arrays are (nz, ny, nx) numpy arrays (x fastest)."""
 
-    def __init__(self, params=None, solid=None, rank=0, world=1, **kw):
-        """world > 1: this context is z-slab `rank` of `world` (connect with comm_init_* before use)."""
+    def __init__(self, params=None, solid=None, rank=0, world=1, zsplit=None, **kw):
+        """world > 1: this context is z-slab `rank` of `world` (connect with comm_init_* before use);
+        zsplit: world + 1 slab boundaries chosen by the caller (dist.balanced_split), default an even split."""
         self.lib = load()
         self.params = params if params is not None else default_params(**kw)
         self.rank, self.world = rank, world
@@ -189,6 +191,9 @@ class Flip:
         h = C.c_void_p()
         if world == 1:
             _check(self.lib.flipb200_create(C.byref(self.params), sp, C.byref(h)), "flipb200_create")
+        elif zsplit is not None:
+            zs = (C.c_int32 * (world + 1))(*[int(z) for z in zsplit])
+            _check(self.lib.flipb200_create_slab_split(C.byref(self.params), sp, rank, world, zs, C.byref(h)), "flipb200_create_slab_split")
         else:
             _check(self.lib.flipb200_create_slab(C.byref(self.params), sp, rank, world, C.byref(h)), "flipb200_create_slab")
         self.h = h

@@ -350,7 +350,7 @@ int fb_reserve_particles(flipb200_ctx* c, int64_t n);
 int fb_init_ids(flipb200_ctx* c, int64_t first, int64_t n, int64_t id0);
 int fb_sort_particles_ex(flipb200_ctx* c, int filter);
 int fb_download_particles(flipb200_ctx* c, double* const dst[6]);
-int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int world, flipb200_ctx** out);
+int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int world, flipb200_ctx** out, const int32_t* zsplit_in);
 
 // ---- z-slab exchanges (comm.cu); every call is a no-op returning 0 when world == 1 -------------
 enum { FB_F64 = 0, FB_I32 = 1, FB_U64 = 2 };

@@ -162,7 +162,27 @@ static int slab_split(int nz, int world, int* zs, int* align_log2) {
   return 0;
 }
 
-int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int world, flipb200_ctx** out) {
+// caller-given slab boundaries (flipb200_create_slab_split): zs[0] = 0 < zs[1] < ... < zs[world] = nz; the alignment is the
+// largest 2^a (a <= 5) that divides every interior boundary and leaves every slab >= 2 * 2^a planes; a >= 1 is required
+static int slab_split_given(int nz, int world, const int32_t* in, int* zs, int* align_log2) {
+  if (in[0] != 0 || in[world] != nz) return -1;
+  for (int r = 0; r < world; ++r) if (in[r + 1] <= in[r]) return -1;
+  int a = 5;
+  for (int r = 1; r < world; ++r) { int t = 0; while (t < 5 && !((in[r] >> t) & 1)) ++t; if (t < a) a = t; }
+  for (;;) {
+    bool ok = true;
+    for (int r = 0; r < world; ++r) if (in[r + 1] - in[r] < (2 << a)) ok = false;
+    if (ok || a == 0) break;
+    --a;
+  }
+  if (a < 1) return -1;
+  for (int r = 0; r < world; ++r) if (in[r + 1] - in[r] < (2 << a) || in[r + 1] - in[r] < 4) return -1;
+  for (int r = 0; r <= world; ++r) zs[r] = in[r];
+  *align_log2 = a;
+  return 0;
+}
+
+int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int world, flipb200_ctx** out, const int32_t* zsplit_in) {
   if (!p || !out) return FLIPB200_ERR_ARG;
   *out = nullptr;
   if (p->nx < 2 * p->wall + 2 || p->ny < 2 * p->wall + 2 || p->nz < 2 * p->wall + 2) return FLIPB200_ERR_ARG;
@@ -179,7 +199,8 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
   if (const char* e = getenv("FLIPB200_P2G")) if (e[0] == 'c' || e[0] == 'p' || e[0] == 't') c->opt_p2g = e[0];
   if (const char* e = getenv("FLIPB200_G2P")) if (e[0] == 'c' || e[0] == 'p' || e[0] == 't') c->opt_g2p = e[0];
   c->rank = rank; c->world = world;
-  if (slab_split(p->nz, world, c->zsplit, &c->slab_align)) { free(c); return FLIPB200_ERR_ARG; }
+  if (zsplit_in && world > 1 ? slab_split_given(p->nz, world, zsplit_in, c->zsplit, &c->slab_align)
+                             : slab_split(p->nz, world, c->zsplit, &c->slab_align)) { free(c); return FLIPB200_ERR_ARG; }
   c->gz0 = c->zsplit[rank]; c->gz1 = c->zsplit[rank + 1];
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -255,7 +276,7 @@ fail:
 extern "C" {
 
 int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb200_ctx** out) {
-  return fb_create(p, solid_host, 0, 1, out);
+  return fb_create(p, solid_host, 0, 1, out, nullptr);
 }
 
 // One z-slab of the box: rank `rank` of `world` owns the global planes reported by
@@ -264,7 +285,17 @@ int flipb200_create(const flipb200_params* p, const uint8_t* solid_host, flipb20
 int flipb200_create_slab(const flipb200_params* p, const uint8_t* solid_host, int32_t rank, int32_t world,
                          flipb200_ctx** out) {
   if (world < 1 || world > 16 || rank < 0 || rank >= world) return FLIPB200_ERR_ARG;
-  return fb_create(p, solid_host, rank, world, out);
+  return fb_create(p, solid_host, rank, world, out, nullptr);
+}
+
+// The same with slab boundaries chosen by the caller (static load balancing: the fluid of a scene rarely fills the
+// box evenly along z, and the pressure solve only sweeps the planes that hold fluid).  zsplit: world + 1 global
+// plane indices, 0 = zsplit[0] < ... < zsplit[world] = nz, interior boundaries multiples of 2^a with a >= 1 and every
+// slab >= 2 * 2^a planes (a decides how many multigrid levels stay distributed).  The same array on every rank.
+int flipb200_create_slab_split(const flipb200_params* p, const uint8_t* solid_host, int32_t rank, int32_t world,
+                               const int32_t* zsplit, flipb200_ctx** out) {
+  if (world < 1 || world > 16 || rank < 0 || rank >= world || !zsplit) return FLIPB200_ERR_ARG;
+  return fb_create(p, solid_host, rank, world, out, zsplit);
 }
 
 int flipb200_slab_range(flipb200_ctx* c, int32_t* z0, int32_t* z1) {

@@ -31,6 +31,36 @@ def slab_split(nz, world):
     return zs, a
 
 
+def balanced_split(nz, world, z_lo, z_hi, max_imbalance=1.12):
+    """Slab boundaries that give every rank about the same number of the planes [z_lo, z_hi) that hold fluid (the
+    pressure solve and the particle kernels only work there).  Boundaries are multiples of 2^a, slabs >= 2 * 2^a planes;
+    the largest a (more distributed multigrid levels) whose busiest rank stays within max_imbalance of the ideal share
+    wins.  Returns the world + 1 boundaries for flipb200_create_slab_split."""
+    if world == 1:
+        return [0, nz]
+    z_lo, z_hi = max(0, int(z_lo)), min(nz, int(z_hi))
+    ideal = (z_hi - z_lo) / world
+    best = None
+    for a in range(5, 0, -1):
+        A = 1 << a
+        zs = [0]
+        for r in range(1, world):
+            b = int(round((z_lo + r * ideal) / A)) * A
+            b = max(b, zs[-1] + 2 * A)
+            zs.append(b)
+        zs.append(nz)
+        if any(zs[r + 1] - zs[r] < max(2 * A, 4) for r in range(world)):
+            continue
+        load = max(max(0, min(zs[r + 1], z_hi) - max(zs[r], z_lo)) for r in range(world))
+        if best is None or load < best[0]:
+            best = (load, zs)
+        if load <= max_imbalance * ideal:
+            return zs
+    if best is None:
+        raise ValueError("no aligned split")
+    return best[1]
+
+
 def owner_of(pz, oz, zs):
     """Rank that owns particles with reference z coordinate pz (array): the rank whose planes hold
     the base plane of the particle's 2x2x2 support (round(p) on the side of the fractional part,
@@ -65,13 +95,13 @@ def broadcast_unique_id(make_id, rank, world, group=None):
     return bytes(t.cpu().tolist())
 
 
-def create_slab_flip(fb, rank, world, device=None, **params):
+def create_slab_flip(fb, rank, world, device=None, zsplit=None, **params):
     """Slab context of this rank, connected over NCCL.  `fb` is the fluid_simulation_b200 module;
-    torch.distributed must be initialised when world > 1."""
+    torch.distributed must be initialised when world > 1.  zsplit: see balanced_split."""
     kw = dict(params)
     if device is not None:
         kw["device"] = device
-    f = fb.Flip(rank=rank, world=world, **kw)
+    f = fb.Flip(rank=rank, world=world, zsplit=zsplit if world > 1 else None, **kw)
     if world > 1:
         uid = broadcast_unique_id(fb.comm_unique_id, rank, world)
         f.comm_init_nccl(uid)

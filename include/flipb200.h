@@ -111,6 +111,10 @@ void flipb200_destroy(flipb200_ctx*);
  * owns; seed_box seeds the rank's part of a global box; get_particles / get_grid return the
  * rank's particles / owned planes.  step_host is not available on slab contexts. */
 int  flipb200_create_slab(const flipb200_params*, const uint8_t* solid_host, int32_t rank, int32_t world, flipb200_ctx**);
+/* create_slab with slab boundaries chosen by the caller (static load balancing along z): zsplit[0..world], 0 = zsplit[0] < ... <
+ * zsplit[world] = nz, interior boundaries multiples of 2^a (a >= 1), every slab >= 2 * 2^a planes; same array on every rank */
+int  flipb200_create_slab_split(const flipb200_params*, const uint8_t* solid_host, int32_t rank, int32_t world,
+                                const int32_t* zsplit, flipb200_ctx**);
 int  flipb200_slab_range(flipb200_ctx*, int32_t* z0, int32_t* z1);
 int  flipb200_comm_unique_id(void* id128);                         /* ncclGetUniqueId, 128 bytes */
 int  flipb200_comm_init_nccl(flipb200_ctx*, const void* id128);    /* ncclCommInitRank(world, id, rank) */

@@ -217,3 +217,35 @@ def test_slab_wide_rows_mixed_precision(fb, fused, monkeypatch):
     assert sum(f.num_particles for f in fs) == f1.num_particles
     for f in fs + [f1]:
         f.close()
+
+
+def test_slab_caller_chosen_split(fb, scenes):
+    """flipb200_create_slab_split: uneven slab boundaries (static load balancing along z, dist.balanced_split) give the
+    same step as the single context; a bad split is rejected."""
+    from fluid_simulation_b200 import dist as fdist
+    sc = moving_scene(scenes, n=48)
+    nx, ny, nz = sc.n
+    ox, oy, oz = sc.origin
+    zs = [0, 8, 16, 48]
+    assert fdist.balanced_split(512, 8, 170, 343) == [0, 192, 216, 232, 256, 280, 296, 320, 512]
+    f1 = fb.Flip.from_scene(sc, track_ids=1)
+    gid = next(_group)
+    fs = [fb.Flip(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=sc.wall, track_ids=1, rank=r, world=3, zsplit=zs) for r in range(3)]
+    assert [(f.z0, f.z1) for f in fs] == [(0, 8), (8, 16), (16, 48)]
+    for f in fs:
+        f.comm_init_local(gid)
+    run_ranks([lambda f=f: f.set_particles(sc.pos, sc.vel) for f in fs])
+    d1, ds = 0.1, [0.1] * 3
+    for step in range(4):
+        d1, st1 = f1.step(d1)
+        res = run_ranks([lambda f=f, d=ds[r]: f.step(d) for r, f in enumerate(fs)])
+        ds = [r[0] for r in res]
+        assert all(r[1].passes == st1.passes and r[1].n_fluid == st1.n_fluid for r in res), step
+        assert rel_l2(gather_grid(fs, fb.GRID_P), f1.get_grid(fb.GRID_P)) < 1e-8, step
+    p1, v1 = f1.get_particles()
+    ps, vs = gather_particles(fs, sc.num_particles)
+    assert rel_l2(ps, p1) < 1e-10 and rel_l2(vs, v1) < 1e-9
+    with pytest.raises(fb.FlipError):
+        fb.Flip(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, rank=0, world=3, zsplit=[0, 7, 16, 48])     # odd boundary
+    for f in fs + [f1]:
+        f.close()
