@@ -74,12 +74,12 @@ k_pcg_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, 
 // on cells that are still fluid; over the relaxation passes of one step the right-hand sides obey
 // b_{k+1} = th b_k + G with th = 1 - 1/relax_div (fluid.cc:1475: velUpdate applies a tenth of the gradient), so
 // from pass 3 on g = x_k + th (x_k - x_{k-1}) (k_warm_extrap).  x0 = gamma g with the residual-minimising
-// gamma = (b . A g) / (A g . A g); then |r0|^2 = |b|^2 - gamma (b . A g) is known from the two dot products
-// before r0 itself is formed, which gives the fp32 / fp16 V-cycle input its O(1) scale in the same pass.
+// gamma = (b . A g) / (A g . A g); |r0|^2 is summed exactly in a 12 B/node pass before r0 is stored, so that the
+// fp32 / fp16 V-cycle input gets its O(1) scale in the pass that writes it.
 //   k_warm_extrap   g = x + th (x - xprev), xprev = x                         (passes >= 3)   32 B/node
 //   k_warm_ax       Ap = A g, (b . Ap), (Ap . Ap)                                             21 B/node
-//   k_warm_scalars  gamma, |r0|^2 estimate -> ring slot 2 (scale of the first V-cycle)
-//   k_warm_init     x = gamma g, r = b - gamma Ap, |r|^2 -> ring slot 3; MG: b0, x1; Jacobi: p, r.z   45 B/node
+//   k_warm_scalars  gamma;  k_warm_rr  |b - gamma Ap|^2 exactly (12 B/node) -> ring slots 2, 3 (scale of the first V-cycle, stop test)
+//   k_warm_init     x = gamma g, r = b - gamma Ap; MG: b0, x1; Jacobi: p, r.z                          45 B/node
 // ---------------------------------------------------------------------------------------------
 // guess of pass k of a step (th = 1 - 1/relax_div); all guesses are masked to the current fluid cells
 //   MODE 0 (first pass):   if pendG: xG = x - th xprev (the last step ended after two passes);  x = src (x itself or xfirst)
@@ -140,17 +140,37 @@ k_warm_ax(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, c
   }
 }
 
-__global__ void k_warm_scalars(DevScalars* ds, double bnorm2) {
+__global__ void k_warm_scalars(DevScalars* ds) {
   const double bAg = ds->part[PART_PAP], AgAg = ds->part[PART_RZ];
-  ds->part[PART_PAP] = 0.0; ds->part[PART_RZ] = 0.0;
+  ds->part[PART_PAP] = 0.0; ds->part[PART_RZ] = 0.0; ds->part[PART_RR] = 0.0;
   double gamma = AgAg > 0.0 ? bAg / AgAg : 0.0;
   if (!(gamma == gamma) || !(fabs(gamma) < 1e300)) gamma = 0.0;
-  double rr = bnorm2 - gamma * bAg;                     // |b - gamma A g|^2 at the optimal gamma
-  const double floor_rr = bnorm2 * 1e-24;               // cancellation guard: the estimate only scales the V-cycle input
-  if (!(rr > floor_rr)) rr = floor_rr > 0.0 ? floor_rr : bnorm2;
   ds->warm_gamma = gamma;
-  ds->rr[2] = rr;                                       // "iteration -1" scale read by the first direction update
-  ds->rr[3] = 0.0;                                      // k_warm_init accumulates the exact |r0|^2 here
+}
+// |b - gamma A g|^2, exactly (12 B/node).  The closed form |b|^2 - gamma (b . A g) is pure cancellation once the guess is good
+// (|r0| / |b| ~ 1e-8 on the extrapolated passes): as the SCALE of the fp16-stored V-cycle input it overflowed fp16 in round 2.
+__global__ void __launch_bounds__(32 * SW_BY)
+k_warm_rr(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, const float* __restrict__ b, const double* __restrict__ Ap,
+          DevScalars* __restrict__ ds) {
+  __shared__ double sm[32];
+  const double gamma = ds->warm_gamma;
+  STREAM_PROLOGUE(S)
+  double acc[1] = {0.0};
+  if (act) {
+    const uchar2 f = *reinterpret_cast<const uchar2*>(fl + q);
+    const float2 bv = ld2<float>(b + q);
+    const double2 av = ld2<double>(Ap + q);
+    const double r0 = (f.x & FB_FLUID) ? (double)bv.x - gamma * av.x : 0.0, r1 = (f.y & FB_FLUID) ? (double)bv.y - gamma * av.y : 0.0;
+    acc[0] = r0 * r0 + r1 * r1;
+  }
+  block_sum<1>(acc, sm);
+  if (threadIdx.x == 0 && threadIdx.y == 0 && acc[0] != 0.0) atomicAdd(&ds->part[PART_RR], acc[0]);
+}
+// after the (all-reduced) sum: ring slots 2 and 3 = |r0|^2 ("iteration -1": scale of the first V-cycle, stop test of the guess)
+__global__ void k_warm_scalars2(DevScalars* ds) {
+  const double rr = ds->part[PART_RR];
+  ds->part[PART_RR] = 0.0;
+  ds->rr[2] = rr; ds->rr[3] = rr;
 }
 
 template <int MODE, typename TB = float>
@@ -189,7 +209,6 @@ k_warm_init(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
   }
   block_sum<2>(acc, sm);
   if (threadIdx.x == 0 && threadIdx.y == 0) {
-    if (acc[0] != 0.0) atomicAdd(dist ? &ds->part[PART_RR] : &ds->rr[3], acc[0]);
     if (MODE == 0 && acc[1] != 0.0) atomicAdd(dist ? &ds->part[PART_RZ] : &ds->rz[3], acc[1]);
   }
   if (MODE == 1) halo_signal(H, ds, k == H.kdn, k == H.kup);
@@ -794,17 +813,22 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
     if (rc) return rc;
     k_warm_ax<<<stencil_grid(S), STENCIL_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->Ap, c->ds);
     if (dist && (rc = fb_allreduce(c, &c->ds->part[PART_PAP], 2, FB_F64, FB_SUM))) return rc;    // (b.Ag, Ag.Ag) are adjacent
-    k_warm_scalars<<<1, 1, 0, c->stream>>>(c->ds, bnorm2);
+    k_warm_scalars<<<1, 1, 0, c->stream>>>(c->ds);
+    k_warm_rr<<<sg, STREAM_BLOCK, 0, c->stream>>>(S, c->flags, bvec, c->Ap, c->ds);
+    if (dist && (rc = fb_allreduce(c, &c->ds->part[PART_RR], 1, FB_F64, FB_SUM))) return rc;
+    k_warm_scalars2<<<1, 1, 0, c->stream>>>(c->ds);
     const PeerHalo Hw = (use_mg && fused) ? fb_halo_make(c, -1, -1, 0, HA_XA, sizeof(float), k0, k1, sg.x * sg.y) : halo_off();
     if (h16) k_warm_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, reinterpret_cast<__half*>(L0.b), L0.xa, bscale, c->ds, dist, Hw);
     else if (use_mg) k_warm_init<1><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, L0.b, L0.xa, 1.0, c->ds, dist, Hw);
-    else k_warm_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, (float*)nullptr, nullptr, 1.0, c->ds, dist, halo_off());
-    if (dist) {
-      if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 2, FB_F64, FB_SUM))) return rc;           // r.z (Jacobi) and r.r are adjacent
-      fb_pcg_publish(c, use_mg ? (1 << PART_RR) : ((1 << PART_RZ) | (1 << PART_RR)), -1);
+    else {
+      k_warm_init<0><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, c->Ap, (float*)nullptr, nullptr, 1.0, c->ds, dist, halo_off());
+      if (dist) {
+        if ((rc = fb_allreduce(c, &c->ds->part[PART_RZ], 1, FB_F64, FB_SUM))) return rc;
+        fb_pcg_publish(c, 1 << PART_RZ, -1);
+      }
     }
     k_warm_check<<<1, 1, 0, c->stream>>>(c->ds);
-    CK_LAUNCH(); c->launches += 5;
+    CK_LAUNCH(); c->launches += 7;
     if ((rc = fb_fetch_scalars(c))) return rc;          // one round trip: |r0|^2 sizes the first batch, and the guess may already pass
   } else if (h16)
     k_pcg_init<1, __half><<<sg, STREAM_BLOCK, 0, c->stream>>>(S, cf, c->flags, bvec, c->x, c->r, c->pd, reinterpret_cast<__half*>(L0.b), L0.xa,

@@ -47,7 +47,8 @@ static inline bool mg_h16_active(const flipb200_ctx* c) {
   return xe - x0 >= 128;
 }
 static inline double mg_h16_bscale(const flipb200_ctx* c) {
-  const double n = (double)(c->box.x1 - c->box.x0) * (c->box.y1 - c->box.y0) * (c->box.z1 - c->box.z0);
+  // the GLOBAL sweep box: every rank of a z-slab run must scale the one global vector by the same power of two
+  const double n = (double)(c->gbox.x1 - c->gbox.x0) * (c->gbox.y1 - c->gbox.y0) * (c->gbox.z1 - c->gbox.z0);
   int e = 0;
   while ((double)(1ll << (2 * (e + 1))) <= n && e < 14) ++e;     // 2^e <= sqrt(n)
   // a quarter of that: typical entries ~0.25, and |r| may grow by an order of magnitude against the

@@ -181,26 +181,27 @@ def test_slab_seed_box_matches_single(fb):
         f.close()
 
 
-@pytest.mark.parametrize("fused", [1, 0])
-def test_slab_wide_rows_mixed_precision(fb, fused, monkeypatch):
+@pytest.mark.parametrize("fused,zsplit", [(1, None), (0, None), (1, [0, 8, 16, 48]), (1, [0, 32, 40, 48])])
+def test_slab_wide_rows_mixed_precision(fb, fused, zsplit, monkeypatch):
     """Rows of >= 128 nodes switch on the four-node sweeps and with them params.mixed (search direction stored as fp32,
     level-0 multigrid right-hand side / residual as fp16): on slabs the ghost planes of those arrays travel at their
     storage width (pushed by the producing kernels, fused = 1, or as halo copies, fused = 0).  Same bars as above, plus
     the warm-started passes of the relaxation loop."""
     monkeypatch.setenv("FLIPB200_FUSED_HALO", str(fused))
-    nx, ny, nz = 136, 24, 32
+    nx, ny, nz = 136, 24, (32 if zsplit is None else zsplit[-1])
+    world = 2 if zsplit is None else len(zsplit) - 1
     kw = dict(nx=nx, ny=ny, nz=nz, ox=nx // 2, oy=ny // 2, oz=nz // 2)
     lo, hi = (2, 2, 2), (nx - 3, ny - 7, nz - 3)
     f1 = fb.Flip(**kw)
     f1.seed_box(lo, hi, seed=5)
     gid = next(_group)
-    fs = [fb.Flip(rank=r, world=2, **kw) for r in range(2)]
+    fs = [fb.Flip(rank=r, world=world, zsplit=zsplit, **kw) for r in range(world)]
     for f in fs:
         f.comm_init_local(gid)
     for f in fs:
         f.seed_box(lo, hi, seed=5)
     assert f1.params.mixed == 3 and f1.params.warm_start == 1
-    d1, ds = 0.1, [0.1, 0.1]
+    d1, ds = 0.1, [0.1] * world
     for step in range(4):
         d1, st1 = f1.step(d1)
         res = run_ranks([lambda f=f, d=ds[r]: f.step(d) for r, f in enumerate(fs)])
