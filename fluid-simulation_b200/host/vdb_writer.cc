@@ -149,9 +149,15 @@ bool Writer::write_grid(const DenseGrid& g) {
   }
 
   // ---- descriptor, Archive.cc:1249-1327 / GridDescriptor.cc:81-100 ----
-  char suffix[32];
-  snprintf(suffix, sizeof(suffix), "\x1e%d", written_);   // GridDescriptor::addSuffix, :178-182
-  put_string(g.name + suffix);
+  // unique descriptor name, Archive.cc:1199-1210: an EMPTY name always gets the suffix "\x1e0" (GridDescriptor::addSuffix,
+  // GridDescriptor.cc:178-182), and any name already written gets "\x1e<n>" with the first free n >= 1.  (The reference
+  // also suffixes the FIRST grid of a duplicated non-empty name, which a streaming writer cannot know; unnamed grids,
+  // all fluid.cc writes, come out identically: "\x1e0", "\x1e1", ...)
+  auto add_suffix = [](const std::string& nm, int n) { char b[32]; snprintf(b, sizeof(b), "\x1e%d", n); return nm + b; };
+  std::string uname = g.name.empty() ? add_suffix(g.name, 0) : g.name;
+  for (int n = 1; names_.count(uname); ++n) uname = add_suffix(g.name, n);
+  names_.insert(uname);
+  put_string(uname);
   put_string("Tree_float_5_4_3");                         // Tree::treeType(), tree/Tree.h:2129
   put_string("");                                         // instance parent
   const int64_t offset_pos = ftello(f_);
@@ -186,16 +192,21 @@ bool Writer::write_grid(const DenseGrid& g) {
 
 }  // namespace flipvdb
 
-// C entry point (tests / Python tooling): write `count` dense grids of identical box to one file.
-extern "C" int flipvdb_write_file(const char* path, int count, const int lo[3], const int dim[3],
-                                  const float* const* grids, int zip) {
+// C entry points (tests / Python tooling): write `count` dense grids of identical box to one file; names[i] may be NULL / ""
+extern "C" int flipvdb_write_file_named(const char* path, int count, const int lo[3], const int dim[3],
+                                        const float* const* grids, int zip, const char* const* names) {
   flipvdb::Writer w(path, count, zip != 0);
   if (!w.ok()) return -1;
   for (int i = 0; i < count; ++i) {
     flipvdb::DenseGrid g;
     for (int a = 0; a < 3; ++a) { g.lo[a] = lo[a]; g.dim[a] = dim[a]; }
+    if (names && names[i]) g.name = names[i];
     g.data = grids[i];
     if (!w.write_grid(g)) return -2;
   }
   return w.close() ? 0 : -3;
+}
+extern "C" int flipvdb_write_file(const char* path, int count, const int lo[3], const int dim[3],
+                                  const float* const* grids, int zip) {
+  return flipvdb_write_file_named(path, count, lo, dim, grids, zip, nullptr);
 }

@@ -16,6 +16,7 @@
 #define FLIPB200_VDB_WRITER_H
 #include <stdint.h>
 #include <stdio.h>
+#include <set>
 #include <string>
 
 namespace flipvdb {
@@ -48,6 +49,7 @@ class Writer {
   bool zip_;
   bool failed_;
   int written_, count_;
+  std::set<std::string> names_;   // descriptor names written so far (unique-name rule of Archive.cc:1199-1210)
 };
 
 }  // namespace flipvdb

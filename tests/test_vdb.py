@@ -96,3 +96,42 @@ def test_run_sh_alternative_scene_with_reseeding(tmp_path):
     mass = [float(g["dense"].sum(dtype=np.float64)) for g in grids]
     assert 0.4 * 630 < mass[0] < 630 and abs(mass[1] - mass[0]) < 0.2 * mass[0]      # 10 * (27 + 36) particles
     assert mass[2] > mass[1] + 0.4 * 8 * 63                                         # step 2 emitted 8 per voxel into both boxes
+
+
+def test_header_and_descriptor_bytes(vdblib, tmp_path):
+    """Byte-level pin of the writer against the REFERENCE'S writer code (not against the sibling reader): every field of
+    the file header and of the first grid descriptor, with the reference line that emits it."""
+    import struct
+    vdblib.flipvdb_write_file_named.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                                C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_char_p)]
+    g = [np.ones((2, 2, 2), np.float32) for _ in range(4)]
+    ptrs = (C.c_void_p * 4)(*[a.ctypes.data for a in g])
+    names = (C.c_char_p * 4)(b"", b"density", b"", b"density")
+    p = tmp_path / "h.vdb"
+    assert vdblib.flipvdb_write_file_named(str(p).encode(), 4, (C.c_int * 3)(0, 0, 0), (C.c_int * 3)(2, 2, 2), ptrs, 0, names) == 0
+    raw = open(p, "rb").read()
+    o = 0
+    assert raw[o:o + 8] == struct.pack("<q", 0x56444220); o += 8        # OPENVDB_MAGIC (version.h:83), int64: Archive.cc:945-946
+    assert raw[o:o + 4] == struct.pack("<I", 224); o += 4               # OPENVDB_FILE_VERSION (version.h:96): Archive.cc:949-950
+    assert raw[o:o + 8] == struct.pack("<II", 4, 0); o += 8             # library major, minor (version.h:46-47): Archive.cc:953-956
+    assert raw[o:o + 1] == b"\x01"; o += 1                              # hasGridOffsets (seekable file): Archive.cc:959-960
+    uuid = raw[o:o + 36].decode("ascii"); o += 36                       # 36-char uuid string, no length prefix: Archive.cc:965-971
+    assert [i for i, ch in enumerate(uuid) if ch == "-"] == [8, 13, 18, 23] and all(ch in "0123456789abcdef-" for ch in uuid)
+    assert raw[o:o + 4] == struct.pack("<I", 0); o += 4                 # file-level MetaMap: count 0 (MetaMap.cc:117; File::write passes an empty map)
+    assert raw[o:o + 4] == struct.pack("<i", 4); o += 4                 # grid count, int32: Archive.cc:1166-1170
+
+    def pstr(off):                                                      # Name I/O: uint32 length + bytes (util/Name.h:58-63)
+        n, = struct.unpack_from("<I", raw, off)
+        return raw[off + 4:off + 4 + n], off + 4 + n
+    nm, o = pstr(o)
+    assert nm == b"\x1e0"                                               # empty name -> addSuffix(name, 0): Archive.cc:1203-1206, GridDescriptor.cc:178-182
+    ty, o = pstr(o)
+    assert ty == b"Tree_float_5_4_3"                                    # Tree::treeType(): tree/Tree.h:2129; GridDescriptor.cc:87
+    par, o = pstr(o)
+    assert par == b""                                                   # instance parent name: GridDescriptor.cc:90
+    gpos, bpos, epos = struct.unpack_from("<qqq", raw, o); o += 24      # grid / block / end stream offsets: GridDescriptor.cc:93-99
+    assert gpos == o and gpos < bpos < epos <= len(raw)
+    assert raw[o:o + 4] == struct.pack("<I", 2)                         # per-grid compression flags, COMPRESS_ACTIVE_MASK (io/Compression.h:78-81): Archive.cc:1269
+    # unique-name rule for the other three grids (Archive.cc:1199-1210)
+    from vdb_reader import read_vdb
+    assert [x["name"] for x in read_vdb(str(p))] == ["\x1e0", "density", "\x1e1", "density\x1e1"]
