@@ -473,3 +473,44 @@ def test_extrapolate(fb, oracle_mod, scenes):
     assert rel_l2(pg, po) < 1e-7
     with pytest.raises(fb.FlipError):                          # z-slab contexts do not support it
         fb.Flip(nx=25, ny=25, nz=25, ox=12, oy=12, oz=12, extrapolate=1, rank=0, world=2)
+
+
+def test_bench_scene_steps_vs_oracle(fb, oracle_mod, scenes):
+    """The scene bench.py times (dam-break full-tank fill, 8 particles per voxel, at rest) at 64^3, stepped 5 times against
+    the oracle: relaxation pass counts exact, grid velocity / pressure <= 1e-5 after the first step, positions <= 1e-4."""
+    n = 64
+    sc = scenes.dam_break(n=n, fill="full")
+    f, o = _pair(fb, oracle_mod, sc)
+    dg = do = 0.1
+    for s in range(5):
+        dg, st = f.step(dg); do, so = o.step(do)
+        assert (st.passes, st.n_fluid) == (so.passes, so.n_fluid), s
+        assert dg == pytest.approx(do, rel=1e-9)
+        if s == 0:
+            assert st.n_fluid == (n - 4) * (n - 5) * (n - 4)
+            assert rel_l2(_grids(fb, f), _ogrids(o)) < TOL_GRID
+            assert rel_l2(f.get_grid(fb.GRID_P), o.dgrid(oracle_mod.D_P)) < TOL_GRID
+    pg, vg = f.get_particles(); po, vo = o.get_particles()
+    assert rel_l2(pg, po) < TOL_POS10 and rel_l2(vg, vo) < 1e-5
+
+
+def test_against_the_reference_main(fb):
+    """The CUDA path against THE REFERENCE ITSELF: fluid.cc main() compiled unmodified (oracle/_ref/libfluid_ref.so, see
+    tests/test_ref_pin.py) runs one step of its own loop on its own scene; the CUDA path steps the same initial particles."""
+    import ref_py
+    if not ref_py.available():
+        pytest.skip("oracle/_ref/libfluid_ref.so not built")
+    m = ref_py.MainRun(1)
+    f = fb.Flip(nx=121, ny=121, nz=121, ox=60, oy=60, oz=60, track_ids=1)          # the literals of fluid.cc:1159,1264
+    f.set_particles(m.pos0, np.zeros_like(m.pos0))
+    dt, st = f.step(0.1)                                                            # dt0 = 0.1, fluid.cc:1367
+    assert st.passes == m.passes[0] == 8                                            # do..while passes (SURVEY 3.2)
+    assert dt == pytest.approx(m.dts[-1], rel=1e-12)
+    assert st.last_error == pytest.approx(m.errors[0], rel=1e-6)
+    u = np.stack([f.get_grid(fb.GRID_U + a) for a in range(3)])
+    assert rel_l2(u, m.vels) < TOL_GRID                                             # north_star: single-step grid velocity <= 1e-5
+    assert rel_l2(f.get_grid(fb.GRID_WEIGHT), m.f["output"]) < 5e-7                 # outputGrid, fluid.cc:1434-1448
+    fl = f.get_grid(fb.GRID_FLAGS)
+    assert np.array_equal((fl & fb.FB_FLUID) != 0, m.indices >= 0)                  # the cells main() numbered, :1416-1433
+    pg, vg = f.get_particles()
+    assert rel_l2(pg, m.pos) < 1e-7 and rel_l2(vg, m.vel) < 1e-5
