@@ -23,6 +23,7 @@ Prints ONE JSON line (rank 0):
   cube_drop_512 BASELINE configs[3]: cube drop in a 512^3 box cut into N z-slabs, STRONG scaling, with a
                3-step agreement check of the slab run against a single-GPU run of the same scene (N >= 2)
   dam_break_column  SURVEY 8d fill (ii): the true dam break (column x < 0.4n, y < 0.6n) at the same n
+  fp32_mode    (N = 1) params.precision = 32 on the headline scene, with its distance from the precision = 64 run
   grid_128, default_scene (N = 1)  BASELINE configs[1] and configs[0] (the reference's own 121^3 cube drop)
 
 Single workloads: --workload flip | dam-break-column | cube-drop | pcg (with --grid-n).  --no-extra keeps
@@ -270,15 +271,15 @@ class Job:
         self.dist.all_gather(out, t)
         return [o.cpu().tolist() for o in out]
 
-    def make(self, n, nzg, cap, world=None, rank=None, origin=None, zsplit=None):
+    def make(self, n, nzg, cap, world=None, rank=None, origin=None, zsplit=None, **kw):
         world = self.world if world is None else world
         rank = self.rank if rank is None else rank
         o = origin if origin is not None else (n // 2, n // 2, nzg // 2)
         if world == 1:
             return self.fb.Flip(nx=n, ny=n, nz=nzg, ox=o[0], oy=o[1], oz=o[2], max_particles=cap, precond=self.args.precond,
-                                device=self.local_rank)
+                                device=self.local_rank, **kw)
         return self.fdist.create_slab_flip(self.fb, rank, world, device=self.local_rank, nx=n, ny=n, nz=nzg, ox=o[0], oy=o[1], oz=o[2],
-                                           max_particles=cap, precond=self.args.precond, zsplit=zsplit)
+                                           max_particles=cap, precond=self.args.precond, zsplit=zsplit, **kw)
 
     def finish(self):
         if self.world > 1:
@@ -565,6 +566,42 @@ def bench_small_scene(job, n, lo, hi, origin, steps, warmup, workload, single=Tr
             "passes": [s["passes"] for s in stats], "pcg_iters": [s["pcg_iters_total"] for s in stats]}
 
 
+def bench_fp32_mode(job, n, steps, warmup):
+    """north_star "fp32 mode reported separately": params.precision = 32 (pressure solves stop at FLT_EPSILON) on the headline
+    scene, single GPU.  Reports its throughput and the rel-L2 distance of its grid velocity / pressure after ONE step from the
+    precision = 64 run of the same particles (the cost of the mode in accuracy, next to its gain in time)."""
+    fb = job.fb
+    lo, hi = full_tank_box(n)
+    total = box_count(lo, hi) * 8
+    cap = int(total * 1.06) + 65536
+    ref = {}
+    for prec in (64, 32):
+        f = job.make(n, n, cap, precision=prec)
+        f.seed_box(lo, hi, seed=1234)
+        dt, st = f.step(0.1)
+        g = {"u": np.stack([f.get_grid(fb.GRID_U + a) for a in range(3)]), "p": f.get_grid(fb.GRID_P), "iters": st.pcg_iters_total}
+        if prec == 64:
+            ref = g
+            f.close()
+            continue
+        def rl2(a, b):
+            return float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
+        diff = {"grid_velocity_rel_l2": rl2(g["u"], ref["u"]), "pressure_rel_l2": rl2(g["p"], ref["p"]),
+                "pcg_iters_step0": {"precision_64": ref["iters"], "precision_32": g["iters"]}}
+        for _ in range(max(0, warmup - 1)):
+            dt, st = f.step(dt)
+        stats = []
+        for _ in range(steps):
+            dt, st = f.step(dt)
+            stats.append(st.as_dict())
+        f.close()
+    dev_s = sum(s["ms_total"] for s in stats) * 1e-3
+    return {"workload": f"dam-break FLIP full-tank fill, {n}^3, 8 particles/cell, params.precision = 32 (pcg_tol = FLT_EPSILON; state and CG arithmetic fp64)",
+            "particles": total, "steps": steps, "warmup": warmup, "value": total * steps / dev_s, "unit": UNIT, "ms_per_step": dev_s / steps * 1e3,
+            "passes": [s["passes"] for s in stats], "pcg_iters": [s["pcg_iters_total"] for s in stats],
+            "pcg_rel_resid": [s["pcg_rel_resid"] for s in stats], "vs_precision_64_after_one_step": diff}
+
+
 def bench_pcg(job, n):
     """BASELINE configs[4]: pressure-projection-only weak scaling.  The system is the one the first relaxation pass of the
     full-tank scene solves (b = divergence after one gravity kick); a step = PCG_BLOCK iterations of the product's CUDA-graph
@@ -726,6 +763,8 @@ def main():
                                         if k not in ("roofline", "data", "higher_is_better", "vs_baseline")}
             if n >= 256:
                 line["cube_drop_512"] = bench_cube_drop(job, 512, extra_steps, 4)
+            if world == 1 and rank == 0:
+                line["fp32_mode"] = bench_fp32_mode(job, n, extra_steps, 3)
             if world == 1 and rank == 0 and n != 128:
                 lo, hi = full_tank_box(128)
                 line["grid_128"] = bench_small_scene(job, 128, lo, hi, 64, extra_steps, 3, "dam-break FLIP full-tank fill, 128^3, 8 particles/cell (BASELINE configs[1])")

@@ -37,7 +37,7 @@ class Params(C.Structure):
         ("precond", C.c_int32), ("device", C.c_int32),
         ("track_ids", C.c_int32), ("extrapolate", C.c_int32),
         ("max_particles", C.c_int64),
-        ("warm_start", C.c_int32), ("mixed", C.c_int32), ("reserved", C.c_int32 * 6),
+        ("warm_start", C.c_int32), ("mixed", C.c_int32), ("precision", C.c_int32), ("reserved", C.c_int32 * 5),
     ]
 
 

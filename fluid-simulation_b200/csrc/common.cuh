@@ -82,6 +82,7 @@ struct DevScalars {
   int pad2;
   unsigned blk_cnt[4];               // fused all-reduce (halo.cuh): finished blocks of the current dot-product kernel
   unsigned red_seq[4];               //   and the sequence number of the last collected sum, per PART_* id
+  int n_fluid_part[64];              // k_classify's per-block counts, spread over 64 words (k_classify_sum adds them up)
 };
 #define PART_PAP 0
 #define PART_RZ 1

@@ -28,6 +28,7 @@ void flipb200_default_params(flipb200_params* p) {
   p->max_particles = 0;
   p->warm_start = 1;
   p->mixed = 3;
+  p->precision = 64;
 }
 
 const char* flipb200_strerror(int s) {
@@ -38,6 +39,7 @@ const char* flipb200_strerror(int s) {
     case FLIPB200_ERR_BREAKDOWN: return "PCG breakdown (p.Ap <= 0 or non-finite)";
     case FLIPB200_ERR_NOCONV: return "PCG reached the iteration limit";
     case FLIPB200_ERR_STATE: return "stage called out of order";
+    case FLIPB200_ERR_LIMIT: return "size exceeds a compiled-in limit (FLIPB200_NOALLOC_MAX_NODES)";
     case FLIPB200_ERR_COMM: return "multi-GPU communication error";
     default: return "unknown status";
   }
@@ -189,9 +191,13 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
   if (p->wall < 1 || p->relax_div < 1 || !(p->dx > 0) || !(p->rho > 0)) return FLIPB200_ERR_ARG;
   if (!(p->flip_ratio >= 0.0 && p->flip_ratio <= 1.0)) return FLIPB200_ERR_ARG;   // 1 = the reference's pure FLIP (fluid.cc:981)
   if (p->extrapolate != 0 && (p->extrapolate != 1 || world > 1)) return FLIPB200_ERR_ARG;   // single GPU only (grid.cu fb_extrapolate)
+  if (p->precision != 0 && p->precision != 32 && p->precision != 64) return FLIPB200_ERR_ARG;
   flipb200_ctx* c = (flipb200_ctx*)calloc(1, sizeof(flipb200_ctx));
   if (!c) return FLIPB200_ERR_ARG;
   c->P = *p;
+  if (c->P.precision == 0) c->P.precision = 64;                  // zero-filled params of an older caller
+  // fp32 mode: solve to single-precision round-off unless the caller set a tolerance of their own
+  if (c->P.precision == 32 && c->P.pcg_tol == 2.220446049250313e-16) c->P.pcg_tol = 1.1920928955078125e-07;
   // experiment switches are read ONCE, here; after that only c->P / c->opt decide (two contexts of one process can differ)
   if (const char* e = getenv("FLIPB200_WARM")) c->P.warm_start = atoi(e);
   if (const char* e = getenv("FLIPB200_MIXED")) c->P.mixed = atoi(e);

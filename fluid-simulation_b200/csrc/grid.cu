@@ -70,9 +70,17 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
       mxx = max(mxx, sred[4][w]); mxy = max(mxy, sred[5][w]); mxz = max(mxz, sred[6][w]);
     }
     if (cnt) {
-      atomicAdd(&ds->n_fluid, cnt);
-      atomicMin(&ds->bbox[0], mnx); atomicMin(&ds->bbox[1], mny); atomicMin(&ds->bbox[2], mnz);
-      atomicMax(&ds->bbox[3], mxx); atomicMax(&ds->bbox[4], mxy); atomicMax(&ds->bbox[5], mxz);
+      // 65 k blocks on a 256^3 tank: one counter word and six bbox words serialised their atomics in L2
+      // (ncu: the kernel's tail was atomic throughput).  Counts go to 64 words picked by block index, bbox
+      // atomics are sent only when they would change the (monotone) value just read.
+      atomicAdd(&ds->n_fluid_part[(blockIdx.x + 3 * blockIdx.y + 7 * blockIdx.z) & 63], cnt);
+      volatile int* bb = ds->bbox;
+      if (mnx < bb[0]) atomicMin(&ds->bbox[0], mnx);
+      if (mny < bb[1]) atomicMin(&ds->bbox[1], mny);
+      if (mnz < bb[2]) atomicMin(&ds->bbox[2], mnz);
+      if (mxx > bb[3]) atomicMax(&ds->bbox[3], mxx);
+      if (mxy > bb[4]) atomicMax(&ds->bbox[4], mxy);
+      if (mxz > bb[5]) atomicMax(&ds->bbox[5], mxz);
     }
   }
 }
@@ -144,7 +152,14 @@ int fb_extrapolate(flipb200_ctx* c) {
   return 0;
 }
 
+__global__ void k_classify_sum(DevScalars* ds) {
+  int v = ds->n_fluid_part[threadIdx.x] + ds->n_fluid_part[threadIdx.x + 32];
+  v = warp_sum_i(v);
+  if (threadIdx.x == 0) ds->n_fluid = v;
+}
 __global__ void k_reset_classify(DevScalars* ds) {
+  ds->n_fluid_part[threadIdx.x] = 0;
+  if (threadIdx.x) return;
   ds->n_fluid = 0;
   ds->bbox[0] = ds->bbox[1] = ds->bbox[2] = 1 << 30;
   ds->bbox[3] = ds->bbox[4] = ds->bbox[5] = -1;
@@ -152,11 +167,12 @@ __global__ void k_reset_classify(DevScalars* ds) {
 
 int fb_classify(flipb200_ctx* c) {
   const Grid& g = c->g;
-  k_reset_classify<<<1, 1, 0, c->stream>>>(c->ds);
+  k_reset_classify<<<1, 64, 0, c->stream>>>(c->ds);
   dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.k1 - g.k0);
   k_classify<<<grd, blk, 0, c->stream>>>(g, c->wacc, c->wf, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1],
                                          c->ub[2], c->x, c->flags_static, c->flags, c->ds, (c->P.warm_start && c->x_valid) ? 1 : 0);
-  CK_LAUNCH(); c->launches += 2;
+  k_classify_sum<<<1, 32, 0, c->stream>>>(c->ds);
+  CK_LAUNCH(); c->launches += 3;
   int rc;
   if (c->P.extrapolate && (rc = fb_extrapolate(c))) return rc;
   if (c->world > 1) {

@@ -32,7 +32,8 @@ enum {
   FLIPB200_ERR_BREAKDOWN = -3,  /* PCG breakdown: p.Ap <= 0 or non-finite scalar  */
   FLIPB200_ERR_NOCONV = -4,     /* PCG hit max iterations (solution still stored) */
   FLIPB200_ERR_STATE = -5,      /* stage called out of order                      */
-  FLIPB200_ERR_COMM = -6        /* NCCL / multi-GPU exchange error                */
+  FLIPB200_ERR_COMM = -6,       /* NCCL / multi-GPU exchange error                */
+  FLIPB200_ERR_LIMIT = -7       /* size beyond a compiled-in limit (flipb200_p2g_noalloc) */
 };
 
 /* POD parameters; defaults (flipb200_default_params) equal the literals of fluid.cc. */
@@ -68,7 +69,12 @@ typedef struct {
   int32_t mixed;             /* storage precision INSIDE the fp64 solve (arithmetic stays fp64 / fp32): bit 0 = CG search direction
                                 stored as fp32, bit 1 = level-0 multigrid right-hand side and residual stored as fp16.
                                 default 3; 0 = everything at full width.  Single GPU, rows >= 128 nodes; ignored otherwise.       */
-  int32_t reserved[6];
+  int32_t precision;         /* 64 (default): the reference's arithmetic -- fp64 CG solved to pcg_tol = DBL_EPSILON.
+                                32: "fp32 mode" (BASELINE north_star): the pressure solve stops at FLT_EPSILON relative residual
+                                (pcg_tol is set to 1.1920928955078125e-07 unless the caller changed it from the default); the
+                                state, the transfers and the CG recurrences stay fp64, so results differ from precision = 64 only
+                                by the solve's tolerance (tests/test_gpu_parity.py::test_fp32_mode states the bound).           */
+  int32_t reserved[5];
 } flipb200_params;
 
 /* per-step statistics (the reference prints none of these except dt and error) */

@@ -80,6 +80,7 @@ fb.__path__ = [os.path.join(ROOT, 'fluid-simulation_b200')]
 fb.Flip = Flip
 fb.KERNEL_SPMV, fb.KERNEL_PCG_ITER, fb.KERNEL_P2G, fb.KERNEL_G2P, fb.KERNEL_SORT = 0, 1, 2, 3, 4
 fb.GRID_P = 6
+fb.GRID_U = 0
 fb.comm_unique_id = lambda: b'0' * 128
 fb.pinned_empty = lambda n, dtype=np.float64: (np.empty(8, dtype=dtype), 0)
 fb.pinned_free = lambda p: None

@@ -39,6 +39,7 @@ def test_cuda_arm_control_flow_and_keys():
     assert flip["pcg"]["metric"] == "pcg_iterations_per_s" and "configs[4]" in flip["pcg"]["config"]["workload"]
     assert "fill (ii)" in flip["dam_break_column"]["config"]["workload"] and flip["dam_break_column"]["check"]["ok"]
     assert "configs[1]" in flip["grid_128"]["workload"] and "configs[0]" in flip["default_scene"]["workload"]
+    assert "precision = 32" in flip["fp32_mode"]["workload"] and flip["fp32_mode"]["vs_precision_64_after_one_step"]["grid_velocity_rel_l2"] >= 0
     assert "configs[3]" in cube["config"]["workload"] and cube["check"]["first_step_cells"]["ok"]
     assert pcg["metric"] == "pcg_iterations_per_s" and "configs[4]" in pcg["config"]["workload"] and pcg["check"]["hydrostatic"]["ok"]
 

@@ -11,7 +11,7 @@ print('value %.4g ms/step %.2f e2e %.4g (%.1f ms) checks_ok %s' % (d['value'], d
 print('dominant', d['roofline']['dominant'])
 for k,v in d['roofline']['by_kernel'].items():
     if 'frac' in v or k in ('sort','pcg_iteration'): print('  ', k, {a:(round(b,3) if isinstance(b,float) else b) for a,b in v.items() if a not in ('what','unit')})
-for k in ('pcg','dam_break_column','cube_drop_512','grid_128','default_scene'):
+for k in ('pcg','dam_break_column','cube_drop_512','grid_128','default_scene','fp32_mode'):
     if k in d: print(k, 'value %.4g ms/step %.2f' % (d[k]['value'], d[k]['ms_per_step']), d[k].get('check',{}).get('ok'))
 print('cpu', {k:v for k,v in d['cpu_baseline'].items() if k not in ('sample','same_config_gpu')}, d['cpu_baseline']['same_config_gpu']['value'])
 for s in d['per_step']: print('  ', s)
