@@ -15,7 +15,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libflipb200.so")
 
 OK = 0
-ERR_ARG, ERR_CUDA, ERR_BREAKDOWN, ERR_NOCONV, ERR_STATE, ERR_COMM = -1, -2, -3, -4, -5, -6
+ERR_ARG, ERR_CUDA, ERR_BREAKDOWN, ERR_NOCONV, ERR_STATE, ERR_COMM, ERR_LIMIT = -1, -2, -3, -4, -5, -6, -7
+NOALLOC_MAX_NODES = 2097152      # FLIPB200_NOALLOC_MAX_NODES: static scratch of flipb200_p2g_noalloc
 
 GRID_U, GRID_V, GRID_W, GRID_UB, GRID_VB, GRID_WB, GRID_P, GRID_WEIGHT, GRID_B, GRID_FLAGS = range(10)
 _GRID_DTYPE = {GRID_WEIGHT: np.float32, GRID_B: np.float32, GRID_FLAGS: np.uint8}
@@ -65,7 +66,7 @@ EXPORTS = [
     "flipb200_host_alloc", "flipb200_host_free",
     "flipb200_create_slab", "flipb200_slab_range", "flipb200_comm_unique_id", "flipb200_comm_init_nccl",
     "flipb200_comm_init_local", "flipb200_get_particle_ids", "flipb200_step_host_slab", "flipb200_halo_mode", "flipb200_debug_info",
-    "flipb200_profile_iteration", "flipb200_create_slab_split",
+    "flipb200_profile_iteration", "flipb200_create_slab_split", "flipb200_p2g_noalloc",
 ]
 
 _lib = None
@@ -127,8 +128,13 @@ def load():
     lib.flipb200_profile_iteration.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, ip]
     lib.flipb200_step_host_slab.argtypes = [vp] + [vp] * 6 + [C.c_int64, C.c_int64, C.POINTER(C.c_int64), dp, vp,
                                                               C.POINTER(Stats)]
+    lib.flipb200_p2g_noalloc.argtypes = [C.c_int32] * 7 + [vp] + [vp] * 6 + [C.c_int64] + [vp] * 4 + [vp]
     _lib = lib
     return lib
+
+
+def strerror(status):
+    return load().flipb200_strerror(int(status)).decode()
 
 
 def comm_unique_id():

@@ -12,7 +12,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libflipb200.so")
-SOURCES = ["ctx.cu", "particles.cu", "rows.cu", "grid.cu", "pcg.cu", "mg.cu", "mg_h16.cu", "pcg_p32.cu", "step.cu", "comm.cu"]
+SOURCES = ["ctx.cu", "particles.cu", "rows.cu", "grid.cu", "pcg.cu", "mg.cu", "mg_h16.cu", "pcg_p32.cu", "step.cu", "comm.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

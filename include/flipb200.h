@@ -200,6 +200,28 @@ int  flipb200_time_kernel(flipb200_ctx*, int which, int32_t iters, float* ms_per
 #define FLIPB200_PROFILE_NAME 40
 int  flipb200_profile_iteration(flipb200_ctx*, int32_t iters, int32_t cap, char* names, float* us, int32_t* n);
 
+/* NO COUNTERPART IN THE REFERENCE.
+ * The particle -> grid transfer of flipb200_p2g + the normalisation of flipb200_classify as ONE call that allocates
+ * nothing: no cudaMalloc / cudaFree or allocating library routine, for callers that cannot allocate (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Its only scratch, the fp64 weight accumulator, is
+ * a static __device__ array of FLIPB200_NOALLOC_MAX_NODES doubles (16 MiB) that every GPU loading the library holds
+ * until exit; grids with nx*ny*nz above that limit are rejected with FLIPB200_ERR_LIMIT (message on stderr).
+ * All pointers are DEVICE pointers owned by the caller, dense [z][y][x] grids of nx*ny*nz elements:
+ *   in : solid_dev (bytes, non-zero = obstacle; NULL = none; the shell of thickness `wall` is always solid),
+ *        px..vz_dev (n particles, SoA, any order)
+ *   out: u_dev, v_dev, w_dev  P2G velocities, divided by the float-rounded weight where it is > 0 (= GRID_U..W after
+ *        flipb200_classify), weight_dev the FloatGrid `weights` (= GRID_WEIGHT); the call clears them first.
+ * Work is queued on `stream` (a cudaStream_t; NULL = the default stream) of the CURRENT device; the call does not
+ * synchronise.  Every call shares the one scratch array: calls that overlap on the GPU (different streams without a
+ * dependency) race on it -- serialise them.  The first call on a device looks up the array's address
+ * (cudaGetSymbolAddress); make it before starting a graph capture. */
+#define FLIPB200_NOALLOC_MAX_NODES 2097152   /* 128^3 */
+int  flipb200_p2g_noalloc(int32_t nx, int32_t ny, int32_t nz, int32_t ox, int32_t oy, int32_t oz, int32_t wall,
+                          const uint8_t* solid_dev,
+                          const double* px_dev, const double* py_dev, const double* pz_dev,
+                          const double* vx_dev, const double* vy_dev, const double* vz_dev, int64_t n,
+                          double* u_dev, double* v_dev, double* w_dev, float* weight_dev, void* stream);
+
 /* Pinned host memory helpers for the e2e path (cudaHostAlloc / cudaFreeHost). */
 int  flipb200_host_alloc(void** ptr, size_t bytes);
 int  flipb200_host_free(void* ptr);
