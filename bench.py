@@ -442,7 +442,7 @@ def bench_flip(job, n, fill, steps, warmup, headline, tag):
     try:
         tj_all = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         tj = tj_all["k_spmv4f" if mixed & 1 else "k_spmv"]
-        if tj["grid"] == [n, n, n] and world == 1:
+        if tj_all.get("_grid", tj.get("grid")) == [n, n, n] and world == 1:
             traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
     except Exception:
         pass
