@@ -430,8 +430,8 @@ def bench_flip(job, n, fill, steps, warmup, headline, tag):
     ms_iter, _ = f.time_kernel(fb.KERNEL_PCG_ITER, args.kernel_iters)
     ms_p2g, npart = f.time_kernel(fb.KERNEL_P2G, 5)
     ms_sort, _ = f.time_kernel(fb.KERNEL_SORT, 5)
-    # params.mixed (single GPU, rows >= 128 nodes): the product's stencil reads the search direction as fp32
-    mixed = int(getattr(f.params, "mixed", 0)) if (world == 1 and n >= 128 and args.precond == 1) else 0
+    # params.mixed (rows >= 128 nodes, also on z-slabs): the product's stencil reads the search direction as fp32
+    mixed = int(getattr(f.params, "mixed", 0)) if (n >= 128 and args.precond == 1) else 0
     if os.environ.get("FLIPB200_MIXED") is not None and mixed:
         mixed = int(os.environ["FLIPB200_MIXED"])
     SB = stage_bytes(mixed)
@@ -633,7 +633,7 @@ def bench_pcg(job, n):
     it_s = PCG_BLOCK * blocks / (ms_block * 1e-3)
     ms_spmv, _ = f.time_kernel(fb.KERNEL_SPMV, args.kernel_iters)
     ms_spmv = job.reduce(ms_spmv)
-    mixed = int(getattr(f.params, "mixed", 0)) if (world == 1 and n >= 128 and args.precond == 1) else 0
+    mixed = int(getattr(f.params, "mixed", 0)) if (n >= 128 and args.precond == 1) else 0
     spmv_bytes = 13.0 if mixed & 1 else 17.0
     ach = spmv_bytes * nodes / (ms_spmv * 1e-3) / 1e9
     its = job.gather_ints([iters_tol, n_fluid])

@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libflipb200.so")
+LIB_PATH = os.environ.get("FLIPB200_LIB_PATH") or os.path.join(_HERE, "libflipb200.so")      # override: A/B builds (tools/)
 
 OK = 0
 ERR_ARG, ERR_CUDA, ERR_BREAKDOWN, ERR_NOCONV, ERR_STATE, ERR_COMM, ERR_LIMIT = -1, -2, -3, -4, -5, -6, -7

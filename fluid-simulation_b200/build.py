@@ -10,15 +10,17 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(HERE, "build")
-LIB = os.path.join(HERE, "libflipb200.so")
+# experiments: FLIPB200_BUILD_SUFFIX=_b FLIPB200_BUILD_DEFS="-DX=1 -DY=2" python build.py  -> libflipb200_b.so beside the product
+SUFFIX = os.environ.get("FLIPB200_BUILD_SUFFIX", "")
+OBJ = os.path.join(HERE, "build" + SUFFIX)
+LIB = os.path.join(HERE, f"libflipb200{SUFFIX}.so")
 SOURCES = ["ctx.cu", "particles.cu", "rows.cu", "grid.cu", "pcg.cu", "mg.cu", "mg_h16.cu", "pcg_p32.cu", "step.cu", "comm.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
     "-ccbin", "/usr/bin/g++",
-]
+] + os.environ.get("FLIPB200_BUILD_DEFS", "").split()
 
 
 def _stale(target, deps):

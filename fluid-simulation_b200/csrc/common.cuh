@@ -233,6 +233,18 @@ struct flipb200_ctx {
 
 #define CK_LAUNCH() CK(cudaGetLastError())
 
+// Minimum resident blocks per SM asked of latency-bound sweep kernels (second argument of __launch_bounds__; 0 = not
+// specified -- 1 is NOT neutral, ptxas then spends registers freely: k_spmv4f 62 -> 72 us).  Without the hint the
+// register allocator settles on 48 / 64 registers, one block per SM short of the next occupancy step.  Chosen by
+// A/B builds on B200 (tools/gpu_ab_lib.sh), per kernel and per PEER (z-slab) instantiation:
+//   k_spmv4f      one GPU 9 (56 regs, 62.0 -> 60.2 us); PEER none (9 would spill 8 bytes: 64 -> 67.6 us)
+//   k_mg_smooth4h PEER 12 (48 -> 40 regs, 53 -> 49.5 us on 2 GPUs); one GPU none (the hint alone costs 4 us at equal registers)
+//   k_mg_resid4h  11 (one GPU 45.0 -> 43.8 us, PEER 61 -> 53 us)      k_mg_prolong4  5 (41.0 -> 38.8 us, PEER 47 -> 44 us)
+#define FB_MINB_SPMV4F(PEER) ((PEER) ? 0 : 9)
+#define FB_MINB_SMOOTH4H(PEER) ((PEER) ? 12 : 0)
+#define FB_MINB_RESID4H 11
+#define FB_MINB_PROLONG4 5
+
 // ---------------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------------

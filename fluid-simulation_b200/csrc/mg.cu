@@ -686,7 +686,7 @@ k_mg_prolong(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const u
 
 // Four fine nodes (two coarse columns) per lane: the issue-bound 2-node shape spends most of its
 // instructions on per-lane overhead.  Used on the levels whose rows fill a 128-node warp.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FB_MINB_PROLONG4)
 k_mg_prolong4(Grid gf, Box fbox, Grid gc, const uint8_t* __restrict__ ff, const uint8_t* __restrict__ nrm,
               const float* __restrict__ ec, float* __restrict__ x, DevScalars* __restrict__ ds,
               int PR_ZC, const __grid_constant__ PeerHalo H) {

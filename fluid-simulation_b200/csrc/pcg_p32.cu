@@ -14,7 +14,7 @@
 
 // K1: Ap = A p (fp64) from the fp32 p; neighbour sums in fp64 (the stored values are exact in fp64)
 template <bool PEER>
-__global__ void __launch_bounds__(32 * ST_BY)
+__global__ void __launch_bounds__(32 * ST_BY, FB_MINB_SPMV4F(PEER))
 k_spmv4f(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
          const float* __restrict__ p, double* __restrict__ Ap, DevScalars* __restrict__ ds, int it_arg, int noexit,
          int dist, const __grid_constant__ PeerHalo H) {

@@ -68,7 +68,7 @@ typedef struct {
                                 0: x0 = 0, what cg.solve() does (Eigen ConjugateGradient.h:233-237)                               */
   int32_t mixed;             /* storage precision INSIDE the fp64 solve (arithmetic stays fp64 / fp32): bit 0 = CG search direction
                                 stored as fp32, bit 1 = level-0 multigrid right-hand side and residual stored as fp16.
-                                default 3; 0 = everything at full width.  Single GPU, rows >= 128 nodes; ignored otherwise.       */
+                                default 3; 0 = everything at full width.  Rows >= 128 nodes (also on z-slabs); ignored otherwise.       */
   int32_t precision;         /* 64 (default): the reference's arithmetic -- fp64 CG solved to pcg_tol = DBL_EPSILON.
                                 32: "fp32 mode" (BASELINE north_star): the pressure solve stops at FLT_EPSILON relative residual
                                 (pcg_tol is set to 1.1920928955078125e-07 unless the caller changed it from the default); the
