@@ -233,15 +233,36 @@ struct flipb200_ctx {
 
 #define CK_LAUNCH() CK(cudaGetLastError())
 
-// Minimum resident blocks per SM asked of latency-bound sweep kernels (second argument of __launch_bounds__; 0 = not
-// specified -- 1 is NOT neutral, ptxas then spends registers freely: k_spmv4f 62 -> 72 us).  Without the hint the
-// register allocator settles on 48 / 64 registers, one block per SM short of the next occupancy step.  Chosen by
-// A/B builds on B200 (tools/gpu_ab_lib.sh), per kernel and per PEER (z-slab) instantiation:
-//   k_spmv4f      one GPU 9 (56 regs, 62.0 -> 60.2 us); PEER none (9 would spill 8 bytes: 64 -> 67.6 us)
-//   k_mg_smooth4h PEER 12 (48 -> 40 regs, 53 -> 49.5 us on 2 GPUs); one GPU none (the hint alone costs 4 us at equal registers)
-//   k_mg_resid4h  11 (one GPU 45.0 -> 43.8 us, PEER 61 -> 53 us)      k_mg_prolong4  5 (41.0 -> 38.8 us, PEER 47 -> 44 us)
+// Minimum resident blocks per SM asked of the sweep kernels (second argument of __launch_bounds__; 0 = not specified --
+// 1 is NOT neutral, ptxas then spends registers freely: k_spmv4f 62 -> 72 us).  Without a hint the register allocator
+// settles on 40 / 48 / 64 registers, one or two blocks per SM short of the next occupancy step.  Every value was chosen
+// by A/B builds on B200 (tools/gpu_ab_lib.sh; profiles/r2_launch_bounds_ab.txt), per kernel and per
+// instantiation -- the effect is not monotonic (k_mg_smooth4h: 12 costs 4 us at equal registers, 16 gains 2-3 us):
+//   k_spmv4f       one GPU 9 (64 -> 56 regs, 62.0 -> 60.2 us); PEER none (9 spills there: 64 -> 67.6 us)
+//   k_mg_smooth4h  one GPU 16 (40 -> 32 regs, no spill: 41.5 / 40.5 / 46.7 -> 39.5 / 39.0 / 43.3 us); PEER 12 (48 -> 40 regs, 53 -> 49.5 us)
+//   k_mg_resid4h   11 (one GPU 45.0 -> 43.8 us, PEER 61 -> 53 us; 14+ spills)
+//   k_mg_prolong4  5 (41.0 -> 38.8 us, PEER 47 -> 44 us)      k_update_p4f  8 (40 -> 32 regs: 90.5 -> 78.5 us)
+//   k_mg_restrict4h 5: slower (32.4 -> 36.9 us, spills), left alone
+#ifndef FB_MINB_SMOOTH4H_DOT
+#define FB_MINB_SMOOTH4H_DOT 16
+#endif
+#ifndef FB_MINB_RESTRICT4H
+#define FB_MINB_RESTRICT4H 0
+#endif
+#ifndef FB_MINB_UPDATE_P4F
+#define FB_MINB_UPDATE_P4F 8      /* 40 -> 32 registers (16 bytes spilled), full occupancy: 90.5 -> 78.5 us */
+#endif
+#ifndef FB_MINB_UPDATE_XR4
+#define FB_MINB_UPDATE_XR4 0
+#endif
 #define FB_MINB_SPMV4F(PEER) ((PEER) ? 0 : 9)
-#define FB_MINB_SMOOTH4H(PEER) ((PEER) ? 12 : 0)
+#ifndef FB_MINB_SMOOTH4H_PRE
+#define FB_MINB_SMOOTH4H_PRE 16
+#endif
+#ifndef FB_MINB_SMOOTH4H_PEER
+#define FB_MINB_SMOOTH4H_PEER 16
+#endif
+#define FB_MINB_SMOOTH4H(DOT, PEER) ((PEER) ? FB_MINB_SMOOTH4H_PEER : ((DOT) ? FB_MINB_SMOOTH4H_DOT : FB_MINB_SMOOTH4H_PRE))
 #define FB_MINB_RESID4H 11
 #define FB_MINB_PROLONG4 5
 

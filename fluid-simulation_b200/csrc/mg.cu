@@ -276,13 +276,13 @@ k_mg_smooth(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
   __shared__ double sm[32];
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
-  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc, kz1 = min(kz0 + S.zc, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   halo_wait(H, ds, bdn, bup);
   double acc[1] = {0.0};
   StencilMarch<float> m;
   if (m.begin(S, xi)) {
-    const int kend = min(m.k + ST_ZP, S.box.z1);
+    const int kend = min(m.k + S.zc, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
       if (m.k >= kend) break;
@@ -320,12 +320,12 @@ k_mg_resid(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, c
            const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
            float* __restrict__ rn, DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
-  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc, kz1 = min(kz0 + S.zc, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   halo_wait(H, ds, bdn, bup);
   StencilMarch<float> m;
   if (m.begin(S, x)) {
-    const int kend = min(m.k + ST_ZP, S.box.z1);
+    const int kend = min(m.k + S.zc, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
       if (m.k >= kend) break;
@@ -369,13 +369,13 @@ k_mg_smooth4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
   __shared__ double sm[32];
   if (ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
-  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc, kz1 = min(kz0 + S.zc, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   if (PEER) halo_wait(H, ds, bdn, bup);
   double acc[1] = {0.0};
   StencilMarch4 m;
   if (m.begin(S, xi)) {
-    const int kend = min(m.k + ST_ZP, S.box.z1);
+    const int kend = min(m.k + S.zc, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
       if (m.k >= kend) break;
@@ -414,12 +414,12 @@ k_mg_resid4(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, 
             const uint8_t* __restrict__ nrm, const float* __restrict__ b, const float* __restrict__ x,
             float* __restrict__ rn, DevScalars* __restrict__ ds, const __grid_constant__ PeerHalo H) {
   if (ds->pcg_done) return;
-  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+  const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc, kz1 = min(kz0 + S.zc, S.box.z1);
   const bool bdn = kz0 <= H.kdn && H.kdn < kz1, bup = kz0 <= H.kup && H.kup < kz1;
   if (PEER) halo_wait(H, ds, bdn, bup);
   StencilMarch4 m;
   if (m.begin(S, x)) {
-    const int kend = min(m.k + ST_ZP, S.box.z1);
+    const int kend = min(m.k + S.zc, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
       if (m.k >= kend) break;
@@ -1027,6 +1027,8 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     S[l] = make_sweep(c->mg[l].g, c->mg[l].box);
     S4[l] = make_sweep(c->mg[l].g, c->mg[l].box, 4);
     w4[l] = st4_on && (S4[l].xe - S4[l].box.x0) >= 128;
+    if (!w4[l] && !c->mg[l].dist) S[l].zc = small_level_zc(S[l]);    // k_mg_smooth / k_mg_resid of the small levels
+    if (w4[l] && l >= 1 && !c->mg[l].dist) S4[l].zc = FB_L1_ZC;
     mc[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA1); mc2[l] = make_mg_coef(c->mg[l].h2inv, MG_OMEGA2);
   }
   if (sweep_empty(S[0])) return 0;

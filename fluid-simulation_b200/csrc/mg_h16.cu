@@ -21,7 +21,7 @@ __device__ __forceinline__ float resid_node(const MgCoef& mc, uint32_t f, uint32
   return (b - mc.h2inv * ((float)kk * c - sum)) * (64.f / (float)nn);
 }
 template <int DOT, bool PEER>
-__global__ void __launch_bounds__(32 * ST_BY, FB_MINB_SMOOTH4H(PEER))
+__global__ void __launch_bounds__(32 * ST_BY, FB_MINB_SMOOTH4H(DOT, PEER))
 k_mg_smooth4h(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc, const uint8_t* __restrict__ fl,
              const __half* __restrict__ b, const float* __restrict__ xi, float* __restrict__ xo,
              const double* __restrict__ r64, DevScalars* __restrict__ ds, int it_arg, int dist,
@@ -103,7 +103,7 @@ k_mg_resid4h(const __grid_constant__ Sweep S, const __grid_constant__ MgCoef mc,
   if (PEER) halo_signal(H, ds, bdn, bup);
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FB_MINB_RESTRICT4H)
 k_mg_restrict4h(Grid gf, Box fbox, Grid gc, Box cbox, MgCoef mcc, const uint8_t* __restrict__ fc,
                const __half* __restrict__ rn, float* __restrict__ bc, float* __restrict__ x1c,
                DevScalars* __restrict__ ds, int RS_ZC, const __grid_constant__ PeerHalo H,

@@ -119,7 +119,7 @@ k_warm_ax(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, c
   double acc[2] = {0.0, 0.0};
   StencilMarch<double> m;
   if (m.begin(S, x)) {
-    const int kend = min(m.k + ST_ZP, S.box.z1);
+    const int kend = min(m.k + S.zc, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
       if (m.k >= kend) break;
@@ -230,13 +230,13 @@ k_spmv(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, cons
   if (!noexit && ds->pcg_done) return;
   const int it = pcg_iter(ds, it_arg);
   {
-    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP, kz1 = min(kz0 + ST_ZP, S.box.z1);
+    const int kz0 = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc, kz1 = min(kz0 + S.zc, S.box.z1);
     halo_wait(H, ds, kz0 <= H.kdn && H.kdn < kz1, kz0 <= H.kup && H.kup < kz1);
   }
   double acc[1] = {0.0};
   StencilMarch<double> m;
   if (m.begin(S, p)) {
-    const int kend = min(m.k + ST_ZP, S.box.z1);
+    const int kend = min(m.k + S.zc, S.box.z1);
 #pragma unroll
     for (int z = 0; z < ST_ZP; ++z) {
       if (m.k >= kend) break;
@@ -367,7 +367,7 @@ k_update_xr(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf,
 // 33 B/node at 256^3.  Same arithmetic per node: identical bits.
 // TB = __half (FLIPB200_MG_H16): b0 is stored as fp16 and scaled by bscale (pcg.cuh); TB = float ignores bscale.
 template <typename TB = float>
-__global__ void __launch_bounds__(32 * SW_BY)
+__global__ void __launch_bounds__(32 * SW_BY, FB_MINB_UPDATE_XR4)
 k_update_xr4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, const uint8_t* __restrict__ fl,
              double* __restrict__ r, const double* __restrict__ Ap, TB* __restrict__ b0, float* __restrict__ x1,
              DevScalars* __restrict__ ds, int it_arg, int noexit, int dist, const __grid_constant__ PeerHalo H, double bscale) {
@@ -736,6 +736,11 @@ static bool get_iteration_graph(flipb200_ctx* c, const Sweep& S, const PcgCoef& 
   const char* ng = getenv("FLIPB200_NO_GRAPH");
   if (ng && ng[0] == '1') return false;
   if (!fb_comm_capturable(c)) return false;      // in-process test transport synchronises on the host
+  // The NCCL-copy fallback of the ghost planes (FLIPB200_FUSED_HALO=0) runs with plain launches: replaying its
+  // send/recv pairs from the captured iteration ended solves early with a wrong pressure on 2 GPUs
+  // (tests/test_gpu_nccl.py [2], round 2; plain launches of the same calls are correct).  The default path -- ghost
+  // planes pushed by the producing kernels -- replays from the graph.
+  if (c->world > 1 && c->halo.mode == 0) return false;
   const int mode = (use_mg ? 1 : 0) | (noexit ? 2 : 0);
   if (c->it_exec && same_box(c->it_box, c->box) && same_box(c->it_gbox, c->gbox) && c->it_dt == dt && c->it_mode == mode) return true;
   fb_graph_invalidate(c);

@@ -55,7 +55,7 @@ k_spmv4f(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, co
 }
 
 // K3 (MG path): x += alpha p_old, p = float(z + beta p_old); four nodes per lane (k_update_p4 of pcg.cu)
-__global__ void __launch_bounds__(32 * SW_BY)
+__global__ void __launch_bounds__(32 * SW_BY, FB_MINB_UPDATE_P4F)
 k_update_p4f(const __grid_constant__ Sweep S, const uint8_t* __restrict__ fl, const float* __restrict__ zf,
              float* __restrict__ p, double* __restrict__ x, DevScalars* __restrict__ ds, int it_arg, int noexit,
              double inv_bscale /* 1, or 1 / bscale with params.mixed bit 1 (pcg.cuh) */, const __grid_constant__ PeerHalo H) {

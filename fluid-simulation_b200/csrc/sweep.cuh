@@ -62,6 +62,7 @@ struct Sweep {
   Box box;
   int xe;        // exclusive x limit for lanes (even, <= px)
   int zp;        // block order in z (zperm): 0 ascending, 1 boundary chunks first (z-slab runs), 2 descending
+  int zc;        // planes a block of the STENCIL shapes marches (<= ST_ZP; ST_ZP on level 0, fewer on the latency-bound coarse levels)
 };
 #define ZP_UP 0
 #define ZP_EDGE 1
@@ -69,6 +70,7 @@ struct Sweep {
 // W = x-nodes per lane (2, or 4 for the fp32 STENCIL4 shape): the lane range is aligned to W
 static inline Sweep make_sweep(const Grid& g, const Box& b, int W = 2) {
   Sweep s; s.g = g; s.box = b; s.zp = (g.k0 > 0) ? 1 : 0;   // slabs have ghost planes below k0
+  s.zc = ST_ZP;
   s.box.x0 = b.x0 & ~(W - 1);
   int xe = (b.x1 + W - 1) & ~(W - 1);
   s.xe = xe < g.px ? xe : g.px;
@@ -81,7 +83,20 @@ static inline dim3 stream_grid(const Sweep& s) {
   return dim3(cdiv(s.xe - s.box.x0, 64), cdiv(s.box.y1 - s.box.y0, SW_BY), s.box.z1 - s.box.z0);
 }
 static inline dim3 stencil_grid(const Sweep& s, int W = 2) {
-  return dim3(cdiv(s.xe - s.box.x0, 32 * W), cdiv(s.box.y1 - s.box.y0, ST_BY), cdiv(s.box.z1 - s.box.z0, ST_ZP));
+  return dim3(cdiv(s.xe - s.box.x0, 32 * W), cdiv(s.box.y1 - s.box.y0, ST_BY), cdiv(s.box.z1 - s.box.z0, s.zc));
+}
+// The coarse multigrid levels (rows < 128 nodes, 2-node shape) are latency-bound: a 64^3 sweep is 256 blocks of 4 warps
+// on 148 SMs, each thread walking ST_ZP planes one dependent round trip after the other.  Fewer planes per block =
+// more blocks and a shorter chain per thread.  FB_SMALL_ZC: chosen by A/B build.
+#ifndef FB_SMALL_ZC
+#define FB_SMALL_ZC 1
+#endif
+#ifndef FB_L1_ZC
+#define FB_L1_ZC 4       // fp32 four-node sweeps of the levels >= 1 (128^3 below a 256^3 grid)
+#endif
+static inline int small_level_zc(const Sweep& s) {
+  const long cells = (long)(s.xe - s.box.x0) * (s.box.y1 - s.box.y0) * (s.box.z1 - s.box.z0);
+  return cells <= (1L << 19) ? FB_SMALL_ZC : ST_ZP;
 }
 #define STREAM_BLOCK dim3(32, SW_BY, 1)
 #define STENCIL_BLOCK dim3(32, ST_BY, 1)
@@ -125,7 +140,7 @@ struct StencilMarch {
     lane = threadIdx.x;
     i = S.box.x0 + blockIdx.x * 64 + 2 * lane;
     j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
-    k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP;
+    k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc;
     if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
     act = i < S.xe;
     jlo = j > 0; jhi = j < S.g.ny - 1;
@@ -167,7 +182,7 @@ struct StencilMarch4 {
     lane = threadIdx.x;
     i = S.box.x0 + blockIdx.x * 128 + 4 * lane;
     j = S.box.y0 + blockIdx.y * ST_BY + threadIdx.y;
-    k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * ST_ZP;
+    k = S.box.z0 + zperm(blockIdx.z, gridDim.z, S.zp) * S.zc;
     if (j >= S.box.y1) return false;                 // whole warp (one row) leaves together
     act = i < S.xe;
     jlo = j > 0; jhi = j < S.g.ny - 1;

@@ -86,7 +86,7 @@ def test_nccl_slabs_match_single(no_graph):
     for p in ps:
         p.start()
     try:
-        res = [q.get(timeout=240) for _ in range(world)]
+        res = [q.get(timeout=120) for _ in range(world)]
         for p in ps:
             p.join(timeout=60)
     finally:

@@ -17,6 +17,6 @@ import json
 d=json.loads(open('$OUT.json').read().strip().splitlines()[-1])
 b=d['roofline']['by_kernel']
 g=lambda k: b.get(k,{}).get('us_per_iteration',float('nan'))
-print('lib$SFX G=$G ms/step %.2f iter %.1f | spmv %.1f xr %.1f sm %.1f rs %.1f rst %.1f pro %.1f sm1 %.1f sm2 %.1f up %.1f | ok %s' % (d['ms_per_step'], b['pcg_iteration']['us'], g('pcg/k_spmv'), g('pcg/k_update_xr'), g('pcg/L0 halo+smooth'), g('pcg/L0 halo+resid'), g('pcg/L0 halo+restrict'), g('pcg/L0 halo+prolong'), g('pcg/L0 halo+smooth (post 1)'), g('pcg/L0 halo+smooth (post 2)'), g('pcg/k_update_p'), d['checks_ok']))
+print('lib$SFX G=$G ms/step %.2f iter %.1f | spmv %.1f xr %.1f sm %.1f rs %.1f rst %.1f pro %.1f sm1 %.1f sm2 %.1f up %.1f | small-levels %.1f | ok %s' % (d['ms_per_step'], b['pcg_iteration']['us'], g('pcg/k_spmv'), g('pcg/k_update_xr'), g('pcg/L0 halo+smooth'), g('pcg/L0 halo+resid'), g('pcg/L0 halo+restrict'), g('pcg/L0 halo+prolong'), g('pcg/L0 halo+smooth (post 1)'), g('pcg/L0 halo+smooth (post 2)'), g('pcg/k_update_p'), b['pcg_iteration']['us_levels_below_0'], d['checks_ok']))
 PY
 done; done
