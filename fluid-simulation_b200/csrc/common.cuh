@@ -203,9 +203,23 @@ struct flipb200_ctx {
   Particles pt;
   int64_t n_sorted;        // particles [0, n_sorted) are in cell order; [n_sorted, n) arrived by migration this step
   bool sorted;             // particle arrays are in cell order and cell_start is valid
+  // experiment switches, all read from the environment ONCE, in fb_create (a live context never re-reads them, so the
+  // captured iteration graph and the solve prologue / epilogue cannot disagree about a storage format)
+  bool opt_sparse;         // FLIPB200_SPARSE != 0: per-step grid passes only sweep the region the fluid can reach (fb_active_region)
+  bool opt_st4;            // FLIPB200_ST4 != 0: four nodes per lane on rows >= 128 nodes
+  bool opt_rz64;           // FLIPB200_RZ64 = 1
+  bool opt_no_graph;       // FLIPB200_NO_GRAPH = 1
+  bool opt_warm_debug;     // FLIPB200_WARM_DEBUG
+  int opt_cheb_steps;      // FLIPB200_CHEB = steps,lmin (0: the compiled-in polynomial)
+  float opt_cheb_lmin;
   char opt_p2g, opt_g2p;   // kernel variants (FLIPB200_P2G / FLIPB200_G2P, read once at create): see particles.cu
   DevScalars* ds;          // device
   DevScalars* hs;          // pinned host mirror
+  // Region outside which every node array is in its EMPTY state (wf = u = ub = x = 0, flags = static flags): the bounding box
+  // `wet` (global node indices, min x,y,z / max x,y,z) of the nodes with weight > 0 found by the last fb_classify.  Valid
+  // (sparse_ok) until particles or grids are replaced from outside (set_particles, seed_box, set_grid, step_host).
+  bool sparse_ok;
+  int wet[6];
   Box box;                 // sweep box of this step (local planes, clipped to the owned range)
   Box gbox;                // the same box over the whole domain (z in GLOBAL planes); == box when world == 1
   int n_fluid;
@@ -363,6 +377,12 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* >= 32
 int fb_sort_particles(flipb200_ctx* c);
 int fb_p2g(flipb200_ctx* c);
 int fb_classify(flipb200_ctx* c);
+// The region (local node indices, half-open, z clipped to the owned planes; z1 == z0: nothing of it on this rank) that
+// this step's per-node passes -- P2G clears and cell sweep, k_classify, k_cell_delta -- have to visit: the whole grid,
+// or, while ctx::sparse_ok holds, the last step's wet bounding box grown by SPARSE_MARGIN nodes.  Particles move at
+// most one cell per step (dt <= dx / maxSpeed, fluid.cc:992-999), so their 2x2x2 supports stay inside wet +- 2.
+#define SPARSE_MARGIN 3
+Box fb_active_region(const flipb200_ctx* c, bool* full);
 int fb_rhs_div(flipb200_ctx* c, double dt, int mode);
 int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters, double* rel);
 int fb_vel_update(flipb200_ctx* c, double dt_sub);

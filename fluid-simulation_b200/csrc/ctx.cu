@@ -202,6 +202,16 @@ int fb_create(const flipb200_params* p, const uint8_t* solid_host, int rank, int
   if (const char* e = getenv("FLIPB200_WARM")) c->P.warm_start = atoi(e);
   if (const char* e = getenv("FLIPB200_MIXED")) c->P.mixed = atoi(e);
   c->opt_p2g = 'c'; c->opt_g2p = 't';
+  { const char* e = getenv("FLIPB200_SPARSE"); c->opt_sparse = !(e && e[0] == '0'); }
+  { const char* e = getenv("FLIPB200_ST4"); c->opt_st4 = !(e && e[0] == '0'); }
+  { const char* e = getenv("FLIPB200_RZ64"); c->opt_rz64 = e && e[0] == '1'; }
+  { const char* e = getenv("FLIPB200_NO_GRAPH"); c->opt_no_graph = e && e[0] == '1'; }
+  c->opt_warm_debug = getenv("FLIPB200_WARM_DEBUG") != nullptr;
+  c->opt_cheb_steps = 0; c->opt_cheb_lmin = 0.f;
+  if (const char* e = getenv("FLIPB200_CHEB")) {   // "steps,lmin"
+    int st = 0; float lm = 0.f;
+    if (sscanf(e, "%d,%f", &st, &lm) == 2 && st > 0 && st <= 200 && lm > 0.f && lm < 1.f) { c->opt_cheb_steps = st; c->opt_cheb_lmin = lm; }
+  }
   if (const char* e = getenv("FLIPB200_P2G")) if (e[0] == 'c' || e[0] == 'p' || e[0] == 't') c->opt_p2g = e[0];
   if (const char* e = getenv("FLIPB200_G2P")) if (e[0] == 'c' || e[0] == 'p' || e[0] == 't') c->opt_g2p = e[0];
   c->rank = rank; c->world = world;
@@ -347,6 +357,7 @@ int flipb200_set_particles(flipb200_ctx* c, const double* px, const double* py, 
   if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
   CK(cudaStreamSynchronize(c->stream));
   c->sorted = false;
+  c->sparse_ok = false;            // new particles: the next step sweeps the whole grid (grid.cu fb_active_region)
  
   if (c->world > 1) {
     // every rank is handed the whole scene and keeps the particles whose base plane it owns
@@ -421,6 +432,7 @@ int flipb200_set_grid(flipb200_ctx* c, int which, const void* host_in, size_t by
   CK(cudaMemcpy2DAsync((char*)d + (size_t)g.k0 * g.plane * esz, g.px * esz, host_in, g.nx * esz, g.nx * esz,
                        (size_t)g.ny * (g.k1 - g.k0), cudaMemcpyHostToDevice, c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  c->sparse_ok = false;            // a grid replaced from outside: nothing is known about where it is empty
   return FLIPB200_OK;
 }
 

@@ -18,13 +18,13 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
            double* __restrict__ u0, double* __restrict__ u1, double* __restrict__ u2,
            double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
            double* __restrict__ xpress,
-           const uint8_t* __restrict__ fs, uint8_t* __restrict__ fl, DevScalars* __restrict__ ds, int keep_x) {
+           const uint8_t* __restrict__ fs, uint8_t* __restrict__ fl, DevScalars* __restrict__ ds, int keep_x, Box R) {
   __shared__ int sred[7][8];
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = g.k0 + blockIdx.z;                      // owned planes
+  int i = R.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int j = R.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int k = R.z0 + blockIdx.z;                      // owned planes of the active region (fb_active_region)
   int cnt = 0, mnx = 1 << 30, mny = 1 << 30, mnz = 1 << 30, mxx = -1, mxy = -1, mxz = -1;
-  if (i < g.nx && j < g.ny) {
+  if (i < R.x1 && j < R.y1) {
     int q = gidx(g, i, j, k);
     float w = (float)wacc[q];
     wf[q] = w;
@@ -42,10 +42,10 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
     // pressure: 0 off the fluid cells (every solver kernel relies on it); with params.warm_start the value of a
     // cell that stays fluid survives as the next solve's initial guess (pcg.cu)
     if (!(keep_x && fluid)) xpress[q] = 0.0;
-    if (fluid) {
-      f |= FB_FLUID; cnt = 1;
-      mnx = mxx = i; mny = mxy = j; mnz = mxz = k + g.kg0;   // bbox in GLOBAL planes
-    }
+    if (fluid) { f |= FB_FLUID; cnt = 1; }
+    // bounding box (GLOBAL planes) of the WET nodes -- every fluid cell, and the rare non-solid node with weight that
+    // is no row of the system: the next step's active region is grown from it, so it must cover all non-empty nodes
+    if (w > 0.0f && !(f & FB_SOLID)) { mnx = mxx = i; mny = mxy = j; mnz = mxz = k + g.kg0; }
     fl[q] = f;
   }
   // block reduction (count, bbox) -> one atomic set per block
@@ -69,11 +69,11 @@ k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
       mnx = min(mnx, sred[1][w]); mny = min(mny, sred[2][w]); mnz = min(mnz, sred[3][w]);
       mxx = max(mxx, sred[4][w]); mxy = max(mxy, sred[5][w]); mxz = max(mxz, sred[6][w]);
     }
-    if (cnt) {
+    if (mxx >= 0) {
       // 65 k blocks on a 256^3 tank: one counter word and six bbox words serialised their atomics in L2
       // (ncu: the kernel's tail was atomic throughput).  Counts go to 64 words picked by block index, bbox
       // atomics are sent only when they would change the (monotone) value just read.
-      atomicAdd(&ds->n_fluid_part[(blockIdx.x + 3 * blockIdx.y + 7 * blockIdx.z) & 63], cnt);
+      if (cnt) atomicAdd(&ds->n_fluid_part[(blockIdx.x + 3 * blockIdx.y + 7 * blockIdx.z) & 63], cnt);
       volatile int* bb = ds->bbox;
       if (mnx < bb[0]) atomicMin(&ds->bbox[0], mnx);
       if (mny < bb[1]) atomicMin(&ds->bbox[1], mny);
@@ -165,12 +165,34 @@ __global__ void k_reset_classify(DevScalars* ds) {
   ds->bbox[3] = ds->bbox[4] = ds->bbox[5] = -1;
 }
 
+Box fb_active_region(const flipb200_ctx* c, bool* full) {
+  const Grid& g = c->g;
+  Box r{0, 0, g.k0, g.nx, g.ny, g.k1};
+  const bool sparse = c->opt_sparse && c->sparse_ok && !c->P.extrapolate;
+  if (full) *full = !sparse;
+  if (!sparse) return r;
+  const int* w = c->wet;
+  r.x0 = max(0, w[0] - SPARSE_MARGIN) & ~31;           // rows stay sector/line aligned
+  r.y0 = max(0, w[1] - SPARSE_MARGIN);
+  r.x1 = min(g.nx, w[3] + SPARSE_MARGIN + 1); r.y1 = min(g.ny, w[4] + SPARSE_MARGIN + 1);
+  r.z0 = max(max(0, w[2] - SPARSE_MARGIN) - g.kg0, g.k0);
+  r.z1 = min(min(g.gnz, w[5] + SPARSE_MARGIN + 1) - g.kg0, g.k1);
+  if (r.z1 < r.z0) r.z1 = r.z0;                        // the region does not reach this rank's planes
+  return r;
+}
+
 int fb_classify(flipb200_ctx* c) {
   const Grid& g = c->g;
+  bool full = true;
+  const Box R = fb_active_region(c, &full);
+  int prev_wet[6];
+  for (int a = 0; a < 6; ++a) prev_wet[a] = c->wet[a];
   k_reset_classify<<<1, 64, 0, c->stream>>>(c->ds);
-  dim3 blk(32, 8, 1), grd(cdiv(g.nx, 32), cdiv(g.ny, 8), g.k1 - g.k0);
-  k_classify<<<grd, blk, 0, c->stream>>>(g, c->wacc, c->wf, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1],
-                                         c->ub[2], c->x, c->flags_static, c->flags, c->ds, (c->P.warm_start && c->x_valid) ? 1 : 0);
+  if (R.z1 > R.z0) {
+    dim3 blk(32, 8, 1), grd(cdiv(R.x1 - R.x0, 32), cdiv(R.y1 - R.y0, 8), R.z1 - R.z0);
+    k_classify<<<grd, blk, 0, c->stream>>>(g, c->wacc, c->wf, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->x,
+                                           c->flags_static, c->flags, c->ds, (c->P.warm_start && c->x_valid) ? 1 : 0, R);
+  }
   k_classify_sum<<<1, 32, 0, c->stream>>>(c->ds);
   CK_LAUNCH(); c->launches += 3;
   int rc;
@@ -190,6 +212,28 @@ int fb_classify(flipb200_ctx* c) {
   rc = fb_fetch_scalars(c);
   if (rc) return rc;
   c->n_fluid = c->hs->n_fluid;
+  {
+    // the wet bounding box of THIS step: the next step's active region.  A sparse sweep whose result reaches the rim of
+    // its region cannot vouch for what lies beyond (it never should: the margin is one node wider than a particle can
+    // travel): start over with the whole grid.
+    const int* bb = c->hs->bbox;
+    const bool have = bb[3] >= bb[0] && bb[4] >= bb[1] && bb[5] >= bb[2];
+    if (!full && have) {
+      const int n[3] = {g.nx, g.ny, g.gnz};
+      bool rim = false;
+      for (int a = 0; a < 3; ++a) {
+        const int lo = max(0, prev_wet[a] - SPARSE_MARGIN), hi = min(n[a], prev_wet[a + 3] + SPARSE_MARGIN + 1);   // [lo, hi)
+        if ((lo > 0 && bb[a] <= lo) || (hi < n[a] && bb[a + 3] >= hi - 1)) rim = true;
+      }
+      if (rim) {
+        c->sparse_ok = false;
+        if ((rc = fb_p2g(c))) return rc;
+        return fb_classify(c);
+      }
+    }
+    c->sparse_ok = have;
+    for (int a = 0; a < 6; ++a) c->wet[a] = bb[a];
+  }
   Box b, gb;
   if (c->n_fluid == 0) {
     b = Box{0, 0, 0, 0, 0, 0}; gb = b;
@@ -384,11 +428,11 @@ int fb_vel_update(flipb200_ctx* c, double dt_sub) {
 __global__ void __launch_bounds__(256)
 k_cell_delta(Grid g, const double* __restrict__ u0, const double* __restrict__ u1, const double* __restrict__ u2,
              const double* __restrict__ b0, const double* __restrict__ b1, const double* __restrict__ b2,
-             double* __restrict__ d0, double* __restrict__ d1, double* __restrict__ d2, double ratio) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int j = blockIdx.y * blockDim.y + threadIdx.y;
-  int k = g.k0 + blockIdx.z;                      // owned planes
-  if (i >= g.px || j >= g.ny) return;
+             double* __restrict__ d0, double* __restrict__ d1, double* __restrict__ d2, double ratio, Box R) {
+  int i = R.x0 + blockIdx.x * blockDim.x + threadIdx.x;
+  int j = R.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  int k = R.z0 + blockIdx.z;                      // owned planes of the active region: every node a particle's support can touch
+  if (i >= R.x1 || j >= R.y1) return;
   int q = gidx(g, i, j, k);
   double a = 0.0, b = 0.0, cc = 0.0;
   if (inside_shell(g, i, j, k)) {
@@ -409,9 +453,13 @@ int fb_cell_delta(flipb200_ctx* c) { return fb_cell_delta_r(c, c->P.flip_ratio);
 // ratio = 0 leaves the plain cell-centred velocity getVelocity(c, vels) in the arrays (PIC gather input)
 int fb_cell_delta_r(flipb200_ctx* c, double ratio) {
   const Grid& g = c->g;
-  dim3 blk(32, 8, 1), grd(cdiv(g.px, 32), cdiv(g.ny, 8), g.k1 - g.k0);
-  k_cell_delta<<<grd, blk, 0, c->stream>>>(g, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->r, c->pd,
-                                           c->Ap, ratio);
+  Box R = fb_active_region(c, nullptr);             // after fb_classify: this step's wet box + margin, or the whole grid
+  if (R.x1 == g.nx) R.x1 = g.px;                    // the pad columns as well, as the whole-grid sweep always did
+  if (R.z1 > R.z0) {
+    dim3 blk(32, 8, 1), grd(cdiv(R.x1 - R.x0, 32), cdiv(R.y1 - R.y0, 8), R.z1 - R.z0);
+    k_cell_delta<<<grd, blk, 0, c->stream>>>(g, c->u[0], c->u[1], c->u[2], c->ub[0], c->ub[1], c->ub[2], c->r, c->pd,
+                                             c->Ap, ratio, R);
+  }
   CK_LAUNCH(); c->launches++;
   // particles of my top base plane read the deltas of plane k1
   double* dc[3] = {c->r, c->pd, c->Ap};

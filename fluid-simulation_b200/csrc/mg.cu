@@ -990,9 +990,8 @@ static TailKernel tail_kernel(int n) {
 // Ghost planes of `arr` before a sweep reads them: a copy (NCCL / in-process pulls), or -- with the
 // pushes fused into the producing kernels (halo.cuh) -- nothing but the test transport's host barrier.
 // planes a restrict / prolong block marches: the largest chunk that still leaves `min_blocks` blocks
-// (8 on the 256^3 level, 1 on the latency-bound coarse levels); the env variable pins it for experiments.
-static int mg_zchunk(const char* env, int blocks_xy, int nz, int min_blocks) {
-  if (const char* e = getenv(env)) { int v = atoi(e); if (v >= 1 && v <= 64) return v; }
+// (8 on the 256^3 level, 1 on the latency-bound coarse levels).
+static int mg_zchunk(int blocks_xy, int nz, int min_blocks) {
   for (int zc = 8; zc > 1; zc >>= 1)
     if ((int64_t)blocks_xy * cdiv(nz, zc) >= min_blocks) return zc;
   return 1;
@@ -1019,8 +1018,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
   // STENCIL4 (four nodes per lane) on the levels whose rows fill a 128-node warp; FLIPB200_ST4=0: never
   Sweep S4[MG_MAX_LEVELS];
   bool w4[MG_MAX_LEVELS];
-  const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
-  const bool rz64 = [] { const char* e = getenv("FLIPB200_RZ64"); return e && e[0] == '1'; }();
+  const bool st4_on = c->opt_st4, rz64 = c->opt_rz64;
   const bool h16 = mg_h16_active(c);                // level 0: b0 and the residual stored as fp16 (experimental, pcg.cuh, mg_h16.cu)
   const float rzs = h16 ? (float)(1.0 / (mg_h16_bscale(c) * mg_h16_bscale(c))) : 1.f;
   for (int l = 0; l < nl; ++l) {
@@ -1074,7 +1072,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
       // the sequence number is taken even when this rank has nothing to restrict
       const bool r4 = w4[l] && cb.x1 - (cb.x0 & ~1) >= 64;
       dim3 cg(max(1, r4 ? cdiv(cb.x1 - (cb.x0 & ~1), 64) : cdiv(cb.x1 - cb.x0, 32)), max(1, cdiv(cb.y1 - cb.y0, 8)), 1);
-      const int zc = mg_zchunk("FLIPB200_RS_ZC", cg.x * cg.y, cb.z1 - cb.z0, r4 ? 512 : 1024);
+      const int zc = mg_zchunk(cg.x * cg.y, cb.z1 - cb.z0, r4 ? 512 : 1024);
       cg.z = max(1, cdiv(cb.z1 - cb.z0, zc));
       PeerHalo H = fb_halo_make(c, l, HA_XA, C.dist ? l + 1 : -1, C.dist ? HA_XA : -1, F, ck0, ck1, cg.x * cg.y);
       const bool some = cb.z1 > cb.z0 && cb.x1 > cb.x0 && cb.y1 > cb.y0;
@@ -1111,10 +1109,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     // (30 on [0.01, 2], 24 on [0.01, 2] ...) saved 5 us per cycle but cost 1-2 CG iterations per step.
     T.cheb_steps = MG_CHEB_STEPS;
     T.cheb_lmin = MG_CHEB_LMIN;
-    if (const char* e = getenv("FLIPB200_CHEB")) {   // "steps,lmin" (experiments)
-      int st = 0; float lm = 0.f;
-      if (sscanf(e, "%d,%f", &st, &lm) == 2 && st > 0 && st <= 200 && lm > 0.f && lm < 1.f) { T.cheb_steps = st; T.cheb_lmin = lm; }
-    }
+    if (c->opt_cheb_steps > 0) { T.cheb_steps = c->opt_cheb_steps; T.cheb_lmin = c->opt_cheb_lmin; }   // FLIPB200_CHEB (experiments)
     size_t smem = 2 * sizeof(float) * (size_t)(b.x1 - b.x0 + 2) * (b.y1 - b.y0 + 2) * (b.z1 - b.z0 + 2);
     if (smem > 160 * 1024 || (int64_t)(b.x1 - b.x0) * (b.y1 - b.y0) * (b.z1 - b.z0) > 4096) return FLIPB200_ERR_ARG;
     tail_kernel(T.n)<<<1, 1024, smem, c->stream>>>(T, c->ds);
@@ -1126,7 +1121,7 @@ int fb_mg_vcycle(flipb200_ctx* c, int it) {
     MgLevel& C = c->mg[l + 1];
     const Box& fb = L.box;
     dim3 pg(w4[l] ? cdiv(((fb.x1 + 3) & ~3) - (fb.x0 & ~3), 128) : cdiv(((fb.x1 + 1) & ~1) - (fb.x0 & ~1), 64), cdiv(fb.y1 - fb.y0, 8), 1);
-    const int pzc = mg_zchunk("FLIPB200_PR_ZC", pg.x * pg.y, fb.z1 - fb.z0, w4[l] ? 512 : 1024);
+    const int pzc = mg_zchunk(pg.x * pg.y, fb.z1 - fb.z0, w4[l] ? 512 : 1024);
     pg.z = cdiv(fb.z1 - fb.z0, pzc);
     const dim3 tg = w4[l] ? stencil_grid(S4[l], 4) : stencil_grid(S[l]);
     const int nbs = tg.x * tg.y, k0 = L.g.k0, k1 = L.g.k1 - 1;

@@ -260,10 +260,22 @@ int fb_p2g_rows(flipb200_ctx* c);                          // rows.cu
 //   'p' one thread per particle with 32 REDs each (reference-shaped; also the path of unsorted input)
 int fb_p2g(flipb200_ctx* c) {
   const Grid& g = c->g;
-  const size_t T = (size_t)g.total;
-  // vels.fill(0) (fluid.cc:1378), weights.fill(0) (:1108)
-  CK(cudaMemsetAsync(c->wacc, 0, T * sizeof(double), c->stream));
-  for (int a = 0; a < 3; ++a) CK(cudaMemsetAsync(c->u[a], 0, T * sizeof(double), c->stream));
+  // vels.fill(0) (fluid.cc:1378), weights.fill(0) (:1108) -- on the planes of the active region (grid.cu fb_active_region:
+  // everything outside is zero already) plus the plane above it that the 2x2x2 splat reaches, and, on z-slabs, the ghost
+  // planes: plane k1 is shipped whole to the upper neighbour (fb_halo_sum_up) whatever the region is
+  bool full = true;
+  const Box AR = fb_active_region(c, &full);
+  double* acc4[4] = {c->wacc, c->u[0], c->u[1], c->u[2]};
+  {
+    int z0 = full ? 0 : AR.z0, z1 = full ? g.nz : min(AR.z1 + 1, g.nz);
+    if (!full && c->world > 1) {
+      // ghost ranges [0, k0) and [k1, nz) always; merged with the region's planes when they touch
+      if (g.k0 > 0) { if (z1 > z0 && z0 <= g.k0) z0 = 0; else for (int a = 0; a < 4; ++a) CK(cudaMemsetAsync(acc4[a], 0, (size_t)g.k0 * g.plane * sizeof(double), c->stream)); }
+      if (g.k1 < g.nz) { if (z1 > z0 && z1 >= g.k1) z1 = g.nz; else for (int a = 0; a < 4; ++a) CK(cudaMemsetAsync(acc4[a] + (size_t)g.k1 * g.plane, 0, (size_t)(g.nz - g.k1) * g.plane * sizeof(double), c->stream)); }
+    }
+    if (z1 > z0)
+      for (int a = 0; a < 4; ++a) CK(cudaMemsetAsync(acc4[a] + (size_t)z0 * g.plane, 0, (size_t)(z1 - z0) * g.plane * sizeof(double), c->stream));
+  }
   Particles& pt = c->pt;
   const char mode = c->opt_p2g;
   if (mode == 'p' && c->world == 1) {
@@ -280,8 +292,9 @@ int fb_p2g(flipb200_ctx* c) {
       int rc = fb_p2g_rows(c);
       if (rc) return rc;
     } else {
-      Box b{0, 0, g.k0, g.nx - 1, g.ny - 1, g.k1};   // base cells of the owned planes
+      Box b{AR.x0, AR.y0, AR.z0, min(AR.x1, g.nx - 1), min(AR.y1, g.ny - 1), AR.z1};   // base cells of the owned planes of the active region
       dim3 blk(32, 4, 1), grd(cdiv(b.x1 - b.x0, 32), cdiv(b.y1 - b.y0, 4), b.z1 - b.z0);
+      if (b.z1 > b.z0 && b.x1 > b.x0 && b.y1 > b.y0)
       k_p2g_cell<<<grd, blk, 0, c->stream>>>(g, b, c->cell_start, c->flags_static, pt.a[0], pt.a[1], pt.a[2], pt.a[3],
                                              pt.a[4], pt.a[5], c->wacc, c->u[0], c->u[1], c->u[2]);
       CK_LAUNCH(); c->launches++;
@@ -647,6 +660,7 @@ int fb_seed_box(flipb200_ctx* c, const int32_t lo[3], const int32_t hi[3], uint6
   CK(cudaStreamSynchronize(c->stream));
   c->pt.n = base + add;
   c->sorted = false;
+  c->sparse_ok = false;            // particles may have appeared anywhere: the next step sweeps the whole grid
   return 0;
 }
 

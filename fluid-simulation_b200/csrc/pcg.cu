@@ -295,7 +295,7 @@ k_spmv4(const __grid_constant__ Sweep S, const __grid_constant__ PcgCoef cf, con
 // launch K1 in the shape that fits the sweep (FLIPB200_ST4=0: always two nodes per lane)
 static void launch_spmv(flipb200_ctx* c, const PcgCoef& cf, int it_arg, int noexit, int dist, const PeerHalo& H, bool p32 = false) {
   if (p32) { fb_p32_spmv(c, cf, it_arg, noexit, dist, H); return; }       // fp32 search direction (pcg_p32.cu)
-  const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();   // read per call: tests toggle it
+  const bool st4_on = c->opt_st4;
   const Sweep S4 = make_sweep(c->g, c->box, 4);
   if (st4_on && S4.xe - S4.box.x0 >= 128) {
     if (H.mode) k_spmv4<true><<<stencil_grid(S4, 4), STENCIL_BLOCK, 0, c->stream>>>(S4, cf, c->flags, c->pd, c->Ap, c->ds, it_arg, noexit, dist, H);
@@ -674,7 +674,7 @@ static int enqueue_iteration(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf,
   }
   fb_prof(c, "allreduce pAp");
   if (use_mg) {
-    const bool st4_on = [] { const char* e = getenv("FLIPB200_ST4"); return !(e && e[0] == '0'); }();
+    const bool st4_on = c->opt_st4;
     const Sweep S4 = make_sweep(c->g, c->box, 4);
     if (st4_on && S4.xe - S4.box.x0 >= 128) {
       const dim3 sg4(cdiv(S4.xe - S4.box.x0, 128), sg.y, sg.z);
@@ -733,8 +733,7 @@ static bool same_box(const Box& a, const Box& b) {
   return a.x0 == b.x0 && a.y0 == b.y0 && a.z0 == b.z0 && a.x1 == b.x1 && a.y1 == b.y1 && a.z1 == b.z1;
 }
 static bool get_iteration_graph(flipb200_ctx* c, const Sweep& S, const PcgCoef& cf, bool use_mg, double dt, int noexit) {
-  const char* ng = getenv("FLIPB200_NO_GRAPH");
-  if (ng && ng[0] == '1') return false;
+  if (c->opt_no_graph) return false;
   if (!fb_comm_capturable(c)) return false;      // in-process test transport synchronises on the host
   // The NCCL-copy fallback of the ghost planes (FLIPB200_FUSED_HALO=0) runs with plain launches: replaying its
   // send/recv pairs from the captured iteration ended solves early with a wrong pressure on 2 GPUs
@@ -910,7 +909,7 @@ int fb_pcg_solve(flipb200_ctx* c, double dt, int* iters_out, double* rel_out) {
   if (c->hs->pcg_iters > 0 && c->hs->rr_final > 0.0 && rr_start > c->hs->rr_final)
     c->last_rate = log10(rr_start / c->hs->rr_final) / c->hs->pcg_iters;
   c->x_valid = c->hs->pcg_status == 0 && c->hs->pcg_done != 0;
-  if (getenv("FLIPB200_WARM_DEBUG"))
+  if (c->opt_warm_debug)
     fprintf(stderr, "flipb200 solve: pass %d warm %d gamma %.6g |r0|/|b| %.3e iters %d rate %.3f digits/it\n", c->pass_idx, (int)warm,
             warm ? c->hs->warm_gamma : 0.0, sqrt(rr_start / bnorm2), c->hs->pcg_iters, c->last_rate / 2);
   if (iters_out) *iters_out = c->hs->pcg_iters;

@@ -41,8 +41,7 @@ __device__ __forceinline__ int pcg_iter(const DevScalars* ds, int it_arg) { retu
 // ghost planes travel as fp16 (halo_push4h).
 static inline bool mg_h16_active(const flipb200_ctx* c) {
   if (!(c->P.mixed & 2) || c->mg_levels < 2) return false;
-  const char* s4 = getenv("FLIPB200_ST4");
-  if (s4 && s4[0] == '0') return false;
+  if (!c->opt_st4) return false;
   const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
   return xe - x0 >= 128;
 }
@@ -70,8 +69,7 @@ void fb_h16_restrict4(flipb200_ctx* c, dim3 g, dim3 blk, const Grid& gf, const B
 // Same conditions as the fp16 variant: multigrid on, four-node sweeps; on z-slabs the ghost planes of p travel as fp32.
 static inline bool pcg_p32_active(const flipb200_ctx* c) {
   if (!(c->P.mixed & 1) || c->mg_levels < 2) return false;
-  const char* s4 = getenv("FLIPB200_ST4");
-  if (s4 && s4[0] == '0') return false;
+  if (!c->opt_st4) return false;
   const int x0 = c->box.x0 & ~3, xe = min(c->g.px, (c->box.x1 + 3) & ~3);      // make_sweep(g, box, 4)
   return xe - x0 >= 128;
 }

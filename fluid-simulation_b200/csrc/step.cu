@@ -95,7 +95,7 @@ static int step_host_impl(flipb200_ctx* c, double* const arr[6], int64_t n, int6
   if (rc) return rc;
   for (int q = 0; q < 6; ++q)
     if (n) CK(cudaMemcpyAsync(c->pt.a[q], arr[q], n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  c->pt.n = n; c->sorted = false;
+  c->pt.n = n; c->sorted = false; c->sparse_ok = false;
   if (fb_init_ids(c, 0, n, 0)) return FLIPB200_ERR_CUDA;
   rc = step_device(c, dt_inout, st);
   if (rc) return rc;
