@@ -250,3 +250,38 @@ def test_slab_caller_chosen_split(fb, scenes):
         fb.Flip(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, rank=0, world=3, zsplit=[0, 7, 16, 48])     # odd boundary
     for f in fs + [f1]:
         f.close()
+
+
+def test_slab_fluid_free_ranks_and_arrival(fb, scenes):
+    """A small cube in the middle slab thrown along +z: the outer slabs start WITHOUT fluid (their share of the active
+    region, grid.cu fb_active_region, is empty: no classify / cell-delta launch, P2G clears ghost planes only) and the
+    upper one receives the fluid after a few steps through the particle migration.  Every step as on a single GPU."""
+    n = 48
+    sc = scenes.small_cube_drop(n=n, half=4, ppv=8, seed=3)
+    sc.vel = np.zeros_like(sc.pos); sc.vel[:, 2] = 6.0; sc.vel[:, 1] = 2.0
+    nx, ny, nz = sc.n
+    ox, oy, oz = sc.origin
+    zs = [0, 16, 32, 48]
+    f1 = fb.Flip.from_scene(sc, track_ids=1)
+    gid = next(_group)
+    fs = [fb.Flip(nx=nx, ny=ny, nz=nz, ox=ox, oy=oy, oz=oz, wall=sc.wall, track_ids=1, rank=r, world=3, zsplit=zs) for r in range(3)]
+    for f in fs:
+        f.comm_init_local(gid)
+    run_ranks([lambda f=f: f.set_particles(sc.pos, sc.vel) for f in fs])
+    assert [f.num_particles for f in fs] == [0, sc.num_particles, 0]
+    d1, ds = 0.1, [0.1] * 3
+    for step in range(14):
+        d1, st1 = f1.step(d1)
+        res = run_ranks([lambda f=f, d=ds[r]: f.step(d) for r, f in enumerate(fs)])
+        ds = [r[0] for r in res]
+        assert all(r[1].passes == st1.passes and r[1].n_fluid == st1.n_fluid for r in res), step
+        assert all(abs(d - d1) <= 1e-9 * d1 for d in ds), step
+    assert fs[2].num_particles > 0                                   # the fluid has crossed into the upper slab
+    for which in (fb.GRID_U, fb.GRID_W, fb.GRID_WEIGHT):
+        assert rel_l2(gather_grid(fs, which), f1.get_grid(which)) < 1e-7, which
+    assert np.array_equal(gather_grid(fs, fb.GRID_FLAGS), f1.get_grid(fb.GRID_FLAGS))
+    p1, v1 = f1.get_particles()
+    ps, vs = gather_particles(fs, sc.num_particles)
+    assert rel_l2(ps, p1) < 1e-8 and rel_l2(vs, v1) < 1e-7
+    for f in fs + [f1]:
+        f.close()
