@@ -266,6 +266,12 @@ struct flipb200_ctx {
 #ifndef FB_MINB_UPDATE_P4F
 #define FB_MINB_UPDATE_P4F 8      /* 40 -> 32 registers (16 bytes spilled), full occupancy: 90.5 -> 78.5 us */
 #endif
+#ifndef FB_MINB_RHS_DIV
+#define FB_MINB_RHS_DIV 6        /* 48 -> 40 registers: grid phase of a 2-pass step 1.718 -> 1.684 ms */
+#endif
+#ifndef FB_MINB_CLASSIFY
+#define FB_MINB_CLASSIFY 6       /* 48 -> 40 registers (68 bytes spilled): 1.718 -> 1.667 ms */
+#endif
 #ifndef FB_MINB_UPDATE_XR4
 #define FB_MINB_UPDATE_XR4 0
 #endif

@@ -13,7 +13,7 @@
 // The second splat PointList::interpolate (fluid.cc:843-882) accumulates the same cw into
 // containerGrid as p2gCatmullRom does into weights, so container := weights (no second pass).
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FB_MINB_CLASSIFY)
 k_classify(Grid g, const double* __restrict__ wacc, float* __restrict__ wf,
            double* __restrict__ u0, double* __restrict__ u1, double* __restrict__ u2,
            double* __restrict__ b0, double* __restrict__ b1, double* __restrict__ b2,
@@ -283,7 +283,7 @@ __device__ __forceinline__ float rhs_div_cell(uint8_t f, double vx, double vy, d
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FB_MINB_RHS_DIV)
 k_rhs_div(Grid g, Box box, int tiles_x, int tiles_y, int nitems, const uint8_t* __restrict__ fl,
           const double* __restrict__ u0, const double* __restrict__ u1, const double* __restrict__ u2,
           const float* __restrict__ bold, float* __restrict__ bout, double scale, double dx, double gx, double gy,
