@@ -31,6 +31,24 @@ def test_slab_split_properties(nz, world):
     assert max(sizes) - min(sizes) <= 2 * A         # balanced up to the alignment
 
 
+@pytest.mark.parametrize("nz,world,z_lo,z_hi", [(512, 8, 170, 343), (512, 4, 170, 343), (512, 2, 170, 343), (256, 4, 0, 256),
+                                                 (256, 8, 100, 130), (128, 2, 2, 20), (2048, 8, 2, 2045)])
+def test_balanced_split_properties(nz, world, z_lo, z_hi):
+    """dist.balanced_split (boundaries for flipb200_create_slab_split): covers [0, nz], boundaries aligned to 2^a with
+    slabs of at least two coarse planes (what fb_create's slab_split_given accepts), and the busiest rank holds no more
+    fluid planes than an even split gives its busiest rank."""
+    d = _dist()
+    zs = d.balanced_split(nz, world, z_lo, z_hi)
+    assert zs[0] == 0 and zs[-1] == nz and len(zs) == world + 1 and all(zs[r + 1] > zs[r] for r in range(world))
+    a = min((b & -b).bit_length() - 1 for b in zs[1:-1])          # common alignment of the inner boundaries
+    assert a >= 1
+    assert all(zs[r + 1] - zs[r] >= max(2 << 1, 4) for r in range(world))
+    load = lambda z: max(max(0, min(z[r + 1], z_hi) - max(z[r], z_lo)) for r in range(world))
+    even, _ = d.slab_split(nz, world)
+    assert load(zs) <= load(even)
+    assert d.balanced_split(nz, 1, z_lo, z_hi) == [0, nz]
+
+
 def test_slab_split_rejects_thin():
     d = _dist()
     with pytest.raises(ValueError):
