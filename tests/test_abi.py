@@ -75,3 +75,27 @@ def test_scenes_counts():
     assert np.all(np.abs(s.pos) < 20.5 + 1e-9)
     d = scenes.dam_break(n=32, fill="full")
     assert d.num_particles == 28 * 26 * 28 * 8
+
+
+def test_struct_layout_matches_the_header(fb, tmp_path):
+    """The ctypes mirrors of flipb200_params / flipb200_stats against the C compiler's view of include/flipb200.h: size and
+    the offset of every field (a field added on one side only would silently shift everything behind it)."""
+    import ctypes as C
+    import subprocess
+    fields_p = [n for n, _ in fb.Params._fields_]
+    fields_s = [n for n, _ in fb.Stats._fields_]
+    src = tmp_path / "layout.c"
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "flipb200.h"', 'int main(void) {',
+             '  printf("P %zu\\n", sizeof(flipb200_params)); printf("S %zu\\n", sizeof(flipb200_stats));']
+    lines += [f'  printf("P.{n} %zu\\n", offsetof(flipb200_params, {n}));' for n in fields_p]
+    lines += [f'  printf("S.{n} %zu\\n", offsetof(flipb200_stats, {n}));' for n in fields_s]
+    lines += ['  return 0; }']
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.check_call(["/usr/bin/gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    out = dict(l.split() for l in subprocess.check_output([str(exe)], text=True).splitlines())
+    assert int(out["P"]) == C.sizeof(fb.Params) and int(out["S"]) == C.sizeof(fb.Stats)
+    for n in fields_p:
+        assert int(out[f"P.{n}"]) == getattr(fb.Params, n).offset, n
+    for n in fields_s:
+        assert int(out[f"S.{n}"]) == getattr(fb.Stats, n).offset, n
